@@ -1,0 +1,156 @@
+/* b200_gguf.h -- C ABI of the B200-native GGUF inference engine (libb200gguf.so).
+ *
+ * This is the boundary the Python host (`llama_cpp.Llama`, the drop-in for the object that
+ * /root/reference/api.py:7,24-28,55-63 drives) sits on, through ctypes. The reference reaches
+ * its engine through llama-cpp-python 0.2.77's ctypes binding of libllama (un-vendored
+ * upstream, pinned at /root/reference/docker/Dockerfile.base:30); each entry point below names
+ * the libllama call(s) of that binding it stands in for. Plain pointers and sizes only; no
+ * torch or C++ types cross this line.
+ *
+ * Conventions: every function returns 0 on success and a negative code on failure;
+ * b2_last_error() returns a thread-local message for the most recent failure on the calling
+ * thread. Functions may be called from any host thread (each call selects the engine's device);
+ * calls on ONE engine must not overlap in time (the Python host serialises them).
+ * "host" pointers are ordinary CPU memory, "dev" pointers are CUDA device memory.
+ */
+#ifndef B200_GGUF_H
+#define B200_GGUF_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2_OK 0
+#define B2_ERR_ARG -1
+#define B2_ERR_CUDA -2
+#define B2_ERR_UNSUPPORTED -3
+#define B2_ERR_STATE -4
+
+/* ggml tensor type ids accepted for weights (gguf/constants.py:4059-4094) */
+#define B2_TYPE_F32 0
+#define B2_TYPE_F16 1
+#define B2_TYPE_Q4_0 2
+#define B2_TYPE_Q8_0 8
+#define B2_TYPE_Q4_K 12
+#define B2_TYPE_Q5_K 13
+#define B2_TYPE_Q6_K 14
+
+typedef struct b2_engine b2_engine;
+
+typedef struct b2_config {
+    int32_t n_layer, n_embd, n_head, n_head_kv, head_dim, n_ff, n_vocab;
+    float rms_eps;
+    float rope_freq_base;
+    int32_t n_ctx;            /* max tokens per sequence (api.py:17,27 passes 1024) */
+    int32_t max_seqs;         /* sequence slots that can be live at once */
+    int32_t kv_block_tokens;  /* tokens per KV page */
+    int32_t kv_num_blocks;    /* pages in the pool shared by all slots */
+    int32_t device;           /* CUDA device ordinal */
+    int32_t flags;            /* B2_FLAG_* */
+} b2_config;
+
+#define B2_FLAG_NO_GRAPH 1      /* launch kernels directly instead of replaying CUDA graphs */
+#define B2_FLAG_NO_PDL 2        /* no programmatic dependent launch between kernels */
+#define B2_FLAG_ACT8 4          /* single int8 activation plane (faster, ~0.5% noise) */
+
+typedef struct b2_sampling {
+    float temperature;        /* <= 0: greedy */
+    float top_p;
+    float min_p;
+    float repeat_penalty;
+    float frequency_penalty;
+    float presence_penalty;
+    int32_t top_k;            /* 1..1024 */
+    int32_t penalty_last_n;   /* <= 64 */
+} b2_sampling;
+
+/* ---- library ------------------------------------------------------------------------- */
+const char* b2_last_error(void);
+int b2_version(void);
+int b2_device_count(int* n);
+
+/* ---- engine lifecycle: replaces llama_load_model_from_file + llama_new_context_with_model
+ *      behind Llama.__init__ (api.py:24-28) and llama_free / llama_free_model. ------------ */
+int b2_engine_create(const b2_config* cfg, b2_engine** out);
+int b2_engine_destroy(b2_engine* e);
+/* Copy one GGUF tensor's raw blocks, unchanged, into HBM (the upload half of llama.cpp's
+ * llama_model_loader::load_all_data). ne0 = contiguous length K, ne1 = rows (1 for vectors). */
+int b2_upload_tensor(b2_engine* e, const char* name, int ggml_type, int64_t ne0, int64_t ne1,
+                     const void* host_data, int64_t nbytes);
+/* All tensors uploaded: validate the set, build the per-layer launch plans. */
+int b2_engine_finalize(b2_engine* e);
+int b2_engine_device_bytes(b2_engine* e, int64_t* weight_bytes, int64_t* kv_bytes);
+
+/* ---- sequences (paged KV): replaces llama_kv_cache_* bookkeeping (llama.cpp llama_kv_cache).
+ *      The page allocator lives in the host (llama_cpp/kv_pages.py); the engine only holds
+ *      each slot's page table. -------------------------------------------------------------- */
+int b2_seq_set_blocks(b2_engine* e, int slot, const int32_t* host_blocks, int n_blocks);
+/* Start (or restart) a slot: n_past tokens are already in its KV pages; `host_history` are the
+ * last <= 64 tokens of the sequence so far (for the penalties); `host_uniforms` are n_uniform
+ * (<= 8192) doubles in [0,1) for the multinomial draws of this sequence. */
+int b2_seq_begin(b2_engine* e, int slot, int n_past, const int32_t* host_history, int n_history,
+                 const b2_sampling* sampling, const double* host_uniforms, int n_uniform);
+
+/* ---- forward: replaces llama_decode (llama.cpp llama_decode_internal) + llama_get_logits +
+ *      llama_sample_* under Llama.eval / Llama.sample (api.py:55-63). ------------------------ */
+/* Append n_tokens prompt tokens at positions n_past.. to the slot, filling its KV pages; the
+ * logits of the LAST token are left in the slot's logit buffer. */
+int b2_prefill(b2_engine* e, int slot, const int32_t* host_tokens, int n_tokens);
+/* Sample from the slot's logit buffer with the slot's sampling settings; the sampled token
+ * becomes the slot's next input. */
+int b2_sample(b2_engine* e, int slot, int32_t* host_token_out);
+/* One decode step for each listed slot: forward the slot's pending token, sample the next.
+ * Writes n sampled tokens. */
+int b2_decode(b2_engine* e, const int32_t* host_slots, int n, int32_t* host_tokens_out);
+/* Teacher forcing / tests: overwrite the slot's pending input token. */
+int b2_seq_set_token(b2_engine* e, int slot, int32_t token);
+/* Forward the slot's pending token without sampling (logits left in the slot's buffer). */
+int b2_forward_pending(b2_engine* e, int slot);
+/* Copy the slot's current logits [n_vocab] to the host (llama_get_logits). */
+int b2_get_logits(b2_engine* e, int slot, float* host_out);
+int b2_synchronize(b2_engine* e);
+
+/* ---- measurement hooks (bench.py): CUDA events on the engine's own stream --------------- */
+int b2_timer_start(b2_engine* e);
+int b2_timer_stop(b2_engine* e, float* ms_out);          /* synchronises */
+int b2_kernel_launch_count(b2_engine* e, int64_t* n);   /* kernels launched since create */
+/* How the engine is running: CUDA graphs on/off, PDL on/off, int8 activation planes (1|2),
+ * CTAs per mat-vec launch, attention split count. Any pointer may be NULL. */
+int b2_engine_mode(b2_engine* e, int* graph, int* pdl, int* act_planes, int* n_ctas, int* n_splits);
+/* Per-kernel-kind device time of ONE un-graphed, un-overlapped decode step of `slot`
+ * (events around every launch). kinds: 0 embed, 1 qkv, 2 attention, 3 attn_out, 4 gate_up,
+ * 5 ffn_down, 6 lm_head, 7 sampler. ms_out[8], launches_out[8], bytes_out[8] (algorithmic). */
+int b2_profile_decode_step(b2_engine* e, int slot, float* ms_out, int32_t* launches_out,
+                           int64_t* bytes_out);
+
+/* ---- single-operator entry points (parity tests call the kernels through these).
+ *      All pointers are HOST memory; the call stages data through device scratch. ---------- */
+/* ggml dequantize_row_* / gguf.quants.dequantize */
+int b2_op_dequantize(int device, int ggml_type, const void* host_blocks, int64_t n_elems, float* host_out);
+/* y[n_rows] = W[n_rows, K] . x  (+ optional fused RMSNorm of x, + optional residual);
+ * ggml-cuda quantize_q8_1 + mul_mat_vec_q (+ rms_norm_f32, add). act_planes = 1 or 2. */
+int b2_op_matvec(int device, int ggml_type, const void* host_w, int n_rows, int K, const float* host_x,
+                 const float* host_norm_w, float eps, const float* host_resid, float* host_y,
+                 int act_planes, int n_ctas);
+/* fused gate/up: y[n_rows] = silu(Wg . x) * (Wu . x), x optionally RMS-normed first */
+int b2_op_gate_up(int device, int type_gate, const void* host_wg, int type_up, const void* host_wu,
+                  int n_rows, int K, const float* host_x, const float* host_norm_w, float eps,
+                  float* host_y, int n_ctas);
+/* ggml rms_norm_f32 * weight */
+int b2_op_rmsnorm(int device, const float* host_x, const float* host_w, float eps, int K, int rows, float* host_y);
+/* Decode attention for one sequence: q [n_head*head_dim] f32 (already rotated), K/V as f16
+ * [n_ctx_tokens][n_kv][head_dim] (token-major; the op scatters them into pages in the order
+ * host_blocks gives), attends to all n_ctx_tokens. out [n_head*head_dim] f32. */
+int b2_op_attention_decode(int device, const float* host_q, const uint16_t* host_k, const uint16_t* host_v,
+                           int n_ctx_tokens, int n_head, int n_kv, int head_dim, int block_tokens,
+                           const int32_t* host_blocks, int n_blocks_total, int n_splits, float* host_out);
+/* penalties + greedy/top-k/top-p/min-p/temperature draw over logits[n_vocab] with the given
+ * recent-token history and uniform u in [0,1). */
+int b2_op_sample(int device, const float* host_logits, int n_vocab, const b2_sampling* sampling,
+                 const int32_t* host_history, int n_history, double u, int32_t* host_token_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_GGUF_H */

@@ -1,0 +1,60 @@
+"""Build the in-tree native libraries.
+
+  lib/libb200gguf.so       CUDA kernels + C ABI (include/b200_gguf.h), nvcc, sm_100a only
+  lib/libb200_hosttest.so  host build of the block arithmetic (CPU self-test, g++)
+
+nvcc cross-compiles without a GPU; the .so files are git-ignored but travel to the GPU box.
+"""
+from __future__ import annotations
+
+import os
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, "csrc")
+LIB = os.path.join(HERE, "lib")
+CUDA_SOURCES = ["engine.cu", "matvec.cu", "attention.cu", "misc.cu", "sampler.cu"]
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+              "-Xcompiler", "-fPIC", "-Xptxas", "-v", "--expt-relaxed-constexpr"]
+
+
+def _newer(target: str, sources) -> bool:
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(s) > t for s in sources)
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    os.makedirs(LIB, exist_ok=True)
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(HERE, "..", "include", "b200_gguf.h")]
+    out = os.path.join(LIB, "libb200gguf.so")
+    if force or _newer(out, deps):
+        objs = []
+        for src in CUDA_SOURCES:
+            obj = os.path.join(LIB, src.replace(".cu", ".o"))
+            cmd = [nvcc, *NVCC_FLAGS, "-c", os.path.join(CSRC, src), "-o", obj]
+            r = subprocess.run(cmd, capture_output=True, text=True)
+            if verbose or r.returncode:
+                sys.stderr.write(r.stdout + r.stderr)
+            if r.returncode:
+                raise RuntimeError(f"nvcc failed on {src}")
+            with open(os.path.join(LIB, src + ".ptxas.log"), "w") as f:
+                f.write(r.stderr)
+            objs.append(obj)
+        cmd = [nvcc, "-shared", "-o", out, *objs, "-gencode", "arch=compute_100a,code=sm_100a"]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode:
+            sys.stderr.write(r.stdout + r.stderr)
+            raise RuntimeError("link failed")
+    host = os.path.join(LIB, "libb200_hosttest.so")
+    hsrc = os.path.join(CSRC, "host_selftest.cpp")
+    if force or _newer(host, [hsrc, os.path.join(CSRC, "quant_blocks.cuh")]):
+        subprocess.run(["g++", "-O2", "-ffp-contract=off", "-fPIC", "-shared", hsrc, "-o", host], check=True)
+    return out
+
+
+if __name__ == "__main__":
+    print(build(force="--force" in sys.argv, verbose=True))

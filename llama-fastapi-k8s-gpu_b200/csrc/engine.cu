@@ -1,0 +1,828 @@
+// Engine object + the C ABI declared in include/b200_gguf.h.
+// Owns the device copies of the GGUF tensors (raw quant blocks, unchanged), the paged f16 KV pool,
+// per-slot activation buffers and the captured CUDA graphs of one decode / prefill step.
+// Stands in for libllama's llama_model + llama_context behind llama-cpp-python's Llama object
+// (/root/reference/api.py:24-28,55-63).
+#include "../../include/b200_gguf.h"
+#include "kernels.h"
+#include "ptx.cuh"
+#include "quant_blocks.cuh"
+
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <mutex>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+using namespace b2;
+
+static thread_local std::string g_err;
+static int fail(int code, const std::string& msg) { g_err = msg; return code; }
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t _e = (call);                                                                   \
+        if (_e != cudaSuccess)                                                                     \
+            return fail(B2_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(_e));         \
+    } while (0)
+
+struct DevTensor {
+    uint8_t* ptr = nullptr;
+    int type = -1;
+    int64_t ne0 = 0, ne1 = 0, nbytes = 0;
+};
+
+struct Layer {
+    DevTensor attn_norm, wq, wk, wv, wo, ffn_norm, wgate, wup, wdown;
+    MvParams p_qkv, p_o, p_gu, p_down;
+};
+
+struct Slot {
+    float *x = nullptr, *q = nullptr, *att = nullptr, *h = nullptr, *logits = nullptr;
+    int* ints = nullptr;           // [0]=token [1]=pos [2]=out_token [3]=step [4]=cursor [5]=pos_base
+    int* block_table = nullptr;
+    int* prompt = nullptr;         // [n_ctx]
+    SamplerState* sst = nullptr;
+    SampleParams* sp = nullptr;
+    double* uniforms = nullptr;    // [8192]
+    cudaGraphExec_t g_decode = nullptr, g_pre_step = nullptr, g_pre_last = nullptr, g_fwd = nullptr;
+    int n_decode_nodes = 0, n_pre_step_nodes = 0, n_pre_last_nodes = 0, n_fwd_nodes = 0;
+    int n_past = 0;                // host mirror of ints[1]
+};
+
+struct b2_engine {
+    b2_config cfg;
+    cudaStream_t stream = nullptr;
+    std::unordered_map<std::string, DevTensor> tensors;
+    std::vector<Layer> layers;
+    DevTensor tok_embd, out_norm, output;
+    MvParams p_head;
+    __half *k_pool = nullptr, *v_pool = nullptr;
+    size_t layer_kv_elems = 0;
+    float* rope_freq = nullptr;
+    float* attn_scratch = nullptr;
+    unsigned* attn_counters = nullptr;
+    int n_splits = 1, max_blocks = 0, n_ctas = 148;
+    std::vector<Slot> slots;
+    int32_t* pinned = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    int64_t launches = 0, weight_bytes = 0, kv_bytes = 0;
+    bool use_graph = true, use_pdl = true, act2 = true, finalized = false;
+    std::mutex mu;
+};
+
+// ------------------------------------------------------------------------------------------
+// small device helpers
+__global__ void prefill_next_kernel(const int* prompt, int* ints, SamplerState* st) {
+    griddep_launch();
+    griddep_wait();
+    int cur = ints[4];
+    int tok = prompt[cur];
+    ints[0] = tok;
+    ints[1] = ints[5] + cur;
+    ints[4] = cur + 1;
+    int n = st->n_hist;
+    st->history[n & (HISTORY_LEN - 1)] = tok;
+    st->n_hist = n + 1;
+}
+
+static cudaError_t launch_prefill_next(Slot& s, cudaStream_t st, bool pdl) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(1); cfg.blockDim = dim3(1); cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, prefill_next_kernel, (const int*)s.prompt, s.ints, s.sst);
+}
+
+// ------------------------------------------------------------------------------------------
+extern "C" const char* b2_last_error(void) { return g_err.c_str(); }
+extern "C" int b2_version(void) { return 100; }
+extern "C" int b2_device_count(int* n) {
+    CK(cudaGetDeviceCount(n));
+    return B2_OK;
+}
+
+extern "C" int b2_engine_create(const b2_config* c, b2_engine** out) {
+    if (!c || !out) return fail(B2_ERR_ARG, "null argument");
+    if (c->n_layer <= 0 || c->n_embd <= 0 || c->n_head <= 0 || c->n_head_kv <= 0 || c->n_vocab <= 0 ||
+        c->n_ff <= 0 || c->n_ctx <= 0 || c->max_seqs <= 0 || c->kv_block_tokens <= 0 || c->kv_num_blocks <= 0)
+        return fail(B2_ERR_ARG, "bad model/config dimensions");
+    if (c->head_dim != 64 && c->head_dim != 128) return fail(B2_ERR_UNSUPPORTED, "head_dim must be 64 or 128");
+    if (c->n_head % c->n_head_kv || c->n_head / c->n_head_kv > 8)
+        return fail(B2_ERR_UNSUPPORTED, "n_head / n_head_kv must be an integer <= 8");
+    if (c->n_embd % 256 || c->n_ff % 256 || (c->n_head * c->head_dim) % 256)
+        return fail(B2_ERR_UNSUPPORTED, "n_embd, n_ff and n_head*head_dim must be multiples of 256");
+    if (c->kv_block_tokens % 16) return fail(B2_ERR_ARG, "kv_block_tokens must be a multiple of 16");
+    CK(cudaSetDevice(c->device));
+    CK(mv_init());
+    CK(attn_init());
+    b2_engine* e = new b2_engine();
+    e->cfg = *c;
+    e->use_graph = !(c->flags & B2_FLAG_NO_GRAPH);
+    e->use_pdl = !(c->flags & B2_FLAG_NO_PDL);
+    e->act2 = !(c->flags & B2_FLAG_ACT8);
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
+    int per = 1;
+    if (const char* s = getenv("B2_CTAS_PER_SM")) per = atoi(s) > 0 ? atoi(s) : 1;
+    e->n_ctas = sms * per;
+    CK(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+    CK(cudaEventCreate(&e->ev0));
+    CK(cudaEventCreate(&e->ev1));
+    CK(cudaMallocHost(&e->pinned, sizeof(int32_t) * (size_t)(c->max_seqs + 16)));
+    // KV pool: [layer][block][kv_head][token][dim] f16
+    e->layer_kv_elems = (size_t)c->kv_num_blocks * c->n_head_kv * c->kv_block_tokens * c->head_dim;
+    size_t kvb = e->layer_kv_elems * c->n_layer * sizeof(__half);
+    CK(cudaMalloc(&e->k_pool, kvb));
+    CK(cudaMalloc(&e->v_pool, kvb));
+    CK(cudaMemsetAsync(e->k_pool, 0, kvb, e->stream));
+    CK(cudaMemsetAsync(e->v_pool, 0, kvb, e->stream));
+    e->kv_bytes = 2 * (int64_t)kvb;
+    // rope table, built like ggml: theta_scale = powf(base, -2/d), multiplied up in float32
+    {
+        std::vector<float> f(c->head_dim / 2);
+        float scale = powf(c->rope_freq_base, -2.0f / (float)c->head_dim), v = 1.0f;
+        for (int i = 0; i < c->head_dim / 2; i++) { f[i] = v; v *= scale; }
+        CK(cudaMalloc(&e->rope_freq, f.size() * 4));
+        CK(cudaMemcpy(e->rope_freq, f.data(), f.size() * 4, cudaMemcpyHostToDevice));
+    }
+    int ns = sms / c->n_head_kv;
+    int max_ns = (c->n_ctx + 15) / 16;
+    if (ns > max_ns) ns = max_ns;
+    if (ns < 1) ns = 1;
+    if (const char* s = getenv("B2_ATTN_SPLITS")) if (atoi(s) > 0) ns = atoi(s);
+    e->n_splits = ns;
+    CK(cudaMalloc(&e->attn_scratch, attn_scratch_floats(c->n_head, c->n_head_kv, c->head_dim, ns) * 4));
+    CK(cudaMalloc(&e->attn_counters, sizeof(unsigned) * c->n_head_kv));
+    CK(cudaMemset(e->attn_counters, 0, sizeof(unsigned) * c->n_head_kv));
+    e->max_blocks = (c->n_ctx + c->kv_block_tokens - 1) / c->kv_block_tokens;
+    e->slots.resize(c->max_seqs);
+    for (auto& s : e->slots) {
+        CK(cudaMalloc(&s.x, sizeof(float) * c->n_embd));
+        CK(cudaMalloc(&s.q, sizeof(float) * c->n_head * c->head_dim));
+        CK(cudaMalloc(&s.att, sizeof(float) * c->n_head * c->head_dim));
+        CK(cudaMalloc(&s.h, sizeof(float) * c->n_ff));
+        CK(cudaMalloc(&s.logits, sizeof(float) * c->n_vocab));
+        CK(cudaMalloc(&s.ints, sizeof(int) * 8));
+        CK(cudaMemset(s.ints, 0, sizeof(int) * 8));
+        CK(cudaMalloc(&s.block_table, sizeof(int) * e->max_blocks));
+        CK(cudaMemset(s.block_table, 0, sizeof(int) * e->max_blocks));
+        CK(cudaMalloc(&s.prompt, sizeof(int) * c->n_ctx));
+        CK(cudaMalloc(&s.sst, sizeof(SamplerState)));
+        CK(cudaMemset(s.sst, 0, sizeof(SamplerState)));
+        CK(cudaMalloc(&s.sp, sizeof(SampleParams)));
+        CK(cudaMemset(s.sp, 0, sizeof(SampleParams)));
+        CK(cudaMalloc(&s.uniforms, sizeof(double) * 8192));
+        CK(cudaMemset(s.uniforms, 0, sizeof(double) * 8192));
+    }
+    CK(cudaStreamSynchronize(e->stream));
+    *out = e;
+    return B2_OK;
+}
+
+static void free_slot_graphs(Slot& s) {
+    if (s.g_decode) cudaGraphExecDestroy(s.g_decode);
+    if (s.g_pre_step) cudaGraphExecDestroy(s.g_pre_step);
+    if (s.g_pre_last) cudaGraphExecDestroy(s.g_pre_last);
+    if (s.g_fwd) cudaGraphExecDestroy(s.g_fwd);
+    s.g_decode = s.g_pre_step = s.g_pre_last = s.g_fwd = nullptr;
+}
+
+extern "C" int b2_engine_destroy(b2_engine* e) {
+    if (!e) return B2_OK;
+    cudaSetDevice(e->cfg.device);
+    cudaStreamSynchronize(e->stream);
+    for (auto& kv : e->tensors) cudaFree(kv.second.ptr);
+    for (auto& s : e->slots) {
+        free_slot_graphs(s);
+        cudaFree(s.x); cudaFree(s.q); cudaFree(s.att); cudaFree(s.h); cudaFree(s.logits);
+        cudaFree(s.ints); cudaFree(s.block_table); cudaFree(s.prompt); cudaFree(s.sst); cudaFree(s.sp);
+        cudaFree(s.uniforms);
+    }
+    cudaFree(e->k_pool); cudaFree(e->v_pool); cudaFree(e->rope_freq);
+    cudaFree(e->attn_scratch); cudaFree(e->attn_counters);
+    cudaFreeHost(e->pinned);
+    cudaEventDestroy(e->ev0); cudaEventDestroy(e->ev1);
+    cudaStreamDestroy(e->stream);
+    delete e;
+    return B2_OK;
+}
+
+extern "C" int b2_upload_tensor(b2_engine* e, const char* name, int type, int64_t ne0, int64_t ne1,
+                                const void* host, int64_t nbytes) {
+    if (!e || !name || !host) return fail(B2_ERR_ARG, "null argument");
+    std::lock_guard<std::mutex> lk(e->mu);
+    CK(cudaSetDevice(e->cfg.device));
+    int be = block_elems(type), bb = block_bytes(type);
+    if (!bb) return fail(B2_ERR_UNSUPPORTED, std::string("tensor ") + name + ": unsupported ggml type " + std::to_string(type));
+    if (ne0 % be || ne0 / be * bb * ne1 != nbytes)
+        return fail(B2_ERR_ARG, std::string("tensor ") + name + ": byte size does not match its shape");
+    if (e->tensors.count(name)) return fail(B2_ERR_STATE, std::string("tensor ") + name + " uploaded twice");
+    DevTensor t;
+    t.type = type; t.ne0 = ne0; t.ne1 = ne1; t.nbytes = nbytes;
+    CK(cudaMalloc(&t.ptr, (size_t)nbytes + 64));   // +64: aligned bulk copies may read a few bytes past a tile
+    CK(cudaMemcpy(t.ptr, host, (size_t)nbytes, cudaMemcpyHostToDevice));
+    CK(cudaMemset(t.ptr + nbytes, 0, 64));
+    e->tensors[name] = t;
+    e->weight_bytes += nbytes;
+    return B2_OK;
+}
+
+static int get_tensor(b2_engine* e, const std::string& name, int64_t ne0, int64_t ne1, bool quant_ok, DevTensor& out) {
+    auto it = e->tensors.find(name);
+    if (it == e->tensors.end()) return fail(B2_ERR_STATE, "missing tensor " + name);
+    const DevTensor& t = it->second;
+    if (t.ne0 != ne0 || t.ne1 != ne1)
+        return fail(B2_ERR_ARG, "tensor " + name + " has shape [" + std::to_string(t.ne0) + "," +
+                                    std::to_string(t.ne1) + "], expected [" + std::to_string(ne0) + "," +
+                                    std::to_string(ne1) + "]");
+    if (!quant_ok && t.type != T_F32) return fail(B2_ERR_UNSUPPORTED, "tensor " + name + " must be F32");
+    if (quant_ok && (t.type == T_F32 || t.type == T_F16))
+        return fail(B2_ERR_UNSUPPORTED, "tensor " + name + ": F32/F16 weight matrices are not supported by the mat-vec yet");
+    out = t;
+    return B2_OK;
+}
+
+static MvSeg make_seg(const DevTensor& t, int out_off = 0) {
+    MvSeg s = {};
+    s.w = t.ptr; s.type = t.type; s.n_rows = (int)t.ne1; s.out_off = out_off;
+    return s;
+}
+
+static int plan_or_fail(MvParams& p, int n_ctas, const char* what) {
+    int rc = mv_plan(p, n_ctas);
+    if (rc) return fail(B2_ERR_UNSUPPORTED, std::string("cannot plan mat-vec for ") + what + " (code " + std::to_string(rc) +
+                                               (rc == -2 ? ": K > 16384 not supported yet)" : ")"));
+    if (mv_smem_bytes(p) > 112 * 1024) return fail(B2_ERR_UNSUPPORTED, std::string("mat-vec ring too large for ") + what);
+    return B2_OK;
+}
+
+extern "C" int b2_engine_finalize(b2_engine* e) {
+    if (!e) return fail(B2_ERR_ARG, "null engine");
+    std::lock_guard<std::mutex> lk(e->mu);
+    const b2_config& c = e->cfg;
+    int rc;
+    int qd = c.n_head * c.head_dim, kvd = c.n_head_kv * c.head_dim;
+    if ((rc = get_tensor(e, "token_embd.weight", c.n_embd, c.n_vocab, true, e->tok_embd))) {
+        // F16/F32 embeddings are fine for the gather
+        auto it = e->tensors.find("token_embd.weight");
+        if (it == e->tensors.end() || it->second.ne0 != c.n_embd || it->second.ne1 != c.n_vocab) return rc;
+        e->tok_embd = it->second;
+    }
+    if ((rc = get_tensor(e, "output_norm.weight", c.n_embd, 1, false, e->out_norm))) return rc;
+    if (e->tensors.count("output.weight")) {
+        if ((rc = get_tensor(e, "output.weight", c.n_embd, c.n_vocab, true, e->output))) return rc;
+    } else {
+        if ((rc = get_tensor(e, "token_embd.weight", c.n_embd, c.n_vocab, true, e->output))) return rc;  // tied
+    }
+    e->layers.resize(c.n_layer);
+    for (int l = 0; l < c.n_layer; l++) {
+        Layer& L = e->layers[l];
+        std::string p = "blk." + std::to_string(l) + ".";
+        if ((rc = get_tensor(e, p + "attn_norm.weight", c.n_embd, 1, false, L.attn_norm))) return rc;
+        if ((rc = get_tensor(e, p + "ffn_norm.weight", c.n_embd, 1, false, L.ffn_norm))) return rc;
+        if ((rc = get_tensor(e, p + "attn_q.weight", c.n_embd, qd, true, L.wq))) return rc;
+        if ((rc = get_tensor(e, p + "attn_k.weight", c.n_embd, kvd, true, L.wk))) return rc;
+        if ((rc = get_tensor(e, p + "attn_v.weight", c.n_embd, kvd, true, L.wv))) return rc;
+        if ((rc = get_tensor(e, p + "attn_output.weight", qd, c.n_embd, true, L.wo))) return rc;
+        if ((rc = get_tensor(e, p + "ffn_gate.weight", c.n_embd, c.n_ff, true, L.wgate))) return rc;
+        if ((rc = get_tensor(e, p + "ffn_up.weight", c.n_embd, c.n_ff, true, L.wup))) return rc;
+        if ((rc = get_tensor(e, p + "ffn_down.weight", c.n_ff, c.n_embd, true, L.wdown))) return rc;
+        MvParams q = {};
+        q.nseg = 3; q.seg[0] = make_seg(L.wq); q.seg[1] = make_seg(L.wk); q.seg[2] = make_seg(L.wv);
+        q.K = c.n_embd; q.mode = MV_QKV; q.norm_w = (const float*)L.attn_norm.ptr; q.eps = c.rms_eps;
+        q.k_cache = e->k_pool + (size_t)l * e->layer_kv_elems; q.v_cache = e->v_pool + (size_t)l * e->layer_kv_elems;
+        q.rope_freq = e->rope_freq; q.head_dim = c.head_dim; q.n_kv = c.n_head_kv; q.block_tokens = c.kv_block_tokens;
+        if ((rc = plan_or_fail(q, e->n_ctas, "attn_q/k/v"))) return rc;
+        L.p_qkv = q;
+        MvParams o = {};
+        o.nseg = 1; o.seg[0] = make_seg(L.wo); o.K = qd; o.mode = MV_RESID;
+        if ((rc = plan_or_fail(o, e->n_ctas, "attn_output"))) return rc;
+        L.p_o = o;
+        MvParams g = {};
+        g.nseg = 2; g.seg[0] = make_seg(L.wgate); g.seg[1] = make_seg(L.wup); g.K = c.n_embd; g.mode = MV_GATEUP;
+        g.norm_w = (const float*)L.ffn_norm.ptr; g.eps = c.rms_eps;
+        if ((rc = plan_or_fail(g, e->n_ctas, "ffn_gate/up"))) return rc;
+        L.p_gu = g;
+        MvParams d = {};
+        d.nseg = 1; d.seg[0] = make_seg(L.wdown); d.K = c.n_ff; d.mode = MV_RESID;
+        if ((rc = plan_or_fail(d, e->n_ctas, "ffn_down"))) return rc;
+        L.p_down = d;
+    }
+    MvParams h = {};
+    h.nseg = 1; h.seg[0] = make_seg(e->output); h.K = c.n_embd; h.mode = MV_STORE;
+    h.norm_w = (const float*)e->out_norm.ptr; h.eps = c.rms_eps;
+    if ((rc = plan_or_fail(h, e->n_ctas, "output"))) return rc;
+    e->p_head = h;
+    e->finalized = true;
+    return B2_OK;
+}
+
+extern "C" int b2_engine_device_bytes(b2_engine* e, int64_t* w, int64_t* kv) {
+    if (!e) return fail(B2_ERR_ARG, "null engine");
+    if (w) *w = e->weight_bytes;
+    if (kv) *kv = e->kv_bytes;
+    return B2_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// forward of one slot's pending token; `timing` (optional) receives per-kind event pairs
+struct KindTimer {
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev[8];
+};
+
+static int forward_launches(b2_engine* e, Slot& s, bool with_head, bool with_sample, bool pdl, KindTimer* kt) {
+    const b2_config& c = e->cfg;
+    cudaStream_t st = e->stream;
+    auto tick = [&](int kind, cudaEvent_t* a) {
+        if (!kt) return;
+        cudaEvent_t x, y;
+        cudaEventCreate(&x); cudaEventCreate(&y);
+        cudaEventRecord(x, st);
+        kt->ev[kind].push_back({x, y});
+        *a = y;
+    };
+    auto tock = [&](cudaEvent_t y) { if (kt) cudaEventRecord(y, st); };
+    cudaEvent_t ye = nullptr;
+    int* tok = s.ints + 0; int* pos = s.ints + 1;
+    tick(0, &ye);
+    CK(embed_row_launch(e->tok_embd.type, e->tok_embd.ptr, c.n_embd, tok, s.x, st, pdl));
+    tock(ye);
+    e->launches++;
+    for (int l = 0; l < c.n_layer; l++) {
+        Layer& L = e->layers[l];
+        MvParams q = L.p_qkv;
+        q.x = s.x; q.q_out = s.q; q.pos_ptr = pos; q.block_table = s.block_table;
+        tick(1, &ye);
+        CK(mv_launch(q, e->n_ctas, st, e->act2, pdl));
+        tock(ye);
+        AttnParams a = {};
+        a.q = s.q; a.k_cache = q.k_cache; a.v_cache = q.v_cache; a.block_table = s.block_table; a.pos_ptr = pos;
+        a.out = s.att; a.scratch = e->attn_scratch; a.counters = e->attn_counters;
+        a.n_head = c.n_head; a.n_kv = c.n_head_kv; a.head_dim = c.head_dim; a.block_tokens = c.kv_block_tokens;
+        a.n_splits = e->n_splits; a.scale = 1.0f / sqrtf((float)c.head_dim);
+        tick(2, &ye);
+        CK(attn_decode_launch(a, st, pdl));
+        tock(ye);
+        MvParams o = L.p_o;
+        o.x = s.att; o.y = s.x; o.resid = s.x;
+        tick(3, &ye);
+        CK(mv_launch(o, e->n_ctas, st, e->act2, pdl));
+        tock(ye);
+        MvParams g = L.p_gu;
+        g.x = s.x; g.y = s.h;
+        tick(4, &ye);
+        CK(mv_launch(g, e->n_ctas, st, e->act2, pdl));
+        tock(ye);
+        MvParams d = L.p_down;
+        d.x = s.h; d.y = s.x; d.resid = s.x;
+        tick(5, &ye);
+        CK(mv_launch(d, e->n_ctas, st, e->act2, pdl));
+        tock(ye);
+        e->launches += 5;
+    }
+    if (with_head) {
+        MvParams h = e->p_head;
+        h.x = s.x; h.y = s.logits;
+        tick(6, &ye);
+        CK(mv_launch(h, e->n_ctas, st, e->act2, pdl));
+        tock(ye);
+        e->launches++;
+    }
+    if (with_sample) {
+        tick(7, &ye);
+        CK(sample_launch(s.logits, c.n_vocab, s.sp, s.sst, s.uniforms, s.ints + 3, s.ints + 2, tok, pos, st, pdl));
+        tock(ye);
+        e->launches++;
+    }
+    return B2_OK;
+}
+
+enum GraphKind { GK_DECODE, GK_PRE_STEP, GK_PRE_LAST, GK_FWD };
+
+static int record_step(b2_engine* e, Slot& s, GraphKind k, bool pdl) {
+    if (k == GK_PRE_STEP || k == GK_PRE_LAST) {
+        CK(launch_prefill_next(s, e->stream, pdl));
+        e->launches++;
+    }
+    bool head = (k != GK_PRE_STEP), samp = (k == GK_DECODE);
+    return forward_launches(e, s, head, samp, pdl, nullptr);
+}
+
+// run one step of kind k for slot s, through a captured graph when enabled
+static int run_step(b2_engine* e, Slot& s, GraphKind k) {
+    cudaGraphExec_t* ge = k == GK_DECODE ? &s.g_decode : k == GK_PRE_STEP ? &s.g_pre_step : k == GK_PRE_LAST ? &s.g_pre_last : &s.g_fwd;
+    int* nn = k == GK_DECODE ? &s.n_decode_nodes : k == GK_PRE_STEP ? &s.n_pre_step_nodes : k == GK_PRE_LAST ? &s.n_pre_last_nodes : &s.n_fwd_nodes;
+    if (!e->use_graph) return record_step(e, s, k, e->use_pdl);
+    if (!*ge) {
+        for (int attempt = 0; attempt < 2 && !*ge; attempt++) {
+            bool pdl = e->use_pdl && attempt == 0;
+            int64_t before = e->launches;
+            cudaGraph_t g = nullptr;
+            CK(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
+            int rc = record_step(e, s, k, pdl);
+            cudaError_t ce = cudaStreamEndCapture(e->stream, &g);
+            *nn = (int)(e->launches - before);
+            e->launches = before;
+            if (rc == B2_OK && ce == cudaSuccess && g) {
+                cudaGraphExec_t x = nullptr;
+                ce = cudaGraphInstantiate(&x, g, 0);
+                if (ce == cudaSuccess) *ge = x;
+            }
+            if (g) cudaGraphDestroy(g);
+            if (!*ge) {
+                cudaGetLastError();
+                if (!pdl) {            // graphs unusable here: fall back to direct launches for good
+                    e->use_graph = false;
+                    return record_step(e, s, k, e->use_pdl);
+                }
+                e->use_pdl = false;    // PDL edges rejected by capture/instantiate: retry without
+            }
+        }
+    }
+    CK(cudaGraphLaunch(*ge, e->stream));
+    e->launches += *nn;
+    return B2_OK;
+}
+
+static int check_slot(b2_engine* e, int slot) {
+    if (!e) return fail(B2_ERR_ARG, "null engine");
+    if (!e->finalized) return fail(B2_ERR_STATE, "engine not finalized");
+    if (slot < 0 || slot >= (int)e->slots.size()) return fail(B2_ERR_ARG, "slot out of range");
+    return B2_OK;
+}
+
+extern "C" int b2_seq_set_blocks(b2_engine* e, int slot, const int32_t* blocks, int n) {
+    int rc = check_slot(e, slot); if (rc) return rc;
+    std::lock_guard<std::mutex> lk(e->mu);
+    if (n < 0 || n > e->max_blocks) return fail(B2_ERR_ARG, "too many KV pages for n_ctx");
+    for (int i = 0; i < n; i++)
+        if (blocks[i] < 0 || blocks[i] >= e->cfg.kv_num_blocks) return fail(B2_ERR_ARG, "KV page id out of range");
+    CK(cudaSetDevice(e->cfg.device));
+    if (n) CK(cudaMemcpyAsync(e->slots[slot].block_table, blocks, sizeof(int) * n, cudaMemcpyHostToDevice, e->stream));
+    CK(cudaStreamSynchronize(e->stream));   // `blocks` is caller memory
+    return B2_OK;
+}
+
+extern "C" int b2_seq_begin(b2_engine* e, int slot, int n_past, const int32_t* hist, int n_hist,
+                            const b2_sampling* sp, const double* uni, int n_uni) {
+    int rc = check_slot(e, slot); if (rc) return rc;
+    std::lock_guard<std::mutex> lk(e->mu);
+    if (!sp) return fail(B2_ERR_ARG, "null sampling");
+    if (n_past < 0 || n_past >= e->cfg.n_ctx) return fail(B2_ERR_ARG, "n_past out of range");
+    if (n_hist < 0 || n_hist > HISTORY_LEN) return fail(B2_ERR_ARG, "history longer than 64");
+    if (n_uni < 0 || n_uni > 8192) return fail(B2_ERR_ARG, "at most 8192 uniforms");
+    if (sp->temperature > 0.f && (sp->top_k < 1 || sp->top_k > SAMPLER_MAX_K))
+        return fail(B2_ERR_UNSUPPORTED, "top_k must be in 1..1024 on the device sampler");
+    CK(cudaSetDevice(e->cfg.device));
+    Slot& s = e->slots[slot];
+    SamplerState h = {};
+    for (int i = 0; i < n_hist; i++) h.history[i] = hist[i];
+    h.n_hist = n_hist;
+    SampleParams p = {};
+    p.temperature = sp->temperature; p.top_p = sp->top_p; p.min_p = sp->min_p;
+    p.repeat_penalty = sp->repeat_penalty; p.freq_penalty = sp->frequency_penalty;
+    p.presence_penalty = sp->presence_penalty; p.top_k = sp->top_k;
+    p.penalty_last_n = sp->penalty_last_n;
+    int ints[8] = {0, n_past, 0, 0, 0, n_past, 0, 0};
+    CK(cudaMemcpyAsync(s.sst, &h, sizeof(h), cudaMemcpyHostToDevice, e->stream));
+    CK(cudaMemcpyAsync(s.sp, &p, sizeof(p), cudaMemcpyHostToDevice, e->stream));
+    CK(cudaMemcpyAsync(s.ints, ints, sizeof(ints), cudaMemcpyHostToDevice, e->stream));
+    if (n_uni) CK(cudaMemcpyAsync(s.uniforms, uni, sizeof(double) * n_uni, cudaMemcpyHostToDevice, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    s.n_past = n_past;
+    return B2_OK;
+}
+
+extern "C" int b2_prefill(b2_engine* e, int slot, const int32_t* tokens, int n) {
+    int rc = check_slot(e, slot); if (rc) return rc;
+    std::lock_guard<std::mutex> lk(e->mu);
+    Slot& s = e->slots[slot];
+    if (n <= 0) return fail(B2_ERR_ARG, "empty prompt chunk");
+    if (s.n_past + n > e->cfg.n_ctx) return fail(B2_ERR_ARG, "prompt does not fit n_ctx");
+    for (int i = 0; i < n; i++)
+        if (tokens[i] < 0 || tokens[i] >= e->cfg.n_vocab) return fail(B2_ERR_ARG, "token id out of range");
+    CK(cudaSetDevice(e->cfg.device));
+    int hdr[2] = {0, s.n_past};   // cursor, pos_base
+    CK(cudaMemcpyAsync(s.prompt, tokens, sizeof(int) * n, cudaMemcpyHostToDevice, e->stream));
+    CK(cudaMemcpyAsync(s.ints + 4, hdr, sizeof(hdr), cudaMemcpyHostToDevice, e->stream));
+    for (int i = 0; i < n; i++) {
+        rc = run_step(e, s, i == n - 1 ? GK_PRE_LAST : GK_PRE_STEP);
+        if (rc) return rc;
+    }
+    CK(cudaStreamSynchronize(e->stream));
+    s.n_past += n;     // device pos stays at the last token; b2_sample / set_token move it on
+    return B2_OK;
+}
+
+__global__ void set_ints_kernel(int* ints, int tok, int pos) { if (tok >= 0) ints[0] = tok; ints[1] = pos; }
+
+extern "C" int b2_sample(b2_engine* e, int slot, int32_t* out) {
+    int rc = check_slot(e, slot); if (rc) return rc;
+    std::lock_guard<std::mutex> lk(e->mu);
+    Slot& s = e->slots[slot];
+    CK(cudaSetDevice(e->cfg.device));
+    // sampler bumps pos: make it point at the last evaluated token first
+    set_ints_kernel<<<1, 1, 0, e->stream>>>(s.ints, -1, s.n_past - 1);
+    CK(sample_launch(s.logits, e->cfg.n_vocab, s.sp, s.sst, s.uniforms, s.ints + 3, s.ints + 2, s.ints + 0,
+                     s.ints + 1, e->stream, false));
+    e->launches += 2;
+    CK(cudaMemcpyAsync(e->pinned, s.ints + 2, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    if (out) *out = e->pinned[0];
+    return B2_OK;
+}
+
+extern "C" int b2_decode(b2_engine* e, const int32_t* slots, int n, int32_t* out) {
+    if (!e || !slots || n <= 0) return fail(B2_ERR_ARG, "bad arguments");
+    if (!e->finalized) return fail(B2_ERR_STATE, "engine not finalized");
+    std::lock_guard<std::mutex> lk(e->mu);
+    if (n > (int)e->slots.size()) return fail(B2_ERR_ARG, "more slots than max_seqs");
+    CK(cudaSetDevice(e->cfg.device));
+    for (int i = 0; i < n; i++) {
+        if (slots[i] < 0 || slots[i] >= (int)e->slots.size()) return fail(B2_ERR_ARG, "slot out of range");
+        Slot& s = e->slots[slots[i]];
+        if (s.n_past + 1 > e->cfg.n_ctx) return fail(B2_ERR_ARG, "context window full");
+        int rc = run_step(e, s, GK_DECODE);
+        if (rc) return rc;
+        CK(cudaMemcpyAsync(e->pinned + i, s.ints + 2, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+        s.n_past += 1;
+    }
+    CK(cudaStreamSynchronize(e->stream));
+    if (out) for (int i = 0; i < n; i++) out[i] = e->pinned[i];
+    return B2_OK;
+}
+
+extern "C" int b2_seq_set_token(b2_engine* e, int slot, int32_t token) {
+    int rc = check_slot(e, slot); if (rc) return rc;
+    std::lock_guard<std::mutex> lk(e->mu);
+    if (token < 0 || token >= e->cfg.n_vocab) return fail(B2_ERR_ARG, "token id out of range");
+    CK(cudaSetDevice(e->cfg.device));
+    Slot& s = e->slots[slot];
+    set_ints_kernel<<<1, 1, 0, e->stream>>>(s.ints, token, s.n_past);
+    e->launches++;
+    CK(cudaGetLastError());
+    return B2_OK;
+}
+
+extern "C" int b2_forward_pending(b2_engine* e, int slot) {
+    int rc = check_slot(e, slot); if (rc) return rc;
+    std::lock_guard<std::mutex> lk(e->mu);
+    Slot& s = e->slots[slot];
+    if (s.n_past + 1 > e->cfg.n_ctx) return fail(B2_ERR_ARG, "context window full");
+    CK(cudaSetDevice(e->cfg.device));
+    set_ints_kernel<<<1, 1, 0, e->stream>>>(s.ints, -1, s.n_past);
+    e->launches++;
+    rc = run_step(e, s, GK_FWD);
+    if (rc) return rc;
+    CK(cudaStreamSynchronize(e->stream));
+    s.n_past += 1;
+    return B2_OK;
+}
+
+extern "C" int b2_get_logits(b2_engine* e, int slot, float* out) {
+    int rc = check_slot(e, slot); if (rc) return rc;
+    std::lock_guard<std::mutex> lk(e->mu);
+    CK(cudaSetDevice(e->cfg.device));
+    CK(cudaMemcpyAsync(out, e->slots[slot].logits, sizeof(float) * e->cfg.n_vocab, cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    return B2_OK;
+}
+
+extern "C" int b2_synchronize(b2_engine* e) {
+    if (!e) return fail(B2_ERR_ARG, "null engine");
+    CK(cudaSetDevice(e->cfg.device));
+    CK(cudaStreamSynchronize(e->stream));
+    return B2_OK;
+}
+
+extern "C" int b2_timer_start(b2_engine* e) {
+    if (!e) return fail(B2_ERR_ARG, "null engine");
+    CK(cudaSetDevice(e->cfg.device));
+    CK(cudaStreamSynchronize(e->stream));
+    CK(cudaEventRecord(e->ev0, e->stream));
+    return B2_OK;
+}
+extern "C" int b2_timer_stop(b2_engine* e, float* ms) {
+    if (!e || !ms) return fail(B2_ERR_ARG, "null argument");
+    CK(cudaSetDevice(e->cfg.device));
+    CK(cudaEventRecord(e->ev1, e->stream));
+    CK(cudaEventSynchronize(e->ev1));
+    CK(cudaEventElapsedTime(ms, e->ev0, e->ev1));
+    return B2_OK;
+}
+extern "C" int b2_kernel_launch_count(b2_engine* e, int64_t* n) {
+    if (!e || !n) return fail(B2_ERR_ARG, "null argument");
+    *n = e->launches;
+    return B2_OK;
+}
+extern "C" int b2_engine_mode(b2_engine* e, int* graph, int* pdl, int* act_planes, int* n_ctas, int* n_splits) {
+    if (!e) return fail(B2_ERR_ARG, "null engine");
+    if (graph) *graph = e->use_graph; if (pdl) *pdl = e->use_pdl; if (act_planes) *act_planes = e->act2 ? 2 : 1;
+    if (n_ctas) *n_ctas = e->n_ctas; if (n_splits) *n_splits = e->n_splits;
+    return B2_OK;
+}
+
+static int64_t seg_bytes(const MvParams& p) {
+    int64_t b = 0;
+    for (int i = 0; i < p.nseg; i++) b += (int64_t)p.seg[i].n_rows * p.seg[i].row_bytes;
+    return b;
+}
+
+extern "C" int b2_profile_decode_step(b2_engine* e, int slot, float* ms, int32_t* nl, int64_t* bytes) {
+    int rc = check_slot(e, slot); if (rc) return rc;
+    std::lock_guard<std::mutex> lk(e->mu);
+    Slot& s = e->slots[slot];
+    if (s.n_past + 1 > e->cfg.n_ctx) return fail(B2_ERR_ARG, "context window full");
+    CK(cudaSetDevice(e->cfg.device));
+    KindTimer kt;
+    rc = forward_launches(e, s, true, true, false, &kt);
+    if (rc) return rc;
+    CK(cudaStreamSynchronize(e->stream));
+    const b2_config& c = e->cfg;
+    for (int k = 0; k < 8; k++) {
+        float tot = 0.f;
+        for (auto& pr : kt.ev[k]) {
+            float t = 0.f;
+            cudaEventElapsedTime(&t, pr.first, pr.second);
+            tot += t;
+            cudaEventDestroy(pr.first); cudaEventDestroy(pr.second);
+        }
+        ms[k] = tot; nl[k] = (int)kt.ev[k].size(); bytes[k] = 0;
+    }
+    int be = block_elems(e->tok_embd.type), bb = block_bytes(e->tok_embd.type);
+    bytes[0] = (int64_t)c.n_embd / be * bb;
+    for (auto& L : e->layers) {
+        bytes[1] += seg_bytes(L.p_qkv); bytes[3] += seg_bytes(L.p_o);
+        bytes[4] += seg_bytes(L.p_gu); bytes[5] += seg_bytes(L.p_down);
+    }
+    bytes[2] = (int64_t)c.n_layer * 2 * c.n_head_kv * c.head_dim * 2 * (s.n_past + 1);
+    bytes[6] = seg_bytes(e->p_head);
+    bytes[7] = (int64_t)c.n_vocab * 4;
+    s.n_past += 1;
+    return B2_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// single-operator entry points (host buffers in, host buffers out)
+struct DevBuf {
+    void* p = nullptr;
+    ~DevBuf() { if (p) cudaFree(p); }
+    cudaError_t alloc(size_t n) { return cudaMalloc(&p, n ? n : 1); }
+    template <typename T> T* as() { return (T*)p; }
+};
+
+extern "C" int b2_op_dequantize(int device, int type, const void* blocks, int64_t n, float* out) {
+    if (!blocks || !out || n < 0) return fail(B2_ERR_ARG, "bad arguments");
+    int be = block_elems(type), bb = block_bytes(type);
+    if (!bb) return fail(B2_ERR_UNSUPPORTED, "unsupported ggml type");
+    if (n % be) return fail(B2_ERR_ARG, "n_elems is not a whole number of blocks");
+    if (n == 0) return B2_OK;
+    CK(cudaSetDevice(device));
+    DevBuf in, o;
+    CK(in.alloc((size_t)(n / be * bb))); CK(o.alloc((size_t)n * 4));
+    CK(cudaMemcpy(in.p, blocks, (size_t)(n / be * bb), cudaMemcpyHostToDevice));
+    CK(dequantize_launch(type, in.as<uint8_t>(), n, o.as<float>(), 0));
+    CK(cudaMemcpy(out, o.p, (size_t)n * 4, cudaMemcpyDeviceToHost));
+    return B2_OK;
+}
+
+static int op_matvec_common(int device, MvParams& p, const void* w0, const void* w1, int n_rows, int K,
+                            const float* x, const float* nw, const float* resid, float* y, int planes, int n_ctas) {
+    if (n_ctas <= 0) { int sms = 148; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device); n_ctas = sms; }
+    CK(mv_init());
+    int rc = mv_plan(p, n_ctas);
+    if (rc) return fail(B2_ERR_UNSUPPORTED, "mat-vec shape/type not supported (plan code " + std::to_string(rc) + ")");
+    DevBuf dw0, dw1, dx, dn, dy;
+    size_t wb0 = (size_t)n_rows * p.seg[0].row_bytes;
+    CK(dw0.alloc(wb0 + 64)); CK(cudaMemcpy(dw0.p, w0, wb0, cudaMemcpyHostToDevice));
+    p.seg[0].w = dw0.as<uint8_t>();
+    if (w1) {
+        size_t wb1 = (size_t)n_rows * p.seg[1].row_bytes;
+        CK(dw1.alloc(wb1 + 64)); CK(cudaMemcpy(dw1.p, w1, wb1, cudaMemcpyHostToDevice));
+        p.seg[1].w = dw1.as<uint8_t>();
+    }
+    CK(dx.alloc((size_t)K * 4)); CK(cudaMemcpy(dx.p, x, (size_t)K * 4, cudaMemcpyHostToDevice));
+    p.x = dx.as<float>();
+    if (nw) { CK(dn.alloc((size_t)K * 4)); CK(cudaMemcpy(dn.p, nw, (size_t)K * 4, cudaMemcpyHostToDevice)); p.norm_w = dn.as<float>(); }
+    CK(dy.alloc((size_t)n_rows * 4));
+    if (resid) CK(cudaMemcpy(dy.p, resid, (size_t)n_rows * 4, cudaMemcpyHostToDevice));
+    p.y = dy.as<float>(); p.resid = dy.as<float>();
+    CK(mv_launch(p, n_ctas, 0, planes != 1, false));
+    CK(cudaDeviceSynchronize());
+    CK(cudaMemcpy(y, dy.p, (size_t)n_rows * 4, cudaMemcpyDeviceToHost));
+    return B2_OK;
+}
+
+extern "C" int b2_op_matvec(int device, int type, const void* w, int n_rows, int K, const float* x,
+                            const float* nw, float eps, const float* resid, float* y, int planes, int n_ctas) {
+    if (!w || !x || !y || n_rows <= 0 || K <= 0) return fail(B2_ERR_ARG, "bad arguments");
+    if (n_rows % 2) return fail(B2_ERR_ARG, "n_rows must be even");
+    CK(cudaSetDevice(device));
+    MvParams p = {};
+    p.nseg = 1; p.seg[0].type = type; p.seg[0].n_rows = n_rows; p.K = K;
+    p.mode = resid ? MV_RESID : MV_STORE; p.eps = eps;
+    return op_matvec_common(device, p, w, nullptr, n_rows, K, x, nw, resid, y, planes, n_ctas);
+}
+
+extern "C" int b2_op_gate_up(int device, int tg, const void* wg, int tu, const void* wu, int n_rows, int K,
+                             const float* x, const float* nw, float eps, float* y, int n_ctas) {
+    if (!wg || !wu || !x || !y || n_rows <= 0 || K <= 0) return fail(B2_ERR_ARG, "bad arguments");
+    if (n_rows % 2) return fail(B2_ERR_ARG, "n_rows must be even");
+    CK(cudaSetDevice(device));
+    MvParams p = {};
+    p.nseg = 2; p.seg[0].type = tg; p.seg[0].n_rows = n_rows; p.seg[1].type = tu; p.seg[1].n_rows = n_rows;
+    p.K = K; p.mode = MV_GATEUP; p.eps = eps;
+    return op_matvec_common(device, p, wg, wu, n_rows, K, x, nw, nullptr, y, 2, n_ctas);
+}
+
+extern "C" int b2_op_rmsnorm(int device, const float* x, const float* w, float eps, int K, int rows, float* y) {
+    if (!x || !w || !y || K <= 0 || rows < 0) return fail(B2_ERR_ARG, "bad arguments");
+    if (rows == 0) return B2_OK;
+    CK(cudaSetDevice(device));
+    DevBuf dx, dw, dy;
+    size_t n = (size_t)K * rows * 4;
+    CK(dx.alloc(n)); CK(dw.alloc((size_t)K * 4)); CK(dy.alloc(n));
+    CK(cudaMemcpy(dx.p, x, n, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(dw.p, w, (size_t)K * 4, cudaMemcpyHostToDevice));
+    CK(rmsnorm_launch(dx.as<float>(), dw.as<float>(), eps, K, rows, dy.as<float>(), 0));
+    CK(cudaMemcpy(y, dy.p, n, cudaMemcpyDeviceToHost));
+    return B2_OK;
+}
+
+extern "C" int b2_op_attention_decode(int device, const float* q, const uint16_t* k, const uint16_t* v, int T,
+                                      int n_head, int n_kv, int hd, int bt, const int32_t* blocks, int nblk_total,
+                                      int n_splits, float* out) {
+    if (!q || !k || !v || !blocks || !out || T <= 0) return fail(B2_ERR_ARG, "bad arguments");
+    if (hd != 64 && hd != 128) return fail(B2_ERR_UNSUPPORTED, "head_dim must be 64 or 128");
+    if (n_head % n_kv || n_head / n_kv > 8) return fail(B2_ERR_UNSUPPORTED, "n_head / n_kv must be an integer <= 8");
+    if (bt <= 0 || bt % 16) return fail(B2_ERR_ARG, "block_tokens must be a multiple of 16");
+    int need = (T + bt - 1) / bt;
+    if (n_splits < 1) n_splits = 1;
+    for (int i = 0; i < need; i++) if (blocks[i] < 0 || blocks[i] >= nblk_total) return fail(B2_ERR_ARG, "page id out of range");
+    CK(cudaSetDevice(device));
+    CK(attn_init());
+    size_t pool_elems = (size_t)nblk_total * n_kv * bt * hd;
+    std::vector<uint16_t> hk(pool_elems, 0), hv(pool_elems, 0);
+    for (int t = 0; t < T; t++) {
+        int page = blocks[t / bt], slot = t % bt;
+        for (int h = 0; h < n_kv; h++) {
+            size_t dst = (((size_t)page * n_kv + h) * bt + slot) * hd, src = ((size_t)t * n_kv + h) * hd;
+            memcpy(&hk[dst], &k[src], hd * 2); memcpy(&hv[dst], &v[src], hd * 2);
+        }
+    }
+    DevBuf dk, dv, dq, dout, dbt, dpos, dscr, dcnt;
+    CK(dk.alloc(pool_elems * 2)); CK(dv.alloc(pool_elems * 2));
+    CK(cudaMemcpy(dk.p, hk.data(), pool_elems * 2, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(dv.p, hv.data(), pool_elems * 2, cudaMemcpyHostToDevice));
+    CK(dq.alloc((size_t)n_head * hd * 4)); CK(cudaMemcpy(dq.p, q, (size_t)n_head * hd * 4, cudaMemcpyHostToDevice));
+    CK(dout.alloc((size_t)n_head * hd * 4));
+    CK(dbt.alloc((size_t)need * 4)); CK(cudaMemcpy(dbt.p, blocks, (size_t)need * 4, cudaMemcpyHostToDevice));
+    int pos = T - 1;
+    CK(dpos.alloc(4)); CK(cudaMemcpy(dpos.p, &pos, 4, cudaMemcpyHostToDevice));
+    CK(dscr.alloc(attn_scratch_floats(n_head, n_kv, hd, n_splits) * 4));
+    CK(dcnt.alloc((size_t)n_kv * 4)); CK(cudaMemset(dcnt.p, 0, (size_t)n_kv * 4));
+    AttnParams a = {};
+    a.q = dq.as<float>(); a.k_cache = dk.as<__half>(); a.v_cache = dv.as<__half>(); a.block_table = dbt.as<int>();
+    a.pos_ptr = dpos.as<int>(); a.out = dout.as<float>(); a.scratch = dscr.as<float>(); a.counters = dcnt.as<unsigned>();
+    a.n_head = n_head; a.n_kv = n_kv; a.head_dim = hd; a.block_tokens = bt; a.n_splits = n_splits;
+    a.scale = 1.0f / sqrtf((float)hd);
+    CK(attn_decode_launch(a, 0, false));
+    CK(cudaDeviceSynchronize());
+    CK(cudaMemcpy(out, dout.p, (size_t)n_head * hd * 4, cudaMemcpyDeviceToHost));
+    return B2_OK;
+}
+
+extern "C" int b2_op_sample(int device, const float* logits, int V, const b2_sampling* sp, const int32_t* hist,
+                            int n_hist, double u, int32_t* tok) {
+    if (!logits || !sp || !tok || V <= 0) return fail(B2_ERR_ARG, "bad arguments");
+    if (n_hist < 0 || n_hist > HISTORY_LEN) return fail(B2_ERR_ARG, "history longer than 64");
+    if (sp->temperature > 0.f && (sp->top_k < 1 || sp->top_k > SAMPLER_MAX_K))
+        return fail(B2_ERR_UNSUPPORTED, "top_k must be in 1..1024 on the device sampler");
+    CK(cudaSetDevice(device));
+    DevBuf dl, dsp, dst, du, di;
+    CK(dl.alloc((size_t)V * 4)); CK(cudaMemcpy(dl.p, logits, (size_t)V * 4, cudaMemcpyHostToDevice));
+    SampleParams p = {};
+    p.temperature = sp->temperature; p.top_p = sp->top_p; p.min_p = sp->min_p; p.repeat_penalty = sp->repeat_penalty;
+    p.freq_penalty = sp->frequency_penalty; p.presence_penalty = sp->presence_penalty; p.top_k = sp->top_k;
+    p.penalty_last_n = sp->penalty_last_n;
+    CK(dsp.alloc(sizeof(p))); CK(cudaMemcpy(dsp.p, &p, sizeof(p), cudaMemcpyHostToDevice));
+    SamplerState h = {};
+    for (int i = 0; i < n_hist; i++) h.history[i] = hist[i];
+    h.n_hist = n_hist;
+    CK(dst.alloc(sizeof(h))); CK(cudaMemcpy(dst.p, &h, sizeof(h), cudaMemcpyHostToDevice));
+    std::vector<double> uu(8192, u);
+    CK(du.alloc(sizeof(double) * 8192)); CK(cudaMemcpy(du.p, uu.data(), sizeof(double) * 8192, cudaMemcpyHostToDevice));
+    CK(di.alloc(sizeof(int) * 8)); CK(cudaMemset(di.p, 0, sizeof(int) * 8));
+    int* ints = di.as<int>();
+    CK(sample_launch(dl.as<float>(), V, dsp.as<SampleParams>(), dst.as<SamplerState>(), du.as<double>(), ints + 3,
+                     ints + 2, ints + 0, ints + 1, 0, false));
+    CK(cudaDeviceSynchronize());
+    CK(cudaMemcpy(tok, ints + 2, sizeof(int), cudaMemcpyDeviceToHost));
+    return B2_OK;
+}

@@ -1,0 +1,93 @@
+// Internal launch interfaces between the engine (engine.cu) and the kernels. Not part of the
+// C ABI -- that is include/b200_gguf.h.
+#pragma once
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace b2 {
+
+// ---------------------------------------------------------------- mat-vec (matvec.cu)
+enum MvMode { MV_STORE = 0, MV_RESID = 1, MV_QKV = 2, MV_GATEUP = 3 };
+constexpr int MV_MAX_STAGES = 8;
+constexpr int MV_MAX_PAIRS = 4;
+
+struct MvSeg {
+    const uint8_t* w;   // quantised rows, unchanged GGUF bytes
+    int type;           // ggml type id
+    int n_rows;
+    int row_bytes;      // filled by mv_plan
+    int cta0, ncta;     // CTA range that works on this segment (filled by mv_plan)
+    int out_off;        // element offset into y / resid
+};
+
+struct MvParams {
+    MvSeg seg[3];
+    int nseg;
+    int K;
+    int mode;
+    const float* x;         // [K] float32 input
+    const float* norm_w;    // optional fused RMSNorm weight [K]
+    float eps;
+    float* y;
+    const float* resid;
+    // MV_QKV epilogue
+    float* q_out;
+    __half* k_cache;        // this layer's K pool
+    __half* v_cache;
+    const int* pos_ptr;     // position of the token being decoded (device)
+    const int* block_table; // this sequence's page table (device)
+    const float* rope_freq; // [head_dim / 2]
+    int head_dim, n_kv, block_tokens;
+    // plan (mv_plan)
+    int warps_per_row, rows_per_tile, stage_bytes, n_stages;
+};
+
+cudaError_t mv_init();   // once per device, outside stream capture
+int mv_plan(MvParams& p, int n_ctas);
+size_t mv_smem_bytes(const MvParams& p);
+cudaError_t mv_launch(const MvParams& p, int n_ctas, cudaStream_t stream, bool act2, bool pdl);
+
+// ---------------------------------------------------------------- flash-decode (attention.cu)
+struct AttnParams {
+    const float* q;          // [n_head * head_dim] float32 (already rotated)
+    const __half* k_cache;   // layer pool [num_blocks][n_kv][block_tokens][head_dim]
+    const __half* v_cache;
+    const int* block_table;  // [max_blocks] pages of this sequence
+    const int* pos_ptr;      // current position; attends to positions [0, pos]
+    float* out;              // [n_head * head_dim] float32
+    float* scratch;          // split-K partials: [n_kv][n_splits][G][head_dim + 2]
+    unsigned int* counters;  // [n_kv] arrival tickets (zero between launches)
+    int n_head, n_kv, head_dim, block_tokens, n_splits;
+    float scale;             // 1 / sqrt(head_dim)
+};
+cudaError_t attn_init();
+size_t attn_scratch_floats(int n_head, int n_kv, int head_dim, int n_splits);
+cudaError_t attn_decode_launch(const AttnParams& p, cudaStream_t stream, bool pdl);
+
+// ---------------------------------------------------------------- small kernels (misc.cu)
+cudaError_t dequantize_launch(int type, const uint8_t* raw, long n_elems, float* out, cudaStream_t s);
+// x[0..K) = dequantised row `*token_ptr` of the embedding table
+cudaError_t embed_row_launch(int type, const uint8_t* table, int K, const int* token_ptr, float* x,
+                             cudaStream_t s, bool pdl);
+cudaError_t rmsnorm_launch(const float* x, const float* w, float eps, int K, int rows, float* y, cudaStream_t s);
+
+// ---------------------------------------------------------------- sampler (sampler.cu)
+struct SampleParams {
+    float temperature, top_p, min_p, repeat_penalty, freq_penalty, presence_penalty;
+    int top_k;          // 1..SAMPLER_MAX_K
+    int penalty_last_n; // <= 64... window over the history ring
+};
+constexpr int SAMPLER_MAX_K = 1024;
+constexpr int HISTORY_LEN = 64;
+struct SamplerState {            // per sequence slot, device resident
+    int history[HISTORY_LEN];    // ring of the last tokens (prompt + generated)
+    int n_hist;                  // total tokens ever pushed
+};
+// logits[V] (modified in place by the penalties) -> *out_token; also pushes the token into the
+// history ring, stores it in *next_token_ptr and bumps *pos_ptr (device-resident decode loop).
+cudaError_t sample_launch(float* logits, int n_vocab, const SampleParams* params_dev, SamplerState* st,
+                          const double* uniforms, int* step_ptr, int* out_token, int* next_token_ptr,
+                          int* pos_ptr, cudaStream_t s, bool pdl);
+
+}  // namespace b2

@@ -1,0 +1,356 @@
+// ggml quant-block arithmetic shared by every kernel (and by the host self-test).
+//
+// Two families of routines:
+//  * dequant_elem<T>(blk, e): the value of element e of one block, in float32 with a separate
+//    multiply and subtract -- bit-identical to gguf-py's numpy dequantize (the dequant parity
+//    bar is bit-exact). Used by the dequantise / embedding-row kernels.
+//  * chunk_dot<T>(row, u, act): integer dot product of one 64-weight chunk of a quantised row
+//    with a quantised activation chunk, scaled back to float. This is the inner loop of the
+//    decode mat-vec: weights stay packed (nibbles/bytes), activations are two int8 planes
+//    (x ~= dx * (a + b/252), ~16 bits), products go through dp4a, so the only floating-point
+//    work is one fused scale per 16- or 32-element group.
+//
+// Block layouts: see oracle/ggml_blocks.py (restated from gguf-py quants.py) -- replaces
+// ggml-cuda's dequantize_block_* / vec_dot_*_q8_1 that the reference reaches through
+// llama-cpp-python (SURVEY.md 2.3 K1,K4,K5).
+//
+// Everything here compiles for the host too (B2_HOST_EMU) so tests/host_selftest.cpp can check
+// the bit-twiddling against the oracle without a GPU.
+#pragma once
+#include <stdint.h>
+#include <string.h>
+
+#if defined(__CUDACC__) && !defined(B2_HOST_EMU)
+#include <cuda_fp16.h>
+#define B2_HD __host__ __device__ __forceinline__
+#define B2_D __device__ __forceinline__
+#else
+#define B2_HD inline
+#define B2_D inline
+#endif
+
+namespace b2 {
+
+enum GgmlType { T_F32 = 0, T_F16 = 1, T_Q4_0 = 2, T_Q8_0 = 8, T_Q4_K = 12, T_Q5_K = 13, T_Q6_K = 14 };
+
+B2_HD int block_elems(int t) {
+    return (t == T_F32 || t == T_F16) ? 1 : (t == T_Q4_0 || t == T_Q8_0) ? 32 : 256;
+}
+B2_HD int block_bytes(int t) {
+    switch (t) {
+        case T_F32: return 4;
+        case T_F16: return 2;
+        case T_Q4_0: return 18;
+        case T_Q8_0: return 34;
+        case T_Q4_K: return 144;
+        case T_Q5_K: return 176;
+        case T_Q6_K: return 210;
+        default: return 0;
+    }
+}
+
+// ---------------------------------------------------------------- primitives
+#if defined(__CUDA_ARCH__) && !defined(B2_HOST_EMU)
+B2_D float h2f(uint32_t h) { return __half2float(__ushort_as_half((unsigned short)h)); }
+B2_D int dp4a(int a, int b, int c) { return __dp4a(a, b, c); }
+B2_D uint32_t fshr(uint32_t lo, uint32_t hi, uint32_t s) { return __funnelshift_r(lo, hi, s); }
+B2_D float fmul(float a, float b) { return __fmul_rn(a, b); }
+B2_D float fsub(float a, float b) { return __fsub_rn(a, b); }
+B2_D uint32_t ld32(const uint8_t* p) { return *reinterpret_cast<const uint32_t*>(p); }
+B2_D uint32_t ld16(const uint8_t* p) { return *reinterpret_cast<const uint16_t*>(p); }
+struct U4 { uint32_t x, y, z, w; };
+B2_D U4 ld128(const uint8_t* p) {
+    uint4 v = *reinterpret_cast<const uint4*>(p);
+    U4 r; r.x = v.x; r.y = v.y; r.z = v.z; r.w = v.w; return r;
+}
+#else
+inline float h2f(uint32_t h) {
+    uint32_t s = (h >> 15) & 1, e = (h >> 10) & 31, m = h & 1023, o;
+    if (e == 0) {
+        if (m == 0) o = s << 31;
+        else { int k = 0; while (!(m & 1024)) { m <<= 1; k++; } m &= 1023; o = (s << 31) | ((uint32_t)(113 - k) << 23) | (m << 13); }
+    } else if (e == 31) o = (s << 31) | 0x7f800000u | (m << 13);
+    else o = (s << 31) | ((e + 112) << 23) | (m << 13);
+    float f; memcpy(&f, &o, 4); return f;
+}
+inline int dp4a(int a, int b, int c) {
+    for (int i = 0; i < 4; i++) c += (int)(int8_t)(a >> (8 * i)) * (int)(int8_t)(b >> (8 * i));
+    return c;
+}
+inline uint32_t fshr(uint32_t lo, uint32_t hi, uint32_t s) {
+    s &= 31; return s ? (lo >> s) | (hi << (32 - s)) : lo;
+}
+inline float fmul(float a, float b) { volatile float r = a * b; return r; }
+inline float fsub(float a, float b) { volatile float r = a - b; return r; }
+inline uint32_t ld32(const uint8_t* p) { uint32_t v; memcpy(&v, p, 4); return v; }
+inline uint32_t ld16(const uint8_t* p) { uint16_t v; memcpy(&v, p, 2); return v; }
+struct U4 { uint32_t x, y, z, w; };
+inline U4 ld128(const uint8_t* p) { U4 r; memcpy(&r, p, 16); return r; }
+#endif
+
+// load n 32-bit words starting at a 2-byte-aligned address (aligned loads + funnel shift)
+template <int N>
+B2_D void ld_words_u2(const uint8_t* p, uint32_t (&w)[N]) {
+    uint32_t mis = (uint32_t)(reinterpret_cast<uintptr_t>(p) & 3);
+    const uint8_t* pa = p - mis;          // pointer arithmetic keeps the (shared) address space
+    uint32_t sh = mis * 8;                // 0 or 16
+    uint32_t prev = ld32(pa);
+#pragma unroll
+    for (int i = 0; i < N; i++) {
+        uint32_t next = ld32(pa + 4 * (i + 1));
+        w[i] = fshr(prev, next, sh);
+        prev = next;
+    }
+}
+
+// 6-bit (scale, min) of sub-block `is` from the 12-byte K-quant scale field
+B2_HD void k_scale_min(const uint8_t* s, int is, uint32_t& sc, uint32_t& m) {
+    if (is < 4) {
+        sc = s[is] & 63; m = s[is + 4] & 63;
+    } else {
+        sc = (s[is + 4] & 15) | ((s[is - 4] >> 6) << 4);
+        m = (s[is + 4] >> 4) | ((s[is] >> 6) << 4);
+    }
+}
+
+// ---------------------------------------------------------------- exact element dequant
+// blk points at one block (any alignment: byte loads only), e = element index in the block.
+B2_D float dequant_elem(int type, const uint8_t* blk, int e) {
+    switch (type) {
+        case T_F32: { uint32_t v = blk[0] | (blk[1] << 8) | (blk[2] << 16) | ((uint32_t)blk[3] << 24); float f; memcpy(&f, &v, 4); return f; }
+        case T_F16: return h2f(blk[0] | (blk[1] << 8));
+        case T_Q4_0: {
+            float d = h2f(blk[0] | (blk[1] << 8));
+            int q = (e < 16) ? (blk[2 + e] & 15) : (blk[2 + e - 16] >> 4);
+            return fmul(d, (float)(q - 8));
+        }
+        case T_Q8_0: {
+            float d = h2f(blk[0] | (blk[1] << 8));
+            return fmul((float)(int8_t)blk[2 + e], d);
+        }
+        case T_Q4_K:
+        case T_Q5_K: {
+            float d = h2f(blk[0] | (blk[1] << 8)), dmin = h2f(blk[2] | (blk[3] << 8));
+            int is = e >> 5, l = e & 31;
+            uint32_t sc, m;
+            k_scale_min(blk + 4, is, sc, m);
+            const uint8_t* qs = blk + (type == T_Q4_K ? 16 : 48);
+            int byte = qs[(is >> 1) * 32 + l];
+            int q = (is & 1) ? (byte >> 4) : (byte & 15);
+            if (type == T_Q5_K) q |= ((blk[16 + l] >> is) & 1) << 4;
+            float dl = fmul(d, (float)sc), ml = fmul(dmin, (float)m);
+            return fsub(fmul(dl, (float)q), ml);
+        }
+        case T_Q6_K: {
+            int hf = e >> 7, ep = e & 127, nib = ep >> 6, kq = ep >> 5, l = ep & 31;
+            int lo = blk[64 * hf + (ep & 63)];
+            lo = nib ? (lo >> 4) : (lo & 15);
+            int hi = (blk[128 + 32 * hf + l] >> (2 * kq)) & 3;
+            int q = (lo | (hi << 4)) - 32;
+            float d = h2f(blk[208] | (blk[209] << 8));
+            float dl = fmul(d, (float)(int8_t)blk[192 + (e >> 4)]);
+            return fmul(dl, (float)q);
+        }
+    }
+    return 0.f;
+}
+
+// ---------------------------------------------------------------- activation chunk
+// One lane's 64 activations, quantised to two int8 planes per 32-element block:
+//   x[i] ~= dx[i/32] * (a[i] + b[i] / ACT_RES)        |a| <= 127, |b| <= 126
+// s16[g] = exact float sum of x over 16-element group g (for the "-min", "-8", "-32" terms).
+#define B2_ACT_RES 252.0f
+struct ActChunk {
+    int a[16];
+    int b[16];
+    float dx[2];
+    float s16[4];
+};
+
+// Quantise 32 floats t[0..31] (already multiplied by any norm weight) into words a[8], b[8].
+// Returns amax; dx = amax / 127.
+B2_D float quantize32(const float* t, int* a, int* b, float& sum_lo, float& sum_hi) {
+    float amax = 0.f, s0 = 0.f, s1 = 0.f;
+#pragma unroll
+    for (int i = 0; i < 32; i++) {
+        float v = t[i];
+        amax = fmaxf(amax, fabsf(v));
+        if (i < 16) s0 += v; else s1 += v;
+    }
+    sum_lo = s0; sum_hi = s1;
+    float id = amax > 0.f ? 127.0f / amax : 0.f;
+    float dxl = amax / 127.0f;
+    float id2 = id * B2_ACT_RES;
+    const float MAGIC = 12582912.0f;  // 1.5 * 2^23: float add rounds to nearest integer
+#pragma unroll
+    for (int w = 0; w < 8; w++) {
+        uint32_t aw = 0, bw = 0;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            float v = t[4 * w + j];
+            float ra = v * id + MAGIC;
+            float af = ra - MAGIC;
+            float r = v - af * dxl;
+            float rb = r * id2 + MAGIC;
+            uint32_t ia, ib;
+            memcpy(&ia, &ra, 4); memcpy(&ib, &rb, 4);
+            aw |= (ia & 0xffu) << (8 * j);
+            bw |= (ib & 0xffu) << (8 * j);
+        }
+        a[w] = (int)aw; b[w] = (int)bw;
+    }
+    return amax;
+}
+
+// ---------------------------------------------------------------- chunk dot products
+// `row` = first byte of the quantised row (in shared memory on the GPU), u = 64-weight chunk
+// index within the row. ACT2 = use the second (residual) activation plane.
+
+template <bool ACT2>
+B2_D float fin(int A, int B, float dx) {
+    return ACT2 ? dx * ((float)A + (float)B * (1.0f / B2_ACT_RES)) : dx * (float)A;
+}
+
+template <bool ACT2>
+B2_D float chunk_dot_q4k(const uint8_t* row, int u, const ActChunk& act) {
+    int j = u >> 2, c = u & 3;
+    const uint8_t* blk = row + j * 144;
+    U4 h = ld128(blk);
+    U4 q0 = ld128(blk + 16 + 32 * c), q1 = ld128(blk + 32 + 32 * c);
+    uint32_t qw[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+    uint32_t sh = (c & 1) * 16;
+    uint32_t w0 = h.y >> sh, w1 = h.z >> sh, w2 = h.w >> sh;
+    uint32_t scp, mp;
+    if (c < 2) { scp = w0 & 0x3F3Fu; mp = w1 & 0x3F3Fu; }
+    else { scp = (w2 & 0x0F0Fu) | ((w0 >> 2) & 0x3030u); mp = ((w2 >> 4) & 0x0F0Fu) | ((w1 >> 2) & 0x3030u); }
+    float d = h2f(h.x & 0xffffu), dmin = h2f(h.x >> 16);
+    int Alo = 0, Blo = 0, Ahi = 0, Bhi = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        int lo = (int)(qw[k] & 0x0F0F0F0Fu), hi = (int)((qw[k] >> 4) & 0x0F0F0F0Fu);
+        Alo = dp4a(lo, act.a[k], Alo);
+        Ahi = dp4a(hi, act.a[8 + k], Ahi);
+        if (ACT2) { Blo = dp4a(lo, act.b[k], Blo); Bhi = dp4a(hi, act.b[8 + k], Bhi); }
+    }
+    float r = d * (float)(scp & 0xffu) * fin<ACT2>(Alo, Blo, act.dx[0])
+            - dmin * (float)(mp & 0xffu) * (act.s16[0] + act.s16[1]);
+    r += d * (float)(scp >> 8) * fin<ACT2>(Ahi, Bhi, act.dx[1])
+       - dmin * (float)(mp >> 8) * (act.s16[2] + act.s16[3]);
+    return r;
+}
+
+template <bool ACT2>
+B2_D float chunk_dot_q5k(const uint8_t* row, int u, const ActChunk& act) {
+    int j = u >> 2, c = u & 3;
+    const uint8_t* blk = row + j * 176;
+    U4 h = ld128(blk);
+    U4 h0 = ld128(blk + 16), h1 = ld128(blk + 32);
+    U4 q0 = ld128(blk + 48 + 32 * c), q1 = ld128(blk + 64 + 32 * c);
+    uint32_t qw[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+    uint32_t hw[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+    uint32_t sh = (c & 1) * 16;
+    uint32_t w0 = h.y >> sh, w1 = h.z >> sh, w2 = h.w >> sh;
+    uint32_t scp, mp;
+    if (c < 2) { scp = w0 & 0x3F3Fu; mp = w1 & 0x3F3Fu; }
+    else { scp = (w2 & 0x0F0Fu) | ((w0 >> 2) & 0x3030u); mp = ((w2 >> 4) & 0x0F0Fu) | ((w1 >> 2) & 0x3030u); }
+    float d = h2f(h.x & 0xffffu), dmin = h2f(h.x >> 16);
+    int Alo = 0, Blo = 0, Ahi = 0, Bhi = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        uint32_t hb = hw[k] >> (2 * c);
+        int lo = (int)((qw[k] & 0x0F0F0F0Fu) | ((hb & 0x01010101u) << 4));
+        int hi = (int)(((qw[k] >> 4) & 0x0F0F0F0Fu) | (((hb >> 1) & 0x01010101u) << 4));
+        Alo = dp4a(lo, act.a[k], Alo);
+        Ahi = dp4a(hi, act.a[8 + k], Ahi);
+        if (ACT2) { Blo = dp4a(lo, act.b[k], Blo); Bhi = dp4a(hi, act.b[8 + k], Bhi); }
+    }
+    float r = d * (float)(scp & 0xffu) * fin<ACT2>(Alo, Blo, act.dx[0])
+            - dmin * (float)(mp & 0xffu) * (act.s16[0] + act.s16[1]);
+    r += d * (float)(scp >> 8) * fin<ACT2>(Ahi, Bhi, act.dx[1])
+       - dmin * (float)(mp >> 8) * (act.s16[2] + act.s16[3]);
+    return r;
+}
+
+template <bool ACT2>
+B2_D float chunk_dot_q6k(const uint8_t* row, int u, const ActChunk& act) {
+    int j = u >> 2, hf = (u >> 1) & 1, nib = u & 1;
+    const uint8_t* blk = row + j * 210;  // 2-byte aligned only
+    uint32_t ql[16], qh[8], scw[1];
+    ld_words_u2<16>(blk + 64 * hf, ql);
+    ld_words_u2<8>(blk + 128 + 32 * hf, qh);
+    ld_words_u2<1>(blk + 192 + 8 * hf + 4 * nib, scw);
+    float d = h2f(ld16(blk + 208));
+    float r = 0.f;
+#pragma unroll
+    for (int g = 0; g < 4; g++) {       // 16-element groups
+        int A = 0, B = 0;
+#pragma unroll
+        for (int kk = 0; kk < 4; kk++) {
+            int k = 4 * g + kk;
+            uint32_t l4 = (ql[k] >> (4 * nib)) & 0x0F0F0F0Fu;
+            uint32_t h2 = (qh[k & 7] >> (4 * nib + 2 * (k >> 3))) & 0x03030303u;
+            int q = (int)(l4 | (h2 << 4));
+            A = dp4a(q, act.a[k], A);
+            if (ACT2) B = dp4a(q, act.b[k], B);
+        }
+        float sc = (float)(int8_t)(scw[0] >> (8 * g));
+        r += (d * sc) * (fin<ACT2>(A, B, act.dx[g >> 1]) - 32.0f * act.s16[g]);
+    }
+    return r;
+}
+
+template <bool ACT2>
+B2_D float chunk_dot_q4_0(const uint8_t* row, int u, const ActChunk& act) {
+    const uint8_t* p = row + 36 * u;   // two 18-byte blocks; 4-byte aligned
+    uint32_t W[9];
+#pragma unroll
+    for (int i = 0; i < 9; i++) W[i] = ld32(p + 4 * i);
+    float d0 = h2f(W[0] & 0xffffu), d1 = h2f(W[4] >> 16);
+    int A0 = 0, B0 = 0, A1 = 0, B1 = 0;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        uint32_t q0 = fshr(W[k], W[k + 1], 16), q1 = W[5 + k];
+        int lo0 = (int)(q0 & 0x0F0F0F0Fu), hi0 = (int)((q0 >> 4) & 0x0F0F0F0Fu);
+        int lo1 = (int)(q1 & 0x0F0F0F0Fu), hi1 = (int)((q1 >> 4) & 0x0F0F0F0Fu);
+        A0 = dp4a(lo0, act.a[k], A0); A0 = dp4a(hi0, act.a[4 + k], A0);
+        A1 = dp4a(lo1, act.a[8 + k], A1); A1 = dp4a(hi1, act.a[12 + k], A1);
+        if (ACT2) {
+            B0 = dp4a(lo0, act.b[k], B0); B0 = dp4a(hi0, act.b[4 + k], B0);
+            B1 = dp4a(lo1, act.b[8 + k], B1); B1 = dp4a(hi1, act.b[12 + k], B1);
+        }
+    }
+    return d0 * (fin<ACT2>(A0, B0, act.dx[0]) - 8.0f * (act.s16[0] + act.s16[1]))
+         + d1 * (fin<ACT2>(A1, B1, act.dx[1]) - 8.0f * (act.s16[2] + act.s16[3]));
+}
+
+template <bool ACT2>
+B2_D float chunk_dot_q8_0(const uint8_t* row, int u, const ActChunk& act) {
+    const uint8_t* p = row + 68 * u;   // two 34-byte blocks; 4-byte aligned
+    uint32_t W[17];
+#pragma unroll
+    for (int i = 0; i < 17; i++) W[i] = ld32(p + 4 * i);
+    float d0 = h2f(W[0] & 0xffffu), d1 = h2f(W[8] >> 16);
+    int A0 = 0, B0 = 0, A1 = 0, B1 = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        int q0 = (int)fshr(W[k], W[k + 1], 16), q1 = (int)W[9 + k];
+        A0 = dp4a(q0, act.a[k], A0);
+        A1 = dp4a(q1, act.a[8 + k], A1);
+        if (ACT2) { B0 = dp4a(q0, act.b[k], B0); B1 = dp4a(q1, act.b[8 + k], B1); }
+    }
+    return d0 * fin<ACT2>(A0, B0, act.dx[0]) + d1 * fin<ACT2>(A1, B1, act.dx[1]);
+}
+
+template <bool ACT2>
+B2_D float chunk_dot(int type, const uint8_t* row, int u, const ActChunk& act) {
+    switch (type) {
+        case T_Q4_K: return chunk_dot_q4k<ACT2>(row, u, act);
+        case T_Q6_K: return chunk_dot_q6k<ACT2>(row, u, act);
+        case T_Q5_K: return chunk_dot_q5k<ACT2>(row, u, act);
+        case T_Q4_0: return chunk_dot_q4_0<ACT2>(row, u, act);
+        case T_Q8_0: return chunk_dot_q8_0<ACT2>(row, u, act);
+    }
+    return 0.f;
+}
+
+}  // namespace b2
