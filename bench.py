@@ -1,0 +1,313 @@
+#!/usr/bin/env python
+"""Headline benchmark: decode tok/s of the Llama-3-8B-arch Q4_K_M synthetic GGUF at batch 1
+(BASELINE.json configs[1]) on N B200s (N independent replicas, weak scaling).
+
+    python bench.py --gpus 1 --steps 256 --warmup 16
+    torchrun ... bench.py --gpus N ...            (one rank per GPU)
+    python bench.py --impl reference              (the CPU restatement of the reference's
+                                                   llama.cpp CPU path, on the host cores)
+
+One "step" = one decoded token for one sequence (every weight byte and every live KV byte read
+once). `value` times K steps with CUDA events on the engine's stream with the sequence state
+resident in HBM; `e2e` times the same K tokens through the public `Llama.create_completion`
+call (host token ids in, host text out). See DESIGN.md "Measurement".
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "llama-fastapi-k8s-gpu_b200")
+for p in (ROOT, PKG):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+WORKLOADS = {
+    # name: (arch, ftype, prompt tokens)   -- BASELINE.json configs
+    "llama3-8b-q4_k_m-bs1": ("llama-3-8b", "Q4_K_M", 512),
+    "tinyllama-1.1b-q4_0-bs1": ("tinyllama-1.1b", "Q4_0", 128),
+    "llama3-8b-q8_0-bs1": ("llama-3-8b", "Q8_0", 512),
+    "mistral-7b-q4_k_m-8k": ("mistral-7b", "Q4_K_M", 8192 - 512),
+    "tiny-q4_k_m": ("tiny", "Q4_K_M", 32),
+}
+
+
+def model_path(arch, ftype, seed=1):
+    base = "/dev/shm" if os.path.isdir("/dev/shm") else "/tmp"
+    return os.path.join(base, "b200_gguf_models", f"{arch}-{ftype}-seed{seed}.gguf")
+
+
+def ensure_model(arch, ftype, seed=1):
+    from llama_cpp import synth
+    path = model_path(arch, ftype, seed)
+    if not os.path.exists(path):
+        synth.write_synthetic_model(path, arch, ftype, seed=seed, output_std=0.1, with_vocab=True)
+    return path
+
+
+def algorithmic_bytes(gguf, ctx_mean):
+    """W_read (all tensors but token_embd, plus one embedding row) + ctx * KV bytes."""
+    md = gguf.metadata
+    total = sum(t.nbytes for t in gguf.tensors.values())
+    emb = gguf.tensors["token_embd.weight"]
+    w_read = total - emb.nbytes + emb.nbytes // emb.shape[1]
+    n_head = int(md["llama.attention.head_count"])
+    kv = int(md.get("llama.attention.head_count_kv", n_head))
+    hd = int(md["llama.embedding_length"]) // n_head
+    kv_pos = int(md["llama.block_count"]) * 2 * kv * hd * 2
+    return w_read, kv_pos, w_read + ctx_mean * kv_pos
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons of one GPU through NVML while the timed region runs."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.stop_flag, self.max_mhz = index, [], set(), False, None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {"hw_slowdown": nv.nvmlClocksThrottleReasonHwSlowdown,
+                 "hw_thermal_slowdown": nv.nvmlClocksThrottleReasonHwThermalSlowdown,
+                 "sw_thermal_slowdown": nv.nvmlClocksThrottleReasonSwThermalSlowdown,
+                 "sw_power_cap": nv.nvmlClocksThrottleReasonSwPowerCap}
+        while not self.stop_flag:
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for k, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            time.sleep(0.01)
+
+    def result(self):
+        self.stop_flag = True
+        self.join(timeout=2)
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+def measured_peak_gbs():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def ncu_traffic_bytes():
+    """dram read+write bytes per decode step from the committed ncu capture, if there is one."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            return json.load(f).get("dram_bytes_per_step")
+    except Exception:
+        return None
+
+
+def cpu_reference_run(path, n_warm, n_steps, budget_s, prompt_len=16):
+    """Time the CPU restatement of the reference's llama.cpp CPU path: decode tokens one at a time."""
+    from oracle.cpu_ref import CpuRef
+    import numpy as np
+    c = CpuRef(path, n_ctx=prompt_len + n_warm + n_steps + 8)
+    rng = np.random.default_rng(0)
+    toks = rng.integers(0, c.n_vocab, size=prompt_len + n_warm + n_steps)
+    t0 = time.perf_counter()
+    c.eval(int(toks[0]))
+    first = time.perf_counter() - t0
+    for t in toks[1:prompt_len]:
+        c.eval(int(t), want_logits=False)
+    per = max(first, 1e-4)
+    n_warm = max(0, min(n_warm, int(0.2 * budget_s / per)))
+    n_steps = max(1, min(n_steps, int(0.8 * budget_s / per)))
+    i = prompt_len
+    for _ in range(n_warm):
+        c.eval(int(toks[i])); i += 1
+    t0 = time.perf_counter()
+    for _ in range(n_steps):
+        c.eval(int(toks[i])); i += 1
+    dt = time.perf_counter() - t0
+    threads = c.threads
+    c.close()
+    return dict(value=n_steps / dt, ms_per_step=dt / n_steps * 1e3, steps=n_steps, warmup=n_warm, cores=threads,
+                sample=f"{n_steps} single-token decode steps (all layers + lm_head) after a {prompt_len}-token context; "
+                       f"KV reads are <2% of the bytes at the workload's context, weights are streamed in full")
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=256)
+    ap.add_argument("--warmup", type=int, default=16)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="llama3-8b-q4_k_m-bs1", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-budget-s", type=float, default=20.0)
+    ap.add_argument("--profile-kernels", action="store_true", help="also print a per-kernel-kind breakdown to stderr")
+    ap.add_argument("--ncu-mode", action="store_true", help="short run for ncu: skip e2e, cpu baseline, clocks")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    arch, ftype, n_prompt = WORKLOADS[args.workload]
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    cfg = {"workload": f"{args.workload}: {arch}-arch {ftype} synthetic GGUF (seed 1), {n_prompt}-token prompt then "
+                       f"batch-1 greedy decode", "prompt_tokens": n_prompt, "batch": 1,
+           "parallelism": f"replicas x{world}" if world > 1 else "single GPU",
+           "l2": "inputs (weights 4.6 GB/step) larger than L2; no flush needed"}
+
+    if args.impl == "reference":
+        # the reference's own CPU implementation of the path (restated: llama_cpp is not installable here)
+        if rank != 0:
+            return 0
+        path = ensure_model(arch, ftype)
+        r = cpu_reference_run(path, args.warmup, args.steps, budget_s=150.0)
+        line = {"impl": "reference", "metric": "decode_tokens_per_s", "value": r["value"], "unit": "tok/s", "n_gpus": 0,
+                "steps": r["steps"], "steps_requested": args.steps, "warmup": r["warmup"], "ms_per_step": r["ms_per_step"],
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8 x int4/6 dot, f32 accumulate",
+                "data": "synthetic", "config": cfg,
+                "cpu_baseline": {"value": r["value"], "unit": "tok/s", "cores": r["cores"], "kind": "port", "sample": r["sample"]},
+                "e2e": {"value": r["value"], "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line))
+        return 0
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    os.environ["B200_DEVICE"] = str(local_rank)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    if local_rank == 0:
+        path = ensure_model(arch, ftype)
+    barrier()
+    path = model_path(arch, ftype)
+
+    from llama_cpp import Llama
+    from llama_cpp.engine import SamplingSettings
+    from llama_cpp.gguf_file import GGUFFile
+    K, W = args.steps, args.warmup
+    n_ctx = n_prompt + W + K + 16
+    t_load = time.perf_counter()
+    llm = Llama(model_path=path, n_gpu_layers=-1, n_ctx=n_ctx, seed=1, verbose=False)
+    t_load = time.perf_counter() - t_load
+    eng = llm._engine
+    rng = np.random.default_rng(123 + rank)
+    prompt = [int(t) for t in rng.integers(0, eng.dims.n_vocab, size=n_prompt)]
+
+    # ---- kernel-resident timing: prompt KV and all state already in HBM -------------------------
+    greedy = SamplingSettings(temperature=0.0, repeat_penalty=1.0)
+    with eng.lock:
+        eng.ensure_pages(0, n_ctx)
+        eng.seq_begin(0, 0, [], greedy)
+        t0 = time.perf_counter()
+        eng.prefill(0, prompt)
+        ttft_ms = (time.perf_counter() - t0) * 1e3
+        eng.sample(0)
+        eng.decode_n(0, W)                         # warm-up (also captures the CUDA graph)
+        clocks = ClockSampler(local_rank)
+        if not args.ncu_mode:
+            clocks.start()
+        launches0 = eng.launch_count()
+        barrier()
+        eng.timer_start()
+        eng.decode_n(0, K)
+        ms = eng.timer_stop()
+        barrier()
+        launches = eng.launch_count() - launches0
+        clk = clocks.result() if not args.ncu_mode else {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        kinds = eng.profile_decode_step(0) if (args.profile_kernels or not args.ncu_mode) else None
+        mode = eng.mode()
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max = float(t.item())
+    value = world * K / (ms_max / 1e3)
+
+    # ---- end to end through the public API: host token ids in, host text out -------------------
+    e2e = None
+    if not args.ncu_mode:
+        llm.reset()
+        prompt2 = [int(x) for x in rng.integers(0, eng.dims.n_vocab, size=n_prompt)]
+        llm.create_completion(prompt2[:64], max_tokens=8, temperature=0.0, repeat_penalty=1.0)     # warm the API path
+        barrier()
+        t0 = time.perf_counter()
+        out = llm.create_completion(prompt2, max_tokens=K, temperature=0.0, repeat_penalty=1.0)
+        wall = time.perf_counter() - t0
+        barrier()
+        tm = llm.last_timings
+        n_gen = out["usage"]["completion_tokens"]
+        dec_s = tm["decode_ms"] / 1e3
+        t2 = torch.tensor([dec_s, tm["ttft_ms"]], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t2, op=dist.ReduceOp.MAX)
+        e2e = {"value": world * max(n_gen - 1, 1) / float(t2[0].item()), "unit": "tok/s",
+               "h2d_bytes_per_step": round(4 * n_prompt / max(n_gen, 1), 2), "d2h_bytes_per_step": 4,
+               "tokens": n_gen, "ttft_ms": float(t2[1].item()), "wall_s": wall,
+               "note": "Llama.create_completion(token ids, max_tokens=K, temperature=0): decode phase of the call "
+                       "(first token to last), host-timed; includes per-chunk D2H of sampled ids, stop checks, detokenise"}
+
+    if rank != 0:
+        return 0
+    g = GGUFFile(path)
+    ctx_mean = n_prompt + W + K / 2.0
+    w_read, kv_pos, step_bytes = algorithmic_bytes(g, ctx_mean)
+    peak, peak_src = measured_peak_gbs()
+    achieved = step_bytes / (ms_max / K / 1e3) / 1e9
+    roof = {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
+            "traffic": ncu_traffic_bytes(), "peak_source": peak_src, "bytes_per_launch": int(step_bytes),
+            "launch": "one decode step = one CUDA-graph launch (embed, 32 x [qkv, attention, attn_out, gate_up, ffn_down], "
+                      "lm_head, sampler); algorithmic bytes = W_read + mean_ctx * KV bytes/position",
+            "frac_of_8TBs_nominal": round(achieved / 8000.0, 4)}
+    if kinds:
+        roof["kernels"] = {k: {"ms": round(v["ms"], 4), "launches": v["launches"],
+                               "GBps": round(v["bytes"] / max(v["ms"], 1e-9) / 1e6, 1)} for k, v in kinds.items()}
+        roof["kernels_note"] = "one un-graphed decode step with events around every launch (no overlap between kernels)"
+    line = {"metric": "decode_tokens_per_s", "value": round(value, 2), "unit": "tok/s", "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": round(ms_max / K, 5), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "int8x2 activations x int4/6 weights (dp4a), f32 accumulate, f16 KV", "data": "synthetic",
+            "config": cfg, "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof,
+            "engine": mode, "ttft_ms_sequential_prefill": round(ttft_ms, 2), "load_s": round(t_load, 2),
+            "w_read_bytes": int(w_read), "kv_bytes_per_pos": kv_pos, "ctx_mean": ctx_mean}
+    if not args.no_cpu_baseline and not args.ncu_mode:
+        try:
+            r = cpu_reference_run(path, 1, 64, budget_s=args.cpu_budget_s)
+            line["cpu_baseline"] = {"value": round(r["value"], 3), "unit": "tok/s", "cores": r["cores"], "kind": "port",
+                                    "sample": r["sample"]}
+        except Exception as exc:  # noqa: BLE001
+            line["cpu_baseline"] = {"value": None, "unit": "tok/s", "cores": 0, "kind": "port", "sample": f"failed: {exc}"}
+    print(json.dumps(line))
+    llm.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -103,6 +103,15 @@ int b2_sample(b2_engine* e, int slot, int32_t* host_token_out);
 /* One decode step for each listed slot: forward the slot's pending token, sample the next.
  * Writes n sampled tokens. */
 int b2_decode(b2_engine* e, const int32_t* host_slots, int n, int32_t* host_tokens_out);
+/* n decode steps of ONE slot queued back to back (the sampled token never leaves the device
+ * between steps); the n sampled tokens come back in one copy at the end. Used for run-ahead
+ * decoding: the host checks stop conditions afterwards and rewinds with b2_seq_rewind. */
+int b2_decode_n(b2_engine* e, int slot, int n, int32_t* host_tokens_out);
+/* Forget everything after the first n_keep tokens of the slot (KV pages beyond are simply
+ * overwritten later); the token at position n_keep becomes the pending input. Needs the
+ * recent-token history as it stood at that point (for the penalties). */
+int b2_seq_rewind(b2_engine* e, int slot, int n_keep, int32_t pending_token,
+                  const int32_t* host_history, int n_history);
 /* Teacher forcing / tests: overwrite the slot's pending input token. */
 int b2_seq_set_token(b2_engine* e, int slot, int32_t token);
 /* Forward the slot's pending token without sampling (logits left in the slot's buffer). */

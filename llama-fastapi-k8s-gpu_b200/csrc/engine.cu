@@ -45,12 +45,14 @@ struct Slot {
     int* ints = nullptr;           // [0]=token [1]=pos [2]=out_token [3]=step [4]=cursor [5]=pos_base
     int* block_table = nullptr;
     int* prompt = nullptr;         // [n_ctx]
+    int* ring = nullptr;           // [n_ctx + 1] sampled token by position
     SamplerState* sst = nullptr;
     SampleParams* sp = nullptr;
     double* uniforms = nullptr;    // [8192]
     cudaGraphExec_t g_decode = nullptr, g_pre_step = nullptr, g_pre_last = nullptr, g_fwd = nullptr;
     int n_decode_nodes = 0, n_pre_step_nodes = 0, n_pre_last_nodes = 0, n_fwd_nodes = 0;
     int n_past = 0;                // host mirror of ints[1]
+    int n_sampled = 0;             // host mirror of ints[3]
 };
 
 struct b2_engine {
@@ -134,7 +136,7 @@ extern "C" int b2_engine_create(const b2_config* c, b2_engine** out) {
     CK(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
     CK(cudaEventCreate(&e->ev0));
     CK(cudaEventCreate(&e->ev1));
-    CK(cudaMallocHost(&e->pinned, sizeof(int32_t) * (size_t)(c->max_seqs + 16)));
+    CK(cudaMallocHost(&e->pinned, sizeof(int32_t) * (size_t)(c->max_seqs + c->n_ctx + 16)));
     // KV pool: [layer][block][kv_head][token][dim] f16
     e->layer_kv_elems = (size_t)c->kv_num_blocks * c->n_head_kv * c->kv_block_tokens * c->head_dim;
     size_t kvb = e->layer_kv_elems * c->n_layer * sizeof(__half);
@@ -173,6 +175,8 @@ extern "C" int b2_engine_create(const b2_config* c, b2_engine** out) {
         CK(cudaMalloc(&s.block_table, sizeof(int) * e->max_blocks));
         CK(cudaMemset(s.block_table, 0, sizeof(int) * e->max_blocks));
         CK(cudaMalloc(&s.prompt, sizeof(int) * c->n_ctx));
+        CK(cudaMalloc(&s.ring, sizeof(int) * (c->n_ctx + 1)));
+        CK(cudaMemset(s.ring, 0, sizeof(int) * (c->n_ctx + 1)));
         CK(cudaMalloc(&s.sst, sizeof(SamplerState)));
         CK(cudaMemset(s.sst, 0, sizeof(SamplerState)));
         CK(cudaMalloc(&s.sp, sizeof(SampleParams)));
@@ -201,7 +205,7 @@ extern "C" int b2_engine_destroy(b2_engine* e) {
     for (auto& s : e->slots) {
         free_slot_graphs(s);
         cudaFree(s.x); cudaFree(s.q); cudaFree(s.att); cudaFree(s.h); cudaFree(s.logits);
-        cudaFree(s.ints); cudaFree(s.block_table); cudaFree(s.prompt); cudaFree(s.sst); cudaFree(s.sp);
+        cudaFree(s.ints); cudaFree(s.block_table); cudaFree(s.prompt); cudaFree(s.ring); cudaFree(s.sst); cudaFree(s.sp);
         cudaFree(s.uniforms);
     }
     cudaFree(e->k_pool); cudaFree(e->v_pool); cudaFree(e->rope_freq);
@@ -396,7 +400,7 @@ static int forward_launches(b2_engine* e, Slot& s, bool with_head, bool with_sam
     }
     if (with_sample) {
         tick(7, &ye);
-        CK(sample_launch(s.logits, c.n_vocab, s.sp, s.sst, s.uniforms, s.ints + 3, s.ints + 2, tok, pos, st, pdl));
+        CK(sample_launch(s.logits, c.n_vocab, s.sp, s.sst, s.uniforms, s.ints + 3, s.ints + 2, tok, pos, s.ring, c.n_ctx + 1, st, pdl));
         tock(ye);
         e->launches++;
     }
@@ -496,6 +500,7 @@ extern "C" int b2_seq_begin(b2_engine* e, int slot, int n_past, const int32_t* h
     if (n_uni) CK(cudaMemcpyAsync(s.uniforms, uni, sizeof(double) * n_uni, cudaMemcpyHostToDevice, e->stream));
     CK(cudaStreamSynchronize(e->stream));
     s.n_past = n_past;
+    s.n_sampled = 0;
     return B2_OK;
 }
 
@@ -530,11 +535,12 @@ extern "C" int b2_sample(b2_engine* e, int slot, int32_t* out) {
     // sampler bumps pos: make it point at the last evaluated token first
     set_ints_kernel<<<1, 1, 0, e->stream>>>(s.ints, -1, s.n_past - 1);
     CK(sample_launch(s.logits, e->cfg.n_vocab, s.sp, s.sst, s.uniforms, s.ints + 3, s.ints + 2, s.ints + 0,
-                     s.ints + 1, e->stream, false));
+                     s.ints + 1, s.ring, e->cfg.n_ctx + 1, e->stream, false));
     e->launches += 2;
     CK(cudaMemcpyAsync(e->pinned, s.ints + 2, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
     CK(cudaStreamSynchronize(e->stream));
     if (out) *out = e->pinned[0];
+    s.n_sampled += 1;
     return B2_OK;
 }
 
@@ -552,9 +558,51 @@ extern "C" int b2_decode(b2_engine* e, const int32_t* slots, int n, int32_t* out
         if (rc) return rc;
         CK(cudaMemcpyAsync(e->pinned + i, s.ints + 2, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
         s.n_past += 1;
+        s.n_sampled += 1;
     }
     CK(cudaStreamSynchronize(e->stream));
     if (out) for (int i = 0; i < n; i++) out[i] = e->pinned[i];
+    return B2_OK;
+}
+
+extern "C" int b2_decode_n(b2_engine* e, int slot, int n, int32_t* out) {
+    int rc = check_slot(e, slot); if (rc) return rc;
+    std::lock_guard<std::mutex> lk(e->mu);
+    Slot& s = e->slots[slot];
+    if (n <= 0) return fail(B2_ERR_ARG, "n must be positive");
+    if (s.n_past + n > e->cfg.n_ctx) return fail(B2_ERR_ARG, "context window full");
+    CK(cudaSetDevice(e->cfg.device));
+    for (int i = 0; i < n; i++) {
+        rc = run_step(e, s, GK_DECODE);
+        if (rc) return rc;
+    }
+    // step i forwards the token at position n_past+i and its sample lands at ring[n_past+i+1]
+    CK(cudaMemcpyAsync(e->pinned, s.ring + s.n_past + 1, sizeof(int) * n, cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    if (out) memcpy(out, e->pinned, sizeof(int) * n);
+    s.n_past += n;
+    s.n_sampled += n;
+    return B2_OK;
+}
+
+extern "C" int b2_seq_rewind(b2_engine* e, int slot, int n_keep, int32_t pending, const int32_t* hist, int n_hist) {
+    int rc = check_slot(e, slot); if (rc) return rc;
+    std::lock_guard<std::mutex> lk(e->mu);
+    Slot& s = e->slots[slot];
+    if (n_keep < 0 || n_keep > s.n_past) return fail(B2_ERR_ARG, "n_keep out of range");
+    if (pending < 0 || pending >= e->cfg.n_vocab) return fail(B2_ERR_ARG, "token id out of range");
+    if (n_hist < 0 || n_hist > HISTORY_LEN) return fail(B2_ERR_ARG, "history longer than 64");
+    CK(cudaSetDevice(e->cfg.device));
+    int dropped = s.n_past - n_keep;
+    SamplerState h = {};
+    for (int i = 0; i < n_hist; i++) h.history[i] = hist[i];
+    h.n_hist = n_hist;
+    s.n_sampled = s.n_sampled > dropped ? s.n_sampled - dropped : 0;
+    int ints[4] = {pending, n_keep, pending, s.n_sampled};
+    CK(cudaMemcpyAsync(s.sst, &h, sizeof(h), cudaMemcpyHostToDevice, e->stream));
+    CK(cudaMemcpyAsync(s.ints, ints, sizeof(ints), cudaMemcpyHostToDevice, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    s.n_past = n_keep;
     return B2_OK;
 }
 
@@ -821,7 +869,7 @@ extern "C" int b2_op_sample(int device, const float* logits, int V, const b2_sam
     CK(di.alloc(sizeof(int) * 8)); CK(cudaMemset(di.p, 0, sizeof(int) * 8));
     int* ints = di.as<int>();
     CK(sample_launch(dl.as<float>(), V, dsp.as<SampleParams>(), dst.as<SamplerState>(), du.as<double>(), ints + 3,
-                     ints + 2, ints + 0, ints + 1, 0, false));
+                     ints + 2, ints + 0, ints + 1, nullptr, 0, 0, false));
     CK(cudaDeviceSynchronize());
     CK(cudaMemcpy(tok, ints + 2, sizeof(int), cudaMemcpyDeviceToHost));
     return B2_OK;

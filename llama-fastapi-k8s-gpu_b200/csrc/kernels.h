@@ -85,9 +85,10 @@ struct SamplerState {            // per sequence slot, device resident
     int n_hist;                  // total tokens ever pushed
 };
 // logits[V] (modified in place by the penalties) -> *out_token; also pushes the token into the
-// history ring, stores it in *next_token_ptr and bumps *pos_ptr (device-resident decode loop).
+// history ring, stores it in *next_token_ptr, bumps *pos_ptr and records the token at
+// out_ring[new pos] (device-resident decode loop: the host can read many steps back at once).
 cudaError_t sample_launch(float* logits, int n_vocab, const SampleParams* params_dev, SamplerState* st,
                           const double* uniforms, int* step_ptr, int* out_token, int* next_token_ptr,
-                          int* pos_ptr, cudaStream_t s, bool pdl);
+                          int* pos_ptr, int* out_ring, int ring_len, cudaStream_t s, bool pdl);
 
 }  // namespace b2

@@ -61,7 +61,8 @@ __device__ void select_bin(SmShared& sh, int nbins, unsigned k) {
 __global__ void __launch_bounds__(SM_THREADS) sample_kernel(float* logits, int V, const SampleParams* prm,
                                                             SamplerState* st, const double* uniforms,
                                                             int n_uniform, int* step_ptr, int* out_token,
-                                                            int* next_token_ptr, int* pos_ptr) {
+                                                            int* next_token_ptr, int* pos_ptr, int* out_ring,
+                                                            int ring_len) {
     __shared__ SmShared sh;
     const int t = threadIdx.x, lane = t & 31, w = t >> 5;
     griddep_launch();
@@ -204,9 +205,7 @@ __global__ void __launch_bounds__(SM_THREADS) sample_kernel(float* logits, int V
             // std::discrete_distribution: normalise in double, cumulative sums, lower_bound(u)
             double tot = 0.0;
             for (int i = 0; i < n; i++) tot += (double)(__uint_as_float(sh.hist[i]) / sumf);
-            int step = *step_ptr;
-            double u = uniforms[step % n_uniform];
-            *step_ptr = step + 1;
+            double u = uniforms[*step_ptr % n_uniform];
             double c = 0.0; int pick = n - 1;
             for (int i = 0; i < n - 1; i++) {
                 c += (double)(__uint_as_float(sh.hist[i]) / sumf) / tot;
@@ -218,9 +217,12 @@ __global__ void __launch_bounds__(SM_THREADS) sample_kernel(float* logits, int V
     if (t == 0) {
         *out_token = result;
         *next_token_ptr = result;
+        *step_ptr = *step_ptr + 1;      // one uniform consumed per sampled token (greedy too)
         st->history[n_hist & (HISTORY_LEN - 1)] = result;
         st->n_hist = n_hist + 1;
-        *pos_ptr = *pos_ptr + 1;
+        int np = *pos_ptr + 1;          // position the sampled token will occupy
+        *pos_ptr = np;
+        if (out_ring && np < ring_len) out_ring[np] = result;
     }
 }
 
@@ -228,7 +230,7 @@ struct SampleLaunchArgs { int dummy; };
 
 cudaError_t sample_launch(float* logits, int n_vocab, const SampleParams* params_dev, SamplerState* st,
                           const double* uniforms, int* step_ptr, int* out_token, int* next_token_ptr,
-                          int* pos_ptr, cudaStream_t s, bool pdl) {
+                          int* pos_ptr, int* out_ring, int ring_len, cudaStream_t s, bool pdl) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(1); cfg.blockDim = dim3(SM_THREADS); cfg.stream = s;
     cudaLaunchAttribute at[1];
@@ -237,7 +239,7 @@ cudaError_t sample_launch(float* logits, int n_vocab, const SampleParams* params
     cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
     int n_uniform = 8192;
     return cudaLaunchKernelEx(&cfg, sample_kernel, logits, n_vocab, params_dev, st, uniforms, n_uniform,
-                              step_ptr, out_token, next_token_ptr, pos_ptr);
+                              step_ptr, out_token, next_token_ptr, pos_ptr, out_ring, ring_len);
 }
 
 }  // namespace b2

@@ -43,6 +43,8 @@ SIGNATURES = {
     "b2_prefill": (c_int, [c_void_p, c_int, POINTER(c_int32), c_int]),
     "b2_sample": (c_int, [c_void_p, c_int, POINTER(c_int32)]),
     "b2_decode": (c_int, [c_void_p, POINTER(c_int32), c_int, POINTER(c_int32)]),
+    "b2_decode_n": (c_int, [c_void_p, c_int, c_int, POINTER(c_int32)]),
+    "b2_seq_rewind": (c_int, [c_void_p, c_int, c_int, c_int32, POINTER(c_int32), c_int]),
     "b2_seq_set_token": (c_int, [c_void_p, c_int, c_int32]),
     "b2_forward_pending": (c_int, [c_void_p, c_int]),
     "b2_get_logits": (c_int, [c_void_p, c_int, c_void_p]),

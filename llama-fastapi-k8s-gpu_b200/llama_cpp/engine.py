@@ -168,6 +168,17 @@ class Engine:
         check(self.lib.b2_decode(self._h, self._slots, n, self._tok), "b2_decode")
         return [self._tok[i] for i in range(n)]
 
+    def decode_n(self, slot: int, n: int) -> List[int]:
+        """n back-to-back decode steps of one slot; tokens come back in one copy."""
+        out = (ctypes.c_int32 * n)()
+        check(self.lib.b2_decode_n(self._h, slot, n, out), "b2_decode_n")
+        return list(out)
+
+    def rewind(self, slot: int, n_keep: int, pending_token: int, history: Sequence[int]):
+        hist = list(history)[-64:]
+        ha = (ctypes.c_int32 * max(1, len(hist)))(*hist)
+        check(self.lib.b2_seq_rewind(self._h, slot, n_keep, pending_token, ha, len(hist)), "b2_seq_rewind")
+
     def set_token(self, slot: int, token: int):
         check(self.lib.b2_seq_set_token(self._h, slot, token), "b2_seq_set_token")
 

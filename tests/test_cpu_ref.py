@@ -1,0 +1,24 @@
+"""The C restatement of ggml's CPU path (oracle/cpu_ref.c, the timed CPU baseline) against the
+float32 oracle: equal up to the int8-activation noise ggml accepts (SURVEY.md 7 hard part #3)."""
+import os
+
+import numpy as np
+import pytest
+
+
+@pytest.mark.parametrize("arch,ftype,seed", [("tiny", "Q4_K_M", 1), ("tiny128", "Q4_0", 2), ("tiny", "Q8_0", 3), ("tiny128", "Q5_K", 4)])
+def test_cpu_ref_close_to_float_oracle(tmp_models, arch, ftype, seed):
+    from llama_cpp import synth
+    from oracle.cpu_ref import CpuRef
+    from oracle.llama_ref import RefModel
+    path = os.path.join(tmp_models, f"cr_{arch}_{ftype}.gguf")
+    synth.write_synthetic_model(path, arch, ftype, seed=seed, output_std=0.1)
+    toks = np.random.default_rng(0).integers(0, 700, size=10)
+    ref = RefModel(path).forward(toks)
+    c = CpuRef(path, 64)
+    for i, t in enumerate(toks):
+        lg = c.eval(int(t))
+        # int8 activations: a few percent of the logit spread; the arg-max agrees when the margin is clear
+        assert np.abs(lg - ref[i]).max() < 0.05 * ref[i].std() * 4 + 0.05, i
+    assert c.threads >= 1
+    c.close()
