@@ -96,7 +96,7 @@ __global__ void __launch_bounds__(AT_THREADS) attn_decode_kernel(const AttnParam
         const int st = ti & 1;
         const int t0 = p0 + ti * AT_TT, tl = min(p1, t0 + AT_TT) - t0;
         if (tid == 0 && ti + 1 < ntile) issue(ti + 1);
-        mbar_wait(&sh.full[st], (ti >> 1) & 1);
+        mbar_wait(&sh.full[st], (ti >> 1) & 1, p.err, 0x20001u);
 
         // ---- phase 1: scores
         {

@@ -29,6 +29,19 @@ static int fail(int code, const std::string& msg) { g_err = msg; return code; }
             return fail(B2_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(_e));         \
     } while (0)
 
+// kernel watchdogs (ptx.cuh mbar_wait) report through a host-mapped word; call after a sync
+static int check_kernel_error() {
+    unsigned int* w = kernel_error_word();
+    if (w && *w) {
+        unsigned int c = *w;
+        *w = 0;
+        char buf[96];
+        snprintf(buf, sizeof(buf), "kernel barrier wait timed out (watchdog code 0x%x)", c);
+        return fail(B2_ERR_CUDA, buf);
+    }
+    return B2_OK;
+}
+
 struct DevTensor {
     uint8_t* ptr = nullptr;
     int type = -1;
@@ -302,25 +315,26 @@ extern "C" int b2_engine_finalize(b2_engine* e) {
         q.K = c.n_embd; q.mode = MV_QKV; q.norm_w = (const float*)L.attn_norm.ptr; q.eps = c.rms_eps;
         q.k_cache = e->k_pool + (size_t)l * e->layer_kv_elems; q.v_cache = e->v_pool + (size_t)l * e->layer_kv_elems;
         q.rope_freq = e->rope_freq; q.head_dim = c.head_dim; q.n_kv = c.n_head_kv; q.block_tokens = c.kv_block_tokens;
+        q.err = kernel_error_word();
         if ((rc = plan_or_fail(q, e->n_ctas, "attn_q/k/v"))) return rc;
         L.p_qkv = q;
         MvParams o = {};
-        o.nseg = 1; o.seg[0] = make_seg(L.wo); o.K = qd; o.mode = MV_RESID;
+        o.nseg = 1; o.seg[0] = make_seg(L.wo); o.K = qd; o.mode = MV_RESID; o.err = kernel_error_word();
         if ((rc = plan_or_fail(o, e->n_ctas, "attn_output"))) return rc;
         L.p_o = o;
         MvParams g = {};
         g.nseg = 2; g.seg[0] = make_seg(L.wgate); g.seg[1] = make_seg(L.wup); g.K = c.n_embd; g.mode = MV_GATEUP;
-        g.norm_w = (const float*)L.ffn_norm.ptr; g.eps = c.rms_eps;
+        g.norm_w = (const float*)L.ffn_norm.ptr; g.eps = c.rms_eps; g.err = kernel_error_word();
         if ((rc = plan_or_fail(g, e->n_ctas, "ffn_gate/up"))) return rc;
         L.p_gu = g;
         MvParams d = {};
-        d.nseg = 1; d.seg[0] = make_seg(L.wdown); d.K = c.n_ff; d.mode = MV_RESID;
+        d.nseg = 1; d.seg[0] = make_seg(L.wdown); d.K = c.n_ff; d.mode = MV_RESID; d.err = kernel_error_word();
         if ((rc = plan_or_fail(d, e->n_ctas, "ffn_down"))) return rc;
         L.p_down = d;
     }
     MvParams h = {};
     h.nseg = 1; h.seg[0] = make_seg(e->output); h.K = c.n_embd; h.mode = MV_STORE;
-    h.norm_w = (const float*)e->out_norm.ptr; h.eps = c.rms_eps;
+    h.norm_w = (const float*)e->out_norm.ptr; h.eps = c.rms_eps; h.err = kernel_error_word();
     if ((rc = plan_or_fail(h, e->n_ctas, "output"))) return rc;
     e->p_head = h;
     e->finalized = true;
@@ -369,7 +383,7 @@ static int forward_launches(b2_engine* e, Slot& s, bool with_head, bool with_sam
         a.q = s.q; a.k_cache = q.k_cache; a.v_cache = q.v_cache; a.block_table = s.block_table; a.pos_ptr = pos;
         a.out = s.att; a.scratch = e->attn_scratch; a.counters = e->attn_counters;
         a.n_head = c.n_head; a.n_kv = c.n_head_kv; a.head_dim = c.head_dim; a.block_tokens = c.kv_block_tokens;
-        a.n_splits = e->n_splits; a.scale = 1.0f / sqrtf((float)c.head_dim);
+        a.n_splits = e->n_splits; a.scale = 1.0f / sqrtf((float)c.head_dim); a.err = kernel_error_word();
         tick(2, &ye);
         CK(attn_decode_launch(a, st, pdl));
         tock(ye);
@@ -521,6 +535,7 @@ extern "C" int b2_prefill(b2_engine* e, int slot, const int32_t* tokens, int n) 
         if (rc) return rc;
     }
     CK(cudaStreamSynchronize(e->stream));
+    if ((rc = check_kernel_error())) return rc;
     s.n_past += n;     // device pos stays at the last token; b2_sample / set_token move it on
     return B2_OK;
 }
@@ -561,6 +576,7 @@ extern "C" int b2_decode(b2_engine* e, const int32_t* slots, int n, int32_t* out
         s.n_sampled += 1;
     }
     CK(cudaStreamSynchronize(e->stream));
+    { int rc2 = check_kernel_error(); if (rc2) return rc2; }
     if (out) for (int i = 0; i < n; i++) out[i] = e->pinned[i];
     return B2_OK;
 }
@@ -579,6 +595,7 @@ extern "C" int b2_decode_n(b2_engine* e, int slot, int n, int32_t* out) {
     // step i forwards the token at position n_past+i and its sample lands at ring[n_past+i+1]
     CK(cudaMemcpyAsync(e->pinned, s.ring + s.n_past + 1, sizeof(int) * n, cudaMemcpyDeviceToHost, e->stream));
     CK(cudaStreamSynchronize(e->stream));
+    if ((rc = check_kernel_error())) return rc;
     if (out) memcpy(out, e->pinned, sizeof(int) * n);
     s.n_past += n;
     s.n_sampled += n;
@@ -629,6 +646,7 @@ extern "C" int b2_forward_pending(b2_engine* e, int slot) {
     rc = run_step(e, s, GK_FWD);
     if (rc) return rc;
     CK(cudaStreamSynchronize(e->stream));
+    if ((rc = check_kernel_error())) return rc;
     s.n_past += 1;
     return B2_OK;
 }
@@ -761,8 +779,11 @@ static int op_matvec_common(int device, MvParams& p, const void* w0, const void*
     CK(dy.alloc((size_t)n_rows * 4));
     if (resid) CK(cudaMemcpy(dy.p, resid, (size_t)n_rows * 4, cudaMemcpyHostToDevice));
     p.y = dy.as<float>(); p.resid = dy.as<float>();
+    p.err = kernel_error_word();
     CK(mv_launch(p, n_ctas, 0, planes != 1, false));
     CK(cudaDeviceSynchronize());
+    { int rc2 = check_kernel_error(); if (rc2) return rc2; }
+
     CK(cudaMemcpy(y, dy.p, (size_t)n_rows * 4, cudaMemcpyDeviceToHost));
     return B2_OK;
 }
@@ -839,9 +860,10 @@ extern "C" int b2_op_attention_decode(int device, const float* q, const uint16_t
     a.q = dq.as<float>(); a.k_cache = dk.as<__half>(); a.v_cache = dv.as<__half>(); a.block_table = dbt.as<int>();
     a.pos_ptr = dpos.as<int>(); a.out = dout.as<float>(); a.scratch = dscr.as<float>(); a.counters = dcnt.as<unsigned>();
     a.n_head = n_head; a.n_kv = n_kv; a.head_dim = hd; a.block_tokens = bt; a.n_splits = n_splits;
-    a.scale = 1.0f / sqrtf((float)hd);
+    a.scale = 1.0f / sqrtf((float)hd); a.err = kernel_error_word();
     CK(attn_decode_launch(a, 0, false));
     CK(cudaDeviceSynchronize());
+    { int rc2 = check_kernel_error(); if (rc2) return rc2; }
     CK(cudaMemcpy(out, dout.p, (size_t)n_head * hd * 4, cudaMemcpyDeviceToHost));
     return B2_OK;
 }

@@ -5,6 +5,23 @@
 #include <math.h>
 #include "quant_blocks.cuh"
 
+template <int T>
+static float host_row(const uint8_t* rowp, int K, const b2::ActView& v, bool act2) {
+    // what one warp does for one row: loop over K-slices, 32 lanes each
+    const int sb = b2::slice_bytes(T);
+    float acc = 0.f;
+    for (int s = 0; s * B2_SLICE < K; s++) {
+        int se = K - s * B2_SLICE < B2_SLICE ? K - s * B2_SLICE : B2_SLICE;
+        for (int lane = 0; lane < 32; lane++) {
+            if (lane * 64 >= se) continue;
+            b2::LaneAct la;
+            if (act2) { b2::load_act<T, true>(la, v, s * B2_SLICE, lane); acc += b2::row_dot<T, true>(rowp + (size_t)s * sb, lane, la); }
+            else { b2::load_act<T, false>(la, v, s * B2_SLICE, lane); acc += b2::row_dot<T, false>(rowp + (size_t)s * sb, lane, la); }
+        }
+    }
+    return acc;
+}
+
 extern "C" {
 
 // dequantise n_elems elements (whole blocks) with the exact element routine
@@ -15,35 +32,49 @@ int b2_host_dequant(int type, const uint8_t* raw, long n_elems, float* out) {
     return 0;
 }
 
-// y[r] = W[r,:] . x through quantize32 + chunk_dot, one 64-chunk at a time (what one GPU lane does)
+// y[r] = W[r,:] . x through quantize32 + load_act + row_dot (what the GPU lanes do)
 int b2_host_matvec(int type, const uint8_t* w, int n_rows, int K, const float* x, float* y, int act2,
                    int misalign) {
     if (K % 256) return -1;
     long row_bytes = (long)K / b2::block_elems(type) * b2::block_bytes(type);
-    // copy each row into a scratch buffer at a chosen alignment (tests the 2-byte-aligned path)
     uint8_t* buf = new uint8_t[row_bytes + 64];
     memset(buf, 0xA5, row_bytes + 64);
-    int nchunk = K / 64;
-    b2::ActChunk* acts = new b2::ActChunk[nchunk];
-    for (int u = 0; u < nchunk; u++) {
-        for (int h = 0; h < 2; h++) {
-            float lo, hi;
-            float amax = b2::quantize32(x + 64 * u + 32 * h, acts[u].a + 8 * h, acts[u].b + 8 * h, lo, hi);
-            acts[u].dx[h] = amax / 127.0f;
-            acts[u].s16[2 * h] = lo; acts[u].s16[2 * h + 1] = hi;
+    // activation planes (16-byte aligned like the shared-memory arrays)
+    const int Kp = (K + B2_SLICE - 1) / B2_SLICE * B2_SLICE;   // planes padded to whole slices
+    uint8_t* abuf = new uint8_t[2 * Kp + 64];
+    memset(abuf, 0, 2 * Kp + 64);
+    uint8_t* aa = (uint8_t*)(((uintptr_t)abuf + 15) & ~(uintptr_t)15);
+    uint8_t* ab = aa + Kp;
+    float* dx = new float[K / 32 + 4];
+    float* s16 = new float[K / 16 + 4];
+    const int layout = b2::act_layout_of(type);
+    for (int b = 0; b < K / 32; b++) {
+        int qa[8], qb[8]; float lo, hi;
+        float amax = b2::quantize32(x + 32 * b, qa, qb, lo, hi);
+        for (int h2 = 0; h2 < 2; h2++) {       // two 16-byte units per 32-block, permuted inside the slice
+            int u = 2 * b + h2, sl = u / 128, pos = b2::act_unit_pos(layout, u % 128);
+            memcpy(aa + sl * B2_SLICE + 16 * pos, qa + 4 * h2, 16);
+            memcpy(ab + sl * B2_SLICE + 16 * pos, qb + 4 * h2, 16);
         }
+        dx[b] = amax / 127.0f; s16[2 * b] = lo; s16[2 * b + 1] = hi;
     }
+    b2::ActView v; v.a = aa; v.b = ab; v.dx = dx; v.s16 = s16;
     uintptr_t base = ((uintptr_t)buf + 15) & ~(uintptr_t)15;
     uint8_t* rowp = (uint8_t*)base + misalign;
+    int rc = 0;
     for (int r = 0; r < n_rows; r++) {
         memcpy(rowp, w + r * row_bytes, row_bytes);
-        float acc = 0.f;
-        for (int u = 0; u < nchunk; u++)
-            acc += act2 ? b2::chunk_dot<true>(type, rowp, u, acts[u]) : b2::chunk_dot<false>(type, rowp, u, acts[u]);
-        y[r] = acc;
+        switch (type) {
+            case b2::T_Q4_0: y[r] = host_row<b2::T_Q4_0>(rowp, K, v, act2); break;
+            case b2::T_Q8_0: y[r] = host_row<b2::T_Q8_0>(rowp, K, v, act2); break;
+            case b2::T_Q4_K: y[r] = host_row<b2::T_Q4_K>(rowp, K, v, act2); break;
+            case b2::T_Q5_K: y[r] = host_row<b2::T_Q5_K>(rowp, K, v, act2); break;
+            case b2::T_Q6_K: y[r] = host_row<b2::T_Q6_K>(rowp, K, v, act2); break;
+            default: rc = -2;
+        }
     }
-    delete[] acts; delete[] buf;
-    return 0;
+    delete[] buf; delete[] abuf; delete[] dx; delete[] s16;
+    return rc;
 }
 
 // reconstruct the quantised activations (for checking the ~16-bit claim)

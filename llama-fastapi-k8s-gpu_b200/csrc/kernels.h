@@ -9,8 +9,9 @@ namespace b2 {
 
 // ---------------------------------------------------------------- mat-vec (matvec.cu)
 enum MvMode { MV_STORE = 0, MV_RESID = 1, MV_QKV = 2, MV_GATEUP = 3 };
-constexpr int MV_MAX_STAGES = 8;
-constexpr int MV_MAX_PAIRS = 4;
+constexpr int MV_MAX_STAGES = 24;
+constexpr int MV_ROWS = 4;                 // rows per group (one warp, one ring stage)
+constexpr int MV_SMEM_MAX = 112 * 1024;    // two CTAs per SM: this kernel + the next one prefetching
 
 struct MvSeg {
     const uint8_t* w;   // quantised rows, unchanged GGUF bytes
@@ -39,8 +40,13 @@ struct MvParams {
     const int* block_table; // this sequence's page table (device)
     const float* rope_freq; // [head_dim / 2]
     int head_dim, n_kv, block_tokens;
+    unsigned int* err;      // host-mapped error word (kernel watchdogs)
     // plan (mv_plan)
-    int warps_per_row, rows_per_tile, stage_bytes, n_stages;
+    int n_slices;           // K-slices of 2048 elements per row
+    int slot_bytes;         // one row-slice slot in a stage
+    int stage_bytes, n_stages;
+    int act_layout, act_dual; // activation plane layout (quant_blocks.cuh); both layouts present?
+    int ring_off;           // byte offset of the ring in dynamic shared memory (after the activations)
 };
 
 cudaError_t mv_init();   // once per device, outside stream capture
@@ -60,12 +66,15 @@ struct AttnParams {
     unsigned int* counters;  // [n_kv] arrival tickets (zero between launches)
     int n_head, n_kv, head_dim, block_tokens, n_splits;
     float scale;             // 1 / sqrt(head_dim)
+    unsigned int* err;       // host-mapped error word (kernel watchdogs)
 };
 cudaError_t attn_init();
 size_t attn_scratch_floats(int n_head, int n_kv, int head_dim, int n_splits);
 cudaError_t attn_decode_launch(const AttnParams& p, cudaStream_t stream, bool pdl);
 
 // ---------------------------------------------------------------- small kernels (misc.cu)
+// One pinned, device-mapped word per process that kernel watchdogs write to; 0 = no error.
+unsigned int* kernel_error_word();
 cudaError_t dequantize_launch(int type, const uint8_t* raw, long n_elems, float* out, cudaStream_t s);
 // x[0..K) = dequantised row `*token_ptr` of the embedding table
 cudaError_t embed_row_launch(int type, const uint8_t* table, int K, const int* token_ptr, float* x,

@@ -4,63 +4,58 @@
 // runs under llm.create_chat_completion (/root/reference/api.py:55-63; SURVEY.md 2.3 K2-K7,K11).
 //
 // Structure (one CTA per SM, 9 warps):
-//   * warp 8, one lane: TMA producer. Streams this CTA's contiguous row range through a ring of
-//     shared-memory stages with 1-D bulk copies (cp.async.bulk + mbarrier complete_tx). It never
-//     touches activations, so with programmatic dependent launch it starts prefetching weights
-//     while the previous kernel is still running.
-//   * warps 0-7: consumers. Each lane owns one 64-element chunk of the input vector for the whole
-//     kernel: it loads its 64 floats once (after griddepcontrol.wait), optionally applies the fused
-//     RMSNorm, quantises them to two int8 planes held in registers, and then only streams weight
-//     chunks out of shared memory through dp4a. W_k = ceil(K/2048) warps cover one row; the 8
-//     warps form G = 8 / W_k groups that work on different row pairs of a stage.
-//   * epilogue (one lane per row pair): plain store, residual add, RoPE + paged-KV store for the
-//     fused QKV projection, or SiLU(gate) * up for the fused FFN projection.
+//   * warp 8: TMA producer. A tile = one K-slice (2048 elements) of a group of R=4 consecutive
+//     rows = 4 row-slices of 1-2 KB, brought into one ring stage with 1-D bulk copies
+//     (cp.async.bulk + mbarrier complete_tx); 4 lanes serve a tile, 8 tiles are issued per round.
+//     The producer never touches activations, so with programmatic dependent launch it starts
+//     prefetching weights while the previous kernel is still running.
+//   * warps 0-7: autonomous consumers. Tile q belongs to warp q % 8; a warp walks its row groups,
+//     and for each group the K-slices in order, keeping 4 row accumulators in registers. Per
+//     slice a lane loads its 64 quantised activations (two int8 planes) from shared memory once
+//     and reuses them for the 4 rows; weights stay packed and go through dp4a. No cross-warp
+//     reduction and no block-wide barrier in the main loop: a warp only waits on its own tile's
+//     mbarrier, reduces its 4 rows with a transposed butterfly (6 shuffles) and writes them out.
+//   * prologue (all consumers, after griddepcontrol.wait): x -> optional fused RMSNorm -> two
+//     int8 planes + per-32 scale + per-16 sums in shared memory.
+//   * epilogue (lanes 0 and 16, a row pair each): plain store, residual add, RoPE + paged-KV
+//     store for the fused QKV projection, or SiLU(gate) * up for the fused FFN projection.
 //
 // Roofline: HBM. Algorithmic bytes per launch = sum of the weight bytes of its segments.
 #include "kernels.h"
 #include "ptx.cuh"
 #include "quant_blocks.cuh"
 #include <cuda_fp16.h>
+#include <stdlib.h>
 
 namespace b2 {
 
 constexpr int NCW = 8;                 // consumer warps
 constexpr int NTHREADS = (NCW + 1) * 32;
+constexpr int R = MV_ROWS;             // rows per group
+constexpr int TPB = 32 / R;            // tiles the producer warp issues per round
 
 struct __align__(16) MvShared {
     uint64_t full[MV_MAX_STAGES];
     uint64_t empty[MV_MAX_STAGES];
-    float red[NCW];                    // sum-of-squares partials
-    float part[2][NCW][MV_MAX_PAIRS][2];   // cross-warp partial dot products, double buffered by tile
-    float gate[NCW][MV_MAX_PAIRS][2];  // gate results waiting for the matching up tile
+    float red[NCW];
 };
 
-struct TileInfo {
-    const uint8_t* src;    // 16-byte aligned start of the bulk copy
-    uint32_t bytes;        // multiple of 16
-    uint32_t off;          // offset of the first row inside the stage
-    int seg;               // weight matrix index
-    int row0;              // first row (within the segment)
-    int nrows;
-};
-
-// CTA-uniform description of the work: which segment(s), which rows.
 struct CtaWork {
-    int mode_gateup;
-    int seg;        // segment for non-gateup modes
-    int r0, r1;     // row range [r0, r1)
-    int R;          // rows per tile
-    int ntiles;
+    int seg;            // segment (non gate/up modes)
+    int r0, r1;         // row range [r0, r1)
+    int ng;             // row groups
+    int tpg;            // tiles per group
+    int rounds, rem;    // full rounds of NCW groups, groups in the last partial round
+    int total;          // tiles for the whole CTA
 };
 
 __device__ __forceinline__ CtaWork cta_work(const MvParams& p) {
     CtaWork w;
-    w.mode_gateup = (p.mode == MV_GATEUP);
+    const bool gu = (p.mode == MV_GATEUP);
     int cta = blockIdx.x, s = 0, c0 = 0, nc = gridDim.x;
-    if (!w.mode_gateup) {
-        for (s = 0; s < p.nseg - 1; s++) {
+    if (!gu) {
+        for (s = 0; s < p.nseg - 1; s++)
             if (cta < p.seg[s].cta0 + p.seg[s].ncta) break;
-        }
         c0 = p.seg[s].cta0; nc = p.seg[s].ncta;
     }
     w.seg = s;
@@ -68,26 +63,33 @@ __device__ __forceinline__ CtaWork cta_work(const MvParams& p) {
     int i = cta - c0;
     long u0 = (long)units * i / nc, u1 = (long)units * (i + 1) / nc;
     w.r0 = (int)u0 * 2; w.r1 = (int)u1 * 2;
-    w.R = p.rows_per_tile;
-    int nt = (w.r1 - w.r0 + w.R - 1) / w.R;
-    w.ntiles = w.mode_gateup ? 2 * nt : nt;
+    w.ng = (w.r1 - w.r0 + R - 1) / R;
+    w.tpg = p.n_slices * (gu ? 2 : 1);
+    w.rounds = w.ng / NCW; w.rem = w.ng % NCW;
+    w.total = w.ng * w.tpg;
     return w;
 }
 
-__device__ __forceinline__ TileInfo tile_info(const MvParams& p, const CtaWork& w, int t) {
-    TileInfo ti;
-    int tt = w.mode_gateup ? (t >> 1) : t;
-    ti.seg = w.mode_gateup ? (t & 1) : w.seg;
-    ti.row0 = w.r0 + tt * w.R;
-    ti.nrows = min(w.R, w.r1 - ti.row0);
-    const MvSeg& sg = p.seg[ti.seg];
-    uintptr_t start = (uintptr_t)sg.w + (uintptr_t)ti.row0 * sg.row_bytes;
-    uintptr_t end = start + (uintptr_t)ti.nrows * sg.row_bytes;
-    uintptr_t a0 = start & ~(uintptr_t)15, a1 = (end + 15) & ~(uintptr_t)15;
-    ti.src = (const uint8_t*)a0;
-    ti.bytes = (uint32_t)(a1 - a0);
-    ti.off = (uint32_t)(start - a0);
-    return ti;
+struct TileId { int warp, gi, seg, slice; };
+
+// q-th tile in issue order -> owner warp, row group, matrix, K-slice
+__device__ __forceinline__ TileId tile_of(const MvParams& p, const CtaWork& w, int q) {
+    TileId t;
+    int full_tiles = w.rounds * w.tpg * NCW;
+    int lt;
+    if (q < full_tiles) { t.warp = q % NCW; lt = q / NCW; }
+    else { int qq = q - full_tiles; t.warp = qq % w.rem; lt = w.rounds * w.tpg + qq / w.rem; }
+    t.gi = t.warp + NCW * (lt / w.tpg);
+    int within = lt % w.tpg;
+    t.seg = (p.mode == MV_GATEUP) ? within / p.n_slices : w.seg;
+    t.slice = within % p.n_slices;
+    return t;
+}
+// issue-order index of warp `warp`'s lt-th tile
+__device__ __forceinline__ int q_of(const CtaWork& w, int warp, int lt) {
+    int full_lt = w.rounds * w.tpg;
+    if (lt < full_lt) return lt * NCW + warp;
+    return full_lt * NCW + (lt - full_lt) * w.rem + warp;
 }
 
 // one lane finishes a row pair
@@ -95,12 +97,11 @@ __device__ __forceinline__ void epilogue_pair(const MvParams& p, int seg, int ro
     const MvSeg& sg = p.seg[seg];
     if (p.mode == MV_STORE) {
         float* y = p.y + sg.out_off;
-        y[row] = v0; y[row + 1] = v1;
+        *reinterpret_cast<float2*>(y + row) = make_float2(v0, v1);
     } else if (p.mode == MV_RESID) {
         float* y = p.y + sg.out_off;
-        const float* r = p.resid + sg.out_off;
-        float a = r[row], b = r[row + 1];
-        y[row] = a + v0; y[row + 1] = b + v1;
+        float2 r = *reinterpret_cast<const float2*>(p.resid + sg.out_off + row);
+        *reinterpret_cast<float2*>(y + row) = make_float2(r.x + v0, r.y + v1);
     } else if (p.mode == MV_QKV) {
         int hd = p.head_dim;
         int pos = *p.pos_ptr;
@@ -113,7 +114,7 @@ __device__ __forceinline__ void epilogue_pair(const MvParams& p, int seg, int ro
             v0 = a; v1 = b;
         }
         if (seg == 0) {
-            p.q_out[row] = v0; p.q_out[row + 1] = v1;
+            *reinterpret_cast<float2*>(p.q_out + row) = make_float2(v0, v1);
         } else {
             int bt = p.block_tokens;
             int page = p.block_table[pos / bt], slot = pos % bt;
@@ -125,132 +126,209 @@ __device__ __forceinline__ void epilogue_pair(const MvParams& p, int seg, int ro
     }
 }
 
+// accumulate one tile (R row-slices in a ring stage) into acc[R].
+// row_lo = low bits of the global address of row0's slice: each bulk copy started at the 16-byte
+// boundary below its row-slice, so the data sits (address & 15) bytes into its slot.
+template <int T, bool ACT2>
+__device__ __forceinline__ void tile_dots(const uint8_t* stage, int slot_bytes, uint32_t row_lo, uint32_t row_bytes,
+                                          int nrows, int slice, int lane, bool lane_active, const ActView& av,
+                                          float (&acc)[R]) {
+    if (!lane_active) return;
+    LaneAct la;
+    load_act<T, ACT2>(la, av, slice * B2_SLICE, lane);
+    if (nrows == R) {
+#pragma unroll
+        for (int r = 0; r < R; r++)
+            acc[r] += row_dot<T, ACT2>(stage + r * slot_bytes + ((row_lo + r * row_bytes) & 15u), lane, la);
+    } else {
+#pragma unroll 1
+        for (int r = 0; r < nrows; r++) {
+            float v = row_dot<T, ACT2>(stage + r * slot_bytes + ((row_lo + r * row_bytes) & 15u), lane, la);
+#pragma unroll
+            for (int k = 0; k < R; k++) if (k == r) acc[k] += v;
+        }
+    }
+}
+
 template <bool ACT2>
 __global__ void __launch_bounds__(NTHREADS, 2) matvec_kernel(const MvParams p) {
     extern __shared__ __align__(128) uint8_t smem_raw[];
     MvShared& sh = *reinterpret_cast<MvShared*>(smem_raw);
-    uint8_t* ring = smem_raw + ((sizeof(MvShared) + 127) & ~127);
+    const int Kp = p.n_slices * B2_SLICE;                 // planes padded to whole slices
+    uint8_t* act_a = smem_raw + ((sizeof(MvShared) + 127) & ~127);
+    uint8_t* act_b = act_a + Kp;
+    uint8_t* act_a2 = p.act_dual ? act_b + Kp : act_a;    // second layout (gate/up of different quant families)
+    uint8_t* act_b2 = p.act_dual ? act_a2 + Kp : act_b;
+    float* act_dx = reinterpret_cast<float*>((p.act_dual ? act_b2 : act_b) + Kp);
+    float* act_s16 = act_dx + p.K / 32;
+    uint8_t* ring = smem_raw + p.ring_off;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int S = p.n_stages;
-    const int Wk = p.warps_per_row, G = NCW / Wk;
     const CtaWork work = cta_work(p);
+    // plane layout follows the quant family this CTA reads (gate/up: seg 0's, plus a second copy if they differ)
+    const int cta_layout = (p.mode == MV_GATEUP) ? p.act_layout : act_layout_of(p.seg[work.seg].type);
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < S; s++) { mbar_init(&sh.full[s], 1); mbar_init(&sh.empty[s], G * Wk); }
+        for (int s = 0; s < S; s++) { mbar_init(&sh.full[s], 1); mbar_init(&sh.empty[s], 1); }
         fence_mbar_init();
     }
     __syncthreads();
     griddep_launch();   // let the next kernel start prefetching its own weights
 
     if (warp == NCW) {
-        // ------------------------------------------------------------ producer
-        if (lane == 0) {
-            for (int t = 0; t < work.ntiles; t++) {
-                int s = t % S; uint32_t ph = (t / S) & 1;
-                mbar_wait(&sh.empty[s], ph ^ 1);
-                TileInfo ti = tile_info(p, work, t);
-                mbar_arrive_expect_tx(&sh.full[s], ti.bytes);
-                tma_load_1d(ring + (size_t)s * p.stage_bytes, ti.src, ti.bytes, &sh.full[s]);
+        // ------------------------------------------------------------ producer warp
+        const int tsub = lane / R, rsub = lane % R;
+        for (int qb = 0; qb < work.total; qb += TPB) {
+            int q = qb + tsub;
+            bool have = q < work.total;
+            const uint8_t* src = nullptr; uint32_t bytes = 0; uint8_t* dst = nullptr; int st = 0;
+            if (have) {
+                TileId t = tile_of(p, work, q);
+                const MvSeg& sg = p.seg[t.seg];
+                int row0 = work.r0 + t.gi * R, nrows = min(R, work.r1 - row0);
+                st = q % S;
+                if (rsub < nrows) {
+                    int sb = slice_bytes(sg.type);
+                    int len = min(sb, sg.row_bytes - t.slice * sb);        // last slice may be shorter
+                    uintptr_t start = (uintptr_t)sg.w + (size_t)(row0 + rsub) * sg.row_bytes + (size_t)t.slice * sb;
+                    uintptr_t a0 = start & ~(uintptr_t)15, a1 = (start + len + 15) & ~(uintptr_t)15;
+                    src = (const uint8_t*)a0; bytes = (uint32_t)(a1 - a0);
+                    dst = ring + (size_t)st * p.stage_bytes + rsub * p.slot_bytes;
+                }
+                if (rsub == 0) mbar_wait(&sh.empty[st], ((q / S) & 1) ^ 1, p.err, 0x10001u);
             }
+            __syncwarp();
+            // total bytes of the tile = sum over its R lanes
+            uint32_t tot = bytes;
+#pragma unroll
+            for (int o = 1; o < R; o <<= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
+            if (have && rsub == 0) mbar_arrive_expect_tx(&sh.full[st], tot);
+            __syncwarp();
+            if (bytes) tma_load_1d(dst, src, bytes, &sh.full[st]);
         }
         return;
     }
 
-    // ---------------------------------------------------------------- consumers
-    const int g = warp / Wk, wk = warp % Wk;
-    const bool warp_active = g < G;
-    const int u = wk * 32 + lane;                       // this lane's 64-element chunk
-    const bool lane_active = warp_active && (u * 64 < p.K);
-
-    ActChunk act;
-    float ssq = 0.f;
+    // ---------------------------------------------------------------- consumers: quantise x
+    griddep_wait();     // activations written by the previous kernel are visible from here on
     {
         const bool has_norm = p.norm_w != nullptr;
-        griddep_wait();  // activations written by the previous kernel are visible from here on
-        if (lane_active) {
-            const float4* xp4 = reinterpret_cast<const float4*>(p.x + 64 * u);
-            const float4* np4 = reinterpret_cast<const float4*>(p.norm_w + 64 * u);
+        const int t = threadIdx.x;
+        float ssq = 0.f;
+        for (int blk = t; blk < p.K / 32; blk += NCW * 32) {
+            const float4* xp4 = reinterpret_cast<const float4*>(p.x + 32 * blk);
+            const float4* np4 = reinterpret_cast<const float4*>(p.norm_w + 32 * blk);
+            float v[32];
 #pragma unroll
-            for (int h = 0; h < 2; h++) {
-                float t[32];
-#pragma unroll
-                for (int i = 0; i < 8; i++) {
-                    float4 v = xp4[8 * h + i];
-                    ssq += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
-                    if (has_norm) { float4 w4 = __ldg(np4 + 8 * h + i); v.x *= w4.x; v.y *= w4.y; v.z *= w4.z; v.w *= w4.w; }
-                    t[4 * i] = v.x; t[4 * i + 1] = v.y; t[4 * i + 2] = v.z; t[4 * i + 3] = v.w;
-                }
-                float lo, hi;
-                float amax = quantize32(t, act.a + 8 * h, act.b + 8 * h, lo, hi);
-                act.dx[h] = amax / 127.0f;
-                act.s16[2 * h] = lo; act.s16[2 * h + 1] = hi;
+            for (int i = 0; i < 8; i++) {
+                float4 f = xp4[i];
+                ssq += f.x * f.x + f.y * f.y + f.z * f.z + f.w * f.w;
+                if (has_norm) { float4 w4 = __ldg(np4 + i); f.x *= w4.x; f.y *= w4.y; f.z *= w4.z; f.w *= w4.w; }
+                v[4 * i] = f.x; v[4 * i + 1] = f.y; v[4 * i + 2] = f.z; v[4 * i + 3] = f.w;
             }
-        } else {
+            int qa[8], qb[8]; float lo, hi;
+            float amax = quantize32(v, qa, qb, lo, hi);
+            // two 16-byte units per block, permuted inside the slice for conflict-free lane reads
+            const int u0 = 2 * blk, sbase = (u0 >> 7) * B2_SLICE;
 #pragma unroll
-            for (int i = 0; i < 16; i++) { act.a[i] = 0; act.b[i] = 0; }
-            act.dx[0] = act.dx[1] = 0.f;
-            act.s16[0] = act.s16[1] = act.s16[2] = act.s16[3] = 0.f;
+            for (int h2 = 0; h2 < 2; h2++) {
+                const int4 wa = make_int4(qa[4 * h2], qa[4 * h2 + 1], qa[4 * h2 + 2], qa[4 * h2 + 3]);
+                const int4 wb = make_int4(qb[4 * h2], qb[4 * h2 + 1], qb[4 * h2 + 2], qb[4 * h2 + 3]);
+                const int pos = sbase + 16 * act_unit_pos(cta_layout, (u0 + h2) & 127);
+                *reinterpret_cast<int4*>(act_a + pos) = wa;
+                *reinterpret_cast<int4*>(act_b + pos) = wb;
+                if (p.act_dual) {
+                    const int pos2 = sbase + 16 * act_unit_pos(1 - cta_layout, (u0 + h2) & 127);
+                    *reinterpret_cast<int4*>(act_a2 + pos2) = wa;
+                    *reinterpret_cast<int4*>(act_b2 + pos2) = wb;
+                }
+            }
+            act_dx[blk] = amax / 127.0f;
+            act_s16[2 * blk] = lo; act_s16[2 * blk + 1] = hi;
         }
         if (has_norm) {
             // rsqrt(mean(x^2) + eps) scales dx and the group sums; the int8 planes do not change
             ssq = warp_sum(ssq);
-            if (lane == 0) sh.red[warp] = (g == 0) ? ssq : 0.f;
+            if (lane == 0) sh.red[warp] = ssq;
             named_bar_sync(1, NCW * 32);
             float tot = 0.f;
+#pragma unroll
             for (int i = 0; i < NCW; i++) tot += sh.red[i];
             float rs = rsqrtf(tot / (float)p.K + p.eps);
-            act.dx[0] *= rs; act.dx[1] *= rs;
-#pragma unroll
-            for (int i = 0; i < 4; i++) act.s16[i] *= rs;
+            for (int blk = t; blk < p.K / 32; blk += NCW * 32) {
+                act_dx[blk] *= rs; act_s16[2 * blk] *= rs; act_s16[2 * blk + 1] *= rs;
+            }
         }
+        named_bar_sync(1, NCW * 32);
     }
-    if (!warp_active) return;
+    ActView av0, av1;
+    av0.a = act_a; av0.b = act_b; av0.dx = act_dx; av0.s16 = act_s16;
+    av1.a = act_a2; av1.b = act_b2; av1.dx = act_dx; av1.s16 = act_s16;
 
-    const int bar_id = 2 + g, bar_n = Wk * 32;
-    for (int t = 0; t < work.ntiles; t++) {
-        int s = t % S; uint32_t ph = (t / S) & 1;
-        TileInfo ti = tile_info(p, work, t);
-        const MvSeg& sg = p.seg[ti.seg];
-        mbar_wait(&sh.full[s], ph);
-        const uint8_t* base = ring + (size_t)s * p.stage_bytes + ti.off;
-        int npairs = ti.nrows >> 1;
-        int pi = 0;
-        for (int pp = g; pp < npairs; pp += G, pi++) {
-            const uint8_t* r0p = base + (size_t)(2 * pp) * sg.row_bytes;
-            float a0 = 0.f, a1 = 0.f;
-            if (lane_active) {
-                a0 = chunk_dot<ACT2>(sg.type, r0p, u, act);
-                a1 = chunk_dot<ACT2>(sg.type, r0p + sg.row_bytes, u, act);
-            }
-            // 2-row transposed butterfly: lanes 0-15 end with row 0's sum, lanes 16-31 with row 1's
-            float send = (lane & 16) ? a0 : a1, keep = (lane & 16) ? a1 : a0;
-            keep += __shfl_xor_sync(0xffffffffu, send, 16);
+    // ---------------------------------------------------------------- consumers: stream tiles
+    const int my_groups = work.rounds + (warp < work.rem ? 1 : 0);
+    int lt = 0;
+    for (int g = 0; g < my_groups; g++) {
+        const int gi = warp + NCW * g;
+        const int row0 = work.r0 + gi * R, nrows = min(R, work.r1 - row0);
+        float gate0 = 0.f, gate1 = 0.f;
+        const int nmat = (p.mode == MV_GATEUP) ? 2 : 1;
+        for (int m = 0; m < nmat; m++) {
+            const int seg = (p.mode == MV_GATEUP) ? m : work.seg;
+            const MvSeg& sg = p.seg[seg];
+            const int type = sg.type;
+            const uint32_t row_bytes = (uint32_t)sg.row_bytes;
+            const uint32_t row_lo0 = (uint32_t)(uintptr_t)sg.w + (uint32_t)row0 * row_bytes;   // low address bits suffice
+            const uint32_t sbytes = (uint32_t)slice_bytes(type);
+            const ActView& av = (act_layout_of(type) == cta_layout) ? av0 : av1;
+            float acc[R];
 #pragma unroll
-            for (int o = 8; o > 0; o >>= 1) keep += __shfl_xor_sync(0xffffffffu, keep, o);
-            if ((lane & 15) == 0) sh.part[t & 1][warp][pi][lane >> 4] = keep;
-        }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&sh.empty[s]);       // stage can be refilled
-        if (Wk > 1) named_bar_sync(bar_id, bar_n); else __syncwarp();
-        if (wk == 0 && lane < pi) {
-            // lane i finishes pair i of this group
-            int pp = g + lane * G;
-            float v0 = 0.f, v1 = 0.f;
-            for (int w2 = 0; w2 < Wk; w2++) {
-                v0 += sh.part[t & 1][g * Wk + w2][lane][0];
-                v1 += sh.part[t & 1][g * Wk + w2][lane][1];
-            }
-            int row = ti.row0 + 2 * pp;
-            if (p.mode == MV_GATEUP) {
-                if (ti.seg == 0) { sh.gate[g][lane][0] = v0; sh.gate[g][lane][1] = v1; }
-                else {
-                    float g0 = sh.gate[g][lane][0], g1 = sh.gate[g][lane][1];
-                    float* y = p.y;
-                    y[row] = g0 / (1.0f + __expf(-g0)) * v0;
-                    y[row + 1] = g1 / (1.0f + __expf(-g1)) * v1;
+            for (int r = 0; r < R; r++) acc[r] = 0.f;
+            for (int sl = 0; sl < p.n_slices; sl++, lt++) {
+                const int q = q_of(work, warp, lt);
+                const int st = q % S;
+                mbar_wait(&sh.full[st], (q / S) & 1, p.err, 0x10002u);
+                const uint8_t* stage = ring + (size_t)st * p.stage_bytes;
+                const bool lane_active = sl * B2_SLICE + lane * 64 < p.K;
+                const uint32_t row_lo = row_lo0 + (uint32_t)sl * sbytes;
+                const int sb = p.slot_bytes;
+                switch (type) {
+                    case T_Q4_K: tile_dots<T_Q4_K, ACT2>(stage, sb, row_lo, row_bytes, nrows, sl, lane, lane_active, av, acc); break;
+                    case T_Q6_K: tile_dots<T_Q6_K, ACT2>(stage, sb, row_lo, row_bytes, nrows, sl, lane, lane_active, av, acc); break;
+                    case T_Q8_0: tile_dots<T_Q8_0, ACT2>(stage, sb, row_lo, row_bytes, nrows, sl, lane, lane_active, av, acc); break;
+                    case T_Q4_0: tile_dots<T_Q4_0, ACT2>(stage, sb, row_lo, row_bytes, nrows, sl, lane, lane_active, av, acc); break;
+                    case T_Q5_K: tile_dots<T_Q5_K, ACT2>(stage, sb, row_lo, row_bytes, nrows, sl, lane, lane_active, av, acc); break;
                 }
-            } else {
-                epilogue_pair(p, ti.seg, row, v0, v1);
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&sh.empty[st]);      // stage can be refilled
+            }
+            // transposed butterfly over the 4 rows: lane 0 / 8 / 16 / 24 end with row 0 / 1 / 2 / 3
+            const bool hi16 = lane & 16, hi8 = lane & 8;
+            float s0 = hi16 ? acc[0] : acc[2], s1 = hi16 ? acc[1] : acc[3];
+            float k0 = hi16 ? acc[2] : acc[0], k1 = hi16 ? acc[3] : acc[1];
+            k0 += __shfl_xor_sync(0xffffffffu, s0, 16);
+            k1 += __shfl_xor_sync(0xffffffffu, s1, 16);
+            float snd = hi8 ? k0 : k1, kp = hi8 ? k1 : k0;
+            kp += __shfl_xor_sync(0xffffffffu, snd, 8);
+            kp += __shfl_xor_sync(0xffffffffu, kp, 4);
+            kp += __shfl_xor_sync(0xffffffffu, kp, 2);
+            kp += __shfl_xor_sync(0xffffffffu, kp, 1);
+            float odd = __shfl_down_sync(0xffffffffu, kp, 8);   // lane 0 <- row 1, lane 16 <- row 3
+            if ((lane & 15) == 0) {
+                int pr = lane >> 4;                             // pair 0 or 1 of the group
+                if (2 * pr < nrows) {
+                    int row = row0 + 2 * pr;
+                    if (p.mode == MV_GATEUP) {
+                        if (m == 0) { gate0 = kp; gate1 = odd; }
+                        else {
+                            float h0 = gate0 / (1.0f + __expf(-gate0)) * kp;
+                            float h1 = gate1 / (1.0f + __expf(-gate1)) * odd;
+                            *reinterpret_cast<float2*>(p.y + row) = make_float2(h0, h1);
+                        }
+                    } else {
+                        epilogue_pair(p, seg, row, kp, odd);
+                    }
+                }
             }
         }
     }
@@ -258,42 +336,44 @@ __global__ void __launch_bounds__(NTHREADS, 2) matvec_kernel(const MvParams p) {
 
 // ---------------------------------------------------------------- host side
 cudaError_t mv_init() {   // per device: allow > 48 KB dynamic shared memory
-    cudaError_t e = cudaFuncSetAttribute(matvec_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(matvec_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, MV_SMEM_MAX);
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(matvec_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024);
+    return cudaFuncSetAttribute(matvec_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, MV_SMEM_MAX);
 }
 
 int mv_plan(MvParams& p, int n_ctas) {
-    // decide tile shape, ring depth and the CTA split between segments
     if (p.K % 256 || p.K <= 0) return -1;
-    int chunks = p.K / 64;
-    int Wk = (chunks + 31) / 32;
-    if (Wk > NCW) return -2;          // K > 16384 needs 2 chunks per lane (not built yet)
-    p.warps_per_row = Wk;
-    int G = NCW / Wk;
-    int max_rb = 0;
+    if (p.K > 32768) return -2;
+    int max_sb = 0;
     for (int s = 0; s < p.nseg; s++) {
         int be = block_elems(p.seg[s].type), bb = block_bytes(p.seg[s].type);
         if (!bb || be == 1) return -3;
         p.seg[s].row_bytes = p.K / be * bb;
         if (p.seg[s].n_rows % 2) return -4;
-        max_rb = p.seg[s].row_bytes > max_rb ? p.seg[s].row_bytes : max_rb;
+        int sb = slice_bytes(p.seg[s].type);
+        if (sb > p.seg[s].row_bytes) sb = p.seg[s].row_bytes;
+        max_sb = sb > max_sb ? sb : max_sb;
     }
-    const int ring_budget = 104 * 1024;
-    int R = 2 * G;                                           // one pair per group
-    while (R + 2 * G <= 2 * G * MV_MAX_PAIRS && (long)(R + 2 * G) * max_rb + 32 <= 28 * 1024) R += 2 * G;
-    while (R > 2 && (long)R * max_rb + 32 > ring_budget / 2) R -= 2;
-    p.rows_per_tile = R;
-    p.stage_bytes = (int)((((long)R * max_rb + 32) + 127) / 128 * 128);
-    int S = ring_budget / p.stage_bytes;
+    p.n_slices = (p.K + B2_SLICE - 1) / B2_SLICE;
+    p.slot_bytes = (max_sb + 16 + 15) / 16 * 16;           // + slack for the 16-byte alignment of each copy
+    p.stage_bytes = (R * p.slot_bytes + 127) / 128 * 128;
+    p.act_layout = act_layout_of(p.seg[0].type);
+    p.act_dual = 0;
+    for (int s = 1; s < p.nseg; s++)
+        if (p.mode == MV_GATEUP && act_layout_of(p.seg[s].type) != p.act_layout) p.act_dual = 1;
+    int act_bytes = (p.act_dual ? 4 : 2) * p.n_slices * B2_SLICE + (p.K / 32) * 4 + (p.K / 16) * 4;
+    p.ring_off = (((int)sizeof(MvShared) + 127) / 128 * 128 + act_bytes + 127) / 128 * 128;
+    int S = (MV_SMEM_MAX - p.ring_off) / p.stage_bytes;
     if (S > MV_MAX_STAGES) S = MV_MAX_STAGES;
-    if (S < 2) return -5;
+    if (const char* cap = getenv("B2_MV_STAGES")) { int c = atoi(cap); if (c >= TPB && c < S) S = c; }   // tuning knob
+    if (S < TPB) return -5;                                // the producer fills TPB stages per round
     p.n_stages = S;
     // CTA split proportional to bytes (gate/up: every CTA handles both matrices)
     if (p.mode == MV_GATEUP) {
         if (p.nseg != 2 || p.seg[0].n_rows != p.seg[1].n_rows) return -6;
         p.seg[0].cta0 = p.seg[1].cta0 = 0; p.seg[0].ncta = p.seg[1].ncta = n_ctas;
     } else {
+        if (n_ctas < p.nseg) return -7;
         double tot = 0;
         for (int s = 0; s < p.nseg; s++) tot += (double)p.seg[s].n_rows * p.seg[s].row_bytes;
         int left = n_ctas, c0 = 0;
@@ -313,15 +393,12 @@ int mv_plan(MvParams& p, int n_ctas) {
     return 0;
 }
 
-size_t mv_smem_bytes(const MvParams& p) {
-    return ((sizeof(MvShared) + 127) & ~127) + (size_t)p.n_stages * p.stage_bytes;
-}
+size_t mv_smem_bytes(const MvParams& p) { return (size_t)p.ring_off + (size_t)p.n_stages * p.stage_bytes; }
 
 cudaError_t mv_launch(const MvParams& p, int n_ctas, cudaStream_t stream, bool act2, bool pdl) {
-    size_t smem = mv_smem_bytes(p);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(n_ctas); cfg.blockDim = dim3(NTHREADS);
-    cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+    cfg.dynamicSmemBytes = mv_smem_bytes(p); cfg.stream = stream;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;

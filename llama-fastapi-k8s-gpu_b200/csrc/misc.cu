@@ -7,6 +7,15 @@
 
 namespace b2 {
 
+unsigned int* kernel_error_word() {
+    static unsigned int* w = nullptr;
+    if (!w) {
+        if (cudaHostAlloc(&w, sizeof(unsigned int), cudaHostAllocMapped | cudaHostAllocPortable) != cudaSuccess) return nullptr;
+        *w = 0;
+    }
+    return w;
+}
+
 __global__ void dequantize_kernel(int type, const uint8_t* __restrict__ raw, long n, float* __restrict__ out) {
     const int be = block_elems(type), bb = block_bytes(type);
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x)

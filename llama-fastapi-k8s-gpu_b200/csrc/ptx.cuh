@@ -35,12 +35,17 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
         : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
     return ok != 0;
 }
-// Spin with a watchdog: a protocol bug traps (-> CUDA error at the next sync) instead of
-// hanging the GPU. try_wait already suspends the thread for a hardware time slice.
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+// Spin with a watchdog: if a barrier never completes (a protocol bug) the kernel records `code`
+// in the host-visible error word and carries on with garbage instead of hanging the GPU; every
+// engine call checks that word after it synchronises and fails loudly.
+// try_wait already suspends the thread for a hardware time slice.
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, unsigned int* err, unsigned int code) {
     uint32_t spins = 0;
     while (!mbar_try_wait(bar, parity)) {
-        if (++spins > (1u << 24)) __trap();
+        if (++spins > (1u << 22)) {
+            if (err) *reinterpret_cast<volatile unsigned int*>(err) = code;   // plain store: the word lives in host memory
+            return;
+        }
     }
 }
 // 1-D bulk async copy global -> shared, completion signalled on an mbarrier (complete_tx).

@@ -53,6 +53,11 @@ B2_HD int block_bytes(int t) {
 #if defined(__CUDA_ARCH__) && !defined(B2_HOST_EMU)
 B2_D float h2f(uint32_t h) { return __half2float(__ushort_as_half((unsigned short)h)); }
 B2_D int dp4a(int a, int b, int c) { return __dp4a(a, b, c); }
+B2_D int dp4a_us(uint32_t a, int b, int c) {
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
 B2_D uint32_t fshr(uint32_t lo, uint32_t hi, uint32_t s) { return __funnelshift_r(lo, hi, s); }
 B2_D float fmul(float a, float b) { return __fmul_rn(a, b); }
 B2_D float fsub(float a, float b) { return __fsub_rn(a, b); }
@@ -75,6 +80,10 @@ inline float h2f(uint32_t h) {
 }
 inline int dp4a(int a, int b, int c) {
     for (int i = 0; i < 4; i++) c += (int)(int8_t)(a >> (8 * i)) * (int)(int8_t)(b >> (8 * i));
+    return c;
+}
+inline int dp4a_us(uint32_t a, int b, int c) {
+    for (int i = 0; i < 4; i++) c += (int)(uint8_t)(a >> (8 * i)) * (int)(int8_t)(b >> (8 * i));
     return c;
 }
 inline uint32_t fshr(uint32_t lo, uint32_t hi, uint32_t s) {
@@ -155,16 +164,27 @@ B2_D float dequant_elem(int type, const uint8_t* blk, int e) {
     return 0.f;
 }
 
-// ---------------------------------------------------------------- activation chunk
-// One lane's 64 activations, quantised to two int8 planes per 32-element block:
-//   x[i] ~= dx[i/32] * (a[i] + b[i] / ACT_RES)        |a| <= 127, |b| <= 126
-// s16[g] = exact float sum of x over 16-element group g (for the "-min", "-8", "-32" terms).
+// ---------------------------------------------------------------- quantised activations
+// The mat-vec input vector lives in shared memory as two int8 planes per 32-element block,
+//   x[i] ~= dx[i/32] * (a[i] + b[i] / ACT_RES)        |a| <= 127, |b| <= 126   (~16 bits)
+// plus the exact float sum of x over every 16-element group (for the "-min", "-8", "-32" terms).
 #define B2_ACT_RES 252.0f
-struct ActChunk {
+#define B2_SLICE 2048            // elements of K one warp step covers (32 lanes x 64)
+struct ActView {
+    const uint8_t* a;            // [K] int8
+    const uint8_t* b;            // [K] int8
+    const float* dx;             // [K/32]
+    const float* s16;            // [K/16]
+};
+// What one lane keeps in registers for one K-slice: 64 activations (16+16 words) and their scales.
+// Q4_0/Q8_0/Q4_K/Q5_K: the contiguous chunk [64*lane, 64*lane+64): f[0..1] = dx of its two
+// 32-blocks, f[2..3] = float sums of the two 32-blocks.
+// Q6_K: lane (j, hf, qt) = (lane>>2, (lane>>1)&1, lane&1) owns the four 16-element runs
+// 256j + 128hf + 32kq + 16qt (kq = 0..3): a[4kq..4kq+3]; f[kq] = dx, f[4+kq] = sum of the run.
+struct LaneAct {
     int a[16];
     int b[16];
-    float dx[2];
-    float s16[4];
+    float f[8];
 };
 
 // Quantise 32 floats t[0..31] (already multiplied by any norm weight) into words a[8], b[8].
@@ -202,18 +222,60 @@ B2_D float quantize32(const float* t, int* a, int* b, float& sum_lo, float& sum_
     return amax;
 }
 
-// ---------------------------------------------------------------- chunk dot products
-// `row` = first byte of the quantised row (in shared memory on the GPU), u = 64-weight chunk
-// index within the row. ACT2 = use the second (residual) activation plane.
-
 template <bool ACT2>
 B2_D float fin(int A, int B, float dx) {
     return ACT2 ? dx * ((float)A + (float)B * (1.0f / B2_ACT_RES)) : dx * (float)A;
 }
 
+// ---------------------------------------------------------------- activation layout
+// The int8 planes are stored in 16-byte units, permuted inside each 2048-element slice so that the
+// 32 lanes of a warp read 32 consecutive units (conflict-free LDS.128):
+//   layout 0 (Q4_0/Q8_0/Q4_K/Q5_K, lane = 64-element chunk): unit u -> (u & 3) * 32 + (u >> 2)
+//   layout 1 (Q6_K, lane = (j, hf, qt)):  u = 16j + 8hf + 2kq + qt -> kq * 32 + (4j + 2hf + qt)
+B2_HD int act_layout_of(int type) { return type == T_Q6_K ? 1 : 0; }
+B2_HD int act_unit_pos(int layout, int u /* 16-byte unit within the slice, 0..127 */) {
+    if (layout == 0) return (u & 3) * 32 + (u >> 2);
+    int j = u >> 4, hf = (u >> 3) & 1, kq = (u >> 1) & 3, qt = u & 1;
+    return kq * 32 + 4 * j + 2 * hf + qt;
+}
+
+// ---------------------------------------------------------------- per-lane activation load
+template <int T, bool ACT2>
+B2_D void load_act(LaneAct& r, const ActView& v, int e0 /* first element of the slice */, int lane) {
+    const uint8_t* pa = v.a + e0 + 16 * lane;
+    const uint8_t* pb = v.b + e0 + 16 * lane;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        U4 wa = ld128(pa + 512 * i);
+        r.a[4 * i] = (int)wa.x; r.a[4 * i + 1] = (int)wa.y; r.a[4 * i + 2] = (int)wa.z; r.a[4 * i + 3] = (int)wa.w;
+        if (ACT2) {
+            U4 wb = ld128(pb + 512 * i);
+            r.b[4 * i] = (int)wb.x; r.b[4 * i + 1] = (int)wb.y; r.b[4 * i + 2] = (int)wb.z; r.b[4 * i + 3] = (int)wb.w;
+        }
+    }
+    if (T == T_Q6_K) {
+        int eb = e0 + 256 * (lane >> 2) + 128 * ((lane >> 1) & 1) + 16 * (lane & 1);
+#pragma unroll
+        for (int kq = 0; kq < 4; kq++) {
+            int e = eb + 32 * kq;
+            r.f[kq] = v.dx[e >> 5];
+            r.f[4 + kq] = v.s16[e >> 4];
+        }
+    } else {
+        int e = e0 + 64 * lane;
+        r.f[0] = v.dx[e >> 5]; r.f[1] = v.dx[(e >> 5) + 1];
+        r.f[2] = v.s16[e >> 4] + v.s16[(e >> 4) + 1];
+        r.f[3] = v.s16[(e >> 4) + 2] + v.s16[(e >> 4) + 3];
+    }
+}
+
+// ---------------------------------------------------------------- per-lane row dot products
+// `row` = first byte of this row's K-slice (shared memory on the GPU). Returns the lane's share of
+// the dot product of that slice with the activations in `act`.
+
 template <bool ACT2>
-B2_D float chunk_dot_q4k(const uint8_t* row, int u, const ActChunk& act) {
-    int j = u >> 2, c = u & 3;
+B2_D float row_dot_q4k(const uint8_t* row, int lane, const LaneAct& act) {
+    int j = lane >> 2, c = lane & 3;
     const uint8_t* blk = row + j * 144;
     U4 h = ld128(blk);
     U4 q0 = ld128(blk + 16 + 32 * c), q1 = ld128(blk + 32 + 32 * c);
@@ -227,21 +289,21 @@ B2_D float chunk_dot_q4k(const uint8_t* row, int u, const ActChunk& act) {
     int Alo = 0, Blo = 0, Ahi = 0, Bhi = 0;
 #pragma unroll
     for (int k = 0; k < 8; k++) {
-        int lo = (int)(qw[k] & 0x0F0F0F0Fu), hi = (int)((qw[k] >> 4) & 0x0F0F0F0Fu);
+        int lo = (int)(qw[k] & 0x0F0F0F0Fu);
+        uint32_t hi16 = qw[k] & 0xF0F0F0F0u;          // 16 * high nibble, as unsigned bytes
         Alo = dp4a(lo, act.a[k], Alo);
-        Ahi = dp4a(hi, act.a[8 + k], Ahi);
-        if (ACT2) { Blo = dp4a(lo, act.b[k], Blo); Bhi = dp4a(hi, act.b[8 + k], Bhi); }
+        Ahi = dp4a_us(hi16, act.a[8 + k], Ahi);
+        if (ACT2) { Blo = dp4a(lo, act.b[k], Blo); Bhi = dp4a_us(hi16, act.b[8 + k], Bhi); }
     }
-    float r = d * (float)(scp & 0xffu) * fin<ACT2>(Alo, Blo, act.dx[0])
-            - dmin * (float)(mp & 0xffu) * (act.s16[0] + act.s16[1]);
-    r += d * (float)(scp >> 8) * fin<ACT2>(Ahi, Bhi, act.dx[1])
-       - dmin * (float)(mp >> 8) * (act.s16[2] + act.s16[3]);
+    Ahi >>= 4; Bhi >>= 4;                              // exact: both are multiples of 16
+    float r = d * (float)(scp & 0xffu) * fin<ACT2>(Alo, Blo, act.f[0]) - dmin * (float)(mp & 0xffu) * act.f[2];
+    r += d * (float)(scp >> 8) * fin<ACT2>(Ahi, Bhi, act.f[1]) - dmin * (float)(mp >> 8) * act.f[3];
     return r;
 }
 
 template <bool ACT2>
-B2_D float chunk_dot_q5k(const uint8_t* row, int u, const ActChunk& act) {
-    int j = u >> 2, c = u & 3;
+B2_D float row_dot_q5k(const uint8_t* row, int lane, const LaneAct& act) {
+    int j = lane >> 2, c = lane & 3;
     const uint8_t* blk = row + j * 176;
     U4 h = ld128(blk);
     U4 h0 = ld128(blk + 16), h1 = ld128(blk + 32);
@@ -264,68 +326,72 @@ B2_D float chunk_dot_q5k(const uint8_t* row, int u, const ActChunk& act) {
         Ahi = dp4a(hi, act.a[8 + k], Ahi);
         if (ACT2) { Blo = dp4a(lo, act.b[k], Blo); Bhi = dp4a(hi, act.b[8 + k], Bhi); }
     }
-    float r = d * (float)(scp & 0xffu) * fin<ACT2>(Alo, Blo, act.dx[0])
-            - dmin * (float)(mp & 0xffu) * (act.s16[0] + act.s16[1]);
-    r += d * (float)(scp >> 8) * fin<ACT2>(Ahi, Bhi, act.dx[1])
-       - dmin * (float)(mp >> 8) * (act.s16[2] + act.s16[3]);
+    float r = d * (float)(scp & 0xffu) * fin<ACT2>(Alo, Blo, act.f[0]) - dmin * (float)(mp & 0xffu) * act.f[2];
+    r += d * (float)(scp >> 8) * fin<ACT2>(Ahi, Bhi, act.f[1]) - dmin * (float)(mp >> 8) * act.f[3];
     return r;
 }
 
 template <bool ACT2>
-B2_D float chunk_dot_q6k(const uint8_t* row, int u, const ActChunk& act) {
-    int j = u >> 2, hf = (u >> 1) & 1, nib = u & 1;
-    const uint8_t* blk = row + j * 210;  // 2-byte aligned only
-    uint32_t ql[16], qh[8], scw[1];
-    ld_words_u2<16>(blk + 64 * hf, ql);
-    ld_words_u2<8>(blk + 128 + 32 * hf, qh);
-    ld_words_u2<1>(blk + 192 + 8 * hf + 4 * nib, scw);
+B2_D float row_dot_q6k(const uint8_t* row, int lane, const LaneAct& act) {
+    int j = lane >> 2, hf = (lane >> 1) & 1, qt = lane & 1;
+    const uint8_t* blk = row + j * 210;                // 2-byte aligned only
+    uint32_t wlA[4], wlB[4], wh[4], scw[2];
+    ld_words_u2<4>(blk + 64 * hf + 16 * qt, wlA);       // ql[l .. l+15],      l = 16 qt
+    ld_words_u2<4>(blk + 64 * hf + 32 + 16 * qt, wlB);  // ql[32+l .. 32+l+15]
+    ld_words_u2<4>(blk + 128 + 32 * hf + 16 * qt, wh);  // qh[l .. l+15]
+    ld_words_u2<2>(blk + 192 + 8 * hf, scw);            // the 8 int8 scales of this half
     float d = h2f(ld16(blk + 208));
+    int A[4] = {0, 0, 0, 0}, B[4] = {0, 0, 0, 0};
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        int q0 = (int)((wlA[i] & 0x0F0F0F0Fu) + 16u * (wh[i] & 0x03030303u));
+        int q1 = (int)((wlB[i] & 0x0F0F0F0Fu) + 16u * ((wh[i] >> 2) & 0x03030303u));
+        int q2 = (int)(((wlA[i] >> 4) & 0x0F0F0F0Fu) + 16u * ((wh[i] >> 4) & 0x03030303u));
+        int q3 = (int)(((wlB[i] >> 4) & 0x0F0F0F0Fu) + 16u * ((wh[i] >> 6) & 0x03030303u));
+        A[0] = dp4a(q0, act.a[i], A[0]); A[1] = dp4a(q1, act.a[4 + i], A[1]);
+        A[2] = dp4a(q2, act.a[8 + i], A[2]); A[3] = dp4a(q3, act.a[12 + i], A[3]);
+        if (ACT2) {
+            B[0] = dp4a(q0, act.b[i], B[0]); B[1] = dp4a(q1, act.b[4 + i], B[1]);
+            B[2] = dp4a(q2, act.b[8 + i], B[2]); B[3] = dp4a(q3, act.b[12 + i], B[3]);
+        }
+    }
     float r = 0.f;
 #pragma unroll
-    for (int g = 0; g < 4; g++) {       // 16-element groups
-        int A = 0, B = 0;
-#pragma unroll
-        for (int kk = 0; kk < 4; kk++) {
-            int k = 4 * g + kk;
-            uint32_t l4 = (ql[k] >> (4 * nib)) & 0x0F0F0F0Fu;
-            uint32_t h2 = (qh[k & 7] >> (4 * nib + 2 * (k >> 3))) & 0x03030303u;
-            int q = (int)(l4 | (h2 << 4));
-            A = dp4a(q, act.a[k], A);
-            if (ACT2) B = dp4a(q, act.b[k], B);
-        }
-        float sc = (float)(int8_t)(scw[0] >> (8 * g));
-        r += (d * sc) * (fin<ACT2>(A, B, act.dx[g >> 1]) - 32.0f * act.s16[g]);
+    for (int kq = 0; kq < 4; kq++) {
+        int si = 2 * kq + qt;                           // scale index within the half
+        float sc = (float)(int8_t)((si < 4 ? scw[0] : scw[1]) >> (8 * (si & 3)));
+        r += (d * sc) * (fin<ACT2>(A[kq], B[kq], act.f[kq]) - 32.0f * act.f[4 + kq]);
     }
     return r;
 }
 
 template <bool ACT2>
-B2_D float chunk_dot_q4_0(const uint8_t* row, int u, const ActChunk& act) {
-    const uint8_t* p = row + 36 * u;   // two 18-byte blocks; 4-byte aligned
+B2_D float row_dot_q4_0(const uint8_t* row, int lane, const LaneAct& act) {
+    const uint8_t* p = row + 36 * lane;   // two 18-byte blocks; 4-byte aligned
     uint32_t W[9];
 #pragma unroll
     for (int i = 0; i < 9; i++) W[i] = ld32(p + 4 * i);
     float d0 = h2f(W[0] & 0xffffu), d1 = h2f(W[4] >> 16);
-    int A0 = 0, B0 = 0, A1 = 0, B1 = 0;
+    int A0 = 0, B0 = 0, A1 = 0, B1 = 0, A0h = 0, B0h = 0, A1h = 0, B1h = 0;
 #pragma unroll
     for (int k = 0; k < 4; k++) {
         uint32_t q0 = fshr(W[k], W[k + 1], 16), q1 = W[5 + k];
-        int lo0 = (int)(q0 & 0x0F0F0F0Fu), hi0 = (int)((q0 >> 4) & 0x0F0F0F0Fu);
-        int lo1 = (int)(q1 & 0x0F0F0F0Fu), hi1 = (int)((q1 >> 4) & 0x0F0F0F0Fu);
-        A0 = dp4a(lo0, act.a[k], A0); A0 = dp4a(hi0, act.a[4 + k], A0);
-        A1 = dp4a(lo1, act.a[8 + k], A1); A1 = dp4a(hi1, act.a[12 + k], A1);
+        int lo0 = (int)(q0 & 0x0F0F0F0Fu), lo1 = (int)(q1 & 0x0F0F0F0Fu);
+        uint32_t hi0 = q0 & 0xF0F0F0F0u, hi1 = q1 & 0xF0F0F0F0u;
+        A0 = dp4a(lo0, act.a[k], A0); A0h = dp4a_us(hi0, act.a[4 + k], A0h);
+        A1 = dp4a(lo1, act.a[8 + k], A1); A1h = dp4a_us(hi1, act.a[12 + k], A1h);
         if (ACT2) {
-            B0 = dp4a(lo0, act.b[k], B0); B0 = dp4a(hi0, act.b[4 + k], B0);
-            B1 = dp4a(lo1, act.b[8 + k], B1); B1 = dp4a(hi1, act.b[12 + k], B1);
+            B0 = dp4a(lo0, act.b[k], B0); B0h = dp4a_us(hi0, act.b[4 + k], B0h);
+            B1 = dp4a(lo1, act.b[8 + k], B1); B1h = dp4a_us(hi1, act.b[12 + k], B1h);
         }
     }
-    return d0 * (fin<ACT2>(A0, B0, act.dx[0]) - 8.0f * (act.s16[0] + act.s16[1]))
-         + d1 * (fin<ACT2>(A1, B1, act.dx[1]) - 8.0f * (act.s16[2] + act.s16[3]));
+    A0 += A0h >> 4; B0 += B0h >> 4; A1 += A1h >> 4; B1 += B1h >> 4;
+    return d0 * (fin<ACT2>(A0, B0, act.f[0]) - 8.0f * act.f[2]) + d1 * (fin<ACT2>(A1, B1, act.f[1]) - 8.0f * act.f[3]);
 }
 
 template <bool ACT2>
-B2_D float chunk_dot_q8_0(const uint8_t* row, int u, const ActChunk& act) {
-    const uint8_t* p = row + 68 * u;   // two 34-byte blocks; 4-byte aligned
+B2_D float row_dot_q8_0(const uint8_t* row, int lane, const LaneAct& act) {
+    const uint8_t* p = row + 68 * lane;   // two 34-byte blocks; 4-byte aligned
     uint32_t W[17];
 #pragma unroll
     for (int i = 0; i < 17; i++) W[i] = ld32(p + 4 * i);
@@ -338,19 +404,20 @@ B2_D float chunk_dot_q8_0(const uint8_t* row, int u, const ActChunk& act) {
         A1 = dp4a(q1, act.a[8 + k], A1);
         if (ACT2) { B0 = dp4a(q0, act.b[k], B0); B1 = dp4a(q1, act.b[8 + k], B1); }
     }
-    return d0 * fin<ACT2>(A0, B0, act.dx[0]) + d1 * fin<ACT2>(A1, B1, act.dx[1]);
+    return d0 * fin<ACT2>(A0, B0, act.f[0]) + d1 * fin<ACT2>(A1, B1, act.f[1]);
 }
 
-template <bool ACT2>
-B2_D float chunk_dot(int type, const uint8_t* row, int u, const ActChunk& act) {
-    switch (type) {
-        case T_Q4_K: return chunk_dot_q4k<ACT2>(row, u, act);
-        case T_Q6_K: return chunk_dot_q6k<ACT2>(row, u, act);
-        case T_Q5_K: return chunk_dot_q5k<ACT2>(row, u, act);
-        case T_Q4_0: return chunk_dot_q4_0<ACT2>(row, u, act);
-        case T_Q8_0: return chunk_dot_q8_0<ACT2>(row, u, act);
-    }
+template <int T, bool ACT2>
+B2_D float row_dot(const uint8_t* row, int lane, const LaneAct& act) {
+    if (T == T_Q4_K) return row_dot_q4k<ACT2>(row, lane, act);
+    if (T == T_Q6_K) return row_dot_q6k<ACT2>(row, lane, act);
+    if (T == T_Q5_K) return row_dot_q5k<ACT2>(row, lane, act);
+    if (T == T_Q4_0) return row_dot_q4_0<ACT2>(row, lane, act);
+    if (T == T_Q8_0) return row_dot_q8_0<ACT2>(row, lane, act);
     return 0.f;
 }
+
+// bytes of one full K-slice (2048 elements) of a row
+B2_HD int slice_bytes(int t) { return B2_SLICE / block_elems(t) * block_bytes(t); }
 
 }  // namespace b2

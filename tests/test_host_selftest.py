@@ -35,7 +35,7 @@ def test_host_dequant_bit_exact(host_lib, tname):
 
 
 @pytest.mark.parametrize("tname", QTYPES)
-@pytest.mark.parametrize("K", [256, 2048])
+@pytest.mark.parametrize("K", [256, 2048, 5632])
 def test_host_chunk_dot_vs_oracle(host_lib, tname, K):
     from llama_cpp.synth import random_blocks
     from oracle import ggml_blocks as gb
