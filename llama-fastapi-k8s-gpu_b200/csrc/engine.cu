@@ -166,10 +166,9 @@ extern "C" int b2_engine_create(const b2_config* c, b2_engine** out) {
         CK(cudaMalloc(&e->rope_freq, f.size() * 4));
         CK(cudaMemcpy(e->rope_freq, f.data(), f.size() * 4, cudaMemcpyHostToDevice));
     }
-    int ns = sms / c->n_head_kv;
-    int max_ns = (c->n_ctx + 15) / 16;
-    if (ns > max_ns) ns = max_ns;
-    if (ns < 1) ns = 1;
+    // 8 splits per KV head = one thread-block cluster merging through distributed shared memory
+    int ns = 8;
+    while (ns > 1 && ns * 16 > c->n_ctx) ns >>= 1;
     if (const char* s = getenv("B2_ATTN_SPLITS")) if (atoi(s) > 0) ns = atoi(s);
     e->n_splits = ns;
     CK(cudaMalloc(&e->attn_scratch, attn_scratch_floats(c->n_head, c->n_head_kv, c->head_dim, ns) * 4));
@@ -384,6 +383,7 @@ static int forward_launches(b2_engine* e, Slot& s, bool with_head, bool with_sam
         a.out = s.att; a.scratch = e->attn_scratch; a.counters = e->attn_counters;
         a.n_head = c.n_head; a.n_kv = c.n_head_kv; a.head_dim = c.head_dim; a.block_tokens = c.kv_block_tokens;
         a.n_splits = e->n_splits; a.scale = 1.0f / sqrtf((float)c.head_dim); a.err = kernel_error_word();
+        a.max_pages = e->max_blocks;
         tick(2, &ye);
         CK(attn_decode_launch(a, st, pdl));
         tock(ye);
@@ -860,7 +860,7 @@ extern "C" int b2_op_attention_decode(int device, const float* q, const uint16_t
     a.q = dq.as<float>(); a.k_cache = dk.as<__half>(); a.v_cache = dv.as<__half>(); a.block_table = dbt.as<int>();
     a.pos_ptr = dpos.as<int>(); a.out = dout.as<float>(); a.scratch = dscr.as<float>(); a.counters = dcnt.as<unsigned>();
     a.n_head = n_head; a.n_kv = n_kv; a.head_dim = hd; a.block_tokens = bt; a.n_splits = n_splits;
-    a.scale = 1.0f / sqrtf((float)hd); a.err = kernel_error_word();
+    a.scale = 1.0f / sqrtf((float)hd); a.err = kernel_error_word(); a.max_pages = need;
     CK(attn_decode_launch(a, 0, false));
     CK(cudaDeviceSynchronize());
     { int rc2 = check_kernel_error(); if (rc2) return rc2; }

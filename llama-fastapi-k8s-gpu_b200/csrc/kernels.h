@@ -65,6 +65,7 @@ struct AttnParams {
     float* scratch;          // split-K partials: [n_kv][n_splits][G][head_dim + 2]
     unsigned int* counters;  // [n_kv] arrival tickets (zero between launches)
     int n_head, n_kv, head_dim, block_tokens, n_splits;
+    int max_pages;           // entries of block_table that may be read
     float scale;             // 1 / sqrt(head_dim)
     unsigned int* err;       // host-mapped error word (kernel watchdogs)
 };

@@ -153,7 +153,7 @@ def test_attention_decode_vs_oracle(native_lib, n_head, n_kv, hd, T):
     k = (rng.standard_normal((T, n_kv, hd)) * 0.7).astype(np.float16)
     v = rng.standard_normal((T, n_kv, hd)).astype(np.float16)
     ref = _attn_ref(q, k.astype(np.float32), v.astype(np.float32), n_head, n_kv, hd)
-    for bt, n_splits in ((16, 1), (16, 5), (64, 18), (64, 3)):
+    for bt, n_splits in ((16, 1), (16, 5), (64, 18), (64, 8), (16, 4), (64, 2)):
         nblk = (T + bt - 1) // bt
         total = nblk + 3
         blocks = rng.permutation(total)[:nblk].astype(np.int32)      # scattered pages
