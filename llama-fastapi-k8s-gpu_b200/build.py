@@ -35,7 +35,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
         objs = []
         for src in CUDA_SOURCES:
             obj = os.path.join(LIB, src.replace(".cu", ".o"))
-            cmd = [nvcc, *NVCC_FLAGS, "-c", os.path.join(CSRC, src), "-o", obj]
+            extra = os.environ.get("B2_NVCC_EXTRA", "").split()
+            cmd = [nvcc, *NVCC_FLAGS, *extra, "-c", os.path.join(CSRC, src), "-o", obj]
             r = subprocess.run(cmd, capture_output=True, text=True)
             if verbose or r.returncode:
                 sys.stderr.write(r.stdout + r.stderr)

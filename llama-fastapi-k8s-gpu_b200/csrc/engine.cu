@@ -143,8 +143,8 @@ extern "C" int b2_engine_create(const b2_config* c, b2_engine** out) {
     e->act2 = !(c->flags & B2_FLAG_ACT8);
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
-    int per = 1;
-    if (const char* s = getenv("B2_CTAS_PER_SM")) per = atoi(s) > 0 ? atoi(s) : 1;
+    int per = mv_ctas_per_sm_default();
+    if (const char* s = getenv("B2_CTAS_PER_SM")) per = atoi(s) > 0 ? atoi(s) : per;
     e->n_ctas = sms * per;
     CK(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
     CK(cudaEventCreate(&e->ev0));
@@ -274,7 +274,6 @@ static int plan_or_fail(MvParams& p, int n_ctas, const char* what) {
     int rc = mv_plan(p, n_ctas);
     if (rc) return fail(B2_ERR_UNSUPPORTED, std::string("cannot plan mat-vec for ") + what + " (code " + std::to_string(rc) +
                                                (rc == -2 ? ": K > 16384 not supported yet)" : ")"));
-    if (mv_smem_bytes(p) > 112 * 1024) return fail(B2_ERR_UNSUPPORTED, std::string("mat-vec ring too large for ") + what);
     return B2_OK;
 }
 
@@ -760,7 +759,7 @@ extern "C" int b2_op_dequantize(int device, int type, const void* blocks, int64_
 
 static int op_matvec_common(int device, MvParams& p, const void* w0, const void* w1, int n_rows, int K,
                             const float* x, const float* nw, const float* resid, float* y, int planes, int n_ctas) {
-    if (n_ctas <= 0) { int sms = 148; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device); n_ctas = sms; }
+    if (n_ctas <= 0) { int sms = 148; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device); n_ctas = sms * mv_ctas_per_sm_default(); }
     CK(mv_init());
     int rc = mv_plan(p, n_ctas);
     if (rc) return fail(B2_ERR_UNSUPPORTED, "mat-vec shape/type not supported (plan code " + std::to_string(rc) + ")");

@@ -9,9 +9,10 @@ namespace b2 {
 
 // ---------------------------------------------------------------- mat-vec (matvec.cu)
 enum MvMode { MV_STORE = 0, MV_RESID = 1, MV_QKV = 2, MV_GATEUP = 3 };
-constexpr int MV_MAX_STAGES = 24;
+constexpr int MV_MAX_STAGES = 40;
+constexpr int MV_MAX_PROD = 4;               // TMA producer warps per CTA (upper bound)
+constexpr int MV_SHARED_HDR = 1024;          // barriers + reduction scratch at the start of dynamic smem
 constexpr int MV_ROWS = 4;                 // rows per group (one warp, one ring stage)
-constexpr int MV_SMEM_MAX = 112 * 1024;    // two CTAs per SM: this kernel + the next one prefetching
 
 struct MvSeg {
     const uint8_t* w;   // quantised rows, unchanged GGUF bytes
@@ -45,11 +46,15 @@ struct MvParams {
     int n_slices;           // K-slices of 2048 elements per row
     int slot_bytes;         // one row-slice slot in a stage
     int stage_bytes, n_stages;
+    int n_prod;             // producer warps
+    int skip_compute;       // experiment knob (B2_MV_SKIP_COMPUTE): stream tiles, skip the dot products
+    int whole_rows;         // 1: a ring tile is R full rows (one bulk copy); 0: R row-slices (R copies)
     int act_layout, act_dual; // activation plane layout (quant_blocks.cuh); both layouts present?
     int ring_off;           // byte offset of the ring in dynamic shared memory (after the activations)
 };
 
 cudaError_t mv_init();   // once per device, outside stream capture
+int mv_ctas_per_sm_default();   // 2 with 8 consumer warps per CTA, 1 with 16 or 20 (env B2_MV_WARPS)
 int mv_plan(MvParams& p, int n_ctas);
 size_t mv_smem_bytes(const MvParams& p);
 cudaError_t mv_launch(const MvParams& p, int n_ctas, cudaStream_t stream, bool act2, bool pdl);

@@ -29,11 +29,14 @@
 
 namespace b2 {
 
-constexpr int NCW = 8;                 // consumer warps
-constexpr int NTHREADS = (NCW + 1) * 32;
+#ifndef B2_ROW_UNROLL
+#define B2_ROW_UNROLL 1
+#endif
+constexpr int ROW_UNROLL = B2_ROW_UNROLL;  // rows of a group interleaved in the instruction stream
 constexpr int R = MV_ROWS;             // rows per group
 constexpr int TPB = 32 / R;            // tiles the producer warp issues per round
 
+template <int NCW>
 struct __align__(16) MvShared {
     uint64_t full[MV_MAX_STAGES];
     uint64_t empty[MV_MAX_STAGES];
@@ -49,6 +52,7 @@ struct CtaWork {
     int total;          // tiles for the whole CTA
 };
 
+template <int NCW>
 __device__ __forceinline__ CtaWork cta_work(const MvParams& p) {
     CtaWork w;
     const bool gu = (p.mode == MV_GATEUP);
@@ -64,7 +68,7 @@ __device__ __forceinline__ CtaWork cta_work(const MvParams& p) {
     long u0 = (long)units * i / nc, u1 = (long)units * (i + 1) / nc;
     w.r0 = (int)u0 * 2; w.r1 = (int)u1 * 2;
     w.ng = (w.r1 - w.r0 + R - 1) / R;
-    w.tpg = p.n_slices * (gu ? 2 : 1);
+    w.tpg = (p.whole_rows ? 1 : p.n_slices) * (gu ? 2 : 1);
     w.rounds = w.ng / NCW; w.rem = w.ng % NCW;
     w.total = w.ng * w.tpg;
     return w;
@@ -73,6 +77,7 @@ __device__ __forceinline__ CtaWork cta_work(const MvParams& p) {
 struct TileId { int warp, gi, seg, slice; };
 
 // q-th tile in issue order -> owner warp, row group, matrix, K-slice
+template <int NCW>
 __device__ __forceinline__ TileId tile_of(const MvParams& p, const CtaWork& w, int q) {
     TileId t;
     int full_tiles = w.rounds * w.tpg * NCW;
@@ -81,11 +86,13 @@ __device__ __forceinline__ TileId tile_of(const MvParams& p, const CtaWork& w, i
     else { int qq = q - full_tiles; t.warp = qq % w.rem; lt = w.rounds * w.tpg + qq / w.rem; }
     t.gi = t.warp + NCW * (lt / w.tpg);
     int within = lt % w.tpg;
-    t.seg = (p.mode == MV_GATEUP) ? within / p.n_slices : w.seg;
-    t.slice = within % p.n_slices;
+    const int spt = p.whole_rows ? 1 : p.n_slices;      // ring tiles per (group, matrix)
+    t.seg = (p.mode == MV_GATEUP) ? within / spt : w.seg;
+    t.slice = within % spt;
     return t;
 }
 // issue-order index of warp `warp`'s lt-th tile
+template <int NCW>
 __device__ __forceinline__ int q_of(const CtaWork& w, int warp, int lt) {
     int full_lt = w.rounds * w.tpg;
     if (lt < full_lt) return lt * NCW + warp;
@@ -128,34 +135,159 @@ __device__ __forceinline__ void epilogue_pair(const MvParams& p, int seg, int ro
 
 // accumulate one tile (R row-slices in a ring stage) into acc[R].
 // row_lo = low bits of the global address of row0's slice: each bulk copy started at the 16-byte
-// boundary below its row-slice, so the data sits (address & 15) bytes into its slot.
+// boundary below its row-slice, so the data sits (address & 15) bytes into its slot. Only Q6_K
+// rows can be off a 16-byte boundary (K % 2048 != 0); every other type has row_bytes % 16 == 0.
 template <int T, bool ACT2>
 __device__ __forceinline__ void tile_dots(const uint8_t* stage, int slot_bytes, uint32_t row_lo, uint32_t row_bytes,
-                                          int nrows, int slice, int lane, bool lane_active, const ActView& av,
-                                          float (&acc)[R]) {
-    if (!lane_active) return;
+                                          int nrows, int slice, int lane, const ActView& av, float (&acc)[R],
+                                          bool contig = false) {
     LaneAct la;
     load_act<T, ACT2>(la, av, slice * B2_SLICE, lane);
-    if (nrows == R) {
+    // Rows are NOT fully unrolled on purpose: the unrolled body (4 x ~100 instructions per quant type)
+    // overflowed the instruction cache (31% of stall samples were "no instruction"); latency is
+    // hidden by the 16-20 resident warps instead of by interleaving rows inside one warp.
+    float v[R];
 #pragma unroll
-        for (int r = 0; r < R; r++)
-            acc[r] += row_dot<T, ACT2>(stage + r * slot_bytes + ((row_lo + r * row_bytes) & 15u), lane, la);
-    } else {
-#pragma unroll 1
-        for (int r = 0; r < nrows; r++) {
-            float v = row_dot<T, ACT2>(stage + r * slot_bytes + ((row_lo + r * row_bytes) & 15u), lane, la);
+    for (int r = 0; r < R; r++) v[r] = 0.f;
+#pragma unroll ROW_UNROLL
+    for (int r = 0; r < nrows; r++) {
+        uint32_t off = (T == T_Q6_K && !contig) ? ((row_lo + r * row_bytes) & 15u) : 0u;
+        float d = row_dot<T, ACT2>(stage + r * slot_bytes + off, lane, la);
 #pragma unroll
-            for (int k = 0; k < R; k++) if (k == r) acc[k] += v;
+        for (int k = 0; k < R; k++) if (k == r) v[k] = d;
+    }
+#pragma unroll
+    for (int r = 0; r < R; r++) acc[r] += v[r];
+}
+
+// cold path: second matrix of a gate/up pair whose quant family differs from the first
+struct Acc4 { float v[R]; };
+template <bool ACT2>
+__device__ __noinline__ Acc4 tile_dots_any(int type, const uint8_t* stage, int slot_bytes, uint32_t row_lo,
+                                           uint32_t row_bytes, int nrows, int slice, int lane, ActView av, Acc4 in,
+                                           bool contig = false) {
+    float acc[R];
+#pragma unroll
+    for (int r = 0; r < R; r++) acc[r] = in.v[r];
+    switch (type) {
+        case T_Q4_K: tile_dots<T_Q4_K, ACT2>(stage, slot_bytes, row_lo, row_bytes, nrows, slice, lane, av, acc, contig); break;
+        case T_Q6_K: tile_dots<T_Q6_K, ACT2>(stage, slot_bytes, row_lo, row_bytes, nrows, slice, lane, av, acc, contig); break;
+        case T_Q8_0: tile_dots<T_Q8_0, ACT2>(stage, slot_bytes, row_lo, row_bytes, nrows, slice, lane, av, acc, contig); break;
+        case T_Q4_0: tile_dots<T_Q4_0, ACT2>(stage, slot_bytes, row_lo, row_bytes, nrows, slice, lane, av, acc, contig); break;
+        case T_Q5_K: tile_dots<T_Q5_K, ACT2>(stage, slot_bytes, row_lo, row_bytes, nrows, slice, lane, av, acc, contig); break;
+    }
+    Acc4 out;
+#pragma unroll
+    for (int r = 0; r < R; r++) out.v[r] = acc[r];
+    return out;
+}
+
+// One consumer warp's whole job for a CTA whose (first) matrix has quant type T.
+template <int T, bool ACT2, int NCW>
+__device__ __forceinline__ void consume(const MvParams& p, const CtaWork& work, MvShared<NCW>& sh, const uint8_t* ring,
+                                        const ActView& av0, const ActView& av1, int warp, int lane) {
+    const int S = p.n_stages;
+    const int my_groups = work.rounds + (warp < work.rem ? 1 : 0);
+    const bool gateup = (p.mode == MV_GATEUP);
+    const int nmat = gateup ? 2 : 1;
+    const int sb = p.slot_bytes;
+    int lt = 0;
+    for (int g = 0; g < my_groups; g++) {
+        const int gi = warp + NCW * g;
+        const int row0 = work.r0 + gi * R, nrows = min(R, work.r1 - row0);
+        float gate0 = 0.f, gate1 = 0.f;
+        for (int m = 0; m < nmat; m++) {
+            const int seg = gateup ? m : work.seg;
+            const MvSeg& sg = p.seg[seg];
+            const int type = sg.type;
+            const uint32_t row_bytes = (uint32_t)sg.row_bytes;
+            const uint32_t row_lo0 = (uint32_t)(uintptr_t)sg.w + (uint32_t)row0 * row_bytes;   // low address bits suffice
+            const uint32_t sbytes = (uint32_t)slice_bytes(type);
+            float acc[R];
+#pragma unroll
+            for (int r = 0; r < R; r++) acc[r] = 0.f;
+            if (p.whole_rows) {
+                // one ring tile = the R full rows of this group, fetched with a single bulk copy
+                const int q = q_of<NCW>(work, warp, lt++);
+                const int st = q % S;
+                mbar_wait(&sh.full[st], (q / S) & 1, p.err, 0x10002u);
+                const uint8_t* stage = ring + (size_t)st * p.stage_bytes + (row_lo0 & 15u);
+                for (int sl = 0; sl < p.n_slices; sl++) {
+                    if (sl * B2_SLICE + lane * 64 < p.K && !p.skip_compute) {
+                        if (type == T) tile_dots<T, ACT2>(stage + sl * sbytes, (int)row_bytes, 0u, row_bytes, nrows, sl, lane, av0, acc, true);
+                        else {
+                            Acc4 in;
+#pragma unroll
+                            for (int r = 0; r < R; r++) in.v[r] = acc[r];
+                            Acc4 out = tile_dots_any<ACT2>(type, stage + sl * sbytes, (int)row_bytes, 0u, row_bytes, nrows, sl, lane,
+                                                           act_layout_of(type) == act_layout_of(T) ? av0 : av1, in, true);
+#pragma unroll
+                            for (int r = 0; r < R; r++) acc[r] = out.v[r];
+                        }
+                    }
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&sh.empty[st]);
+            } else
+            for (int sl = 0; sl < p.n_slices; sl++, lt++) {
+                const int q = q_of<NCW>(work, warp, lt);
+                const int st = q % S;
+                mbar_wait(&sh.full[st], (q / S) & 1, p.err, 0x10002u);
+                const uint8_t* stage = ring + (size_t)st * p.stage_bytes;
+                if (sl * B2_SLICE + lane * 64 < p.K && !p.skip_compute) {
+                    const uint32_t row_lo = row_lo0 + (uint32_t)sl * sbytes;
+                    if (type == T) tile_dots<T, ACT2>(stage, sb, row_lo, row_bytes, nrows, sl, lane, av0, acc);
+                    else {
+                        Acc4 in;
+#pragma unroll
+                        for (int r = 0; r < R; r++) in.v[r] = acc[r];
+                        Acc4 out = tile_dots_any<ACT2>(type, stage, sb, row_lo, row_bytes, nrows, sl, lane,
+                                                       act_layout_of(type) == act_layout_of(T) ? av0 : av1, in);
+#pragma unroll
+                        for (int r = 0; r < R; r++) acc[r] = out.v[r];
+                    }
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&sh.empty[st]);      // stage can be refilled
+            }
+            // transposed butterfly over the 4 rows: lane 0 / 8 / 16 / 24 end with row 0 / 1 / 2 / 3
+            const bool hi16 = lane & 16, hi8 = lane & 8;
+            float s0 = hi16 ? acc[0] : acc[2], s1 = hi16 ? acc[1] : acc[3];
+            float k0 = hi16 ? acc[2] : acc[0], k1 = hi16 ? acc[3] : acc[1];
+            k0 += __shfl_xor_sync(0xffffffffu, s0, 16);
+            k1 += __shfl_xor_sync(0xffffffffu, s1, 16);
+            float snd = hi8 ? k0 : k1, kp = hi8 ? k1 : k0;
+            kp += __shfl_xor_sync(0xffffffffu, snd, 8);
+            kp += __shfl_xor_sync(0xffffffffu, kp, 4);
+            kp += __shfl_xor_sync(0xffffffffu, kp, 2);
+            kp += __shfl_xor_sync(0xffffffffu, kp, 1);
+            float odd = __shfl_down_sync(0xffffffffu, kp, 8);   // lane 0 <- row 1, lane 16 <- row 3
+            if ((lane & 15) == 0) {
+                int pr = lane >> 4;                             // pair 0 or 1 of the group
+                if (2 * pr < nrows) {
+                    int row = row0 + 2 * pr;
+                    if (gateup) {
+                        if (m == 0) { gate0 = kp; gate1 = odd; }
+                        else {
+                            float h0 = gate0 / (1.0f + __expf(-gate0)) * kp;
+                            float h1 = gate1 / (1.0f + __expf(-gate1)) * odd;
+                            *reinterpret_cast<float2*>(p.y + row) = make_float2(h0, h1);
+                        }
+                    } else {
+                        epilogue_pair(p, seg, row, kp, odd);
+                    }
+                }
+            }
         }
     }
 }
 
-template <bool ACT2>
-__global__ void __launch_bounds__(NTHREADS, 2) matvec_kernel(const MvParams p) {
+template <int NCW, bool ACT2>
+__global__ void __launch_bounds__((NCW + (NCW <= 8 ? 1 : MV_MAX_PROD)) * 32, NCW <= 8 ? 2 : 1) matvec_kernel(const MvParams p) {
     extern __shared__ __align__(128) uint8_t smem_raw[];
-    MvShared& sh = *reinterpret_cast<MvShared*>(smem_raw);
+    MvShared<NCW>& sh = *reinterpret_cast<MvShared<NCW>*>(smem_raw);
     const int Kp = p.n_slices * B2_SLICE;                 // planes padded to whole slices
-    uint8_t* act_a = smem_raw + ((sizeof(MvShared) + 127) & ~127);
+    uint8_t* act_a = smem_raw + MV_SHARED_HDR;
     uint8_t* act_b = act_a + Kp;
     uint8_t* act_a2 = p.act_dual ? act_b + Kp : act_a;    // second layout (gate/up of different quant families)
     uint8_t* act_b2 = p.act_dual ? act_a2 + Kp : act_b;
@@ -164,9 +296,10 @@ __global__ void __launch_bounds__(NTHREADS, 2) matvec_kernel(const MvParams p) {
     uint8_t* ring = smem_raw + p.ring_off;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int S = p.n_stages;
-    const CtaWork work = cta_work(p);
+    const CtaWork work = cta_work<NCW>(p);
     // plane layout follows the quant family this CTA reads (gate/up: seg 0's, plus a second copy if they differ)
-    const int cta_layout = (p.mode == MV_GATEUP) ? p.act_layout : act_layout_of(p.seg[work.seg].type);
+    const int type0 = (p.mode == MV_GATEUP) ? p.seg[0].type : p.seg[work.seg].type;
+    const int cta_layout = act_layout_of(type0);
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < S; s++) { mbar_init(&sh.full[s], 1); mbar_init(&sh.empty[s], 1); }
@@ -175,19 +308,25 @@ __global__ void __launch_bounds__(NTHREADS, 2) matvec_kernel(const MvParams p) {
     __syncthreads();
     griddep_launch();   // let the next kernel start prefetching its own weights
 
-    if (warp == NCW) {
-        // ------------------------------------------------------------ producer warp
-        const int tsub = lane / R, rsub = lane % R;
-        for (int qb = 0; qb < work.total; qb += TPB) {
+    if (warp >= NCW) {
+        // ------------------------------------------------------------ producer warps (rounds interleaved)
+        const int lanes_per_tile = p.whole_rows ? 1 : R;
+        const int tsub = p.whole_rows ? lane : lane / R, rsub = p.whole_rows ? 0 : lane % R;
+        for (int qb = (warp - NCW) * TPB; qb < work.total; qb += TPB * p.n_prod) {
             int q = qb + tsub;
-            bool have = q < work.total;
+            bool have = q < work.total && tsub < TPB;
             const uint8_t* src = nullptr; uint32_t bytes = 0; uint8_t* dst = nullptr; int st = 0;
             if (have) {
-                TileId t = tile_of(p, work, q);
+                TileId t = tile_of<NCW>(p, work, q);
                 const MvSeg& sg = p.seg[t.seg];
                 int row0 = work.r0 + t.gi * R, nrows = min(R, work.r1 - row0);
                 st = q % S;
-                if (rsub < nrows) {
+                if (p.whole_rows) {
+                    uintptr_t start = (uintptr_t)sg.w + (size_t)row0 * sg.row_bytes;
+                    uintptr_t a0 = start & ~(uintptr_t)15, a1 = (start + (size_t)nrows * sg.row_bytes + 15) & ~(uintptr_t)15;
+                    src = (const uint8_t*)a0; bytes = (uint32_t)(a1 - a0);
+                    dst = ring + (size_t)st * p.stage_bytes;
+                } else if (rsub < nrows) {
                     int sb = slice_bytes(sg.type);
                     int len = min(sb, sg.row_bytes - t.slice * sb);        // last slice may be shorter
                     uintptr_t start = (uintptr_t)sg.w + (size_t)(row0 + rsub) * sg.row_bytes + (size_t)t.slice * sb;
@@ -198,10 +337,12 @@ __global__ void __launch_bounds__(NTHREADS, 2) matvec_kernel(const MvParams p) {
                 if (rsub == 0) mbar_wait(&sh.empty[st], ((q / S) & 1) ^ 1, p.err, 0x10001u);
             }
             __syncwarp();
-            // total bytes of the tile = sum over its R lanes
+            // total bytes of the tile = sum over its lanes
             uint32_t tot = bytes;
+            if (lanes_per_tile > 1) {
 #pragma unroll
-            for (int o = 1; o < R; o <<= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
+                for (int o = 1; o < R; o <<= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
+            }
             if (have && rsub == 0) mbar_arrive_expect_tx(&sh.full[st], tot);
             __syncwarp();
             if (bytes) tma_load_1d(dst, src, bytes, &sh.full[st]);
@@ -266,79 +407,40 @@ __global__ void __launch_bounds__(NTHREADS, 2) matvec_kernel(const MvParams p) {
     av1.a = act_a2; av1.b = act_b2; av1.dx = act_dx; av1.s16 = act_s16;
 
     // ---------------------------------------------------------------- consumers: stream tiles
-    const int my_groups = work.rounds + (warp < work.rem ? 1 : 0);
-    int lt = 0;
-    for (int g = 0; g < my_groups; g++) {
-        const int gi = warp + NCW * g;
-        const int row0 = work.r0 + gi * R, nrows = min(R, work.r1 - row0);
-        float gate0 = 0.f, gate1 = 0.f;
-        const int nmat = (p.mode == MV_GATEUP) ? 2 : 1;
-        for (int m = 0; m < nmat; m++) {
-            const int seg = (p.mode == MV_GATEUP) ? m : work.seg;
-            const MvSeg& sg = p.seg[seg];
-            const int type = sg.type;
-            const uint32_t row_bytes = (uint32_t)sg.row_bytes;
-            const uint32_t row_lo0 = (uint32_t)(uintptr_t)sg.w + (uint32_t)row0 * row_bytes;   // low address bits suffice
-            const uint32_t sbytes = (uint32_t)slice_bytes(type);
-            const ActView& av = (act_layout_of(type) == cta_layout) ? av0 : av1;
-            float acc[R];
-#pragma unroll
-            for (int r = 0; r < R; r++) acc[r] = 0.f;
-            for (int sl = 0; sl < p.n_slices; sl++, lt++) {
-                const int q = q_of(work, warp, lt);
-                const int st = q % S;
-                mbar_wait(&sh.full[st], (q / S) & 1, p.err, 0x10002u);
-                const uint8_t* stage = ring + (size_t)st * p.stage_bytes;
-                const bool lane_active = sl * B2_SLICE + lane * 64 < p.K;
-                const uint32_t row_lo = row_lo0 + (uint32_t)sl * sbytes;
-                const int sb = p.slot_bytes;
-                switch (type) {
-                    case T_Q4_K: tile_dots<T_Q4_K, ACT2>(stage, sb, row_lo, row_bytes, nrows, sl, lane, lane_active, av, acc); break;
-                    case T_Q6_K: tile_dots<T_Q6_K, ACT2>(stage, sb, row_lo, row_bytes, nrows, sl, lane, lane_active, av, acc); break;
-                    case T_Q8_0: tile_dots<T_Q8_0, ACT2>(stage, sb, row_lo, row_bytes, nrows, sl, lane, lane_active, av, acc); break;
-                    case T_Q4_0: tile_dots<T_Q4_0, ACT2>(stage, sb, row_lo, row_bytes, nrows, sl, lane, lane_active, av, acc); break;
-                    case T_Q5_K: tile_dots<T_Q5_K, ACT2>(stage, sb, row_lo, row_bytes, nrows, sl, lane, lane_active, av, acc); break;
-                }
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&sh.empty[st]);      // stage can be refilled
-            }
-            // transposed butterfly over the 4 rows: lane 0 / 8 / 16 / 24 end with row 0 / 1 / 2 / 3
-            const bool hi16 = lane & 16, hi8 = lane & 8;
-            float s0 = hi16 ? acc[0] : acc[2], s1 = hi16 ? acc[1] : acc[3];
-            float k0 = hi16 ? acc[2] : acc[0], k1 = hi16 ? acc[3] : acc[1];
-            k0 += __shfl_xor_sync(0xffffffffu, s0, 16);
-            k1 += __shfl_xor_sync(0xffffffffu, s1, 16);
-            float snd = hi8 ? k0 : k1, kp = hi8 ? k1 : k0;
-            kp += __shfl_xor_sync(0xffffffffu, snd, 8);
-            kp += __shfl_xor_sync(0xffffffffu, kp, 4);
-            kp += __shfl_xor_sync(0xffffffffu, kp, 2);
-            kp += __shfl_xor_sync(0xffffffffu, kp, 1);
-            float odd = __shfl_down_sync(0xffffffffu, kp, 8);   // lane 0 <- row 1, lane 16 <- row 3
-            if ((lane & 15) == 0) {
-                int pr = lane >> 4;                             // pair 0 or 1 of the group
-                if (2 * pr < nrows) {
-                    int row = row0 + 2 * pr;
-                    if (p.mode == MV_GATEUP) {
-                        if (m == 0) { gate0 = kp; gate1 = odd; }
-                        else {
-                            float h0 = gate0 / (1.0f + __expf(-gate0)) * kp;
-                            float h1 = gate1 / (1.0f + __expf(-gate1)) * odd;
-                            *reinterpret_cast<float2*>(p.y + row) = make_float2(h0, h1);
-                        }
-                    } else {
-                        epilogue_pair(p, seg, row, kp, odd);
-                    }
-                }
-            }
-        }
+    switch (type0) {
+        case T_Q4_K: consume<T_Q4_K, ACT2, NCW>(p, work, sh, ring, av0, av1, warp, lane); break;
+        case T_Q6_K: consume<T_Q6_K, ACT2, NCW>(p, work, sh, ring, av0, av1, warp, lane); break;
+        case T_Q8_0: consume<T_Q8_0, ACT2, NCW>(p, work, sh, ring, av0, av1, warp, lane); break;
+        case T_Q4_0: consume<T_Q4_0, ACT2, NCW>(p, work, sh, ring, av0, av1, warp, lane); break;
+        case T_Q5_K: consume<T_Q5_K, ACT2, NCW>(p, work, sh, ring, av0, av1, warp, lane); break;
     }
 }
 
 // ---------------------------------------------------------------- host side
-cudaError_t mv_init() {   // per device: allow > 48 KB dynamic shared memory
-    cudaError_t e = cudaFuncSetAttribute(matvec_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, MV_SMEM_MAX);
+static int g_ncw = 0;   // consumer warps per CTA: 8 (two CTAs per SM) or 16 / 20 (one CTA per SM)
+
+static int mv_ncw() {
+    if (!g_ncw) {
+        g_ncw = 16;
+        if (const char* s = getenv("B2_MV_WARPS")) { int v = atoi(s); if (v == 8 || v == 16 || v == 20) g_ncw = v; }
+    }
+    return g_ncw;
+}
+int mv_ctas_per_sm_default() { return mv_ncw() <= 8 ? 2 : 1; }
+static int mv_smem_max() { return mv_ncw() <= 8 ? 112 * 1024 : 224 * 1024; }
+
+template <int NCW>
+static cudaError_t set_attr(int bytes) {
+    cudaError_t e = cudaFuncSetAttribute(matvec_kernel<NCW, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(matvec_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, MV_SMEM_MAX);
+    return cudaFuncSetAttribute(matvec_kernel<NCW, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+}
+
+cudaError_t mv_init() {   // per device: allow > 48 KB dynamic shared memory
+    cudaError_t e;
+    if ((e = set_attr<8>(112 * 1024)) != cudaSuccess) return e;
+    if ((e = set_attr<16>(224 * 1024)) != cudaSuccess) return e;
+    return set_attr<20>(224 * 1024);
 }
 
 int mv_plan(MvParams& p, int n_ctas) {
@@ -357,17 +459,27 @@ int mv_plan(MvParams& p, int n_ctas) {
     p.n_slices = (p.K + B2_SLICE - 1) / B2_SLICE;
     p.slot_bytes = (max_sb + 16 + 15) / 16 * 16;           // + slack for the 16-byte alignment of each copy
     p.stage_bytes = (R * p.slot_bytes + 127) / 128 * 128;
+    // short rows: a group of R consecutive full rows is one contiguous run -> one bulk copy per tile
+    int max_rb = 0;
+    for (int s = 0; s < p.nseg; s++) max_rb = p.seg[s].row_bytes > max_rb ? p.seg[s].row_bytes : max_rb;
+    p.whole_rows = 0;   // measured slower than per-slice tiles on B200 (fewer tiles in flight); kept as a knob
+    if (const char* s = getenv("B2_MV_WHOLE_ROWS")) p.whole_rows = atoi(s) && (R * max_rb + 32 <= 48 * 1024);
+    if (p.whole_rows) p.stage_bytes = (R * max_rb + 32 + 127) / 128 * 128;
     p.act_layout = act_layout_of(p.seg[0].type);
     p.act_dual = 0;
     for (int s = 1; s < p.nseg; s++)
         if (p.mode == MV_GATEUP && act_layout_of(p.seg[s].type) != p.act_layout) p.act_dual = 1;
     int act_bytes = (p.act_dual ? 4 : 2) * p.n_slices * B2_SLICE + (p.K / 32) * 4 + (p.K / 16) * 4;
-    p.ring_off = (((int)sizeof(MvShared) + 127) / 128 * 128 + act_bytes + 127) / 128 * 128;
-    int S = (MV_SMEM_MAX - p.ring_off) / p.stage_bytes;
+    p.ring_off = (MV_SHARED_HDR + act_bytes + 127) / 128 * 128;
+    int S = (mv_smem_max() - p.ring_off) / p.stage_bytes;
     if (S > MV_MAX_STAGES) S = MV_MAX_STAGES;
     if (const char* cap = getenv("B2_MV_STAGES")) { int c = atoi(cap); if (c >= TPB && c < S) S = c; }   // tuning knob
     if (S < TPB) return -5;                                // the producer fills TPB stages per round
     p.n_stages = S;
+    p.skip_compute = getenv("B2_MV_SKIP_COMPUTE") ? 1 : 0;   // experiment: measure the TMA ring alone
+    p.n_prod = mv_ncw() <= 8 ? 1 : 2;
+    if (const char* s = getenv("B2_MV_PROD")) { int v = atoi(s); if (v >= 1 && v <= MV_MAX_PROD && mv_ncw() > 8) p.n_prod = v; }
+    if (S < TPB * p.n_prod) p.n_prod = 1;                  // each producer warp fills TPB stages per round
     // CTA split proportional to bytes (gate/up: every CTA handles both matrices)
     if (p.mode == MV_GATEUP) {
         if (p.nseg != 2 || p.seg[0].n_rows != p.seg[1].n_rows) return -6;
@@ -395,16 +507,25 @@ int mv_plan(MvParams& p, int n_ctas) {
 
 size_t mv_smem_bytes(const MvParams& p) { return (size_t)p.ring_off + (size_t)p.n_stages * p.stage_bytes; }
 
-cudaError_t mv_launch(const MvParams& p, int n_ctas, cudaStream_t stream, bool act2, bool pdl) {
+template <int NCW>
+static cudaError_t launch_t(const MvParams& p, int n_ctas, cudaStream_t stream, bool act2, bool pdl) {
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(n_ctas); cfg.blockDim = dim3(NTHREADS);
+    cfg.gridDim = dim3(n_ctas); cfg.blockDim = dim3((NCW + p.n_prod) * 32);
     cfg.dynamicSmemBytes = mv_smem_bytes(p); cfg.stream = stream;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
-    if (act2) return cudaLaunchKernelEx(&cfg, matvec_kernel<true>, p);
-    return cudaLaunchKernelEx(&cfg, matvec_kernel<false>, p);
+    if (act2) return cudaLaunchKernelEx(&cfg, matvec_kernel<NCW, true>, p);
+    return cudaLaunchKernelEx(&cfg, matvec_kernel<NCW, false>, p);
+}
+
+cudaError_t mv_launch(const MvParams& p, int n_ctas, cudaStream_t stream, bool act2, bool pdl) {
+    switch (mv_ncw()) {
+        case 8: return launch_t<8>(p, n_ctas, stream, act2, pdl);
+        case 20: return launch_t<20>(p, n_ctas, stream, act2, pdl);
+        default: return launch_t<16>(p, n_ctas, stream, act2, pdl);
+    }
 }
 
 }  // namespace b2

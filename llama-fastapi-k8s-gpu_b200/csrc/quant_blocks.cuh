@@ -222,10 +222,9 @@ B2_D float quantize32(const float* t, int* a, int* b, float& sum_lo, float& sum_
     return amax;
 }
 
+// Two activation planes fold into one integer: x.w ~= dx/252 * (252 A + B); LaneAct.f carries dx/252.
 template <bool ACT2>
-B2_D float fin(int A, int B, float dx) {
-    return ACT2 ? dx * ((float)A + (float)B * (1.0f / B2_ACT_RES)) : dx * (float)A;
-}
+B2_D int fold(int A, int B) { return ACT2 ? A * (int)B2_ACT_RES + B : A; }
 
 // ---------------------------------------------------------------- activation layout
 // The int8 planes are stored in 16-byte units, permuted inside each 2048-element slice so that the
@@ -258,12 +257,13 @@ B2_D void load_act(LaneAct& r, const ActView& v, int e0 /* first element of the 
 #pragma unroll
         for (int kq = 0; kq < 4; kq++) {
             int e = eb + 32 * kq;
-            r.f[kq] = v.dx[e >> 5];
-            r.f[4 + kq] = v.s16[e >> 4];
+            r.f[kq] = v.dx[e >> 5] * (ACT2 ? 1.0f / B2_ACT_RES : 1.0f);     // scale of the folded integer T
+            r.f[4 + kq] = 32.0f * v.s16[e >> 4];
         }
     } else {
         int e = e0 + 64 * lane;
-        r.f[0] = v.dx[e >> 5]; r.f[1] = v.dx[(e >> 5) + 1];
+        r.f[0] = v.dx[e >> 5] * (ACT2 ? 1.0f / B2_ACT_RES : 1.0f);           // scale of the folded integer T
+        r.f[1] = v.dx[(e >> 5) + 1] * (ACT2 ? 1.0f / B2_ACT_RES : 1.0f);
         r.f[2] = v.s16[e >> 4] + v.s16[(e >> 4) + 1];
         r.f[3] = v.s16[(e >> 4) + 2] + v.s16[(e >> 4) + 3];
     }
@@ -295,10 +295,12 @@ B2_D float row_dot_q4k(const uint8_t* row, int lane, const LaneAct& act) {
         Ahi = dp4a_us(hi16, act.a[8 + k], Ahi);
         if (ACT2) { Blo = dp4a(lo, act.b[k], Blo); Bhi = dp4a_us(hi16, act.b[8 + k], Bhi); }
     }
-    Ahi >>= 4; Bhi >>= 4;                              // exact: both are multiples of 16
-    float r = d * (float)(scp & 0xffu) * fin<ACT2>(Alo, Blo, act.f[0]) - dmin * (float)(mp & 0xffu) * act.f[2];
-    r += d * (float)(scp >> 8) * fin<ACT2>(Ahi, Bhi, act.f[1]) - dmin * (float)(mp >> 8) * act.f[3];
-    return r;
+    // integer fold: T = 252 A + B, then the 6-bit sub-block scale, one int->float per sub-block
+    int U0 = fold<ACT2>(Alo, Blo) * (int)(scp & 0xffu);
+    int U1 = (fold<ACT2>(Ahi, Bhi) >> 4) * (int)(scp >> 8);       // >> 4 exact: hi sums are multiples of 16
+    float F = (float)U0 * act.f[0] + (float)U1 * act.f[1];
+    float M = (float)(mp & 0xffu) * act.f[2] + (float)(mp >> 8) * act.f[3];
+    return d * F - dmin * M;
 }
 
 template <bool ACT2>
@@ -326,9 +328,11 @@ B2_D float row_dot_q5k(const uint8_t* row, int lane, const LaneAct& act) {
         Ahi = dp4a(hi, act.a[8 + k], Ahi);
         if (ACT2) { Blo = dp4a(lo, act.b[k], Blo); Bhi = dp4a(hi, act.b[8 + k], Bhi); }
     }
-    float r = d * (float)(scp & 0xffu) * fin<ACT2>(Alo, Blo, act.f[0]) - dmin * (float)(mp & 0xffu) * act.f[2];
-    r += d * (float)(scp >> 8) * fin<ACT2>(Ahi, Bhi, act.f[1]) - dmin * (float)(mp >> 8) * act.f[3];
-    return r;
+    int U0 = fold<ACT2>(Alo, Blo) * (int)(scp & 0xffu);
+    int U1 = fold<ACT2>(Ahi, Bhi) * (int)(scp >> 8);
+    float F = (float)U0 * act.f[0] + (float)U1 * act.f[1];
+    float M = (float)(mp & 0xffu) * act.f[2] + (float)(mp >> 8) * act.f[3];
+    return d * F - dmin * M;
 }
 
 template <bool ACT2>
@@ -360,9 +364,9 @@ B2_D float row_dot_q6k(const uint8_t* row, int lane, const LaneAct& act) {
     for (int kq = 0; kq < 4; kq++) {
         int si = 2 * kq + qt;                           // scale index within the half
         float sc = (float)(int8_t)((si < 4 ? scw[0] : scw[1]) >> (8 * (si & 3)));
-        r += (d * sc) * (fin<ACT2>(A[kq], B[kq], act.f[kq]) - 32.0f * act.f[4 + kq]);
+        r += sc * ((float)fold<ACT2>(A[kq], B[kq]) * act.f[kq] - act.f[4 + kq]);
     }
-    return r;
+    return d * r;
 }
 
 template <bool ACT2>
@@ -386,7 +390,7 @@ B2_D float row_dot_q4_0(const uint8_t* row, int lane, const LaneAct& act) {
         }
     }
     A0 += A0h >> 4; B0 += B0h >> 4; A1 += A1h >> 4; B1 += B1h >> 4;
-    return d0 * (fin<ACT2>(A0, B0, act.f[0]) - 8.0f * act.f[2]) + d1 * (fin<ACT2>(A1, B1, act.f[1]) - 8.0f * act.f[3]);
+    return d0 * ((float)fold<ACT2>(A0, B0) * act.f[0] - 8.0f * act.f[2]) + d1 * ((float)fold<ACT2>(A1, B1) * act.f[1] - 8.0f * act.f[3]);
 }
 
 template <bool ACT2>
@@ -404,7 +408,7 @@ B2_D float row_dot_q8_0(const uint8_t* row, int lane, const LaneAct& act) {
         A1 = dp4a(q1, act.a[8 + k], A1);
         if (ACT2) { B0 = dp4a(q0, act.b[k], B0); B1 = dp4a(q1, act.b[8 + k], B1); }
     }
-    return d0 * fin<ACT2>(A0, B0, act.f[0]) + d1 * fin<ACT2>(A1, B1, act.f[1]);
+    return d0 * ((float)fold<ACT2>(A0, B0) * act.f[0]) + d1 * ((float)fold<ACT2>(A1, B1) * act.f[1]);
 }
 
 template <int T, bool ACT2>
