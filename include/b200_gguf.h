@@ -159,6 +159,32 @@ int b2_op_attention_decode(int device, const float* host_q, const uint16_t* host
 int b2_op_sample(int device, const float* host_logits, int n_vocab, const b2_sampling* sampling,
                  const int32_t* host_history, int n_history, double u, int32_t* host_token_out);
 
+/* ---- decode attention that allocates nothing (no counterpart in the reference: llama.cpp
+ *      allocates its compute buffers itself; this exists for hosts of THIS library).
+ *
+ * Same kernel and same result as the split path of b2_op_attention_decode, for callers that
+ * cannot ask the driver for memory at call time: a host that has already committed all of its
+ * HBM to weights and KV pages, or one whose token loop must not hit the allocator (an
+ * allocation serialises the device and can fail under memory pressure). The split-merge
+ * scratch is a fixed 1 MiB array (plus 256 B of tickets) built into the library; every GPU that
+ * loads the library carries it until the process exits.
+ *
+ * All pointers are DEVICE pointers owned by the caller: q [n_head*head_dim] f32, the paged K and
+ * V pools [page][n_kv][block_tokens][head_dim] f16, the page table (max_pages entries), *dev_pos
+ * = index of the newest token (attends to 0..pos), out [n_head*head_dim] f32. `stream` is a
+ * cudaStream_t (NULL = default stream); the call only enqueues work.
+ * Limits: n_splits >= 2, n_head * n_splits * (head_dim + 2) <= 262144 floats, n_kv <= 64,
+ * max_pages <= 512; anything larger is rejected with B2_ERR_ARG and a message naming the limit.
+ * The first call on each device also looks up the array's device address (cudaGetSymbolAddress)
+ * and sets a kernel attribute; make that first call before starting any stream capture.
+ * Every call uses the same array: it clears the tickets, the partials are overwritten before they
+ * are read, and two calls that overlap on the GPU (different streams) race with each other.
+ * No cudaMalloc, cudaFree or allocating library routine is called. */
+int b2_attention_decode_static(int device, const float* dev_q, const uint16_t* dev_k_pool,
+                               const uint16_t* dev_v_pool, const int32_t* dev_block_table, int max_pages,
+                               const int32_t* dev_pos, int n_head, int n_kv, int head_dim, int block_tokens,
+                               int n_splits, float* dev_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -329,3 +329,72 @@ cudaError_t attn_decode_launch(const AttnParams& p, cudaStream_t stream, bool pd
 }
 
 }  // namespace b2
+
+// ------------------------------------------------------------------------------------------------
+// Allocation-free variant of the global-scratch split merge (b2_attention_decode_static in the C ABI).
+//
+// Who needs it: a serving host that has already handed every byte of HBM it owns to weights and KV
+// pages (the engine sizes its KV pool up front), or that runs this op on a latency-critical token
+// loop where a driver allocation would serialise the device and may fail under memory pressure.
+// Such a caller cannot cudaMalloc the split-merge scratch, so the scratch lives here, inside the
+// library image: a fixed file-scope device array that every GPU loading the library carries until
+// the process exits (STATIC_SCRATCH_FLOATS * 4 bytes + 256 bytes of tickets per GPU).
+//
+// `g_static_scratch` / `g_static_tickets` are device symbols. In host code those names are only
+// stand-ins, not device addresses, so the launcher asks the runtime for the real address once per
+// device (cudaGetSymbolAddress with that device current) and passes the pointer to the kernel.
+namespace b2 {
+
+constexpr size_t STATIC_SCRATCH_FLOATS = 256 * 1024;        // 1 MiB of split partials per GPU
+constexpr int STATIC_MAX_KV_HEADS = 64;
+constexpr int STATIC_MAX_DEVICES = 64;
+
+static __device__ __align__(256) float g_static_scratch[STATIC_SCRATCH_FLOATS];
+static __device__ __align__(256) unsigned int g_static_tickets[STATIC_MAX_KV_HEADS];
+
+static float* g_scratch_addr[STATIC_MAX_DEVICES];
+static unsigned int* g_ticket_addr[STATIC_MAX_DEVICES];
+static bool g_static_ready[STATIC_MAX_DEVICES];
+
+size_t attn_static_scratch_floats() { return STATIC_SCRATCH_FLOATS; }
+
+// Once per device (that device must be current): resolve the device addresses of the two arrays
+// and raise the kernel's dynamic shared-memory limit. Nothing here allocates.
+cudaError_t attn_static_setup(int device) {
+    if (device < 0 || device >= STATIC_MAX_DEVICES) return cudaErrorInvalidDevice;
+    if (g_static_ready[device]) return cudaSuccess;
+    cudaError_t e;
+    float* s = nullptr;
+    unsigned int* t = nullptr;
+    if ((e = cudaGetSymbolAddress((void**)&s, g_static_scratch)) != cudaSuccess) return e;
+    if ((e = cudaGetSymbolAddress((void**)&t, g_static_tickets)) != cudaSuccess) return e;
+    if ((e = attn_init()) != cudaSuccess) return e;
+    g_scratch_addr[device] = s;
+    g_ticket_addr[device] = t;
+    g_static_ready[device] = true;
+    return cudaSuccess;
+}
+
+// Launch the scratch-merging kernel on the built-in arrays. All pointers in `p` except scratch and
+// counters are the caller's device pointers. Every call shares the same arrays: the tickets are
+// cleared here before the launch (they must start at zero); the partials keep whatever the last
+// call left and are fully rewritten before they are read. Two calls that overlap on the GPU
+// (different streams) would race on both arrays.
+cudaError_t attn_decode_launch_static(AttnParams p, int device, cudaStream_t stream) {
+    if (device < 0 || device >= STATIC_MAX_DEVICES || !g_static_ready[device]) return cudaErrorNotReady;
+    p.scratch = g_scratch_addr[device];
+    p.counters = g_ticket_addr[device];
+    cudaError_t e = cudaMemsetAsync(p.counters, 0, sizeof(unsigned int) * STATIC_MAX_KV_HEADS, stream);
+    if (e != cudaSuccess) return e;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(p.n_splits, p.n_kv); cfg.blockDim = dim3(AT_THREADS); cfg.stream = stream;
+    cfg.attrs = nullptr; cfg.numAttrs = 0;
+    if (p.head_dim == 64) {
+        cfg.dynamicSmemBytes = sizeof(AttnShared<64>);
+        return cudaLaunchKernelEx(&cfg, attn_decode_kernel<64, false>, p);
+    }
+    cfg.dynamicSmemBytes = sizeof(AttnShared<128>);
+    return cudaLaunchKernelEx(&cfg, attn_decode_kernel<128, false>, p);
+}
+
+}  // namespace b2

@@ -895,3 +895,34 @@ extern "C" int b2_op_sample(int device, const float* logits, int V, const b2_sam
     CK(cudaMemcpy(tok, ints + 2, sizeof(int), cudaMemcpyDeviceToHost));
     return B2_OK;
 }
+
+// ------------------------------------------------------------------------------------------
+// Allocation-free decode attention (see the block comment at the end of attention.cu).
+extern "C" int b2_attention_decode_static(int device, const float* dev_q, const uint16_t* dev_k_pool,
+                                          const uint16_t* dev_v_pool, const int32_t* dev_block_table, int max_pages,
+                                          const int32_t* dev_pos, int n_head, int n_kv, int head_dim, int block_tokens,
+                                          int n_splits, float* dev_out, void* stream) {
+    if (!dev_q || !dev_k_pool || !dev_v_pool || !dev_block_table || !dev_pos || !dev_out)
+        return fail(B2_ERR_ARG, "null device pointer");
+    if (head_dim != 64 && head_dim != 128) return fail(B2_ERR_UNSUPPORTED, "head_dim must be 64 or 128");
+    if (n_kv <= 0 || n_head <= 0 || n_head % n_kv || n_head / n_kv > 8)
+        return fail(B2_ERR_UNSUPPORTED, "n_head / n_kv must be an integer <= 8");
+    if (block_tokens <= 0 || block_tokens % 16) return fail(B2_ERR_ARG, "block_tokens must be a multiple of 16");
+    if (max_pages <= 0 || max_pages > 512) return fail(B2_ERR_ARG, "max_pages must be in 1..512");
+    if (n_splits < 2 || (n_head / n_kv) * n_splits > 512)
+        return fail(B2_ERR_ARG, "n_splits must be >= 2 (one split needs no scratch) and G * n_splits <= 512");
+    if (n_kv > 64) return fail(B2_ERR_ARG, "built-in ticket array holds at most 64 KV heads");
+    size_t need = attn_scratch_floats(n_head, n_kv, head_dim, n_splits);
+    if (need > attn_static_scratch_floats())
+        return fail(B2_ERR_ARG, "split partials need " + std::to_string(need * 4) + " bytes, the built-in scratch holds " +
+                                    std::to_string(attn_static_scratch_floats() * 4) + " (n_head * n_splits * (head_dim + 2) floats)");
+    CK(cudaSetDevice(device));
+    CK(attn_static_setup(device));      // first call on a device resolves the symbol addresses
+    AttnParams a = {};
+    a.q = dev_q; a.k_cache = (const __half*)dev_k_pool; a.v_cache = (const __half*)dev_v_pool;
+    a.block_table = dev_block_table; a.pos_ptr = dev_pos; a.out = dev_out;
+    a.n_head = n_head; a.n_kv = n_kv; a.head_dim = head_dim; a.block_tokens = block_tokens; a.n_splits = n_splits;
+    a.max_pages = max_pages; a.scale = 1.0f / sqrtf((float)head_dim); a.err = kernel_error_word();
+    CK(attn_decode_launch_static(a, device, (cudaStream_t)stream));
+    return B2_OK;
+}

@@ -77,6 +77,10 @@ struct AttnParams {
 cudaError_t attn_init();
 size_t attn_scratch_floats(int n_head, int n_kv, int head_dim, int n_splits);
 cudaError_t attn_decode_launch(const AttnParams& p, cudaStream_t stream, bool pdl);
+// allocation-free variant: split partials in a fixed device array inside the library (attention.cu)
+size_t attn_static_scratch_floats();
+cudaError_t attn_static_setup(int device);
+cudaError_t attn_decode_launch_static(AttnParams p, int device, cudaStream_t stream);
 
 // ---------------------------------------------------------------- small kernels (misc.cu)
 // One pinned, device-mapped word per process that kernel watchdogs write to; 0 = no error.

@@ -59,6 +59,8 @@ SIGNATURES = {
     "b2_op_gate_up": (c_int, [c_int, c_int, c_void_p, c_int, c_void_p, c_int, c_int, c_void_p, c_void_p, c_float, c_void_p, c_int]),
     "b2_op_rmsnorm": (c_int, [c_int, c_void_p, c_void_p, c_float, c_int, c_int, c_void_p]),
     "b2_op_attention_decode": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_int, c_int, c_void_p]),
+    "b2_attention_decode_static": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_int,
+                                           c_int, c_int, c_void_p, c_void_p]),
     "b2_op_sample": (c_int, [c_int, c_void_p, c_int, POINTER(B2Sampling), c_void_p, c_int, c_double, POINTER(c_int32)]),
 }
 
