@@ -127,6 +127,8 @@ class Vocab:
                 out.append(self.special[frag])
                 prev_special = True
                 continue
+            if not frag:
+                continue
             s = frag.decode("utf-8", errors="replace")
             if self.model == "llama":
                 if self.add_space_prefix and prev_special:
