@@ -33,10 +33,11 @@ static int fail(int code, const std::string& msg) { g_err = msg; return code; }
 static int check_kernel_error() {
     unsigned int* w = kernel_error_word();
     if (w && *w) {
-        unsigned int c = *w;
-        *w = 0;
-        char buf[96];
-        snprintf(buf, sizeof(buf), "kernel barrier wait timed out (watchdog code 0x%x)", c);
+        unsigned int c = w[0];
+        char buf[160];
+        snprintf(buf, sizeof(buf), "kernel barrier wait timed out (watchdog code 0x%x, block %u, thread %u, tile %u, parity %u)",
+                 c, w[1], w[2], w[3], w[4]);
+        for (int i = 0; i < 8; i++) w[i] = 0;
         return fail(B2_ERR_CUDA, buf);
     }
     return B2_OK;

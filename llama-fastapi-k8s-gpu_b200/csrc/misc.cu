@@ -10,8 +10,8 @@ namespace b2 {
 unsigned int* kernel_error_word() {
     static unsigned int* w = nullptr;
     if (!w) {
-        if (cudaHostAlloc(&w, sizeof(unsigned int), cudaHostAllocMapped | cudaHostAllocPortable) != cudaSuccess) return nullptr;
-        *w = 0;
+        if (cudaHostAlloc(&w, 8 * sizeof(unsigned int), cudaHostAllocMapped | cudaHostAllocPortable) != cudaSuccess) return nullptr;
+        for (int i = 0; i < 8; i++) w[i] = 0;
     }
     return w;
 }

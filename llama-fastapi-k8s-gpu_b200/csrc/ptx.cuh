@@ -39,11 +39,15 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 // in the host-visible error word and carries on with garbage instead of hanging the GPU; every
 // engine call checks that word after it synchronises and fails loudly.
 // try_wait already suspends the thread for a hardware time slice.
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, unsigned int* err, unsigned int code) {
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, unsigned int* err, unsigned int code,
+                                          unsigned int info = 0) {
     uint32_t spins = 0;
     while (!mbar_try_wait(bar, parity)) {
         if (++spins > (1u << 22)) {
-            if (err) *reinterpret_cast<volatile unsigned int*>(err) = code;   // plain store: the word lives in host memory
+            if (err) {          // plain stores: the words live in host memory. [0] code [1] block [2] thread [3] info [4] parity
+                volatile unsigned int* e = reinterpret_cast<volatile unsigned int*>(err);
+                if (e[0] == 0) { e[1] = blockIdx.x; e[2] = threadIdx.x; e[3] = info; e[4] = parity; e[0] = code; }
+            }
             return;
         }
     }
