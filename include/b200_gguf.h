@@ -53,6 +53,7 @@ typedef struct b2_config {
 #define B2_FLAG_NO_GRAPH 1      /* launch kernels directly instead of replaying CUDA graphs */
 #define B2_FLAG_NO_PDL 2        /* no programmatic dependent launch between kernels */
 #define B2_FLAG_ACT8 4          /* single int8 activation plane (faster, ~0.5% noise) */
+#define B2_FLAG_NO_MEGA 8       /* one kernel per operation instead of the persistent layer kernel */
 
 typedef struct b2_sampling {
     float temperature;        /* <= 0: greedy */

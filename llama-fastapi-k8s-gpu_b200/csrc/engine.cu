@@ -65,6 +65,8 @@ struct Slot {
     double* uniforms = nullptr;    // [8192]
     cudaGraphExec_t g_decode = nullptr, g_pre_step = nullptr, g_pre_last = nullptr, g_fwd = nullptr;
     int n_decode_nodes = 0, n_pre_step_nodes = 0, n_pre_last_nodes = 0, n_fwd_nodes = 0;
+    MvParams* mega_mv = nullptr;   // device tables for the persistent layer kernel (built on first use)
+    AttnParams* mega_at = nullptr;
     int n_past = 0;                // host mirror of ints[1]
     int n_sampled = 0;             // host mirror of ints[3]
 };
@@ -86,7 +88,13 @@ struct b2_engine {
     int32_t* pinned = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     int64_t launches = 0, weight_bytes = 0, kv_bytes = 0;
-    bool use_graph = true, use_pdl = true, act2 = true, finalized = false;
+    bool use_graph = true, use_pdl = true, act2 = true, finalized = false, use_mega = true;
+    MegaParams mega = {};
+    unsigned int* mega_bar = nullptr;
+    int mega_splits = 1;
+    float* mega_scratch = nullptr;
+    unsigned* mega_counters = nullptr;
+    unsigned long long* mega_ts = nullptr;   // B2_MEGA_TS=1: phase timestamps of the last layer-kernel launch
     std::mutex mu;
 };
 
@@ -137,11 +145,15 @@ extern "C" int b2_engine_create(const b2_config* c, b2_engine** out) {
     CK(cudaSetDevice(c->device));
     CK(mv_init());
     CK(attn_init());
+    CK(mega_init());
     b2_engine* e = new b2_engine();
     e->cfg = *c;
     e->use_graph = !(c->flags & B2_FLAG_NO_GRAPH);
     e->use_pdl = !(c->flags & B2_FLAG_NO_PDL);
     e->act2 = !(c->flags & B2_FLAG_ACT8);
+    // The persistent layer kernel is opt-in (B2_MEGA=1): measured slower than the per-kernel graph on B200
+    // (a 148-CTA grid barrier costs ~5 us, as much as a kernel boundary).
+    e->use_mega = getenv("B2_MEGA") && !(c->flags & B2_FLAG_NO_MEGA) && !getenv("B2_NO_MEGA");
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
     int per = mv_ctas_per_sm_default();
@@ -219,8 +231,9 @@ extern "C" int b2_engine_destroy(b2_engine* e) {
         free_slot_graphs(s);
         cudaFree(s.x); cudaFree(s.q); cudaFree(s.att); cudaFree(s.h); cudaFree(s.logits);
         cudaFree(s.ints); cudaFree(s.block_table); cudaFree(s.prompt); cudaFree(s.ring); cudaFree(s.sst); cudaFree(s.sp);
-        cudaFree(s.uniforms);
+        cudaFree(s.uniforms); cudaFree(s.mega_mv); cudaFree(s.mega_at);
     }
+    cudaFree(e->mega_bar); cudaFree(e->mega_scratch); cudaFree(e->mega_counters);
     cudaFree(e->k_pool); cudaFree(e->v_pool); cudaFree(e->rope_freq);
     cudaFree(e->attn_scratch); cudaFree(e->attn_counters);
     cudaFreeHost(e->pinned);
@@ -336,6 +349,29 @@ extern "C" int b2_engine_finalize(b2_engine* e) {
     h.norm_w = (const float*)e->out_norm.ptr; h.eps = c.rms_eps; h.err = kernel_error_word();
     if ((rc = plan_or_fail(h, e->n_ctas, "output"))) return rc;
     e->p_head = h;
+    if (e->use_mega) {
+        // one ring geometry for the whole layer stack; attention inside it merges splits through global scratch
+        std::vector<MvParams> all;
+        for (auto& L : e->layers) { all.push_back(L.p_qkv); all.push_back(L.p_o); all.push_back(L.p_gu); all.push_back(L.p_down); }
+        int sms = e->n_ctas;
+        int G = c.n_head / c.n_head_kv;
+        int ns = sms / c.n_head_kv;
+        if (ns > 32) ns = 32;
+        while (ns > 1 && (G * ns > 512 || (ns - 1) * 16 >= c.n_ctx)) ns--;
+        if (ns < 1) ns = 1;
+        e->mega_splits = ns;
+        int prc = mega_plan(e->mega, all.data(), (int)all.size(), c.head_dim, c.n_head_kv, ns, sms);
+        if (prc != 0 || mv_ctas_per_sm_default() != 1) e->use_mega = false;    // shapes do not fit: per-kernel path
+        else {
+            e->mega.n_layer = c.n_layer; e->mega.err = kernel_error_word();
+            CK(cudaMalloc(&e->mega_bar, sizeof(unsigned int)));
+            CK(cudaMalloc(&e->mega_scratch, attn_scratch_floats(c.n_head, c.n_head_kv, c.head_dim, ns) * 4));
+            CK(cudaMalloc(&e->mega_counters, sizeof(unsigned) * c.n_head_kv));
+            CK(cudaMemset(e->mega_counters, 0, sizeof(unsigned) * c.n_head_kv));
+            e->mega.bar = e->mega_bar;
+            if (getenv("B2_MEGA_TS")) { CK(cudaMalloc(&e->mega_ts, sizeof(unsigned long long) * (5 * c.n_layer + 2 + 16 * c.n_layer))); e->mega.ts = e->mega_ts; }
+        }
+    }
     e->finalized = true;
     return B2_OK;
 }
@@ -352,6 +388,38 @@ extern "C" int b2_engine_device_bytes(b2_engine* e, int64_t* w, int64_t* kv) {
 struct KindTimer {
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev[8];
 };
+
+// per-slot phase tables of the persistent layer kernel: the engine's plans with this slot's buffers filled in
+static int ensure_mega_tables(b2_engine* e, Slot& s) {
+    if (!e->use_mega || s.mega_mv) return B2_OK;
+    const b2_config& c = e->cfg;
+    cudaStream_t st = e->stream;
+    int* pos = s.ints + 1;
+            std::vector<MvParams> mv; std::vector<AttnParams> at;
+            for (int l = 0; l < c.n_layer; l++) {
+                Layer& L = e->layers[l];
+                MvParams q = L.p_qkv; q.x = s.x; q.q_out = s.q; q.pos_ptr = pos; q.block_table = s.block_table;
+                MvParams o = L.p_o; o.x = s.att; o.y = s.x; o.resid = s.x;
+                MvParams g = L.p_gu; g.x = s.x; g.y = s.h;
+                MvParams d = L.p_down; d.x = s.h; d.y = s.x; d.resid = s.x;
+                mv.push_back(q); mv.push_back(o); mv.push_back(g); mv.push_back(d);
+                AttnParams a = {};
+                a.q = s.q; a.k_cache = q.k_cache; a.v_cache = q.v_cache; a.block_table = s.block_table; a.pos_ptr = pos;
+                a.out = s.att; a.scratch = e->mega_scratch; a.counters = e->mega_counters;
+                a.n_head = c.n_head; a.n_kv = c.n_head_kv; a.head_dim = c.head_dim; a.block_tokens = c.kv_block_tokens;
+                a.n_splits = e->mega_splits; a.scale = 1.0f / sqrtf((float)c.head_dim); a.err = kernel_error_word();
+                a.max_pages = e->max_blocks;
+                at.push_back(a);
+            }
+            cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+            cudaStreamIsCapturing(st, &cs);
+            if (cs != cudaStreamCaptureStatusNone) return fail(B2_ERR_STATE, "phase tables must be built outside stream capture");
+            CK(cudaMalloc(&s.mega_mv, sizeof(MvParams) * mv.size()));
+            CK(cudaMalloc(&s.mega_at, sizeof(AttnParams) * at.size()));
+            CK(cudaMemcpy(s.mega_mv, mv.data(), sizeof(MvParams) * mv.size(), cudaMemcpyHostToDevice));
+            CK(cudaMemcpy(s.mega_at, at.data(), sizeof(AttnParams) * at.size(), cudaMemcpyHostToDevice));
+            return B2_OK;
+}
 
 static int forward_launches(b2_engine* e, Slot& s, bool with_head, bool with_sample, bool pdl, KindTimer* kt) {
     const b2_config& c = e->cfg;
@@ -371,6 +439,13 @@ static int forward_launches(b2_engine* e, Slot& s, bool with_head, bool with_sam
     CK(embed_row_launch(e->tok_embd.type, e->tok_embd.ptr, c.n_embd, tok, s.x, st, pdl));
     tock(ye);
     e->launches++;
+    if (e->use_mega && !kt) {
+        { int rc0 = ensure_mega_tables(e, s); if (rc0) return rc0; }
+        MegaParams mp = e->mega;
+        mp.mv = s.mega_mv; mp.at = s.mega_at;
+        CK(mega_launch(mp, e->n_ctas, st, e->act2));
+        e->launches++;
+    } else
     for (int l = 0; l < c.n_layer; l++) {
         Layer& L = e->layers[l];
         MvParams q = L.p_qkv;
@@ -438,6 +513,7 @@ static int run_step(b2_engine* e, Slot& s, GraphKind k) {
     int* nn = k == GK_DECODE ? &s.n_decode_nodes : k == GK_PRE_STEP ? &s.n_pre_step_nodes : k == GK_PRE_LAST ? &s.n_pre_last_nodes : &s.n_fwd_nodes;
     if (!e->use_graph) return record_step(e, s, k, e->use_pdl);
     if (!*ge) {
+        { int rc0 = ensure_mega_tables(e, s); if (rc0) return rc0; }    // cudaMalloc: outside the capture
         for (int attempt = 0; attempt < 2 && !*ge; attempt++) {
             bool pdl = e->use_pdl && attempt == 0;
             int64_t before = e->launches;
@@ -596,6 +672,25 @@ extern "C" int b2_decode_n(b2_engine* e, int slot, int n, int32_t* out) {
     CK(cudaMemcpyAsync(e->pinned, s.ring + s.n_past + 1, sizeof(int) * n, cudaMemcpyDeviceToHost, e->stream));
     CK(cudaStreamSynchronize(e->stream));
     if ((rc = check_kernel_error())) return rc;
+    if (e->mega_ts && e->use_mega) {      // debugging aid: per-phase-kind time of the last token's layer kernel
+        int L = e->cfg.n_layer;
+        std::vector<unsigned long long> ts(5 * L + 2 + 16 * L);
+        cudaMemcpy(ts.data(), e->mega_ts, sizeof(unsigned long long) * ts.size(), cudaMemcpyDeviceToHost);
+        double kind[5] = {0, 0, 0, 0, 0};
+        for (int i = 0; i < 5 * L; i++) kind[i % 5] += (double)(ts[i + 1] - ts[i]) * 1e-3;
+        fprintf(stderr, "[b2 mega] us per token: qkv %.1f attention %.1f attn_out %.1f gate_up %.1f ffn_down %.1f total %.1f\n",
+                kind[0], kind[1], kind[2], kind[3], kind[4], (double)(ts[5 * L] - ts[0]) * 1e-3);
+        // CTA 0, thread 0 inside each mat-vec phase: [params+sync, input quantisation, tiles, grid barrier is the rest]
+        const char* nm[4] = {"qkv", "attn_out", "gate_up", "ffn_down"};
+        for (int k = 0; k < 4; k++) {
+            double a = 0, b = 0, cc = 0;
+            for (int l = 0; l < L; l++) {
+                const unsigned long long* t2 = &ts[5 * L + 2 + (l * 4 + k) * 4];
+                a += (double)(t2[1] - t2[0]); b += (double)(t2[2] - t2[1]); cc += (double)(t2[3] - t2[2]);
+            }
+            fprintf(stderr, "[b2 mega]   %-8s per layer (us): params %.2f  quantise %.2f  tiles %.2f\n", nm[k], a / L * 1e-3, b / L * 1e-3, cc / L * 1e-3);
+        }
+    }
     if (out) memcpy(out, e->pinned, sizeof(int) * n);
     s.n_past += n;
     s.n_sampled += n;

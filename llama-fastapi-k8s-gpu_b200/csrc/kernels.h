@@ -11,7 +11,7 @@ namespace b2 {
 enum MvMode { MV_STORE = 0, MV_RESID = 1, MV_QKV = 2, MV_GATEUP = 3 };
 constexpr int MV_MAX_STAGES = 40;
 constexpr int MV_MAX_PROD = 4;               // TMA producer warps per CTA (upper bound)
-constexpr int MV_SHARED_HDR = 1024;          // barriers + reduction scratch at the start of dynamic smem
+constexpr int MV_SHARED_HDR = 4096;          // barriers + reduction scratch at the start of dynamic smem
 constexpr int MV_ROWS = 4;                 // rows per group (one warp, one ring stage)
 
 struct MvSeg {
@@ -81,6 +81,23 @@ cudaError_t attn_decode_launch(const AttnParams& p, cudaStream_t stream, bool pd
 size_t attn_static_scratch_floats();
 cudaError_t attn_static_setup(int device);
 cudaError_t attn_decode_launch_static(AttnParams p, int device, cudaStream_t stream);
+
+// ---------------------------------------------------------------- persistent decode kernel (mega.cu)
+constexpr int MEGA_SMEM_MAX = 227 * 1024;
+struct MegaParams {
+    const MvParams* mv;      // device: 4 phases per layer (qkv, attn_out, gate_up, ffn_down)
+    const AttnParams* at;    // device: one per layer (global-scratch split merge)
+    int n_layer;
+    unsigned int* bar;       // grid-barrier counter (zeroed before every launch)
+    unsigned int* err;
+    int slot_bytes, stage_bytes, n_stages, ring_off, n_prod;   // one ring geometry for all phases
+    int attn_items;          // n_kv * n_splits CTAs take part in the attention phase
+    unsigned long long* ts;  // optional: CTA 0 records %globaltimer at every phase boundary (5 per layer + 1)
+};
+cudaError_t mega_init();
+int mega_plan(MegaParams& mp, const MvParams* host_mv, int n_phase, int head_dim, int n_kv, int n_splits, int n_sms);
+size_t mega_smem_bytes(const MegaParams& mp);
+cudaError_t mega_launch(const MegaParams& mp, int n_ctas, cudaStream_t stream, bool act2);
 
 // ---------------------------------------------------------------- small kernels (misc.cu)
 // One pinned, device-mapped word per process that kernel watchdogs write to; 0 = no error.

@@ -33,12 +33,9 @@ __global__ void __launch_bounds__((NCW + (NCW <= 8 ? 1 : MV_MAX_PROD)) * 32, NCW
     uint8_t* ring = smem_raw + p.ring_off;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     RingGeom geo; geo.slot_bytes = p.slot_bytes; geo.stage_bytes = p.stage_bytes; geo.n_stages = p.n_stages;
-    const CtaWork work = cta_work<NCW>(p, blockIdx.x, gridDim.x);
+    const CtaWork work = cta_work(p, blockIdx.x, gridDim.x);
 
-    if (threadIdx.x == 0) {
-        for (int s = 0; s < geo.n_stages; s++) { mbar_init(&sh.full[s], 1); mbar_init(&sh.empty[s], 1); }
-        fence_mbar_init();
-    }
+    if (threadIdx.x == 0) mv_ring_init<NCW>(sh, geo.n_stages);
     __syncthreads();
     griddep_launch();   // let the next kernel start prefetching its own weights
 

@@ -1,7 +1,16 @@
 // Device-side building blocks of the streaming mat-vec (see matvec.cu for the design notes):
 // a producer routine that TMA-copies one phase's tiles into the shared-memory ring and a consumer
 // routine that quantises the input vector and eats the tiles. matvec.cu wraps them in a one-phase
-// kernel; mega.cu chains many phases inside one persistent kernel (ring indices run on across phases).
+// kernel; mega.cu chains many phases inside one persistent kernel (ring entries run on across phases).
+//
+// Ring protocol. Ring entry g (a running number across phases) lives in stage g % S and is use
+// number u = g / S of that stage. It is issued by producer warp g % n_prod (S is a multiple of n_prod,
+// so a stage always has the same producer, which therefore sees that stage's `empty` phases in
+// order) and consumed by consumer warp g % NCW. Different uses of a stage are consumed by different
+// warps, and an mbarrier only exposes the parity of its phase, so a consumer that looked at `full`
+// before the previous use had even landed would read "complete" for the wrong phase. The producer
+// therefore publishes `issued[stage] = u + 1` after arming the barrier; a consumer waits for that
+// value first (by then use u-1 has been consumed, hence landed) and only then on the parity.
 #pragma once
 #include "kernels.h"
 #include "ptx.cuh"
@@ -15,12 +24,16 @@ namespace b2 {
 #endif
 constexpr int ROW_UNROLL = B2_ROW_UNROLL;  // rows of a group interleaved in the instruction stream
 constexpr int R = MV_ROWS;             // rows per group
-constexpr int TPB = 32 / R;            // tiles the producer warp issues per round
+constexpr int TPB = 32 / R;            // tiles a producer warp issues per round
+constexpr int MV_GSLOTS = 64;          // row groups whose partial sums can be in flight at once
 
 template <int NCW>
 struct __align__(16) MvShared {
     uint64_t full[MV_MAX_STAGES];
     uint64_t empty[MV_MAX_STAGES];
+    unsigned int issued[MV_MAX_STAGES];         // use number + 1 last armed on each stage
+    float gacc[MV_GSLOTS][2][R];                // per group: row sums (second matrix of gate/up in [1])
+    unsigned int gcnt[MV_GSLOTS];               // tiles of the group finished so far
     float red[NCW];
 };
 
@@ -30,12 +43,10 @@ struct CtaWork {
     int seg;            // segment (non gate/up modes)
     int r0, r1;         // row range [r0, r1)
     int ng;             // row groups
-    int tpg;            // tiles per group
-    int rounds, rem;    // full rounds of NCW groups, groups in the last partial round
+    int tpg;            // tiles per group (slices x matrices)
     int total;          // tiles for the whole CTA
 };
 
-template <int NCW>
 __device__ __forceinline__ CtaWork cta_work(const MvParams& p, int cta, int nctas) {
     CtaWork w;
     const bool gu = (p.mode == MV_GATEUP);
@@ -51,35 +62,20 @@ __device__ __forceinline__ CtaWork cta_work(const MvParams& p, int cta, int ncta
     long u0 = (long)units * i / nc, u1 = (long)units * (i + 1) / nc;
     w.r0 = (int)u0 * 2; w.r1 = (int)u1 * 2;
     w.ng = (w.r1 - w.r0 + R - 1) / R;
-    w.tpg = (p.whole_rows ? 1 : p.n_slices) * (gu ? 2 : 1);
-    w.rounds = w.ng / NCW; w.rem = w.ng % NCW;
+    w.tpg = p.n_slices * (gu ? 2 : 1);
     w.total = w.ng * w.tpg;
     return w;
 }
 
-struct TileId { int warp, gi, seg, slice; };
-
-// q-th tile in issue order -> owner warp, row group, matrix, K-slice
+// one-time set-up of the ring (thread 0 of the CTA, before the first phase)
 template <int NCW>
-__device__ __forceinline__ TileId tile_of(const MvParams& p, const CtaWork& w, int q) {
-    TileId t;
-    int full_tiles = w.rounds * w.tpg * NCW;
-    int lt;
-    if (q < full_tiles) { t.warp = q % NCW; lt = q / NCW; }
-    else { int qq = q - full_tiles; t.warp = qq % w.rem; lt = w.rounds * w.tpg + qq / w.rem; }
-    t.gi = t.warp + NCW * (lt / w.tpg);
-    int within = lt % w.tpg;
-    const int spt = p.whole_rows ? 1 : p.n_slices;      // ring tiles per (group, matrix)
-    t.seg = (p.mode == MV_GATEUP) ? within / spt : w.seg;
-    t.slice = within % spt;
-    return t;
-}
-// issue-order index of warp `warp`'s lt-th tile
-template <int NCW>
-__device__ __forceinline__ int q_of(const CtaWork& w, int warp, int lt) {
-    int full_lt = w.rounds * w.tpg;
-    if (lt < full_lt) return lt * NCW + warp;
-    return full_lt * NCW + (lt - full_lt) * w.rem + warp;
+__device__ __forceinline__ void mv_ring_init(MvShared<NCW>& sh, int n_stages) {
+    for (int s = 0; s < n_stages; s++) { mbar_init(&sh.full[s], 1); mbar_init(&sh.empty[s], 1); sh.issued[s] = 0; }
+    for (int i = 0; i < MV_GSLOTS; i++) {
+        sh.gcnt[i] = 0;
+        for (int m = 0; m < 2; m++) for (int r = 0; r < R; r++) sh.gacc[i][m][r] = 0.f;
+    }
+    fence_mbar_init();
 }
 
 // one lane finishes a row pair
@@ -165,220 +161,230 @@ __device__ __noinline__ Acc4 tile_dots_any(int type, const uint8_t* stage, int s
     return out;
 }
 
-// One consumer warp's whole job for a CTA whose (first) matrix has quant type T.
-template <int T, bool ACT2, int NCW>
-__device__ __forceinline__ void consume(const MvParams& p, const CtaWork& work, MvShared<NCW>& sh, const uint8_t* ring,
-                                        const RingGeom& geo, uint32_t qbase, const ActView& av0, const ActView& av1,
-                                        int warp, int lane) {
-    const uint32_t S = (uint32_t)geo.n_stages;
-    const int my_groups = work.rounds + (warp < work.rem ? 1 : 0);
-    const bool gateup = (p.mode == MV_GATEUP);
-    const int nmat = gateup ? 2 : 1;
-    const int sb = geo.slot_bytes;
-    int lt = 0;
-    for (int g = 0; g < my_groups; g++) {
-        const int gi = warp + NCW * g;
-        const int row0 = work.r0 + gi * R, nrows = min(R, work.r1 - row0);
-        float gate0 = 0.f, gate1 = 0.f;
-        for (int m = 0; m < nmat; m++) {
-            const int seg = gateup ? m : work.seg;
-            const MvSeg& sg = p.seg[seg];
-            const int type = sg.type;
-            const uint32_t row_bytes = (uint32_t)sg.row_bytes;
-            const uint32_t row_lo0 = (uint32_t)(uintptr_t)sg.w + (uint32_t)row0 * row_bytes;   // low address bits suffice
-            const uint32_t sbytes = (uint32_t)slice_bytes(type);
-            float acc[R];
-#pragma unroll
-            for (int r = 0; r < R; r++) acc[r] = 0.f;
-            if (p.whole_rows) {
-                // one ring tile = the R full rows of this group, fetched with a single bulk copy
-                const uint32_t q = qbase + (uint32_t)q_of<NCW>(work, warp, lt++);
-                const uint32_t st = q % S;
-                mbar_wait(&sh.full[st], (q / S) & 1, p.err, 0x10002u, q);
-                const uint8_t* stage = ring + (size_t)st * geo.stage_bytes + (row_lo0 & 15u);
-                for (int sl = 0; sl < p.n_slices; sl++) {
-                    if (sl * B2_SLICE + lane * 64 < p.K && !p.skip_compute) {
-                        if (type == T) tile_dots<T, ACT2>(stage + sl * sbytes, (int)row_bytes, 0u, row_bytes, nrows, sl, lane, av0, acc, true);
-                        else {
-                            Acc4 in;
-#pragma unroll
-                            for (int r = 0; r < R; r++) in.v[r] = acc[r];
-                            Acc4 out = tile_dots_any<ACT2>(type, stage + sl * sbytes, (int)row_bytes, 0u, row_bytes, nrows, sl, lane,
-                                                           act_layout_of(type) == act_layout_of(T) ? av0 : av1, in, true);
-#pragma unroll
-                            for (int r = 0; r < R; r++) acc[r] = out.v[r];
-                        }
-                    }
-                }
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&sh.empty[st]);
-            } else
-            for (int sl = 0; sl < p.n_slices; sl++, lt++) {
-                const uint32_t q = qbase + (uint32_t)q_of<NCW>(work, warp, lt);
-                const uint32_t st = q % S;
-                mbar_wait(&sh.full[st], (q / S) & 1, p.err, 0x10002u, q);
-                const uint8_t* stage = ring + (size_t)st * geo.stage_bytes;
-                if (sl * B2_SLICE + lane * 64 < p.K && !p.skip_compute) {
-                    const uint32_t row_lo = row_lo0 + (uint32_t)sl * sbytes;
-                    if (type == T) tile_dots<T, ACT2>(stage, sb, row_lo, row_bytes, nrows, sl, lane, av0, acc);
-                    else {
-                        Acc4 in;
-#pragma unroll
-                        for (int r = 0; r < R; r++) in.v[r] = acc[r];
-                        Acc4 out = tile_dots_any<ACT2>(type, stage, sb, row_lo, row_bytes, nrows, sl, lane,
-                                                       act_layout_of(type) == act_layout_of(T) ? av0 : av1, in);
-#pragma unroll
-                        for (int r = 0; r < R; r++) acc[r] = out.v[r];
-                    }
-                }
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&sh.empty[st]);      // stage can be refilled
-            }
-            // transposed butterfly over the 4 rows: lane 0 / 8 / 16 / 24 end with row 0 / 1 / 2 / 3
-            const bool hi16 = lane & 16, hi8 = lane & 8;
-            float s0 = hi16 ? acc[0] : acc[2], s1 = hi16 ? acc[1] : acc[3];
-            float k0 = hi16 ? acc[2] : acc[0], k1 = hi16 ? acc[3] : acc[1];
-            k0 += __shfl_xor_sync(0xffffffffu, s0, 16);
-            k1 += __shfl_xor_sync(0xffffffffu, s1, 16);
-            float snd = hi8 ? k0 : k1, kp = hi8 ? k1 : k0;
-            kp += __shfl_xor_sync(0xffffffffu, snd, 8);
-            kp += __shfl_xor_sync(0xffffffffu, kp, 4);
-            kp += __shfl_xor_sync(0xffffffffu, kp, 2);
-            kp += __shfl_xor_sync(0xffffffffu, kp, 1);
-            float odd = __shfl_down_sync(0xffffffffu, kp, 8);   // lane 0 <- row 1, lane 16 <- row 3
-            if ((lane & 15) == 0) {
-                int pr = lane >> 4;                             // pair 0 or 1 of the group
-                if (2 * pr < nrows) {
-                    int row = row0 + 2 * pr;
-                    if (gateup) {
-                        if (m == 0) { gate0 = kp; gate1 = odd; }
-                        else {
-                            float h0 = gate0 / (1.0f + __expf(-gate0)) * kp;
-                            float h1 = gate1 / (1.0f + __expf(-gate1)) * odd;
-                            *reinterpret_cast<float2*>(p.y + row) = make_float2(h0, h1);
-                        }
-                    } else {
-                        epilogue_pair(p, seg, row, kp, odd);
-                    }
-                }
-            }
-        }
-    }
-}
-
-// Producer side of one mat-vec phase: issue this CTA's tiles, TPB per round, tiles interleaved
-// between the n_prod producer warps. Tile q of the phase is ring entry qbase + q.
+// Producer side of one mat-vec phase. Tile q of the phase is ring entry qbase + q; tiles are laid
+// out group-major: q -> (group q / tpg, matrix, K-slice). A round is TPB tiles of this producer
+// (entries n_prod apart), R lanes per tile (one row-slice copy each).
 template <int NCW>
 __device__ __forceinline__ void mv_produce(const MvParams& p, const CtaWork& work, MvShared<NCW>& sh, uint8_t* ring,
                                            const RingGeom& geo, uint32_t qbase, int prod_idx, int n_prod, int lane) {
     const uint32_t S = (uint32_t)geo.n_stages;
-        const int lanes_per_tile = p.whole_rows ? 1 : R;
-        const int tsub = p.whole_rows ? lane : lane / R, rsub = p.whole_rows ? 0 : lane % R;
-        // Ring entry g = qbase + q is always handled by producer g % n_prod. With n_stages a multiple of
-        // n_prod every stage then has exactly one producer, which sees all of its barrier phases in
-        // program order (two producers sharing a stage could mistake an old phase of the same parity
-        // for the one they wait for).
-        const int first = (int)(((uint32_t)prod_idx + (uint32_t)n_prod - qbase % (uint32_t)n_prod) % (uint32_t)n_prod);
-        for (int qb = first; qb < work.total; qb += TPB * n_prod) {
-            int q = qb + tsub * n_prod;
-            bool have = q < work.total && tsub < TPB;
-            const uint8_t* src = nullptr; uint32_t bytes = 0, gq = 0; uint8_t* dst = nullptr; int st = 0;
-            if (have) {
-                TileId t = tile_of<NCW>(p, work, q);
-                const MvSeg& sg = p.seg[t.seg];
-                int row0 = work.r0 + t.gi * R, nrows = min(R, work.r1 - row0);
-                gq = qbase + (uint32_t)q;
-                st = (int)(gq % S);
-                if (p.whole_rows) {
-                    uintptr_t start = (uintptr_t)sg.w + (size_t)row0 * sg.row_bytes;
-                    uintptr_t a0 = start & ~(uintptr_t)15, a1 = (start + (size_t)nrows * sg.row_bytes + 15) & ~(uintptr_t)15;
-                    src = (const uint8_t*)a0; bytes = (uint32_t)(a1 - a0);
-                    dst = ring + (size_t)st * geo.stage_bytes;
-                } else if (rsub < nrows) {
-                    int sb = slice_bytes(sg.type);
-                    int len = min(sb, sg.row_bytes - t.slice * sb);        // last slice may be shorter
-                    uintptr_t start = (uintptr_t)sg.w + (size_t)(row0 + rsub) * sg.row_bytes + (size_t)t.slice * sb;
-                    uintptr_t a0 = start & ~(uintptr_t)15, a1 = (start + len + 15) & ~(uintptr_t)15;
-                    src = (const uint8_t*)a0; bytes = (uint32_t)(a1 - a0);
-                    dst = ring + (size_t)st * geo.stage_bytes + rsub * geo.slot_bytes;
-                }
-                if (rsub == 0) mbar_wait(&sh.empty[st], ((gq / S) & 1) ^ 1, p.err, 0x10001u, gq);
+    const int tsub = lane / R, rsub = lane % R;
+    const int first = (int)(((uint32_t)prod_idx + (uint32_t)n_prod - qbase % (uint32_t)n_prod) % (uint32_t)n_prod);
+    for (int qb = first; qb < work.total; qb += TPB * n_prod) {
+        const int q = qb + tsub * n_prod;
+        const bool have = q < work.total;
+        const uint8_t* src = nullptr; uint32_t bytes = 0, gq = 0; uint8_t* dst = nullptr; int st = 0;
+        if (have) {
+            const int gi = q / work.tpg, within = q % work.tpg;
+            const int seg = (p.mode == MV_GATEUP) ? within / p.n_slices : work.seg;
+            const int slice = within % p.n_slices;
+            const MvSeg& sg = p.seg[seg];
+            const int row0 = work.r0 + gi * R, nrows = min(R, work.r1 - row0);
+            gq = qbase + (uint32_t)q;
+            st = (int)(gq % S);
+            if (rsub < nrows) {
+                const int sb = slice_bytes(sg.type);
+                const int len = min(sb, sg.row_bytes - slice * sb);        // last slice may be shorter
+                const uintptr_t start = (uintptr_t)sg.w + (size_t)(row0 + rsub) * sg.row_bytes + (size_t)slice * sb;
+                const uintptr_t a0 = start & ~(uintptr_t)15, a1 = (start + len + 15) & ~(uintptr_t)15;
+                src = (const uint8_t*)a0; bytes = (uint32_t)(a1 - a0);
+                dst = ring + (size_t)st * geo.stage_bytes + rsub * geo.slot_bytes;
             }
-            __syncwarp();
-            // total bytes of the tile = sum over its lanes
-            uint32_t tot = bytes;
-            if (lanes_per_tile > 1) {
-#pragma unroll
-                for (int o = 1; o < R; o <<= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
-            }
-            if (have && rsub == 0) mbar_arrive_expect_tx(&sh.full[st], tot);
-            __syncwarp();
-            if (bytes) tma_load_1d(dst, src, bytes, &sh.full[st]);
+            if (rsub == 0) mbar_wait(&sh.empty[st], ((gq / S) & 1) ^ 1, p.err, 0x10001u, gq);
         }
+        __syncwarp();
+        uint32_t tot = bytes;                       // bytes of the tile = sum over its R lanes
+#pragma unroll
+        for (int o = 1; o < R; o <<= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
+        if (have && rsub == 0) {
+            mbar_arrive_expect_tx(&sh.full[st], tot);
+            *reinterpret_cast<volatile unsigned int*>(&sh.issued[st]) = gq / S + 1;
+        }
+        __syncwarp();
+        if (bytes) tma_load_1d(dst, src, bytes, &sh.full[st]);
+    }
 }
 
 // Consumer prologue of one phase: x (float32, global) -> optional RMSNorm weight -> two int8 planes +
-// per-32 scale + per-16 sums in shared memory. All NCW consumer warps take part (named barrier 1).
+// per-32 scale + per-16 sums in shared memory. Four threads share a 32-element block (8 values each,
+// max and sums combined with two shuffles). The RMS factor is a scalar, so it is NOT applied here: the
+// per-warp sums of squares go to sh.red[] and mv_rms_scale() turns them into the factor the epilogue
+// multiplies the finished row sums with. All NCW consumer warps take part (named barrier 1).
 template <int NCW>
 __device__ __forceinline__ void mv_quantize_input(const MvParams& p, MvShared<NCW>& sh, int cta_layout, uint8_t* act_a,
                                                   uint8_t* act_b, uint8_t* act_a2, uint8_t* act_b2, float* act_dx,
                                                   float* act_s16, int warp, int lane) {
-    {
-        const bool has_norm = p.norm_w != nullptr;
-        const int t = warp * 32 + lane;
-        float ssq = 0.f;
-        for (int blk = t; blk < p.K / 32; blk += NCW * 32) {
-            const float4* xp4 = reinterpret_cast<const float4*>(p.x + 32 * blk);
-            const float4* np4 = reinterpret_cast<const float4*>(p.norm_w + 32 * blk);
-            float v[32];
+    const bool has_norm = p.norm_w != nullptr;
+    const int t = warp * 32 + lane, sub = t & 3;
+    const float MAGIC = 12582912.0f;                  // 1.5 * 2^23: float add rounds to nearest integer
+    float ssq = 0.f;
+    for (int blk = t >> 2; blk < p.K / 32; blk += NCW * 8) {
+        const float4* xp4 = reinterpret_cast<const float4*>(p.x + 32 * blk + 8 * sub);
+        const float4* np4 = reinterpret_cast<const float4*>(p.norm_w + 32 * blk + 8 * sub);
+        float v[8];
 #pragma unroll
-            for (int i = 0; i < 8; i++) {
-                float4 f = __ldcg(xp4 + i);      // written by other SMs (previous kernel or previous phase)
-                ssq += f.x * f.x + f.y * f.y + f.z * f.z + f.w * f.w;
-                if (has_norm) { float4 w4 = __ldg(np4 + i); f.x *= w4.x; f.y *= w4.y; f.z *= w4.z; f.w *= w4.w; }
-                v[4 * i] = f.x; v[4 * i + 1] = f.y; v[4 * i + 2] = f.z; v[4 * i + 3] = f.w;
-            }
-            int qa[8], qb[8]; float lo, hi;
-            float amax = quantize32(v, qa, qb, lo, hi);
-            // two 16-byte units per block, permuted inside the slice for conflict-free lane reads
-            const int u0 = 2 * blk, sbase = (u0 >> 7) * B2_SLICE;
+        for (int i = 0; i < 2; i++) {
+            float4 f = __ldcg(xp4 + i);               // written by other SMs (previous kernel or previous phase)
+            ssq += f.x * f.x + f.y * f.y + f.z * f.z + f.w * f.w;
+            if (has_norm) { float4 w4 = __ldg(np4 + i); f.x *= w4.x; f.y *= w4.y; f.z *= w4.z; f.w *= w4.w; }
+            v[4 * i] = f.x; v[4 * i + 1] = f.y; v[4 * i + 2] = f.z; v[4 * i + 3] = f.w;
+        }
+        float amax = 0.f, s8 = 0.f;
 #pragma unroll
-            for (int h2 = 0; h2 < 2; h2++) {
-                const int4 wa = make_int4(qa[4 * h2], qa[4 * h2 + 1], qa[4 * h2 + 2], qa[4 * h2 + 3]);
-                const int4 wb = make_int4(qb[4 * h2], qb[4 * h2 + 1], qb[4 * h2 + 2], qb[4 * h2 + 3]);
-                const int pos = sbase + 16 * act_unit_pos(cta_layout, (u0 + h2) & 127);
-                *reinterpret_cast<int4*>(act_a + pos) = wa;
-                *reinterpret_cast<int4*>(act_b + pos) = wb;
-                if (p.act_dual) {
-                    const int pos2 = sbase + 16 * act_unit_pos(1 - cta_layout, (u0 + h2) & 127);
-                    *reinterpret_cast<int4*>(act_a2 + pos2) = wa;
-                    *reinterpret_cast<int4*>(act_b2 + pos2) = wb;
+        for (int i = 0; i < 8; i++) { amax = fmaxf(amax, fabsf(v[i])); s8 += v[i]; }
+        amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
+        amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
+        const float s16 = s8 + __shfl_xor_sync(0xffffffffu, s8, 1);      // sum of this 16-element half
+        const float id = amax > 0.f ? 127.0f / amax : 0.f, dxl = amax / 127.0f, id2 = id * B2_ACT_RES;
+        uint32_t aw[2] = {0u, 0u}, bw[2] = {0u, 0u};
+#pragma unroll
+        for (int i = 0; i < 8; i++) {                 // same arithmetic as quantize32 (quant_blocks.cuh)
+            float ra = v[i] * id + MAGIC;
+            float af = ra - MAGIC;
+            float r = v[i] - af * dxl;
+            float rb = r * id2 + MAGIC;
+            aw[i >> 2] |= (__float_as_uint(ra) & 0xffu) << (8 * (i & 3));
+            bw[i >> 2] |= (__float_as_uint(rb) & 0xffu) << (8 * (i & 3));
+        }
+        // 16-byte unit (2 per block) permuted inside the slice for conflict-free lane reads; 8 bytes per thread
+        const int u = 2 * blk + (sub >> 1), sbase = (u >> 7) * B2_SLICE, half = 8 * (sub & 1);
+        const int pos = sbase + 16 * act_unit_pos(cta_layout, u & 127) + half;
+        *reinterpret_cast<uint2*>(act_a + pos) = make_uint2(aw[0], aw[1]);
+        *reinterpret_cast<uint2*>(act_b + pos) = make_uint2(bw[0], bw[1]);
+        if (p.act_dual) {
+            const int pos2 = sbase + 16 * act_unit_pos(1 - cta_layout, u & 127) + half;
+            *reinterpret_cast<uint2*>(act_a2 + pos2) = make_uint2(aw[0], aw[1]);
+            *reinterpret_cast<uint2*>(act_b2 + pos2) = make_uint2(bw[0], bw[1]);
+        }
+        if (sub == 0) act_dx[blk] = dxl;
+        if ((sub & 1) == 0) act_s16[2 * blk + (sub >> 1)] = s16;
+    }
+    if (has_norm) {
+        ssq = warp_sum(ssq);
+        if (lane == 0) sh.red[warp] = ssq;
+    }
+    named_bar_sync(1, NCW * 32);
+}
+
+// rsqrt(mean(x^2) + eps) of the phase's input (1 when the phase has no fused RMSNorm); call after the prologue
+template <int NCW>
+__device__ __forceinline__ float mv_rms_scale(const MvParams& p, const MvShared<NCW>& sh) {
+    if (p.norm_w == nullptr) return 1.0f;
+    float tot = 0.f;
+#pragma unroll
+    for (int i = 0; i < NCW; i++) tot += sh.red[i];
+    return rsqrtf(tot / (float)p.K + p.eps);
+}
+
+// One consumer warp's share of a phase: every NCW-th ring entry. A tile is reduced over the lanes
+// straight away; groups that span several tiles (K > 2048, or gate/up) collect their row sums in
+// shared memory with atomics and the warp that brings in the last tile runs the epilogue.
+template <int T, bool ACT2, int NCW>
+__device__ __forceinline__ void consume(const MvParams& p, const CtaWork& work, MvShared<NCW>& sh, const uint8_t* ring,
+                                        const RingGeom& geo, uint32_t qbase, const ActView& av0, const ActView& av1,
+                                        float rs, int warp, int lane) {
+    const uint32_t S = (uint32_t)geo.n_stages;
+    const bool gateup = (p.mode == MV_GATEUP);
+    const int sb = geo.slot_bytes;
+    const int tpg = work.tpg;
+    const int first = (int)(((uint32_t)warp + (uint32_t)NCW - qbase % (uint32_t)NCW) % (uint32_t)NCW);
+    for (int q = first; q < work.total; q += NCW) {
+        const int gi = q / tpg, within = q % tpg;
+        const int m = gateup ? within / p.n_slices : 0;
+        const int seg = gateup ? m : work.seg;
+        const int sl = within % p.n_slices;
+        const MvSeg& sg = p.seg[seg];
+        const int type = sg.type;
+        const int row0 = work.r0 + gi * R, nrows = min(R, work.r1 - row0);
+        const uint32_t row_bytes = (uint32_t)sg.row_bytes;
+        const uint32_t row_lo = (uint32_t)(uintptr_t)sg.w + (uint32_t)row0 * row_bytes + (uint32_t)sl * (uint32_t)slice_bytes(type);
+        const uint32_t g = qbase + (uint32_t)q, st = g % S, use = g / S;
+        {   // the producer has armed this use of the stage (see the protocol note at the top)
+            uint32_t spins = 0;
+            while (*reinterpret_cast<volatile unsigned int*>(&sh.issued[st]) != use + 1) {
+                if (++spins > (1u << 26)) {
+                    volatile unsigned int* e = reinterpret_cast<volatile unsigned int*>(p.err);
+                    if (e && e[0] == 0) { e[1] = blockIdx.x; e[2] = threadIdx.x; e[3] = g; e[4] = use; e[0] = 0x10003u; }
+                    break;
                 }
             }
-            act_dx[blk] = amax / 127.0f;
-            act_s16[2 * blk] = lo; act_s16[2 * blk + 1] = hi;
         }
-        if (has_norm) {
-            // rsqrt(mean(x^2) + eps) scales dx and the group sums; the int8 planes do not change
-            ssq = warp_sum(ssq);
-            if (lane == 0) sh.red[warp] = ssq;
-            named_bar_sync(1, NCW * 32);
-            float tot = 0.f;
+        mbar_wait(&sh.full[st], use & 1, p.err, 0x10002u, g);
+        const uint8_t* stage = ring + (size_t)st * geo.stage_bytes;
+        float acc[R];
 #pragma unroll
-            for (int i = 0; i < NCW; i++) tot += sh.red[i];
-            float rs = rsqrtf(tot / (float)p.K + p.eps);
-            for (int blk = t; blk < p.K / 32; blk += NCW * 32) {
-                act_dx[blk] *= rs; act_s16[2 * blk] *= rs; act_s16[2 * blk + 1] *= rs;
+        for (int r = 0; r < R; r++) acc[r] = 0.f;
+        if (sl * B2_SLICE + lane * 64 < p.K && !p.skip_compute) {
+            if (type == T) tile_dots<T, ACT2>(stage, sb, row_lo, row_bytes, nrows, sl, lane, av0, acc);
+            else {
+                Acc4 in;
+#pragma unroll
+                for (int r = 0; r < R; r++) in.v[r] = 0.f;
+                Acc4 out = tile_dots_any<ACT2>(type, stage, sb, row_lo, row_bytes, nrows, sl, lane,
+                                               act_layout_of(type) == act_layout_of(T) ? av0 : av1, in);
+#pragma unroll
+                for (int r = 0; r < R; r++) acc[r] = out.v[r];
             }
         }
-        named_bar_sync(1, NCW * 32);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sh.empty[st]);      // stage can be refilled
+        // transposed butterfly over the 4 rows: lanes 0-7 / 8-15 / 16-23 / 24-31 end with row 0 / 1 / 2 / 3
+        const bool hi16 = lane & 16, hi8 = lane & 8;
+        float s0 = hi16 ? acc[0] : acc[2], s1 = hi16 ? acc[1] : acc[3];
+        float k0 = hi16 ? acc[2] : acc[0], k1 = hi16 ? acc[3] : acc[1];
+        k0 += __shfl_xor_sync(0xffffffffu, s0, 16);
+        k1 += __shfl_xor_sync(0xffffffffu, s1, 16);
+        float snd = hi8 ? k0 : k1, kp = hi8 ? k1 : k0;
+        kp += __shfl_xor_sync(0xffffffffu, snd, 8);
+        kp += __shfl_xor_sync(0xffffffffu, kp, 4);
+        kp += __shfl_xor_sync(0xffffffffu, kp, 2);
+        kp += __shfl_xor_sync(0xffffffffu, kp, 1);
+        float v0, v1, g0 = 0.f, g1 = 0.f;                   // lanes 0 / 16 finish pair 0 / 1 of the group
+        bool finish = true;
+        if (tpg > 1) {
+            const int slot = gi % MV_GSLOTS;
+            if ((lane & 7) == 0) atomicAdd(&sh.gacc[slot][m][lane >> 3], kp);
+            __syncwarp();
+            unsigned int old = 0;
+            if (lane == 0) { __threadfence_block(); old = atomicAdd(&sh.gcnt[slot], 1u); }
+            old = __shfl_sync(0xffffffffu, old, 0);
+            finish = (old == (unsigned)tpg - 1);            // this was the group's last tile
+            if (finish) {
+                __threadfence_block();
+                const int pr = lane >> 4;
+                volatile float* ga = &sh.gacc[slot][0][0];
+                v0 = ga[2 * pr]; v1 = ga[2 * pr + 1];
+                if (gateup) { g0 = v0; g1 = v1; v0 = ga[R + 2 * pr]; v1 = ga[R + 2 * pr + 1]; }
+                __syncwarp();
+                if (lane < 2 * R) ga[lane] = 0.f;           // both matrices' sums: ready for group gi + MV_GSLOTS
+                if (lane == 0) *reinterpret_cast<volatile unsigned int*>(&sh.gcnt[slot]) = 0u;
+            }
+        } else {
+            v0 = kp;
+            v1 = __shfl_down_sync(0xffffffffu, kp, 8);      // lane 0 <- row 1, lane 16 <- row 3
+        }
+        if (finish && (lane & 15) == 0) {
+            const int pr = lane >> 4;
+            if (2 * pr < nrows) {
+                const int row = row0 + 2 * pr;
+                v0 *= rs; v1 *= rs; g0 *= rs; g1 *= rs;         // fused RMSNorm factor (a scalar: applied to the sums)
+                if (gateup) {
+                    float h0 = g0 / (1.0f + __expf(-g0)) * v0;
+                    float h1 = g1 / (1.0f + __expf(-g1)) * v1;
+                    *reinterpret_cast<float2*>(p.y + row) = make_float2(h0, h1);
+                } else {
+                    epilogue_pair(p, seg, row, v0, v1);
+                }
+            }
+        }
     }
 }
 
 // Carve the activation planes out of shared memory and run one whole consumer phase.
 template <int NCW, bool ACT2>
 __device__ __forceinline__ void mv_consume_phase(const MvParams& p, const CtaWork& work, MvShared<NCW>& sh, uint8_t* act_base,
-                                                 const uint8_t* ring, const RingGeom& geo, uint32_t qbase, int warp, int lane) {
+                                                 const uint8_t* ring, const RingGeom& geo, uint32_t qbase, int warp, int lane,
+                                                 unsigned long long* stamp = nullptr) {
     const int Kp = p.n_slices * B2_SLICE;                 // planes padded to whole slices
     uint8_t* act_a = act_base;
     uint8_t* act_b = act_a + Kp;
@@ -390,15 +396,17 @@ __device__ __forceinline__ void mv_consume_phase(const MvParams& p, const CtaWor
     const int type0 = (p.mode == MV_GATEUP) ? p.seg[0].type : p.seg[work.seg].type;
     const int cta_layout = act_layout_of(type0);
     mv_quantize_input<NCW>(p, sh, cta_layout, act_a, act_b, act_a2, act_b2, act_dx, act_s16, warp, lane);
+    if (stamp) { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); *stamp = t; }   // prologue done
     ActView av0, av1;
     av0.a = act_a; av0.b = act_b; av0.dx = act_dx; av0.s16 = act_s16;
     av1.a = act_a2; av1.b = act_b2; av1.dx = act_dx; av1.s16 = act_s16;
+    const float rs = mv_rms_scale<NCW>(p, sh);
     switch (type0) {
-        case T_Q4_K: consume<T_Q4_K, ACT2, NCW>(p, work, sh, ring, geo, qbase, av0, av1, warp, lane); break;
-        case T_Q6_K: consume<T_Q6_K, ACT2, NCW>(p, work, sh, ring, geo, qbase, av0, av1, warp, lane); break;
-        case T_Q8_0: consume<T_Q8_0, ACT2, NCW>(p, work, sh, ring, geo, qbase, av0, av1, warp, lane); break;
-        case T_Q4_0: consume<T_Q4_0, ACT2, NCW>(p, work, sh, ring, geo, qbase, av0, av1, warp, lane); break;
-        case T_Q5_K: consume<T_Q5_K, ACT2, NCW>(p, work, sh, ring, geo, qbase, av0, av1, warp, lane); break;
+        case T_Q4_K: consume<T_Q4_K, ACT2, NCW>(p, work, sh, ring, geo, qbase, av0, av1, rs, warp, lane); break;
+        case T_Q6_K: consume<T_Q6_K, ACT2, NCW>(p, work, sh, ring, geo, qbase, av0, av1, rs, warp, lane); break;
+        case T_Q8_0: consume<T_Q8_0, ACT2, NCW>(p, work, sh, ring, geo, qbase, av0, av1, rs, warp, lane); break;
+        case T_Q4_0: consume<T_Q4_0, ACT2, NCW>(p, work, sh, ring, geo, qbase, av0, av1, rs, warp, lane); break;
+        case T_Q5_K: consume<T_Q5_K, ACT2, NCW>(p, work, sh, ring, geo, qbase, av0, av1, rs, warp, lane); break;
     }
 }
 

@@ -13,7 +13,7 @@ from ctypes import POINTER, c_char_p, c_double, c_float, c_int, c_int32, c_int64
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libb200gguf.so")
 
-B2_FLAG_NO_GRAPH, B2_FLAG_NO_PDL, B2_FLAG_ACT8 = 1, 2, 4
+B2_FLAG_NO_GRAPH, B2_FLAG_NO_PDL, B2_FLAG_ACT8, B2_FLAG_NO_MEGA = 1, 2, 4, 8
 
 
 class B2Config(ctypes.Structure):
