@@ -94,6 +94,11 @@ struct b2_engine {
     int mega_splits = 1;
     float* mega_scratch = nullptr;
     unsigned* mega_counters = nullptr;
+    // prompt (GEMM) workspace, allocated on the first long prompt: PF_T tokens per chunk
+    float *pf_x = nullptr, *pf_qkv = nullptr, *pf_gu = nullptr;
+    __half *pf_xn = nullptr, *pf_qh = nullptr, *pf_att = nullptr, *pf_h = nullptr;
+    bool gemm_ok = false;          // every layer matrix is a block format the GEMM reads
+    int prefill_min = 8;           // prompts chunks shorter than this go token by token through the mat-vec path
     unsigned long long* mega_ts = nullptr;   // B2_MEGA_TS=1: phase timestamps of the last layer-kernel launch
     std::mutex mu;
 };
@@ -372,6 +377,12 @@ extern "C" int b2_engine_finalize(b2_engine* e) {
             if (getenv("B2_MEGA_TS")) { CK(cudaMalloc(&e->mega_ts, sizeof(unsigned long long) * (5 * c.n_layer + 2 + 16 * c.n_layer))); e->mega.ts = e->mega_ts; }
         }
     }
+    e->gemm_ok = !getenv("B2_NO_GEMM_PREFILL");
+    for (auto& L : e->layers)
+        for (const DevTensor* t : {&L.wq, &L.wk, &L.wv, &L.wo, &L.wgate, &L.wup, &L.wdown})
+            if (block_elems(t->type) == 1) e->gemm_ok = false;
+    if (const char* s = getenv("B2_PREFILL_MIN")) if (atoi(s) > 0) e->prefill_min = atoi(s);
+    if (e->gemm_ok) CK(gemm_init());
     e->finalized = true;
     return B2_OK;
 }
@@ -594,6 +605,69 @@ extern "C" int b2_seq_begin(b2_engine* e, int slot, int n_past, const int32_t* h
     return B2_OK;
 }
 
+constexpr int PF_T = 512;    // tokens per GEMM chunk (TMEM columns of one CTA)
+
+static int ensure_prefill_workspace(b2_engine* e) {
+    if (e->pf_x) return B2_OK;
+    const b2_config& c = e->cfg;
+    const size_t qd = (size_t)c.n_head * c.head_dim, kvd = (size_t)c.n_head_kv * c.head_dim;
+    CK(cudaMalloc(&e->pf_x, PF_T * (size_t)c.n_embd * 4));
+    CK(cudaMalloc(&e->pf_qkv, PF_T * (qd + 2 * kvd) * 4));
+    CK(cudaMalloc(&e->pf_gu, PF_T * (size_t)c.n_ff * 2 * 4));
+    CK(cudaMalloc(&e->pf_xn, PF_T * (size_t)c.n_embd * 2));
+    CK(cudaMalloc(&e->pf_qh, PF_T * qd * 2));
+    CK(cudaMalloc(&e->pf_att, PF_T * qd * 2));
+    CK(cudaMalloc(&e->pf_h, PF_T * (size_t)c.n_ff * 2));
+    // rows [T, T_pad) of the f16 operands are read by the MMA (their columns are dropped): keep them finite
+    CK(cudaMemsetAsync(e->pf_xn, 0, PF_T * (size_t)c.n_embd * 2, e->stream));
+    CK(cudaMemsetAsync(e->pf_att, 0, PF_T * qd * 2, e->stream));
+    CK(cudaMemsetAsync(e->pf_h, 0, PF_T * (size_t)c.n_ff * 2, e->stream));
+    return B2_OK;
+}
+
+static int gemm_call(b2_engine* e, const DevTensor& w, const __half* x, int T, float* y, int ldy, bool accumulate) {
+    GemmParams p = {};
+    p.w = w.ptr; p.type = w.type; p.N = (int)w.ne1; p.K = (int)w.ne0;
+    p.row_bytes = (int)(w.ne0 / block_elems(w.type) * block_bytes(w.type));
+    p.x = x; p.T = T; p.T_pad = (T + 15) / 16 * 16; p.y = y; p.ldy = ldy; p.accumulate = accumulate ? 1 : 0;
+    p.err = kernel_error_word();
+    CK(gemm_launch(p, e->stream));
+    e->launches++;
+    return B2_OK;
+}
+
+// One chunk of T <= PF_T prompt tokens (device ids at `tokens`) at positions pos0.. through every layer:
+// tensor-core GEMMs over all T tokens at once, so each weight is read and dequantised once per chunk.
+static int prefill_chunk(b2_engine* e, Slot& s, const int* tokens, int T, int pos0) {
+    const b2_config& c = e->cfg;
+    cudaStream_t st = e->stream;
+    const int E = c.n_embd, F = c.n_ff, hd = c.head_dim;
+    const int qd = c.n_head * hd, kvd = c.n_head_kv * hd, qkvd = qd + 2 * kvd;
+    int rc;
+    CK(embed_rows_launch(e->tok_embd.type, e->tok_embd.ptr, E, tokens, T, e->pf_x, st));
+    e->launches++;
+    for (int l = 0; l < c.n_layer; l++) {
+        Layer& L = e->layers[l];
+        __half* kc = e->k_pool + (size_t)l * e->layer_kv_elems;
+        __half* vc = e->v_pool + (size_t)l * e->layer_kv_elems;
+        CK(rmsnorm_half_launch(e->pf_x, (const float*)L.attn_norm.ptr, c.rms_eps, E, T, e->pf_xn, st));
+        if ((rc = gemm_call(e, L.wq, e->pf_xn, T, e->pf_qkv, qkvd, false))) return rc;
+        if ((rc = gemm_call(e, L.wk, e->pf_xn, T, e->pf_qkv + qd, qkvd, false))) return rc;
+        if ((rc = gemm_call(e, L.wv, e->pf_xn, T, e->pf_qkv + qd + kvd, qkvd, false))) return rc;
+        CK(rope_store_launch(e->pf_qkv, T, pos0, c.n_head, c.n_head_kv, hd, c.kv_block_tokens, s.block_table, e->rope_freq,
+                             e->pf_qh, kc, vc, st));
+        CK(attn_prefill_launch(e->pf_qh, kc, vc, s.block_table, T, pos0, c.n_head, c.n_head_kv, hd, c.kv_block_tokens, e->pf_att, st));
+        if ((rc = gemm_call(e, L.wo, e->pf_att, T, e->pf_x, E, true))) return rc;
+        CK(rmsnorm_half_launch(e->pf_x, (const float*)L.ffn_norm.ptr, c.rms_eps, E, T, e->pf_xn, st));
+        if ((rc = gemm_call(e, L.wgate, e->pf_xn, T, e->pf_gu, 2 * F, false))) return rc;
+        if ((rc = gemm_call(e, L.wup, e->pf_xn, T, e->pf_gu + F, 2 * F, false))) return rc;
+        CK(silu_mul_half_launch(e->pf_gu, F, T, e->pf_h, st));
+        if ((rc = gemm_call(e, L.wdown, e->pf_h, T, e->pf_x, E, true))) return rc;
+        e->launches += 5;
+    }
+    return B2_OK;
+}
+
 extern "C" int b2_prefill(b2_engine* e, int slot, const int32_t* tokens, int n) {
     int rc = check_slot(e, slot); if (rc) return rc;
     std::lock_guard<std::mutex> lk(e->mu);
@@ -606,9 +680,26 @@ extern "C" int b2_prefill(b2_engine* e, int slot, const int32_t* tokens, int n) 
     int hdr[2] = {0, s.n_past};   // cursor, pos_base
     CK(cudaMemcpyAsync(s.prompt, tokens, sizeof(int) * n, cudaMemcpyHostToDevice, e->stream));
     CK(cudaMemcpyAsync(s.ints + 4, hdr, sizeof(hdr), cudaMemcpyHostToDevice, e->stream));
-    for (int i = 0; i < n; i++) {
-        rc = run_step(e, s, i == n - 1 ? GK_PRE_LAST : GK_PRE_STEP);
-        if (rc) return rc;
+    if (e->gemm_ok && n >= e->prefill_min) {
+        // tensor-core path: all layers for up to PF_T tokens at a time, then the output head for the last token only
+        if ((rc = ensure_prefill_workspace(e))) return rc;
+        for (int c0 = 0; c0 < n; c0 += PF_T) {
+            int T = n - c0 < PF_T ? n - c0 : PF_T;
+            if ((rc = prefill_chunk(e, s, s.prompt + c0, T, s.n_past + c0))) return rc;
+            if (c0 + T == n)
+                CK(cudaMemcpyAsync(s.x, e->pf_x + (size_t)(T - 1) * e->cfg.n_embd, sizeof(float) * e->cfg.n_embd,
+                                   cudaMemcpyDeviceToDevice, e->stream));
+        }
+        CK(prefill_finish_launch(s.prompt, n, s.n_past + n - 1, s.ints, s.sst, e->stream));
+        MvParams h = e->p_head;
+        h.x = s.x; h.y = s.logits;
+        CK(mv_launch(h, e->n_ctas, e->stream, e->act2, false));
+        e->launches += 2;
+    } else {
+        for (int i = 0; i < n; i++) {
+            rc = run_step(e, s, i == n - 1 ? GK_PRE_LAST : GK_PRE_STEP);
+            if (rc) return rc;
+        }
     }
     CK(cudaStreamSynchronize(e->stream));
     if ((rc = check_kernel_error())) return rc;
@@ -903,6 +994,36 @@ extern "C" int b2_op_gate_up(int device, int tg, const void* wg, int tu, const v
     p.nseg = 2; p.seg[0].type = tg; p.seg[0].n_rows = n_rows; p.seg[1].type = tu; p.seg[1].n_rows = n_rows;
     p.K = K; p.mode = MV_GATEUP; p.eps = eps;
     return op_matvec_common(device, p, wg, wu, n_rows, K, x, nw, nullptr, y, 2, n_ctas);
+}
+
+extern "C" int b2_op_gemm(int device, int type, const void* w, int n_rows, int K, const float* x, int T,
+                          const float* y_in, float* y, int flags) {
+    (void)flags;
+    if (!w || !x || !y || n_rows <= 0 || K <= 0 || T <= 0) return fail(B2_ERR_ARG, "bad arguments");
+    if (T > 512) return fail(B2_ERR_ARG, "at most 512 tokens per call");
+    int be = block_elems(type), bb = block_bytes(type);
+    if (be == 1 || !bb) return fail(B2_ERR_UNSUPPORTED, "weight type must be a quantised block format");
+    if (K % 256) return fail(B2_ERR_ARG, "K must be a multiple of 256");
+    CK(cudaSetDevice(device));
+    CK(gemm_init());
+    const int T_pad = (T + 15) / 16 * 16;
+    const size_t wbytes = (size_t)n_rows * (K / be) * bb;
+    DevBuf dw, dx, dxh, dy;
+    CK(dw.alloc(wbytes + 64)); CK(dx.alloc((size_t)T * K * 4)); CK(dxh.alloc((size_t)T_pad * K * 2)); CK(dy.alloc((size_t)T * n_rows * 4));
+    CK(cudaMemcpy(dw.p, w, wbytes, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(dx.p, x, (size_t)T * K * 4, cudaMemcpyHostToDevice));
+    CK(cudaMemset(dxh.p, 0, (size_t)T_pad * K * 2));
+    CK(to_half_launch(dx.as<float>(), dxh.as<__half>(), (long)T * K, 0));
+    if (y_in) CK(cudaMemcpy(dy.p, y_in, (size_t)T * n_rows * 4, cudaMemcpyHostToDevice));
+    GemmParams p = {};
+    p.w = dw.as<uint8_t>(); p.type = type; p.N = n_rows; p.K = K; p.row_bytes = K / be * bb;
+    p.x = dxh.as<__half>(); p.T = T; p.T_pad = T_pad; p.y = dy.as<float>(); p.ldy = n_rows;
+    p.accumulate = y_in ? 1 : 0; p.err = kernel_error_word();
+    CK(gemm_launch(p, 0));
+    CK(cudaDeviceSynchronize());
+    if (int rc = check_kernel_error()) return rc;
+    CK(cudaMemcpy(y, dy.p, (size_t)T * n_rows * 4, cudaMemcpyDeviceToHost));
+    return B2_OK;
 }
 
 extern "C" int b2_op_rmsnorm(int device, const float* x, const float* w, float eps, int K, int rows, float* y) {

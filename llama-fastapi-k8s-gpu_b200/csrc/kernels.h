@@ -99,6 +99,33 @@ int mega_plan(MegaParams& mp, const MvParams* host_mv, int n_phase, int head_dim
 size_t mega_smem_bytes(const MegaParams& mp);
 cudaError_t mega_launch(const MegaParams& mp, int n_ctas, cudaStream_t stream, bool act2);
 
+// ---------------------------------------------------------------- tensor-core GEMM (gemm.cu)
+struct GemmParams {
+    const uint8_t* w;       // quantised rows [N][K], unchanged GGUF bytes
+    int type, N, K, row_bytes;
+    const __half* x;        // activations [T_pad][K] f16 (rows >= T may hold anything finite or not: their columns are dropped)
+    int T, T_pad;           // T_pad: multiple of 16, <= 512
+    float* y;               // [T][ldy] float32, element (t, n) at y[t * ldy + n]
+    int ldy;
+    int accumulate;         // 1: y += result (residual add)
+    unsigned int* err;
+};
+cudaError_t gemm_init();
+size_t gemm_smem_bytes(int T_pad);
+cudaError_t gemm_launch(const GemmParams& p, cudaStream_t stream);
+cudaError_t to_half_launch(const float* x, __half* y, long n, cudaStream_t s);
+
+// ---------------------------------------------------------------- prompt kernels (prefill.cu)
+struct SamplerState;
+cudaError_t embed_rows_launch(int type, const uint8_t* table, int K, const int* tokens, int T, float* x, cudaStream_t s);
+cudaError_t rmsnorm_half_launch(const float* x, const float* w, float eps, int K, int T, __half* y, cudaStream_t s);
+cudaError_t rope_store_launch(const float* qkv, int T, int pos0, int n_head, int n_kv, int hd, int bt, const int* block_table,
+                              const float* rope_freq, __half* qh, __half* k_cache, __half* v_cache, cudaStream_t s);
+cudaError_t attn_prefill_launch(const __half* qh, const __half* k_cache, const __half* v_cache, const int* block_table,
+                                int T, int pos0, int n_head, int n_kv, int hd, int bt, __half* out, cudaStream_t s);
+cudaError_t silu_mul_half_launch(const float* gu, int F, int T, __half* h, cudaStream_t s);
+cudaError_t prefill_finish_launch(const int* prompt, int n, int pos_last, int* ints, SamplerState* st, cudaStream_t s);
+
 // ---------------------------------------------------------------- small kernels (misc.cu)
 // One pinned, device-mapped word per process that kernel watchdogs write to; 0 = no error.
 unsigned int* kernel_error_word();

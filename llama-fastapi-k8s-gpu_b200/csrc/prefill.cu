@@ -1,0 +1,272 @@
+// Prompt-processing (prefill) kernels around the tensor-core GEMM (gemm.cu): T tokens of one sequence at once.
+// Replaces the batch > 1 side of ggml-cuda that llama.cpp runs for the prompt under create_chat_completion
+// (/root/reference/api.py:55-63): get_rows (K1), rms_norm_f32 (K2), rope_f32 + the KV-cache copy (K6/K7),
+// the attention mat-muls + soft_max (K8-K10 at batch T), silu/mul (K11).
+//
+//   embed_rows      x[t][:]      = dequantised row tokens[t] of the embedding table          (f32)
+//   rmsnorm_half    xn[t][:]     = f16( x[t] / sqrt(mean(x[t]^2) + eps) * w )
+//   rope_store      q f32 -> rotated f16 [T][n_head*hd]; k rotated, v -> paged f16 KV cache
+//   attn_prefill    causal flash attention over the paged cache, mma.sync m16n8k16 (f16 in, f32 accumulate),
+//                   one warp per 16 queries of one head, the G heads of a KV group share the K/V tiles
+//   silu_mul_half   h[t][:]      = f16( silu(gate) * up )
+//   prefill_finish  pushes the prompt tokens into the penalty history and leaves token / position of the
+//                   last prompt token in the slot registers
+#include "kernels.h"
+#include "ptx.cuh"
+#include "quant_blocks.cuh"
+#include <cuda_fp16.h>
+
+namespace b2 {
+
+// ---------------------------------------------------------------- embedding rows
+__global__ void embed_rows_kernel(int type, const uint8_t* table, int K, const int* tokens, float* x) {
+    const int t = blockIdx.x;
+    const int be = block_elems(type), bb = block_bytes(type);
+    const uint8_t* row = table + (size_t)tokens[t] * (K / be) * bb;
+    for (int i = threadIdx.x; i < K; i += blockDim.x)
+        x[(size_t)t * K + i] = dequant_elem(type, row + (size_t)(i / be) * bb, i % be);
+}
+cudaError_t embed_rows_launch(int type, const uint8_t* table, int K, const int* tokens, int T, float* x, cudaStream_t s) {
+    embed_rows_kernel<<<T, 256, 0, s>>>(type, table, K, tokens, x);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------- RMSNorm -> f16
+__global__ void __launch_bounds__(256) rmsnorm_half_kernel(const float* x, const float* w, float eps, int K, __half* y) {
+    __shared__ float red[8];
+    const int t = blockIdx.x;
+    const float* xr = x + (size_t)t * K;
+    float ss = 0.f;
+    for (int i = threadIdx.x; i < K; i += 256) { float v = xr[i]; ss += v * v; }
+    ss = warp_sum(ss);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+    __syncthreads();
+    float tot = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; i++) tot += red[i];
+    const float r = rsqrtf(tot / (float)K + eps);
+    for (int i = threadIdx.x; i < K; i += 256) y[(size_t)t * K + i] = __float2half_rn(xr[i] * r * w[i]);
+}
+cudaError_t rmsnorm_half_launch(const float* x, const float* w, float eps, int K, int T, __half* y, cudaStream_t s) {
+    rmsnorm_half_kernel<<<T, 256, 0, s>>>(x, w, eps, K, y);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------- RoPE + KV store
+// qkv [T][n_head*hd | n_kv*hd | n_kv*hd] f32. Pair (2i, 2i+1) rotated by pos * freq[i] (ggml "norm" RoPE).
+__global__ void rope_store_kernel(const float* qkv, int T, int pos0, int n_head, int n_kv, int hd, int bt,
+                                  const int* block_table, const float* rope_freq, __half* qh, __half* k_cache, __half* v_cache) {
+    const int t = blockIdx.x, pos = pos0 + t;
+    const int nq = n_head * hd, nk = n_kv * hd, row_len = nq + 2 * nk;
+    const float* r = qkv + (size_t)t * row_len;
+    const int page = block_table[pos / bt], slot = pos % bt;
+    for (int pi = threadIdx.x; pi < row_len / 2; pi += blockDim.x) {
+        const int e = 2 * pi;
+        float v0 = r[e], v1 = r[e + 1];
+        if (e < nq + nk) {
+            const int i = (e % hd) >> 1;
+            float s, c;
+            sincosf((float)pos * rope_freq[i], &s, &c);
+            const float a = v0 * c - v1 * s, b = v0 * s + v1 * c;
+            v0 = a; v1 = b;
+        }
+        const __half2 h = __floats2half2_rn(v0, v1);
+        if (e < nq) {
+            *reinterpret_cast<__half2*>(qh + (size_t)t * nq + e) = h;
+        } else {
+            const int ee = e < nq + nk ? e - nq : e - nq - nk;
+            const int kvh = ee / hd, d = ee % hd;
+            const size_t idx = (((size_t)page * n_kv + kvh) * bt + slot) * hd + d;
+            *reinterpret_cast<__half2*>((e < nq + nk ? k_cache : v_cache) + idx) = h;
+        }
+    }
+}
+cudaError_t rope_store_launch(const float* qkv, int T, int pos0, int n_head, int n_kv, int hd, int bt, const int* block_table,
+                              const float* rope_freq, __half* qh, __half* k_cache, __half* v_cache, cudaStream_t s) {
+    rope_store_kernel<<<T, 256, 0, s>>>(qkv, T, pos0, n_head, n_kv, hd, bt, block_table, rope_freq, qh, k_cache, v_cache);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------- SiLU(gate) * up -> f16
+__global__ void silu_mul_half_kernel(const float* gu, int F, long n, __half* h) {
+    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const long t = i / F, f = i % F;
+    const float g = gu[t * 2 * F + f], u = gu[t * 2 * F + F + f];
+    h[i] = __float2half_rn(g / (1.f + __expf(-g)) * u);
+}
+cudaError_t silu_mul_half_launch(const float* gu, int F, int T, __half* h, cudaStream_t s) {
+    const long n = (long)T * F;
+    silu_mul_half_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(gu, F, n, h);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------- slot registers after a prompt chunk
+__global__ void prefill_finish_kernel(const int* prompt, int n, int pos_last, int* ints, SamplerState* st) {
+    int nh = st->n_hist;
+    for (int i = 0; i < n; i++) { st->history[nh & (HISTORY_LEN - 1)] = prompt[i]; nh++; }
+    st->n_hist = nh;
+    ints[0] = prompt[n - 1];
+    ints[1] = pos_last;
+}
+cudaError_t prefill_finish_launch(const int* prompt, int n, int pos_last, int* ints, SamplerState* st, cudaStream_t s) {
+    prefill_finish_kernel<<<1, 1, 0, s>>>(prompt, n, pos_last, ints, st);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------- causal attention for T queries
+__device__ __forceinline__ void mma16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void ldmatrix_x2_trans(uint32_t& r0, uint32_t& r1, const void* p) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x2.trans.shared.b16 {%0,%1}, [%2];" : "=r"(r0), "=r"(r1) : "r"(smem_u32(p)));
+}
+__device__ __forceinline__ uint32_t pack_half2(float a, float b) {
+    __half2 h = __floats2half2_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&h);
+}
+
+constexpr int PA_KT = 64;        // keys per tile
+
+// grid (query tiles, n_kv); block = G * QW warps: warp w -> head kvh*G + w % G, queries 16 * (w / G) .. +15 of the tile
+template <int HD>
+__global__ void __launch_bounds__(256) attn_prefill_kernel(const __half* qh, const __half* k_cache, const __half* v_cache,
+                                                           const int* block_table, int T, int pos0, int n_head, int n_kv,
+                                                           int bt, int QW, float scale_log2, __half* out) {
+    constexpr int LD = HD + 8;                                  // padded row: conflict-free fragment loads
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    __half* ks = reinterpret_cast<__half*>(smem_raw);           // [PA_KT][LD]
+    __half* vs = ks + PA_KT * LD;
+    const int G = n_head / n_kv;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, tq = lane & 3;
+    const int kvh = blockIdx.y, head = kvh * G + warp % G;
+    const int q0 = blockIdx.x * 16 * QW + 16 * (warp / G);      // first query (chunk-relative) of this warp
+    const int nq = n_head * HD;
+    const bool active = q0 < T;
+
+    // Q fragments: rows q0+g and q0+g+8 (clamped; rows >= T are dropped at the end)
+    uint32_t qa[HD / 16][4];
+    {
+        const int r0 = min(q0 + g, T - 1), r1 = min(q0 + g + 8, T - 1);
+        const __half* p0 = qh + (size_t)r0 * nq + head * HD, * p1 = qh + (size_t)r1 * nq + head * HD;
+#pragma unroll
+        for (int kk = 0; kk < HD / 16; kk++) {
+            qa[kk][0] = *reinterpret_cast<const uint32_t*>(p0 + kk * 16 + 2 * tq);
+            qa[kk][1] = *reinterpret_cast<const uint32_t*>(p1 + kk * 16 + 2 * tq);
+            qa[kk][2] = *reinterpret_cast<const uint32_t*>(p0 + kk * 16 + 8 + 2 * tq);
+            qa[kk][3] = *reinterpret_cast<const uint32_t*>(p1 + kk * 16 + 8 + 2 * tq);
+        }
+    }
+    float o[HD / 8][4];
+#pragma unroll
+    for (int i = 0; i < HD / 8; i++) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
+    float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;   // running max / sum of rows g, g+8 (log2 domain)
+
+    // keys needed by the CTA: positions 0 .. pos0 + (last query of the tile)
+    const int last_q = min(blockIdx.x * 16 * QW + 16 * QW - 1, T - 1);
+    const int n_keys = pos0 + last_q + 1;
+    const int my_last = pos0 + min(q0 + 15, T - 1);             // last key this warp needs
+    for (int k0 = 0; k0 < n_keys; k0 += PA_KT) {
+        __syncthreads();                                        // previous tile fully consumed
+        for (int i = threadIdx.x; i < PA_KT * (HD / 8); i += blockDim.x) {
+            const int j = i / (HD / 8), ch = i % (HD / 8);
+            const int pos = k0 + j;
+            uint4 kv4 = make_uint4(0, 0, 0, 0), vv4 = kv4;
+            if (pos < n_keys) {
+                const size_t base = (((size_t)block_table[pos / bt] * n_kv + kvh) * bt + pos % bt) * HD + ch * 8;
+                kv4 = *reinterpret_cast<const uint4*>(k_cache + base);
+                vv4 = *reinterpret_cast<const uint4*>(v_cache + base);
+            }
+            *reinterpret_cast<uint4*>(ks + j * LD + ch * 8) = kv4;
+            *reinterpret_cast<uint4*>(vs + j * LD + ch * 8) = vv4;
+        }
+        __syncthreads();
+        if (!active || k0 > my_last) continue;
+        // ---- S = Q K^T for 64 keys: 8 n-tiles of 8 keys
+        float sc[PA_KT / 8][4];
+#pragma unroll
+        for (int nt = 0; nt < PA_KT / 8; nt++) {
+            sc[nt][0] = sc[nt][1] = sc[nt][2] = sc[nt][3] = 0.f;
+            const __half* kr = ks + (nt * 8 + g) * LD + 2 * tq;
+#pragma unroll
+            for (int kk = 0; kk < HD / 16; kk++) {
+                const uint32_t b0 = *reinterpret_cast<const uint32_t*>(kr + kk * 16);
+                const uint32_t b1 = *reinterpret_cast<const uint32_t*>(kr + kk * 16 + 8);
+                mma16816(sc[nt], qa[kk], b0, b1);
+            }
+        }
+        // ---- causal mask + online softmax (rows g and g+8; columns 2tq, 2tq+1 of every n-tile)
+        const int p_row0 = pos0 + q0 + g, p_row1 = p_row0 + 8;
+        float mx0 = m0, mx1 = m1;
+#pragma unroll
+        for (int nt = 0; nt < PA_KT / 8; nt++) {
+            const int kp = k0 + nt * 8 + 2 * tq;
+            sc[nt][0] = kp <= p_row0 ? sc[nt][0] * scale_log2 : -INFINITY;
+            sc[nt][1] = kp + 1 <= p_row0 ? sc[nt][1] * scale_log2 : -INFINITY;
+            sc[nt][2] = kp <= p_row1 ? sc[nt][2] * scale_log2 : -INFINITY;
+            sc[nt][3] = kp + 1 <= p_row1 ? sc[nt][3] * scale_log2 : -INFINITY;
+            mx0 = fmaxf(mx0, fmaxf(sc[nt][0], sc[nt][1]));
+            mx1 = fmaxf(mx1, fmaxf(sc[nt][2], sc[nt][3]));
+        }
+        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1)); mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1)); mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+        // key 0 is visible to every query, so after the first tile the maxima are finite
+        const float f0 = exp2f(m0 - mx0), f1 = exp2f(m1 - mx1);
+        m0 = mx0; m1 = mx1;
+        float s0 = 0.f, s1 = 0.f;
+        uint32_t pa[PA_KT / 16][4];
+#pragma unroll
+        for (int nt = 0; nt < PA_KT / 8; nt++) {
+            const float e0 = exp2f(sc[nt][0] - mx0), e1 = exp2f(sc[nt][1] - mx0);
+            const float e2 = exp2f(sc[nt][2] - mx1), e3 = exp2f(sc[nt][3] - mx1);
+            s0 += e0 + e1; s1 += e2 + e3;
+            pa[nt >> 1][(nt & 1) * 2 + 0] = pack_half2(e0, e1);
+            pa[nt >> 1][(nt & 1) * 2 + 1] = pack_half2(e2, e3);
+        }
+        l0 = l0 * f0 + s0; l1 = l1 * f1 + s1;
+#pragma unroll
+        for (int i = 0; i < HD / 8; i++) { o[i][0] *= f0; o[i][1] *= f0; o[i][2] *= f1; o[i][3] *= f1; }
+        // ---- O += P V : k = keys (4 k-tiles of 16), n = head dims (HD / 8 n-tiles)
+#pragma unroll
+        for (int kt = 0; kt < PA_KT / 16; kt++) {
+#pragma unroll
+            for (int nt = 0; nt < HD / 8; nt++) {
+                uint32_t b0, b1;
+                // 16 keys x 8 dims, transposed on load: lanes 0-15 give the row addresses
+                ldmatrix_x2_trans(b0, b1, vs + (kt * 16 + (lane & 15)) * LD + nt * 8);
+                mma16816(o[nt], pa[kt], b0, b1);
+            }
+        }
+    }
+    if (!active) return;
+    l0 += __shfl_xor_sync(0xffffffffu, l0, 1); l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+    l1 += __shfl_xor_sync(0xffffffffu, l1, 1); l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+    const float i0 = 1.f / l0, i1 = 1.f / l1;
+    const int r0 = q0 + g, r1 = q0 + g + 8;
+#pragma unroll
+    for (int nt = 0; nt < HD / 8; nt++) {
+        const int d = nt * 8 + 2 * tq;
+        if (r0 < T) *reinterpret_cast<uint32_t*>(out + (size_t)r0 * nq + head * HD + d) = pack_half2(o[nt][0] * i0, o[nt][1] * i0);
+        if (r1 < T) *reinterpret_cast<uint32_t*>(out + (size_t)r1 * nq + head * HD + d) = pack_half2(o[nt][2] * i1, o[nt][3] * i1);
+    }
+}
+
+cudaError_t attn_prefill_launch(const __half* qh, const __half* k_cache, const __half* v_cache, const int* block_table,
+                                int T, int pos0, int n_head, int n_kv, int hd, int bt, __half* out, cudaStream_t s) {
+    if (n_kv <= 0 || n_head % n_kv) return cudaErrorInvalidValue;
+    const int G = n_head / n_kv;
+    if (G > 8) return cudaErrorInvalidValue;
+    const int QW = G >= 4 ? 1 : 4 / G;
+    const int q_tile = 16 * QW;
+    dim3 grid((T + q_tile - 1) / q_tile, n_kv), block(32 * G * QW);
+    const float scale_log2 = 1.4426950408889634f / sqrtf((float)hd);
+    const size_t smem = (size_t)2 * PA_KT * (hd + 8) * 2;
+    if (hd == 64) attn_prefill_kernel<64><<<grid, block, smem, s>>>(qh, k_cache, v_cache, block_table, T, pos0, n_head, n_kv, bt, QW, scale_log2, out);
+    else if (hd == 128) attn_prefill_kernel<128><<<grid, block, smem, s>>>(qh, k_cache, v_cache, block_table, T, pos0, n_head, n_kv, bt, QW, scale_log2, out);
+    else return cudaErrorInvalidValue;
+    return cudaGetLastError();
+}
+
+}  // namespace b2

@@ -57,6 +57,7 @@ SIGNATURES = {
     "b2_op_dequantize": (c_int, [c_int, c_int, c_void_p, c_int64, c_void_p]),
     "b2_op_matvec": (c_int, [c_int, c_int, c_void_p, c_int, c_int, c_void_p, c_void_p, c_float, c_void_p, c_void_p, c_int, c_int]),
     "b2_op_gate_up": (c_int, [c_int, c_int, c_void_p, c_int, c_void_p, c_int, c_int, c_void_p, c_void_p, c_float, c_void_p, c_int]),
+    "b2_op_gemm": (c_int, [c_int, c_int, c_void_p, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p, c_int]),
     "b2_op_rmsnorm": (c_int, [c_int, c_void_p, c_void_p, c_float, c_int, c_int, c_void_p]),
     "b2_op_attention_decode": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_int, c_int, c_void_p]),
     "b2_attention_decode_static": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_int,

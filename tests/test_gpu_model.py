@@ -188,3 +188,56 @@ def test_persistent_layer_kernel_matches_per_kernel_path(native_lib, tmp_models,
         eng.close()
     assert outs[0][0] == outs[1][0]
     assert np.abs(outs[0][1] - outs[1][1]).max() < LOGIT_TOL
+
+
+@pytest.mark.parametrize("arch,ftype,seed", MODELS)
+def test_tensor_core_prefill_matches_oracle(native_lib, tmp_models, arch, ftype, seed):
+    """Prompt chunks of >= 8 tokens go through the tcgen05 GEMM path (f16 activations, f32 accumulate): logits
+    of the last prompt token against the oracle, for one whole-prompt call, for a prompt split into two calls
+    (the second chunk attends to the first through the paged cache) and for decode continuing after it."""
+    from oracle.llama_ref import RefModel
+    path = _model(tmp_models, arch, ftype, seed)
+    ref = RefModel(path).forward(TOKENS)
+    n = len(TOKENS)
+    for split in (None, 11):
+        eng = _engine(path)
+        eng.ensure_pages(0, n)
+        eng.seq_begin(0, 0, [], _greedy())
+        k = n - 4
+        if split is None:
+            eng.prefill(0, TOKENS[:k])
+        else:
+            eng.prefill(0, TOKENS[:split])
+            assert np.abs(eng.logits(0) - ref[split - 1]).max() <= LOGIT_TOL
+            eng.prefill(0, TOKENS[split:k])
+        worst = np.abs(eng.logits(0) - ref[k - 1]).max()
+        for i in range(k, n):                     # teacher-forced decode on top of the GEMM-written KV cache
+            eng.set_token(0, TOKENS[i])
+            eng.forward_pending(0)
+            worst = max(worst, np.abs(eng.logits(0) - ref[i]).max())
+        assert worst <= LOGIT_TOL, (arch, ftype, split, worst)
+        eng.close()
+
+
+def test_tensor_core_prefill_agrees_with_token_by_token(native_lib, tmp_models, monkeypatch):
+    """Same prompt through the GEMM path and through the mat-vec path (B2_PREFILL_MIN above the prompt
+    length): same greedy continuation, logits within the tolerance; a 700-token prompt spans two 512-token chunks."""
+    path = _model(tmp_models, "tiny128", "Q4_K_M", 9)
+    rng = np.random.default_rng(5)
+    prompt = [int(t) for t in rng.integers(3, 700, size=700)]
+    outs = []
+    for by_token in (False, True):
+        if by_token:
+            monkeypatch.setenv("B2_PREFILL_MIN", "100000")
+        else:
+            monkeypatch.delenv("B2_PREFILL_MIN", raising=False)
+        eng = _engine(path, n_ctx=1024, bt=64)
+        eng.ensure_pages(0, 800)
+        eng.seq_begin(0, 0, [], _greedy())
+        eng.prefill(0, prompt)
+        lg = eng.logits(0).copy()
+        toks = [eng.sample(0)] + [eng.decode([0])[0] for _ in range(8)]
+        outs.append((toks, lg))
+        eng.close()
+    assert np.abs(outs[0][1] - outs[1][1]).max() <= LOGIT_TOL
+    assert outs[0][0] == outs[1][0]

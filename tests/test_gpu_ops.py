@@ -246,3 +246,47 @@ def test_sampler_rejects_unsupported_top_k(native_lib):
     sp = B2Sampling(1.0, 1.0, 0.0, 1.0, 0.0, 0.0, 5000, 64)
     tok = ctypes.c_int32()
     assert native_lib.b2_op_sample(0, ptr(logits), 100, ctypes.byref(sp), None, 0, ctypes.c_double(0.5), ctypes.byref(tok)) != 0
+
+
+# ---------------------------------------------------------------------------------------------------
+# tensor-core GEMM (prefill / batched decode): y[t][n] = sum_k f16(x[t][k]) * W[n][k]
+def _gemm_case(native_lib, tname, K, N, T, accumulate=False, flags=0):
+    from llama_cpp.synth import random_blocks
+    from oracle import ggml_blocks as gb
+    t = TYPE_IDS[tname]
+    be = gb.BLOCK[t][0]
+    rng = np.random.default_rng(K * 7 + N * 3 + T)
+    w = random_blocks(tname, N * K // be, 0.02, seed=K * 13 + N + T).reshape(-1)
+    x = (rng.standard_normal((T, K)) * rng.uniform(0.2, 2.0, size=K)).astype(np.float32)
+    y_in = rng.standard_normal((T, N)).astype(np.float32) if accumulate else None
+    y = np.zeros((T, N), np.float32)
+    rc = native_lib.b2_op_gemm(0, t, ptr(w), N, K, ptr(x), T, ptr(y_in) if accumulate else None, ptr(y), flags)
+    lib_check(native_lib, rc)
+    W = gb.dequantize(w, t).reshape(N, K).astype(np.float64)
+    ref = x.astype(np.float16).astype(np.float64) @ W.T
+    rms = np.sqrt((ref ** 2).mean())
+    if accumulate:
+        ref = ref + y_in
+    return np.abs(y - ref).max() / rms
+
+
+@pytest.mark.parametrize("tname", QTYPES)
+@pytest.mark.parametrize("K,N,T", [(256, 128, 16), (512, 256, 1), (1024, 300, 37), (4096, 1024, 128),
+                                   (2048, 128, 256), (2048, 384, 300), (14336, 256, 512)])
+def test_gemm_vs_oracle(native_lib, tname, K, N, T):
+    # weights are rounded to f16 once (2^-11 relative each), products accumulate in float32 on the tensor core
+    err = _gemm_case(native_lib, tname, K, N, T)
+    assert err < 2e-3, (tname, K, N, T, err)
+
+
+def test_gemm_accumulates_into_residual(native_lib):
+    assert _gemm_case(native_lib, "Q4_K", 1024, 256, 48, accumulate=True) < 2e-3
+
+
+def test_gemm_rejects_bad_shapes(native_lib):
+    w = np.zeros(144 * 128, np.uint8)
+    x = np.zeros((4, 256), np.float32)
+    y = np.zeros((4, 128), np.float32)
+    assert native_lib.b2_op_gemm(0, TYPE_IDS["Q4_K"], ptr(w), 128, 128, ptr(x), 4, None, ptr(y), 0) != 0     # K % 256
+    assert native_lib.b2_op_gemm(0, TYPE_IDS["Q4_K"], ptr(w), 128, 256, ptr(x), 513, None, ptr(y), 0) != 0   # too many tokens
+    assert native_lib.b2_op_gemm(0, TYPE_IDS["F32"], ptr(w), 128, 256, ptr(x), 4, None, ptr(y), 0) != 0      # not a block format
