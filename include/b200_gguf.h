@@ -151,9 +151,9 @@ int b2_op_gate_up(int device, int type_gate, const void* host_wg, int type_up, c
  * y[t][n] = (y_in ? y_in[t][n] : 0) + sum_k f16(x[t][k]) * W[n][k]; x [T][K] f32 (rounded to f16 on the device),
  * W [n_rows][K] raw GGUF blocks, T <= 512, K % 256 == 0. Replaces ggml-cuda's dequantise-to-f16 + cublasGemmEx
  * prompt path that create_chat_completion reaches (/root/reference/api.py:55-63).
- * flags: reserved, pass 0. */
+ * n_splits: K ranges computed by separate CTAs and added in order (0 = the engine's own choice, else 1..16). */
 int b2_op_gemm(int device, int type, const void* host_w, int n_rows, int K, const float* host_x, int T,
-               const float* host_y_in, float* host_y, int flags);
+               const float* host_y_in, float* host_y, int n_splits);
 /* ggml rms_norm_f32 * weight */
 int b2_op_rmsnorm(int device, const float* host_x, const float* host_w, float eps, int K, int rows, float* host_y);
 /* Decode attention for one sequence: q [n_head*head_dim] f32 (already rotated), K/V as f16

@@ -13,6 +13,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
 #include <mutex>
 #include <string>
 #include <unordered_map>
@@ -95,8 +96,10 @@ struct b2_engine {
     float* mega_scratch = nullptr;
     unsigned* mega_counters = nullptr;
     // prompt (GEMM) workspace, allocated on the first long prompt: PF_T tokens per chunk
-    float *pf_x = nullptr, *pf_qkv = nullptr, *pf_gu = nullptr;
+    float *pf_x = nullptr, *pf_part = nullptr;     // residual stream [PF_T][n_embd]; K-split partial sums of the last GEMM
+    size_t pf_part_floats = 0;
     __half *pf_xn = nullptr, *pf_qh = nullptr, *pf_att = nullptr, *pf_h = nullptr;
+    int n_sms = 148;
     bool gemm_ok = false;          // every layer matrix is a block format the GEMM reads
     int prefill_min = 8;           // prompts chunks shorter than this go token by token through the mat-vec path
     unsigned long long* mega_ts = nullptr;   // B2_MEGA_TS=1: phase timestamps of the last layer-kernel launch
@@ -164,6 +167,7 @@ extern "C" int b2_engine_create(const b2_config* c, b2_engine** out) {
     int per = mv_ctas_per_sm_default();
     if (const char* s = getenv("B2_CTAS_PER_SM")) per = atoi(s) > 0 ? atoi(s) : per;
     e->n_ctas = sms * per;
+    e->n_sms = sms;
     CK(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
     CK(cudaEventCreate(&e->ev0));
     CK(cudaEventCreate(&e->ev1));
@@ -611,9 +615,11 @@ static int ensure_prefill_workspace(b2_engine* e) {
     if (e->pf_x) return B2_OK;
     const b2_config& c = e->cfg;
     const size_t qd = (size_t)c.n_head * c.head_dim, kvd = (size_t)c.n_head_kv * c.head_dim;
+    // partial sums: up to 8 K splits of the widest-but-one outputs, 2 of gate|up
+    size_t wide = std::max<size_t>({(size_t)2 * 2 * c.n_ff, (size_t)8 * (qd + 2 * kvd), (size_t)8 * c.n_embd});
+    e->pf_part_floats = PF_T * wide;
     CK(cudaMalloc(&e->pf_x, PF_T * (size_t)c.n_embd * 4));
-    CK(cudaMalloc(&e->pf_qkv, PF_T * (qd + 2 * kvd) * 4));
-    CK(cudaMalloc(&e->pf_gu, PF_T * (size_t)c.n_ff * 2 * 4));
+    CK(cudaMalloc(&e->pf_part, e->pf_part_floats * 4));
     CK(cudaMalloc(&e->pf_xn, PF_T * (size_t)c.n_embd * 2));
     CK(cudaMalloc(&e->pf_qh, PF_T * qd * 2));
     CK(cudaMalloc(&e->pf_att, PF_T * qd * 2));
@@ -625,14 +631,22 @@ static int ensure_prefill_workspace(b2_engine* e) {
     return B2_OK;
 }
 
-static int gemm_call(b2_engine* e, const DevTensor& w, const __half* x, int T, float* y, int ldy, bool accumulate) {
+// One GEMM over up to three matrices that share the input; returns the number of K-split partial sums in pf_part.
+static int gemm_call(b2_engine* e, const DevTensor* const* ws, int nw, const __half* x, int T, int* n_parts, long* part_stride) {
     GemmParams p = {};
-    p.w = w.ptr; p.type = w.type; p.N = (int)w.ne1; p.K = (int)w.ne0;
-    p.row_bytes = (int)(w.ne0 / block_elems(w.type) * block_bytes(w.type));
-    p.x = x; p.T = T; p.T_pad = (T + 15) / 16 * 16; p.y = y; p.ldy = ldy; p.accumulate = accumulate ? 1 : 0;
+    p.nseg = nw; p.K = (int)ws[0]->ne0;
+    int off = 0;
+    for (int i = 0; i < nw; i++) {
+        p.seg[i].w = ws[i]->ptr; p.seg[i].type = ws[i]->type; p.seg[i].n_rows = (int)ws[i]->ne1; p.seg[i].out_off = off;
+        off += (int)ws[i]->ne1;
+    }
+    p.x = x; p.T = T; p.y = e->pf_part; p.ldy = off; p.split_stride = (long)T * off;
     p.err = kernel_error_word();
+    const int max_splits = (int)std::min<size_t>(16, e->pf_part_floats / ((size_t)T * off));
+    if (gemm_plan(p, e->n_sms, max_splits)) return fail(B2_ERR_UNSUPPORTED, "GEMM shape not supported");
     CK(gemm_launch(p, e->stream));
     e->launches++;
+    *n_parts = p.n_splits; *part_stride = p.split_stride;
     return B2_OK;
 }
 
@@ -641,30 +655,34 @@ static int gemm_call(b2_engine* e, const DevTensor& w, const __half* x, int T, f
 static int prefill_chunk(b2_engine* e, Slot& s, const int* tokens, int T, int pos0) {
     const b2_config& c = e->cfg;
     cudaStream_t st = e->stream;
-    const int E = c.n_embd, F = c.n_ff, hd = c.head_dim;
-    const int qd = c.n_head * hd, kvd = c.n_head_kv * hd, qkvd = qd + 2 * kvd;
-    int rc;
+    const int E = c.n_embd, F = c.n_ff, hd = c.head_dim, T_pad = (T + 15) / 16 * 16;
+    int rc, np = 0;
+    long ps = 0;
     CK(embed_rows_launch(e->tok_embd.type, e->tok_embd.ptr, E, tokens, T, e->pf_x, st));
     e->launches++;
     for (int l = 0; l < c.n_layer; l++) {
         Layer& L = e->layers[l];
         __half* kc = e->k_pool + (size_t)l * e->layer_kv_elems;
         __half* vc = e->v_pool + (size_t)l * e->layer_kv_elems;
-        CK(rmsnorm_half_launch(e->pf_x, (const float*)L.attn_norm.ptr, c.rms_eps, E, T, e->pf_xn, st));
-        if ((rc = gemm_call(e, L.wq, e->pf_xn, T, e->pf_qkv, qkvd, false))) return rc;
-        if ((rc = gemm_call(e, L.wk, e->pf_xn, T, e->pf_qkv + qd, qkvd, false))) return rc;
-        if ((rc = gemm_call(e, L.wv, e->pf_xn, T, e->pf_qkv + qd + kvd, qkvd, false))) return rc;
-        CK(rope_store_launch(e->pf_qkv, T, pos0, c.n_head, c.n_head_kv, hd, c.kv_block_tokens, s.block_table, e->rope_freq,
+        // x += ffn_down partials of the previous layer; xn = attn_norm(x)
+        CK(resid_norm_half_launch(e->pf_x, e->pf_part, np, ps, (const float*)L.attn_norm.ptr, c.rms_eps, E, T, T_pad, e->pf_xn, st));
+        const DevTensor* qkv[3] = {&L.wq, &L.wk, &L.wv};
+        if ((rc = gemm_call(e, qkv, 3, e->pf_xn, T, &np, &ps))) return rc;
+        CK(rope_store_launch(e->pf_part, np, ps, T, pos0, c.n_head, c.n_head_kv, hd, c.kv_block_tokens, s.block_table, e->rope_freq,
                              e->pf_qh, kc, vc, st));
-        CK(attn_prefill_launch(e->pf_qh, kc, vc, s.block_table, T, pos0, c.n_head, c.n_head_kv, hd, c.kv_block_tokens, e->pf_att, st));
-        if ((rc = gemm_call(e, L.wo, e->pf_att, T, e->pf_x, E, true))) return rc;
-        CK(rmsnorm_half_launch(e->pf_x, (const float*)L.ffn_norm.ptr, c.rms_eps, E, T, e->pf_xn, st));
-        if ((rc = gemm_call(e, L.wgate, e->pf_xn, T, e->pf_gu, 2 * F, false))) return rc;
-        if ((rc = gemm_call(e, L.wup, e->pf_xn, T, e->pf_gu + F, 2 * F, false))) return rc;
-        CK(silu_mul_half_launch(e->pf_gu, F, T, e->pf_h, st));
-        if ((rc = gemm_call(e, L.wdown, e->pf_h, T, e->pf_x, E, true))) return rc;
+        CK(attn_prefill_launch(e->pf_qh, kc, vc, s.block_table, T, T_pad, pos0, c.n_head, c.n_head_kv, hd, c.kv_block_tokens, e->pf_att, st));
+        const DevTensor* wo[1] = {&L.wo};
+        if ((rc = gemm_call(e, wo, 1, e->pf_att, T, &np, &ps))) return rc;
+        CK(resid_norm_half_launch(e->pf_x, e->pf_part, np, ps, (const float*)L.ffn_norm.ptr, c.rms_eps, E, T, T_pad, e->pf_xn, st));
+        const DevTensor* gu[2] = {&L.wgate, &L.wup};
+        if ((rc = gemm_call(e, gu, 2, e->pf_xn, T, &np, &ps))) return rc;
+        CK(silu_mul_half_launch(e->pf_part, np, ps, F, T, T_pad, e->pf_h, st));
+        const DevTensor* wd[1] = {&L.wdown};
+        if ((rc = gemm_call(e, wd, 1, e->pf_h, T, &np, &ps))) return rc;
         e->launches += 5;
     }
+    CK(resid_norm_half_launch(e->pf_x, e->pf_part, np, ps, nullptr, c.rms_eps, E, T, T_pad, e->pf_xn, st));   // last residual add
+    e->launches++;
     return B2_OK;
 }
 
@@ -996,33 +1014,47 @@ extern "C" int b2_op_gate_up(int device, int tg, const void* wg, int tu, const v
     return op_matvec_common(device, p, wg, wu, n_rows, K, x, nw, nullptr, y, 2, n_ctas);
 }
 
+__global__ void sum_parts_kernel(const float* parts, int n_parts, long stride, const float* y_in, long n, float* y) {
+    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float v = y_in ? y_in[i] : 0.f;
+    for (int s = 0; s < n_parts; s++) v += parts[(size_t)s * stride + i];
+    y[i] = v;
+}
+
 extern "C" int b2_op_gemm(int device, int type, const void* w, int n_rows, int K, const float* x, int T,
-                          const float* y_in, float* y, int flags) {
-    (void)flags;
+                          const float* y_in, float* y, int n_splits) {
     if (!w || !x || !y || n_rows <= 0 || K <= 0 || T <= 0) return fail(B2_ERR_ARG, "bad arguments");
     if (T > 512) return fail(B2_ERR_ARG, "at most 512 tokens per call");
     int be = block_elems(type), bb = block_bytes(type);
     if (be == 1 || !bb) return fail(B2_ERR_UNSUPPORTED, "weight type must be a quantised block format");
     if (K % 256) return fail(B2_ERR_ARG, "K must be a multiple of 256");
+    if (n_splits < 0 || n_splits > 16 || (n_splits > 0 && K / 64 / n_splits < 1)) return fail(B2_ERR_ARG, "bad n_splits");
     CK(cudaSetDevice(device));
     CK(gemm_init());
-    const int T_pad = (T + 15) / 16 * 16;
-    const size_t wbytes = (size_t)n_rows * (K / be) * bb;
-    DevBuf dw, dx, dxh, dy;
-    CK(dw.alloc(wbytes + 64)); CK(dx.alloc((size_t)T * K * 4)); CK(dxh.alloc((size_t)T_pad * K * 2)); CK(dy.alloc((size_t)T * n_rows * 4));
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    const size_t wbytes = (size_t)n_rows * (K / be) * bb, out_n = (size_t)T * n_rows;
+    GemmParams p = {};
+    p.nseg = 1; p.K = K; p.seg[0].type = type; p.seg[0].n_rows = n_rows; p.seg[0].out_off = 0;
+    p.T = T; p.ldy = n_rows; p.split_stride = (long)out_n; p.err = kernel_error_word();
+    if (gemm_plan(p, sms, 16)) return fail(B2_ERR_UNSUPPORTED, "GEMM shape not supported");
+    if (n_splits > 0) p.n_splits = n_splits;
+    DevBuf dw, dx, dxh, dpart, dyin, dy;
+    CK(dw.alloc(wbytes + 64)); CK(dx.alloc((size_t)T * K * 4)); CK(dxh.alloc((size_t)p.T_pad * K * 2));
+    CK(dpart.alloc(out_n * 4 * p.n_splits)); CK(dy.alloc(out_n * 4));
     CK(cudaMemcpy(dw.p, w, wbytes, cudaMemcpyHostToDevice));
     CK(cudaMemcpy(dx.p, x, (size_t)T * K * 4, cudaMemcpyHostToDevice));
-    CK(cudaMemset(dxh.p, 0, (size_t)T_pad * K * 2));
-    CK(to_half_launch(dx.as<float>(), dxh.as<__half>(), (long)T * K, 0));
-    if (y_in) CK(cudaMemcpy(dy.p, y_in, (size_t)T * n_rows * 4, cudaMemcpyHostToDevice));
-    GemmParams p = {};
-    p.w = dw.as<uint8_t>(); p.type = type; p.N = n_rows; p.K = K; p.row_bytes = K / be * bb;
-    p.x = dxh.as<__half>(); p.T = T; p.T_pad = T_pad; p.y = dy.as<float>(); p.ldy = n_rows;
-    p.accumulate = y_in ? 1 : 0; p.err = kernel_error_word();
+    CK(to_half_blocked_launch(dx.as<float>(), T, p.T_pad, K, dxh.as<__half>(), 0));
+    if (y_in) { CK(dyin.alloc(out_n * 4)); CK(cudaMemcpy(dyin.p, y_in, out_n * 4, cudaMemcpyHostToDevice)); }
+    p.seg[0].w = dw.as<uint8_t>(); p.x = dxh.as<__half>(); p.y = dpart.as<float>();
     CK(gemm_launch(p, 0));
+    sum_parts_kernel<<<(unsigned)((out_n + 255) / 256), 256>>>(dpart.as<float>(), p.n_splits, (long)out_n,
+                                                               y_in ? dyin.as<float>() : nullptr, (long)out_n, dy.as<float>());
+    CK(cudaGetLastError());
     CK(cudaDeviceSynchronize());
     if (int rc = check_kernel_error()) return rc;
-    CK(cudaMemcpy(y, dy.p, (size_t)T * n_rows * 4, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(y, dy.p, out_n * 4, cudaMemcpyDeviceToHost));
     return B2_OK;
 }
 

@@ -1,23 +1,29 @@
 // Prefill / batched-decode GEMM on the 5th-generation tensor cores:
-//     Y[t][n] (+)= sum_k X[t][k] * W[n][k]        X: f16 activations [T][K], W: GGUF-quantised [N][K]
-// Replaces ggml-cuda's "dequantise the whole matrix to an f16 scratch copy, then cublasGemmEx" prefill
-// path (convert.cu + cuBLAS) that llama-cpp-python runs for the prompt under
-// create_chat_completion (/root/reference/api.py:55-63). No f16 copy of W ever exists in HBM: the quant
-// blocks are dequantised straight into the shared-memory operand tile of the MMA.
+//     P[s][t][n] = sum_{k in split s} X[t][k] * W[n][k]      X: f16 activations, W: GGUF-quantised [N][K]
+// Replaces ggml-cuda's "dequantise the whole matrix to an f16 scratch copy, then cublasGemmEx" prompt
+// path (convert.cu + cuBLAS) that llama-cpp-python runs under create_chat_completion
+// (/root/reference/api.py:55-63), and its batched mul_mat_q path for several sequences per step. No f16 copy
+// of W ever exists in HBM: quant blocks go from HBM to registers to the shared-memory operand tile of the MMA.
 //
-// One CTA owns 128 weight rows (the MMA "M" dimension = TMEM lanes) and ALL T <= 512 tokens (the MMA "N"
-// dimension = TMEM columns), so every weight is read and dequantised exactly once per call:
-//   per 64-wide K block, double buffered:
-//     * thread r dequantises the 64 weights of row r into the A tile      (128 x 64 f16, 16 KB)
-//     * all threads copy the activations of the block into the B tile     (T x 64 f16)
-//       both tiles use the K-major no-swizzle canonical layout: 8x8 core matrices, LBO = stride between
-//       core matrices along K, SBO = stride between 8-row groups
-//     * fence.proxy.async + barrier, then ONE thread issues 4 (x2 if T > 256) tcgen05.mma
-//       (kind::f16, M = 128, N = T, K = 16) accumulating into TMEM, and tcgen05.commit arrives on the
-//       mbarrier that frees the stage
-//   epilogue: each warp reads its 32 TMEM lanes with tcgen05.ld (32x32b.x8) and stores / accumulates
-//   into the float32 output, token-major.
-// Roofline: tensor pipe for large T; for T <= ~64 the dequantisation (CUDA cores) and HBM bound it.
+// Work decomposition. A CTA owns one tile of 128 weight rows (MMA "M" = TMEM lanes) of one of up to three
+// matrices that share the input (q|k|v, gate|up), ALL T <= 512 tokens (MMA "N" = TMEM columns) and one of
+// n_splits contiguous K ranges; split s writes its partial sums to y + s * split_stride and the consumer
+// kernel (RoPE/KV store, residual+RMSNorm, SiLU*mul: prefill.cu) adds the splits in a fixed order, so results
+// are deterministic. Splitting K is what fills 148 SMs when N is only 1024-4096 rows.
+//
+// Pipeline per CTA, S stages of 64 K-elements (A tile 16 KB + B tile T*128 B):
+//   warps 0-3 (thread r <-> weight row r): raw quant bytes of the NEXT block are already in registers
+//       (software prefetch) while the current block is expanded to f16 with byte-permute + half2 arithmetic
+//       (exact small integers 1024+q via byte-permute; scales applied without losing bits: ~2-2.5 instr/weight)
+//       and stored as 8 core-matrix rows of the A tile; fence.proxy.async; arrive on a_full[stage].
+//   warp 4, one thread: the B tile of a block is ONE 1-D TMA bulk copy (cp.async.bulk + mbarrier complete_tx):
+//       activations live in HBM in the MMA's own K-major core-matrix order [K/8][T][8] (the producing kernels
+//       write that layout), so the tile is contiguous. Waits a_full/b_full, issues 4 (x2 when T > 256)
+//       tcgen05.mma kind::f16 M=128 N=T K=16 accumulating in TMEM; tcgen05.commit arrives on empty[stage].
+//   epilogue: warps 0-3 read their 32 TMEM lanes (tcgen05.ld 32x32b.x16) and store float32, token-major.
+// Shared-memory operand layout: K-major, no swizzle: 8x8 f16 core matrices (8 rows x 16 B), LBO = byte stride
+// between core matrices along K, SBO = stride between 8-row groups (128 B).
+// Roofline: tensor pipe for large T; for T <= ~64 HBM (weights read once per call) and the dequantisation.
 #include "kernels.h"
 #include "ptx.cuh"
 #include "quant_blocks.cuh"
@@ -25,9 +31,11 @@
 
 namespace b2 {
 
-constexpr int GM_THREADS = 128;
+constexpr int GM_THREADS = 160;     // 4 dequantising warps + 1 control warp
 constexpr int GM_BM = 128;          // weight rows per CTA
 constexpr int GM_BK = 64;           // K per stage
+constexpr int GM_HDR = 256;         // barriers at the start of dynamic shared memory
+constexpr int GM_MAX_STAGES = 6;
 
 __device__ __forceinline__ void tmem_alloc(uint32_t* smem_dst, uint32_t ncols) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)), "r"(ncols) : "memory");
@@ -48,14 +56,15 @@ __device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t desc_a, uint6
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
-__device__ __forceinline__ void tmem_ld8(uint32_t taddr, float (&v)[8]) {
-    uint32_t r[8];
-    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
-                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
+    uint32_t r[16];
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                   "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
                  : "r"(taddr) : "memory");
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
-    for (int i = 0; i < 8; i++) v[i] = __uint_as_float(r[i]);
+    for (int i = 0; i < 16; i++) v[i] = __uint_as_float(r[i]);
 }
 
 // shared-memory matrix descriptor, K-major, no swizzle: start, LBO (K direction), SBO (M/N direction)
@@ -72,226 +81,362 @@ __device__ __forceinline__ uint32_t instr_desc(int M, int N) {
     return (1u << 4) | (0u << 7) | (0u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
-// ---------------------------------------------------------------- dequantise 64 weights of one row
-// k0 = first element of the block (multiple of 64). Writes 8 uint4 (8 x f16 each) through `emit(c, v)`.
-struct H8 { uint32_t w[4]; };
-__device__ __forceinline__ uint32_t pack_h2(float a, float b) {
-    __half2 h = __floats2half2_rn(a, b);
-    return *reinterpret_cast<uint32_t*>(&h);
-}
+// ---------------------------------------------------------------- raw block bytes -> f16
+// One K block = 64 consecutive weights of one row. RAW_WORDS covers the largest format (Q6_K).
+constexpr int RAW_WORDS = 26;
+struct RawKB { uint32_t w[RAW_WORDS]; };
 
-template <typename Emit>
-__device__ __forceinline__ void dequant_row64(int type, const uint8_t* row, int k0, Emit emit) {
-    float v[8];
-    if (type == T_Q4_K || type == T_Q5_K) {
-        const int bb = type == T_Q4_K ? 144 : 176;
-        const uint8_t* blk = row + (k0 >> 8) * bb;
-        const int c = (k0 & 255) >> 6;                                 // 64-chunk: sub-blocks 2c (low nibbles), 2c+1 (high)
-        U4 h = ld128(blk);
-        const uint8_t* qs = blk + (type == T_Q4_K ? 16 : 48) + 32 * c;
-        U4 q0 = ld128(qs), q1 = ld128(qs + 16);
-        uint32_t qw[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
-        uint32_t hw[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-        if (type == T_Q5_K) { U4 a = ld128(blk + 16), b = ld128(blk + 32); hw[0] = a.x; hw[1] = a.y; hw[2] = a.z; hw[3] = a.w; hw[4] = b.x; hw[5] = b.y; hw[6] = b.z; hw[7] = b.w; }
-        uint32_t sh = (c & 1) * 16, w0 = h.y >> sh, w1 = h.z >> sh, w2 = h.w >> sh, scp, mp;
-        if (c < 2) { scp = w0 & 0x3F3Fu; mp = w1 & 0x3F3Fu; }
-        else { scp = (w2 & 0x0F0Fu) | ((w0 >> 2) & 0x3030u); mp = ((w2 >> 4) & 0x0F0Fu) | ((w1 >> 2) & 0x3030u); }
-        const float d = h2f(h.x & 0xffffu), dmin = h2f(h.x >> 16);
-        const float dl[2] = {d * (float)(scp & 0xffu), d * (float)(scp >> 8)};
-        const float ml[2] = {dmin * (float)(mp & 0xffu), dmin * (float)(mp >> 8)};
-#pragma unroll
-        for (int ch = 0; ch < 8; ch++) {                               // 8 output chunks of 8 elements
-            const int hi = ch >> 2;                                    // chunks 0-3: low nibbles, 4-7: high nibbles
-#pragma unroll
-            for (int i = 0; i < 8; i++) {
-                const int l = (ch & 3) * 8 + i;                        // byte index within the 32-byte run
-                uint32_t q = (qw[l >> 2] >> (8 * (l & 3) + 4 * hi)) & 15u;
-                if (type == T_Q5_K) q |= ((hw[l >> 2] >> (8 * (l & 3) + 2 * c + hi)) & 1u) << 4;
-                v[i] = dl[hi] * (float)q - ml[hi];
-            }
-            H8 o; o.w[0] = pack_h2(v[0], v[1]); o.w[1] = pack_h2(v[2], v[3]); o.w[2] = pack_h2(v[4], v[5]); o.w[3] = pack_h2(v[6], v[7]);
-            emit(ch, o);
-        }
+__device__ __forceinline__ void load_raw(int type, const uint8_t* row, int k0, RawKB& r) {
+    if (type == T_Q4_K) {
+        const uint8_t* blk = row + (k0 >> 8) * 144;
+        const U4 h = ld128(blk), a = ld128(blk + 16 + 32 * ((k0 & 255) >> 6)), b = ld128(blk + 32 + 32 * ((k0 & 255) >> 6));
+        r.w[0] = h.x; r.w[1] = h.y; r.w[2] = h.z; r.w[3] = h.w;
+        r.w[4] = a.x; r.w[5] = a.y; r.w[6] = a.z; r.w[7] = a.w; r.w[8] = b.x; r.w[9] = b.y; r.w[10] = b.z; r.w[11] = b.w;
+    } else if (type == T_Q5_K) {
+        const uint8_t* blk = row + (k0 >> 8) * 176;
+        const uint8_t* qs = blk + 48 + 32 * ((k0 & 255) >> 6);
+        const U4 h = ld128(blk), a = ld128(qs), b = ld128(qs + 16), c = ld128(blk + 16), d = ld128(blk + 32);
+        r.w[0] = h.x; r.w[1] = h.y; r.w[2] = h.z; r.w[3] = h.w;
+        r.w[4] = a.x; r.w[5] = a.y; r.w[6] = a.z; r.w[7] = a.w; r.w[8] = b.x; r.w[9] = b.y; r.w[10] = b.z; r.w[11] = b.w;
+        r.w[12] = c.x; r.w[13] = c.y; r.w[14] = c.z; r.w[15] = c.w; r.w[16] = d.x; r.w[17] = d.y; r.w[18] = d.z; r.w[19] = d.w;
     } else if (type == T_Q6_K) {
         const uint8_t* blk = row + (k0 >> 8) * 210;
-        const int e0 = k0 & 255, hf = e0 >> 7, nib = (e0 >> 6) & 1;   // 64 elements = one nibble plane of one half
-        uint32_t ql[16], qh[8], scw[1];
+        const int e0 = k0 & 255, hf = e0 >> 7, nib = (e0 >> 6) & 1;
+        uint32_t ql[16], qh[8], sc[1];
         ld_words_u2<16>(blk + 64 * hf, ql);
         ld_words_u2<8>(blk + 128 + 32 * hf, qh);
-        ld_words_u2<1>(blk + 192 + 8 * hf + 4 * nib, scw);
-        const float d = h2f(ld16(blk + 208));
+        ld_words_u2<1>(blk + 192 + 8 * hf + 4 * nib, sc);
 #pragma unroll
-        for (int ch = 0; ch < 8; ch++) {
-            const float dl = d * (float)(int8_t)(scw[0] >> (8 * (ch >> 1)));
+        for (int i = 0; i < 16; i++) r.w[i] = ql[i];
 #pragma unroll
-            for (int i = 0; i < 8; i++) {
-                const int e = ch * 8 + i;                              // 0..63 within the plane
-                const int l = e & 31, kq = 2 * nib + (e >> 5);
-                uint32_t lo = (ql[e >> 2] >> (8 * (e & 3) + 4 * nib)) & 15u;
-                uint32_t hi2 = (qh[l >> 2] >> (8 * (l & 3) + 2 * kq)) & 3u;
-                v[i] = dl * (float)((int)(lo | (hi2 << 4)) - 32);
-            }
-            H8 o; o.w[0] = pack_h2(v[0], v[1]); o.w[1] = pack_h2(v[2], v[3]); o.w[2] = pack_h2(v[4], v[5]); o.w[3] = pack_h2(v[6], v[7]);
-            emit(ch, o);
-        }
+        for (int i = 0; i < 8; i++) r.w[16 + i] = qh[i];
+        r.w[24] = sc[0];
+        r.w[25] = ld16(blk + 208);
     } else if (type == T_Q8_0) {
         const uint8_t* p = row + (k0 >> 5) * 34;                       // two 34-byte blocks, 4-byte aligned
-        uint32_t W[17];
 #pragma unroll
-        for (int i = 0; i < 17; i++) W[i] = ld32(p + 4 * i);
-        const float d0 = h2f(W[0] & 0xffffu), d1 = h2f(W[8] >> 16);
+        for (int i = 0; i < 17; i++) r.w[i] = ld32(p + 4 * i);
+    } else {                                                           // Q4_0: two 18-byte blocks, 4-byte aligned
+        const uint8_t* p = row + (k0 >> 5) * 18;
 #pragma unroll
-        for (int ch = 0; ch < 8; ch++) {
-            const float dd = ch < 4 ? d0 : d1;
+        for (int i = 0; i < 9; i++) r.w[i] = ld32(p + 4 * i);
+    }
+}
+
+// four unsigned bytes -> two half2 holding (1024 + byte) exactly: 0x64xx is the f16 with value 1024 + xx
+__device__ __forceinline__ void bytes_to_h2(uint32_t b, __half2& lo, __half2& hi) {
+    const uint32_t l = __byte_perm(b, 0x64646464u, 0x4140), h = __byte_perm(b, 0x64646464u, 0x4342);
+    lo = *reinterpret_cast<const __half2*>(&l);
+    hi = *reinterpret_cast<const __half2*>(&h);
+}
+__device__ __forceinline__ uint32_t h2_bits(__half2 h) { return *reinterpret_cast<uint32_t*>(&h); }
+
+// Expanding 8 byte-valued weights (two words) to one 16-byte core-matrix row. All three variants round the
+// weight to f16 once (plus one more rounding where a tiny correction term is added): the scales themselves
+// never lose bits, so a whole sub-block is not biased by a rounded scale.
+// K-quants with a minimum (Q4_K, Q5_K): w = d*(sc*q) - dmin*m. sc*q <= 63*31 is an exact f16 integer:
+//   t = (1024+q)*sc - 1024*sc (exact), v = t*d + mh, w = v + ml   with mh + ml = -dmin*m to ~22 bits
+__device__ __forceinline__ uint4 expand8_k(uint32_t b0, uint32_t b1, __half2 sc, __half2 nsc, __half2 d, __half2 mh, __half2 ml) {
+    __half2 p0, p1, p2, p3;
+    bytes_to_h2(b0, p0, p1);
+    bytes_to_h2(b1, p2, p3);
+    uint4 o;
+    o.x = h2_bits(__hadd2(__hfma2(__hfma2(p0, sc, nsc), d, mh), ml));
+    o.y = h2_bits(__hadd2(__hfma2(__hfma2(p1, sc, nsc), d, mh), ml));
+    o.z = h2_bits(__hadd2(__hfma2(__hfma2(p2, sc, nsc), d, mh), ml));
+    o.w = h2_bits(__hadd2(__hfma2(__hfma2(p3, sc, nsc), d, mh), ml));
+    return o;
+}
+// scale that is not an f16 (Q6_K: d * int8): s = s_hi + s_lo, w = q*s_hi + q*s_lo
+__device__ __forceinline__ uint4 expand8_s(uint32_t b0, uint32_t b1, __half2 off, __half2 s_hi, __half2 s_lo) {
+    __half2 p0, p1, p2, p3;
+    bytes_to_h2(b0, p0, p1);
+    bytes_to_h2(b1, p2, p3);
+    p0 = __hsub2(p0, off); p1 = __hsub2(p1, off); p2 = __hsub2(p2, off); p3 = __hsub2(p3, off);
+    uint4 o;
+    o.x = h2_bits(__hfma2(p0, s_hi, __hmul2(p0, s_lo)));
+    o.y = h2_bits(__hfma2(p1, s_hi, __hmul2(p1, s_lo)));
+    o.z = h2_bits(__hfma2(p2, s_hi, __hmul2(p2, s_lo)));
+    o.w = h2_bits(__hfma2(p3, s_hi, __hmul2(p3, s_lo)));
+    return o;
+}
+// f16 scale (Q8_0, Q4_0): w = q * d, one rounding
+__device__ __forceinline__ uint4 expand8_d(uint32_t b0, uint32_t b1, __half2 off, __half2 d) {
+    __half2 p0, p1, p2, p3;
+    bytes_to_h2(b0, p0, p1);
+    bytes_to_h2(b1, p2, p3);
+    uint4 o;
+    o.x = h2_bits(__hmul2(__hsub2(p0, off), d));
+    o.y = h2_bits(__hmul2(__hsub2(p1, off), d));
+    o.z = h2_bits(__hmul2(__hsub2(p2, off), d));
+    o.w = h2_bits(__hmul2(__hsub2(p3, off), d));
+    return o;
+}
+__device__ __forceinline__ void split_f16(float v, __half2& hi, __half2& lo) {
+    const __half h = __float2half_rn(v);
+    hi = __half2half2(h);
+    lo = __float2half2_rn(v - __half2float(h));
+}
+__device__ __forceinline__ __half2 h2_from_bits16(uint32_t b) { return __half2half2(__ushort_as_half((unsigned short)b)); }
+
+// dst: this thread's 16-byte slot in chunk 0 of the A tile; chunk ch is at dst + ch * lbo
+__device__ __forceinline__ void dequant_store(int type, const RawKB& r, int k0, uint8_t* dst, uint32_t lbo) {
+    auto put = [&](int ch, const uint4& v) { *reinterpret_cast<uint4*>(dst + ch * lbo) = v; };
+    if (type == T_Q4_K || type == T_Q5_K) {
+        const int c = (k0 & 255) >> 6;                                 // 64-chunk: sub-blocks 2c (low nibbles), 2c+1 (high)
+        const uint32_t sh = (c & 1) * 16, w0 = r.w[1] >> sh, w1 = r.w[2] >> sh, w2 = r.w[3] >> sh;
+        uint32_t scp, mp;
+        if (c < 2) { scp = w0 & 0x3F3Fu; mp = w1 & 0x3F3Fu; }
+        else { scp = (w2 & 0x0F0Fu) | ((w0 >> 2) & 0x3030u); mp = ((w2 >> 4) & 0x0F0Fu) | ((w1 >> 2) & 0x3030u); }
+        const __half2 d = h2_from_bits16(r.w[0] & 0xffffu);
+        const float dmin = h2f(r.w[0] >> 16);
+        const float sc0 = (float)(scp & 0xffu), sc1 = (float)(scp >> 8);
+        const __half2 s0 = __float2half2_rn(sc0), s1 = __float2half2_rn(sc1);
+        const __half2 n0 = __float2half2_rn(-1024.f * sc0), n1 = __float2half2_rn(-1024.f * sc1);
+        __half2 mh0, ml0, mh1, ml1;
+        split_f16(-dmin * (float)(mp & 0xffu), mh0, ml0);
+        split_f16(-dmin * (float)(mp >> 8), mh1, ml1);
 #pragma unroll
-            for (int i = 0; i < 8; i++) {
-                const int j = (ch & 3) * 8 + i;                        // int8 index within the block
-                uint32_t word = ch < 4 ? fshr(W[j >> 2], W[(j >> 2) + 1], 16) : W[9 + (j >> 2)];
-                v[i] = dd * (float)(int8_t)(word >> (8 * (j & 3)));
+        for (int j = 0; j < 4; j++) {                                  // 8 bytes -> 8 low-nibble + 8 high-nibble weights
+            uint32_t a = r.w[4 + 2 * j], b = r.w[5 + 2 * j];
+            uint32_t lo0 = a & 0x0F0F0F0Fu, lo1 = b & 0x0F0F0F0Fu, hi0 = (a >> 4) & 0x0F0F0F0Fu, hi1 = (b >> 4) & 0x0F0F0F0Fu;
+            if (type == T_Q5_K) {                                      // fifth bit: bit 2c (low) / 2c+1 (high) of qh byte l
+                const uint32_t ha = r.w[12 + 2 * j] >> (2 * c), hb = r.w[13 + 2 * j] >> (2 * c);
+                lo0 |= (ha & 0x01010101u) << 4; lo1 |= (hb & 0x01010101u) << 4;
+                hi0 |= ((ha >> 1) & 0x01010101u) << 4; hi1 |= ((hb >> 1) & 0x01010101u) << 4;
             }
-            H8 o; o.w[0] = pack_h2(v[0], v[1]); o.w[1] = pack_h2(v[2], v[3]); o.w[2] = pack_h2(v[4], v[5]); o.w[3] = pack_h2(v[6], v[7]);
-            emit(ch, o);
+            put(j, expand8_k(lo0, lo1, s0, n0, d, mh0, ml0));
+            put(4 + j, expand8_k(hi0, hi1, s1, n1, d, mh1, ml1));
         }
-    } else if (type == T_Q4_0) {
-        const uint8_t* p = row + (k0 >> 5) * 18;                       // two 18-byte blocks, 4-byte aligned
-        uint32_t W[9];
+    } else if (type == T_Q6_K) {
+        const int nib = ((k0 & 255) >> 6) & 1;                         // which nibble plane of the 128-element half
+        const float d = h2f(r.w[25] & 0xffffu);
+        const __half2 off = __float2half2_rn(1024.f + 32.f);
 #pragma unroll
-        for (int i = 0; i < 9; i++) W[i] = ld32(p + 4 * i);
-        const float d0 = h2f(W[0] & 0xffffu), d1 = h2f(W[4] >> 16);
+        for (int ch = 0; ch < 8; ch++) {                               // elements e = 8ch..8ch+7 of the plane
+            __half2 s_hi, s_lo;
+            split_f16(d * (float)(int8_t)(r.w[24] >> (8 * (ch >> 1))), s_hi, s_lo);
+            const int kq = 2 * nib + (ch >> 2);                        // 2-bit field of the qh byte
+            uint32_t b[2];
+#pragma unroll
+            for (int i = 0; i < 2; i++) {
+                const uint32_t lo = (r.w[2 * ch + i] >> (4 * nib)) & 0x0F0F0F0Fu;
+                const uint32_t hi = (r.w[16 + 2 * (ch & 3) + i] >> (2 * kq)) & 0x03030303u;
+                b[i] = lo | (hi << 4);
+            }
+            put(ch, expand8_s(b[0], b[1], off, s_hi, s_lo));
+        }
+    } else if (type == T_Q8_0) {
+        const __half2 d0 = h2_from_bits16(r.w[0] & 0xffffu), d1 = h2_from_bits16(r.w[8] >> 16);
+        const __half2 off = __float2half2_rn(1024.f + 128.f);
 #pragma unroll
         for (int ch = 0; ch < 8; ch++) {
-            const int b = ch >> 2, part = ch & 3;                      // block, 8-element part: 0,1 low nibbles; 2,3 high
-            const float dd = b ? d1 : d0;
+            uint32_t b0, b1;
+            if (ch < 4) { b0 = fshr(r.w[2 * ch], r.w[2 * ch + 1], 16); b1 = fshr(r.w[2 * ch + 1], r.w[2 * ch + 2], 16); }
+            else { b0 = r.w[9 + 2 * (ch - 4)]; b1 = r.w[10 + 2 * (ch - 4)]; }
+            // signed byte + 128 is an unsigned byte
+            put(ch, expand8_d(b0 ^ 0x80808080u, b1 ^ 0x80808080u, off, ch < 4 ? d0 : d1));
+        }
+    } else {                                                           // Q4_0
+        const __half2 d0 = h2_from_bits16(r.w[0] & 0xffffu), d1 = h2_from_bits16(r.w[4] >> 16);
+        const __half2 off = __float2half2_rn(1024.f + 8.f);
 #pragma unroll
-            for (int i = 0; i < 8; i++) {
-                const int j = (part & 1) * 8 + i;                      // qs byte 0..15
-                uint32_t word = b ? W[5 + (j >> 2)] : fshr(W[j >> 2], W[(j >> 2) + 1], 16);
-                uint32_t q = (word >> (8 * (j & 3) + 4 * (part >> 1))) & 15u;
-                v[i] = dd * (float)((int)q - 8);
+        for (int blk = 0; blk < 2; blk++) {
+#pragma unroll
+            for (int j = 0; j < 2; j++) {                              // qs bytes 8j..8j+7: low nibbles = elems 8j.., high = 16+8j..
+                uint32_t a, b;
+                if (blk == 0) { a = fshr(r.w[2 * j], r.w[2 * j + 1], 16); b = fshr(r.w[2 * j + 1], r.w[2 * j + 2], 16); }
+                else { a = r.w[5 + 2 * j]; b = r.w[6 + 2 * j]; }
+                put(blk * 4 + j, expand8_d(a & 0x0F0F0F0Fu, b & 0x0F0F0F0Fu, off, blk ? d1 : d0));
+                put(blk * 4 + 2 + j, expand8_d((a >> 4) & 0x0F0F0F0Fu, (b >> 4) & 0x0F0F0F0Fu, off, blk ? d1 : d0));
             }
-            H8 o; o.w[0] = pack_h2(v[0], v[1]); o.w[1] = pack_h2(v[2], v[3]); o.w[2] = pack_h2(v[4], v[5]); o.w[3] = pack_h2(v[6], v[7]);
-            emit(ch, o);
         }
     }
 }
 
-struct __align__(16) GemmShared {
-    uint64_t mma_done[2];
+struct GemmBars {
+    uint64_t a_full[GM_MAX_STAGES], b_full[GM_MAX_STAGES], empty[GM_MAX_STAGES];
     uint32_t tmem_base;
-    uint32_t pad[3];
 };
+static_assert(sizeof(GemmBars) <= GM_HDR, "barrier header");
 
 __global__ void __launch_bounds__(GM_THREADS) gemm_q_kernel(const GemmParams p) {
     extern __shared__ __align__(128) uint8_t smem_raw[];
-    GemmShared& sh = *reinterpret_cast<GemmShared*>(smem_raw);
-    const int tid = threadIdx.x, warp = tid >> 5;
-    const int T = p.T_pad;
-    const uint32_t a_bytes = GM_BM * GM_BK * 2, b_bytes = (uint32_t)(T + 1) * 16 * (GM_BK / 8);   // B chunks padded by 16 B: conflict-free stores
-    uint8_t* stage0 = smem_raw + 128;
+    GemmBars& sh = *reinterpret_cast<GemmBars*>(smem_raw);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int T = p.T_pad, S = p.n_stages;
+    const uint32_t a_bytes = GM_BM * GM_BK * 2, b_bytes = (uint32_t)T * GM_BK * 2;
     const uint32_t stage_bytes = a_bytes + b_bytes;
+    uint8_t* stage0 = smem_raw + GM_HDR;
     uint32_t ncols = 32;
     while ((int)ncols < T) ncols <<= 1;
 
-    if (tid == 0) { mbar_init(&sh.mma_done[0], 1); mbar_init(&sh.mma_done[1], 1); fence_mbar_init(); }
-    if (warp == 0) tmem_alloc(&sh.tmem_base, ncols);
+    // ---- which tile / K range
+    const int split = blockIdx.x % p.n_splits, tile_g = blockIdx.x / p.n_splits;
+    int seg = 0;
+    while (seg + 1 < p.nseg && tile_g >= p.seg[seg + 1].tile0) seg++;
+    const GemmSeg& sg = p.seg[seg];
+    const int m0 = (tile_g - sg.tile0) * GM_BM;
+    const int n_kb_all = p.K / GM_BK;
+    const int kb0 = (int)((long)n_kb_all * split / p.n_splits), kb1 = (int)((long)n_kb_all * (split + 1) / p.n_splits);
+    const int n = kb1 - kb0;
+
+    if (warp == 4) {
+        if (lane == 0) {
+            for (int i = 0; i < S; i++) { mbar_init(&sh.a_full[i], GM_BM); mbar_init(&sh.b_full[i], 1); mbar_init(&sh.empty[i], 1); }
+            fence_mbar_init();
+        }
+        __syncwarp();
+        tmem_alloc(&sh.tmem_base, ncols);
+    }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = sh.tmem_base;
-
-    const int m0 = blockIdx.x * GM_BM;
-    const int my_row = min(m0 + tid, p.N - 1);                        // rows past N are computed and dropped
-    const uint8_t* wrow = p.w + (size_t)my_row * p.row_bytes;
-    const uint32_t idesc_lo = instr_desc(GM_BM, T > 256 ? 256 : T);
-    const uint32_t idesc_hi = T > 256 ? instr_desc(GM_BM, T - 256) : 0u;
     // K-major, no swizzle: element (r, k) of a tile with R rows sits at (k/8) * (R*16) + r*16 + (k%8)*2
-    const uint32_t lbo_a = GM_BM * 16, lbo_b = (uint32_t)(T + 1) * 16, sbo = 128;
-    const int n_kb = p.K / GM_BK;
+    const uint32_t lbo_a = GM_BM * 16, lbo_b = (uint32_t)T * 16, sbo = 128;
 
-    for (int kb = 0; kb < n_kb; kb++) {
-        const int s = kb & 1;
-        uint8_t* sa = stage0 + (size_t)s * stage_bytes;
-        uint8_t* sb = sa + a_bytes;
-        if (kb >= 2) mbar_wait(&sh.mma_done[s], ((kb >> 1) - 1) & 1, p.err, 0x40001u, (unsigned)kb);   // MMAs of kb-2 done with this stage
-        // ---- A tile: this thread's weight row, 64 values -> 8 core-matrix rows
-        dequant_row64(p.type, wrow, kb * GM_BK, [&](int ch, const H8& o) {
-            *reinterpret_cast<uint4*>(sa + ch * lbo_a + tid * 16) = make_uint4(o.w[0], o.w[1], o.w[2], o.w[3]);
-        });
-        // ---- B tile: activations of the block, T rows x 8 chunks of 16 bytes
-        for (int i = tid; i < T * 8; i += GM_THREADS) {
-            const int t = i >> 3, ch = i & 7;
-            const uint4 v = *reinterpret_cast<const uint4*>(p.x + (size_t)t * p.K + kb * GM_BK + ch * 8);
-            *reinterpret_cast<uint4*>(sb + ch * lbo_b + t * 16) = v;
+    if (warp < 4) {
+        // ================= dequantising threads: thread <-> weight row
+        const int my_row = min(m0 + tid, sg.n_rows - 1);               // rows past N are computed and dropped
+        const uint8_t* wrow = sg.w + (size_t)my_row * sg.row_bytes;
+        const int type = sg.type;
+        RawKB cur, nxt;
+        load_raw(type, wrow, kb0 * GM_BK, cur);
+        for (int i = 0; i < n; i++) {
+            const int s = i % S, use = i / S;
+            if (i + 1 < n) load_raw(type, wrow, (kb0 + i + 1) * GM_BK, nxt);     // in flight while this block is expanded
+            if (use > 0) mbar_wait(&sh.empty[s], (use - 1) & 1, p.err, 0x40001u, (unsigned)i);   // MMAs that read the stage are done
+            uint8_t* sa = stage0 + (size_t)s * stage_bytes;
+            dequant_store(type, cur, (kb0 + i) * GM_BK, sa + tid * 16, lbo_a);
+            fence_proxy_async();        // generic-proxy writes -> visible to the tensor core (async proxy)
+            mbar_arrive(&sh.a_full[s]);
+            cur = nxt;
         }
-        fence_proxy_async();            // generic-proxy smem writes -> visible to the tensor core (async proxy)
-        __syncthreads();
-        if (tid == 0) {
+        // ================= epilogue: TMEM lane = tid
+        const int last = n - 1;
+        mbar_wait(&sh.empty[last % S], (last / S) & 1, p.err, 0x40002u, (unsigned)last);
+        tc_fence_after();
+        const int row = m0 + tid;
+        const uint32_t lane_addr = tmem + ((uint32_t)(warp * 32) << 16);
+        float* ybase = p.y + (size_t)split * p.split_stride + sg.out_off + row;
+        for (int c0 = 0; c0 < T; c0 += 16) {
+            float v[16];
+            tmem_ld16(lane_addr + c0, v);
+            if (row < sg.n_rows) {
+#pragma unroll
+                for (int j = 0; j < 16; j++)
+                    if (c0 + j < p.T) ybase[(size_t)(c0 + j) * p.ldy] = v[j];
+            }
+        }
+    } else if (lane == 0) {
+        // ================= control thread: B tiles by TMA, MMA issue
+        const uint32_t idesc_lo = instr_desc(GM_BM, T > 256 ? 256 : T);
+        const uint32_t idesc_hi = T > 256 ? instr_desc(GM_BM, T - 256) : 0u;
+        const uint8_t* xb = reinterpret_cast<const uint8_t*>(p.x);     // block kb = 8 chunks x T x 16 B, contiguous
+        auto load_b = [&](int i) {
+            const int s = i % S;
+            mbar_arrive_expect_tx(&sh.b_full[s], b_bytes);
+            tma_load_1d(stage0 + (size_t)s * stage_bytes + a_bytes, xb + (size_t)(kb0 + i) * b_bytes, b_bytes, &sh.b_full[s]);
+        };
+        for (int i = 0; i < S && i < n; i++) load_b(i);
+        for (int i = 0; i < n; i++) {
+            const int s = i % S, use = i / S;
+            mbar_wait(&sh.b_full[s], use & 1, p.err, 0x40003u, (unsigned)i);
+            mbar_wait(&sh.a_full[s], use & 1, p.err, 0x40004u, (unsigned)i);
             tc_fence_after();
-            const uint32_t a_addr = smem_u32(sa), b_addr = smem_u32(sb);
+            const uint32_t a_addr = smem_u32(stage0 + (size_t)s * stage_bytes), b_addr = a_addr + a_bytes;
 #pragma unroll
             for (int ks = 0; ks < GM_BK / 16; ks++) {
                 const uint64_t da = smem_desc(a_addr + ks * 2 * lbo_a, lbo_a, sbo);
                 const uint64_t db = smem_desc(b_addr + ks * 2 * lbo_b, lbo_b, sbo);
-                const uint32_t acc = (kb > 0 || ks > 0) ? 1u : 0u;
+                const uint32_t acc = (i > 0 || ks > 0) ? 1u : 0u;
                 umma_f16(tmem, da, db, idesc_lo, acc);
                 if (T > 256) {
                     const uint64_t db2 = smem_desc(b_addr + ks * 2 * lbo_b + 256 * 16, lbo_b, sbo);
                     umma_f16(tmem + 256, da, db2, idesc_hi, acc);
                 }
             }
-            umma_commit(&sh.mma_done[s]);   // arrives when the MMAs above have finished reading the stage
-        }
-    }
-    // ---- wait for the last MMAs, then read the accumulators back
-    {
-        const int last = n_kb - 1;
-        mbar_wait(&sh.mma_done[last & 1], (last >> 1) & 1, p.err, 0x40002u, (unsigned)last);
-        if (n_kb >= 2) mbar_wait(&sh.mma_done[(last - 1) & 1], ((last - 1) >> 1) & 1, p.err, 0x40003u, (unsigned)last);
-    }
-    tc_fence_after();
-    const int row = m0 + tid;                                          // TMEM lane = tid (warp w owns lanes 32w..32w+31)
-    const uint32_t lane_addr = tmem + ((uint32_t)(warp * 32) << 16);
-    for (int c0 = 0; c0 < T; c0 += 8) {
-        float v[8];
-        tmem_ld8(lane_addr + c0, v);
-        if (row < p.N) {
-#pragma unroll
-            for (int i = 0; i < 8; i++) {
-                const int t = c0 + i;
-                if (t < p.T) {
-                    float* y = p.y + (size_t)t * p.ldy + row;
-                    *y = p.accumulate ? *y + v[i] : v[i];
-                }
+            umma_commit(&sh.empty[s]);      // arrives when the MMAs above have finished reading the stage
+            if (i >= 1 && i - 1 + S < n) {  // refill the stage of the previous block as soon as its MMAs retire
+                const int ip = i - 1;
+                mbar_wait(&sh.empty[ip % S], (ip / S) & 1, p.err, 0x40005u, (unsigned)ip);
+                load_b(ip + S);
             }
         }
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 0) tmem_dealloc(tmem, ncols);
+    if (warp == 4) tmem_dealloc(tmem, ncols);
 }
 
-size_t gemm_smem_bytes(int T_pad) { return 128 + 2 * ((size_t)GM_BM * GM_BK * 2 + (size_t)(T_pad + 1) * 16 * (GM_BK / 8)); }
+// ---------------------------------------------------------------- host side
+size_t gemm_smem_bytes(int T_pad, int n_stages) {
+    return GM_HDR + (size_t)n_stages * ((size_t)GM_BM * GM_BK * 2 + (size_t)T_pad * GM_BK * 2);
+}
 
 cudaError_t gemm_init() {
-    return cudaFuncSetAttribute(gemm_q_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gemm_smem_bytes(512));
+    return cudaFuncSetAttribute(gemm_q_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+}
+
+// Fill tile ranges, the stage count and the K split. n_sms: SMs to fill; max_splits: what the partial buffer allows.
+int gemm_plan(GemmParams& p, int n_sms, int max_splits) {
+    if (p.nseg < 1 || p.nseg > 3 || p.K <= 0 || p.K % 256) return -1;
+    if (p.T < 1 || p.T > 512) return -2;
+    p.T_pad = (p.T + 15) / 16 * 16;
+    int tiles = 0;
+    for (int s = 0; s < p.nseg; s++) {
+        GemmSeg& g = p.seg[s];
+        const int be = block_elems(g.type), bb = block_bytes(g.type);
+        if (be == 1 || !bb || g.n_rows <= 0) return -3;
+        g.row_bytes = p.K / be * bb;
+        g.tile0 = tiles;
+        g.n_tiles = (g.n_rows + GM_BM - 1) / GM_BM;
+        tiles += g.n_tiles;
+    }
+    p.n_tiles = tiles;
+    const size_t stage = (size_t)GM_BM * GM_BK * 2 + (size_t)p.T_pad * GM_BK * 2;
+    // small T: several CTAs per SM hide the weight-load latency; each gets <= ~100 KB
+    const size_t budget = p.T_pad <= 128 ? 100 * 1024 : 227 * 1024 - 1024;
+    int S = (int)((budget - GM_HDR) / stage);
+    if (S > 4) S = 4;
+    if (S < 2) return -4;
+    p.n_stages = S;
+    const int per_sm = p.T_pad <= 128 ? 2 : 1;
+    const int slots = n_sms * per_sm;
+    const int n_kb = p.K / GM_BK;
+    // choose the K split that minimises (waves) x (blocks per CTA + fixed cost), fixed cost ~ epilogue + ramp
+    const int fixed = 6 + p.T_pad / 32;
+    long best_cost = -1;
+    int best = 1;
+    for (int s = 1; s <= max_splits && s <= 16 && n_kb / s >= 4; s++) {
+        const long waves = ((long)tiles * s + slots - 1) / slots;
+        const long cost = waves * ((n_kb + s - 1) / s + fixed);
+        if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = s; }
+    }
+    p.n_splits = best;
+    return 0;
 }
 
 cudaError_t gemm_launch(const GemmParams& p, cudaStream_t stream) {
-    if (p.T_pad < 16 || p.T_pad > 512 || p.T_pad % 16 || p.T > p.T_pad || p.K % GM_BK || p.K % 256) return cudaErrorInvalidValue;
-    if (p.T_pad > 256 && (p.T_pad - 256) % 16) return cudaErrorInvalidValue;
-    int be = block_elems(p.type);
-    if (be == 1 || !block_bytes(p.type)) return cudaErrorInvalidValue;
-    const int grid = (p.N + GM_BM - 1) / GM_BM;
-    gemm_q_kernel<<<grid, GM_THREADS, gemm_smem_bytes(p.T_pad), stream>>>(p);
+    if (p.n_stages < 2 || p.n_stages > GM_MAX_STAGES || p.n_splits < 1 || p.n_tiles < 1) return cudaErrorInvalidValue;
+    if (p.T_pad < 16 || p.T_pad > 512 || p.T_pad % 16 || p.T > p.T_pad) return cudaErrorInvalidValue;
+    gemm_q_kernel<<<p.n_tiles * p.n_splits, GM_THREADS, gemm_smem_bytes(p.T_pad, p.n_stages), stream>>>(p);
     return cudaGetLastError();
 }
 
-__global__ void to_half_kernel(const float* x, __half* y, long n) {
-    long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) y[i] = __float2half_rn(x[i]);
+// x [T][K] float32 -> f16 in the MMA operand order [K/8][T_pad][8] (rows >= T zero)
+__global__ void to_half_blocked_kernel(const float* x, int T, int T_pad, int K, __half* y) {
+    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;      // one output element
+    if (i >= (long)T_pad * K) return;
+    const int e = (int)(i & 7);
+    const long r = i >> 3;
+    const int t = (int)(r % T_pad), ch = (int)(r / T_pad);
+    y[i] = t < T ? __float2half_rn(x[(size_t)t * K + ch * 8 + e]) : __float2half_rn(0.f);
 }
-cudaError_t to_half_launch(const float* x, __half* y, long n, cudaStream_t s) {
-    to_half_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(x, y, n);
+cudaError_t to_half_blocked_launch(const float* x, int T, int T_pad, int K, __half* y, cudaStream_t s) {
+    const long n = (long)T_pad * K;
+    to_half_blocked_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(x, T, T_pad, K, y);
     return cudaGetLastError();
 }
 

@@ -100,30 +100,47 @@ size_t mega_smem_bytes(const MegaParams& mp);
 cudaError_t mega_launch(const MegaParams& mp, int n_ctas, cudaStream_t stream, bool act2);
 
 // ---------------------------------------------------------------- tensor-core GEMM (gemm.cu)
+struct GemmSeg {
+    const uint8_t* w;       // quantised rows [n_rows][K], unchanged GGUF bytes
+    int type, n_rows;
+    int out_off;            // column offset of this matrix in the output row
+    int row_bytes, tile0, n_tiles;   // filled by gemm_plan
+};
 struct GemmParams {
-    const uint8_t* w;       // quantised rows [N][K], unchanged GGUF bytes
-    int type, N, K, row_bytes;
-    const __half* x;        // activations [T_pad][K] f16 (rows >= T may hold anything finite or not: their columns are dropped)
-    int T, T_pad;           // T_pad: multiple of 16, <= 512
-    float* y;               // [T][ldy] float32, element (t, n) at y[t * ldy + n]
+    GemmSeg seg[3];         // matrices that share the input (q|k|v, gate|up)
+    int nseg, K;
+    const __half* x;        // activations in MMA operand order [K/8][T_pad][8] f16 (rows >= T: anything)
+    int T, T_pad;           // T_pad: multiple of 16, <= 512 (gemm_plan)
+    float* y;               // partial sums of K split s at y + s * split_stride, element (t, n) at [t * ldy + n]
     int ldy;
-    int accumulate;         // 1: y += result (residual add)
+    long split_stride;
     unsigned int* err;
+    int n_tiles, n_splits, n_stages;   // filled by gemm_plan
 };
 cudaError_t gemm_init();
-size_t gemm_smem_bytes(int T_pad);
+int gemm_plan(GemmParams& p, int n_sms, int max_splits);
+size_t gemm_smem_bytes(int T_pad, int n_stages);
 cudaError_t gemm_launch(const GemmParams& p, cudaStream_t stream);
-cudaError_t to_half_launch(const float* x, __half* y, long n, cudaStream_t s);
+cudaError_t to_half_blocked_launch(const float* x, int T, int T_pad, int K, __half* y, cudaStream_t s);
 
-// ---------------------------------------------------------------- prompt kernels (prefill.cu)
+// ---------------------------------------------------------------- prompt / batch kernels (prefill.cu)
+// f16 activation matrices are in the GEMM operand order: element (t, k) at ((k / 8) * T_pad + t) * 8 + k % 8.
+// "parts": n_parts partial sums (K splits of the GEMM that produced the input) part_stride floats apart.
 struct SamplerState;
 cudaError_t embed_rows_launch(int type, const uint8_t* table, int K, const int* tokens, int T, float* x, cudaStream_t s);
-cudaError_t rmsnorm_half_launch(const float* x, const float* w, float eps, int K, int T, __half* y, cudaStream_t s);
-cudaError_t rope_store_launch(const float* qkv, int T, int pos0, int n_head, int n_kv, int hd, int bt, const int* block_table,
-                              const float* rope_freq, __half* qh, __half* k_cache, __half* v_cache, cudaStream_t s);
+// x[t] += sum of parts (if n_parts > 0); then, if w: xn[t] = f16(rmsnorm(x[t]) * w) in operand order
+cudaError_t resid_norm_half_launch(float* x, const float* parts, int n_parts, long part_stride, const float* w, float eps,
+                                   int K, int T, int T_pad, __half* xn, cudaStream_t s);
+// qkv parts [T][n_head*hd | n_kv*hd | n_kv*hd]: RoPE on q,k at pos0 + t; q -> qh [T][n_head*hd] f16 (token-major),
+// k, v -> paged cache
+cudaError_t rope_store_launch(const float* parts, int n_parts, long part_stride, int T, int pos0, int n_head, int n_kv, int hd,
+                              int bt, const int* block_table, const float* rope_freq, __half* qh, __half* k_cache,
+                              __half* v_cache, cudaStream_t s);
+// causal attention of T queries at pos0.. over the paged cache; out in operand order (T_pad)
 cudaError_t attn_prefill_launch(const __half* qh, const __half* k_cache, const __half* v_cache, const int* block_table,
-                                int T, int pos0, int n_head, int n_kv, int hd, int bt, __half* out, cudaStream_t s);
-cudaError_t silu_mul_half_launch(const float* gu, int F, int T, __half* h, cudaStream_t s);
+                                int T, int T_pad, int pos0, int n_head, int n_kv, int hd, int bt, __half* out, cudaStream_t s);
+// gate|up parts [T][2F] -> h = f16(silu(gate) * up) in operand order
+cudaError_t silu_mul_half_launch(const float* parts, int n_parts, long part_stride, int F, int T, int T_pad, __half* h, cudaStream_t s);
 cudaError_t prefill_finish_launch(const int* prompt, int n, int pos_last, int* ints, SamplerState* st, cudaStream_t s);
 
 // ---------------------------------------------------------------- small kernels (misc.cu)

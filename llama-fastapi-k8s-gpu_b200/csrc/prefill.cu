@@ -3,9 +3,11 @@
 // (/root/reference/api.py:55-63): get_rows (K1), rms_norm_f32 (K2), rope_f32 + the KV-cache copy (K6/K7),
 // the attention mat-muls + soft_max (K8-K10 at batch T), silu/mul (K11).
 //
+// f16 activation matrices that feed the GEMM are written in its operand order [K/8][T_pad][8]; the GEMM's
+// outputs arrive as n_parts K-split partial sums that the consumer adds in a fixed order.
 //   embed_rows      x[t][:]      = dequantised row tokens[t] of the embedding table          (f32)
-//   rmsnorm_half    xn[t][:]     = f16( x[t] / sqrt(mean(x[t]^2) + eps) * w )
-//   rope_store      q f32 -> rotated f16 [T][n_head*hd]; k rotated, v -> paged f16 KV cache
+//   resid_norm_half x[t] += sum(parts); xn[t] = f16( x[t] / sqrt(mean(x[t]^2) + eps) * w )
+//   rope_store      sum(parts) -> q rotated f16 [T][n_head*hd]; k rotated, v -> paged f16 KV cache
 //   attn_prefill    causal flash attention over the paged cache, mma.sync m16n8k16 (f16 in, f32 accumulate),
 //                   one warp per 16 queries of one head, the G heads of a KV group share the K/V tiles
 //   silu_mul_half   h[t][:]      = f16( silu(gate) * up )
@@ -31,13 +33,22 @@ cudaError_t embed_rows_launch(int type, const uint8_t* table, int K, const int* 
     return cudaGetLastError();
 }
 
-// ---------------------------------------------------------------- RMSNorm -> f16
-__global__ void __launch_bounds__(256) rmsnorm_half_kernel(const float* x, const float* w, float eps, int K, __half* y) {
+__device__ __forceinline__ size_t op_index(int t, int k, int T_pad) { return ((size_t)(k >> 3) * T_pad + t) * 8 + (k & 7); }
+
+// ---------------------------------------------------------------- residual add + RMSNorm -> f16
+__global__ void __launch_bounds__(256) resid_norm_half_kernel(float* x, const float* parts, int n_parts, long part_stride,
+                                                              const float* w, float eps, int K, int T_pad, __half* xn) {
     __shared__ float red[8];
     const int t = blockIdx.x;
-    const float* xr = x + (size_t)t * K;
+    float* xr = x + (size_t)t * K;
     float ss = 0.f;
-    for (int i = threadIdx.x; i < K; i += 256) { float v = xr[i]; ss += v * v; }
+    for (int i = threadIdx.x; i < K; i += 256) {
+        float v = xr[i];
+        for (int s = 0; s < n_parts; s++) v += parts[(size_t)s * part_stride + (size_t)t * K + i];
+        if (n_parts) xr[i] = v;
+        ss += v * v;
+    }
+    if (!w) return;
     ss = warp_sum(ss);
     if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
     __syncthreads();
@@ -45,29 +56,43 @@ __global__ void __launch_bounds__(256) rmsnorm_half_kernel(const float* x, const
 #pragma unroll
     for (int i = 0; i < 8; i++) tot += red[i];
     const float r = rsqrtf(tot / (float)K + eps);
-    for (int i = threadIdx.x; i < K; i += 256) y[(size_t)t * K + i] = __float2half_rn(xr[i] * r * w[i]);
+    for (int c = threadIdx.x; c < K / 8; c += 256) {                   // 8 consecutive k = one 16-byte run in operand order
+        const float4 a = *reinterpret_cast<const float4*>(xr + 8 * c), b = *reinterpret_cast<const float4*>(xr + 8 * c + 4);
+        const float4 wa = *reinterpret_cast<const float4*>(w + 8 * c), wb = *reinterpret_cast<const float4*>(w + 8 * c + 4);
+        const __half2 h0 = __floats2half2_rn(a.x * r * wa.x, a.y * r * wa.y), h1 = __floats2half2_rn(a.z * r * wa.z, a.w * r * wa.w);
+        const __half2 h2 = __floats2half2_rn(b.x * r * wb.x, b.y * r * wb.y), h3 = __floats2half2_rn(b.z * r * wb.z, b.w * r * wb.w);
+        *reinterpret_cast<uint4*>(xn + ((size_t)c * T_pad + t) * 8) =
+            make_uint4(*reinterpret_cast<const uint32_t*>(&h0), *reinterpret_cast<const uint32_t*>(&h1),
+                       *reinterpret_cast<const uint32_t*>(&h2), *reinterpret_cast<const uint32_t*>(&h3));
+    }
 }
-cudaError_t rmsnorm_half_launch(const float* x, const float* w, float eps, int K, int T, __half* y, cudaStream_t s) {
-    rmsnorm_half_kernel<<<T, 256, 0, s>>>(x, w, eps, K, y);
+cudaError_t resid_norm_half_launch(float* x, const float* parts, int n_parts, long part_stride, const float* w, float eps,
+                                   int K, int T, int T_pad, __half* xn, cudaStream_t s) {
+    resid_norm_half_kernel<<<T, 256, 0, s>>>(x, parts, n_parts, part_stride, w, eps, K, T_pad, xn);
     return cudaGetLastError();
 }
 
 // ---------------------------------------------------------------- RoPE + KV store
-// qkv [T][n_head*hd | n_kv*hd | n_kv*hd] f32. Pair (2i, 2i+1) rotated by pos * freq[i] (ggml "norm" RoPE).
-__global__ void rope_store_kernel(const float* qkv, int T, int pos0, int n_head, int n_kv, int hd, int bt,
-                                  const int* block_table, const float* rope_freq, __half* qh, __half* k_cache, __half* v_cache) {
+// parts: [T][n_head*hd | n_kv*hd | n_kv*hd] f32. Pair (2i, 2i+1) rotated by pos * freq[i] (ggml "norm" RoPE).
+__global__ void rope_store_kernel(const float* parts, int n_parts, long part_stride, int T, int pos0, int n_head, int n_kv,
+                                  int hd, int bt, const int* block_table, const float* rope_freq, __half* qh,
+                                  __half* k_cache, __half* v_cache) {
     const int t = blockIdx.x, pos = pos0 + t;
     const int nq = n_head * hd, nk = n_kv * hd, row_len = nq + 2 * nk;
-    const float* r = qkv + (size_t)t * row_len;
+    const float* r = parts + (size_t)t * row_len;
     const int page = block_table[pos / bt], slot = pos % bt;
     for (int pi = threadIdx.x; pi < row_len / 2; pi += blockDim.x) {
         const int e = 2 * pi;
-        float v0 = r[e], v1 = r[e + 1];
+        float v0 = 0.f, v1 = 0.f;
+        for (int s = 0; s < n_parts; s++) {
+            const float2 v = *reinterpret_cast<const float2*>(r + (size_t)s * part_stride + e);
+            v0 += v.x; v1 += v.y;
+        }
         if (e < nq + nk) {
             const int i = (e % hd) >> 1;
-            float s, c;
-            sincosf((float)pos * rope_freq[i], &s, &c);
-            const float a = v0 * c - v1 * s, b = v0 * s + v1 * c;
+            float sn, cs;
+            sincosf((float)pos * rope_freq[i], &sn, &cs);
+            const float a = v0 * cs - v1 * sn, b = v0 * sn + v1 * cs;
             v0 = a; v1 = b;
         }
         const __half2 h = __floats2half2_rn(v0, v1);
@@ -81,23 +106,39 @@ __global__ void rope_store_kernel(const float* qkv, int T, int pos0, int n_head,
         }
     }
 }
-cudaError_t rope_store_launch(const float* qkv, int T, int pos0, int n_head, int n_kv, int hd, int bt, const int* block_table,
-                              const float* rope_freq, __half* qh, __half* k_cache, __half* v_cache, cudaStream_t s) {
-    rope_store_kernel<<<T, 256, 0, s>>>(qkv, T, pos0, n_head, n_kv, hd, bt, block_table, rope_freq, qh, k_cache, v_cache);
+cudaError_t rope_store_launch(const float* parts, int n_parts, long part_stride, int T, int pos0, int n_head, int n_kv, int hd,
+                              int bt, const int* block_table, const float* rope_freq, __half* qh, __half* k_cache,
+                              __half* v_cache, cudaStream_t s) {
+    rope_store_kernel<<<T, 256, 0, s>>>(parts, n_parts, part_stride, T, pos0, n_head, n_kv, hd, bt, block_table, rope_freq, qh, k_cache, v_cache);
     return cudaGetLastError();
 }
 
 // ---------------------------------------------------------------- SiLU(gate) * up -> f16
-__global__ void silu_mul_half_kernel(const float* gu, int F, long n, __half* h) {
+__global__ void silu_mul_half_kernel(const float* parts, int n_parts, long part_stride, int F, int T, int T_pad, __half* h) {
+    // thread <-> (8 consecutive f, token): one 16-byte store in operand order
     const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const long t = i / F, f = i % F;
-    const float g = gu[t * 2 * F + f], u = gu[t * 2 * F + F + f];
-    h[i] = __float2half_rn(g / (1.f + __expf(-g)) * u);
+    const int t = (int)(i % T), ch = (int)(i / T);
+    if (ch >= F / 8) return;
+    float g[8] = {0, 0, 0, 0, 0, 0, 0, 0}, u[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int s = 0; s < n_parts; s++) {
+        const float* row = parts + (size_t)s * part_stride + (size_t)t * 2 * F + ch * 8;
+        const float4 g0 = *reinterpret_cast<const float4*>(row), g1 = *reinterpret_cast<const float4*>(row + 4);
+        const float4 u0 = *reinterpret_cast<const float4*>(row + F), u1 = *reinterpret_cast<const float4*>(row + F + 4);
+        g[0] += g0.x; g[1] += g0.y; g[2] += g0.z; g[3] += g0.w; g[4] += g1.x; g[5] += g1.y; g[6] += g1.z; g[7] += g1.w;
+        u[0] += u0.x; u[1] += u0.y; u[2] += u0.z; u[3] += u0.w; u[4] += u1.x; u[5] += u1.y; u[6] += u1.z; u[7] += u1.w;
+    }
+    uint32_t o[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        const float a = g[2 * j] / (1.f + __expf(-g[2 * j])) * u[2 * j], b = g[2 * j + 1] / (1.f + __expf(-g[2 * j + 1])) * u[2 * j + 1];
+        const __half2 hh = __floats2half2_rn(a, b);
+        o[j] = *reinterpret_cast<const uint32_t*>(&hh);
+    }
+    *reinterpret_cast<uint4*>(h + ((size_t)ch * T_pad + t) * 8) = make_uint4(o[0], o[1], o[2], o[3]);
 }
-cudaError_t silu_mul_half_launch(const float* gu, int F, int T, __half* h, cudaStream_t s) {
-    const long n = (long)T * F;
-    silu_mul_half_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(gu, F, n, h);
+cudaError_t silu_mul_half_launch(const float* parts, int n_parts, long part_stride, int F, int T, int T_pad, __half* h, cudaStream_t s) {
+    const long n = (long)T * (F / 8);
+    silu_mul_half_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(parts, n_parts, part_stride, F, T, T_pad, h);
     return cudaGetLastError();
 }
 
@@ -133,8 +174,8 @@ constexpr int PA_KT = 64;        // keys per tile
 // grid (query tiles, n_kv); block = G * QW warps: warp w -> head kvh*G + w % G, queries 16 * (w / G) .. +15 of the tile
 template <int HD>
 __global__ void __launch_bounds__(256) attn_prefill_kernel(const __half* qh, const __half* k_cache, const __half* v_cache,
-                                                           const int* block_table, int T, int pos0, int n_head, int n_kv,
-                                                           int bt, int QW, float scale_log2, __half* out) {
+                                                           const int* block_table, int T, int T_pad, int pos0, int n_head,
+                                                           int n_kv, int bt, int QW, float scale_log2, __half* out) {
     constexpr int LD = HD + 8;                                  // padded row: conflict-free fragment loads
     extern __shared__ __align__(16) uint8_t smem_raw[];
     __half* ks = reinterpret_cast<__half*>(smem_raw);           // [PA_KT][LD]
@@ -247,14 +288,14 @@ __global__ void __launch_bounds__(256) attn_prefill_kernel(const __half* qh, con
     const int r0 = q0 + g, r1 = q0 + g + 8;
 #pragma unroll
     for (int nt = 0; nt < HD / 8; nt++) {
-        const int d = nt * 8 + 2 * tq;
-        if (r0 < T) *reinterpret_cast<uint32_t*>(out + (size_t)r0 * nq + head * HD + d) = pack_half2(o[nt][0] * i0, o[nt][1] * i0);
-        if (r1 < T) *reinterpret_cast<uint32_t*>(out + (size_t)r1 * nq + head * HD + d) = pack_half2(o[nt][2] * i1, o[nt][3] * i1);
+        const int d = head * HD + nt * 8 + 2 * tq;      // column of the [T][n_head*hd] matrix, stored in operand order
+        if (r0 < T) *reinterpret_cast<uint32_t*>(out + op_index(r0, d, T_pad)) = pack_half2(o[nt][0] * i0, o[nt][1] * i0);
+        if (r1 < T) *reinterpret_cast<uint32_t*>(out + op_index(r1, d, T_pad)) = pack_half2(o[nt][2] * i1, o[nt][3] * i1);
     }
 }
 
 cudaError_t attn_prefill_launch(const __half* qh, const __half* k_cache, const __half* v_cache, const int* block_table,
-                                int T, int pos0, int n_head, int n_kv, int hd, int bt, __half* out, cudaStream_t s) {
+                                int T, int T_pad, int pos0, int n_head, int n_kv, int hd, int bt, __half* out, cudaStream_t s) {
     if (n_kv <= 0 || n_head % n_kv) return cudaErrorInvalidValue;
     const int G = n_head / n_kv;
     if (G > 8) return cudaErrorInvalidValue;
@@ -263,8 +304,8 @@ cudaError_t attn_prefill_launch(const __half* qh, const __half* k_cache, const _
     dim3 grid((T + q_tile - 1) / q_tile, n_kv), block(32 * G * QW);
     const float scale_log2 = 1.4426950408889634f / sqrtf((float)hd);
     const size_t smem = (size_t)2 * PA_KT * (hd + 8) * 2;
-    if (hd == 64) attn_prefill_kernel<64><<<grid, block, smem, s>>>(qh, k_cache, v_cache, block_table, T, pos0, n_head, n_kv, bt, QW, scale_log2, out);
-    else if (hd == 128) attn_prefill_kernel<128><<<grid, block, smem, s>>>(qh, k_cache, v_cache, block_table, T, pos0, n_head, n_kv, bt, QW, scale_log2, out);
+    if (hd == 64) attn_prefill_kernel<64><<<grid, block, smem, s>>>(qh, k_cache, v_cache, block_table, T, T_pad, pos0, n_head, n_kv, bt, QW, scale_log2, out);
+    else if (hd == 128) attn_prefill_kernel<128><<<grid, block, smem, s>>>(qh, k_cache, v_cache, block_table, T, T_pad, pos0, n_head, n_kv, bt, QW, scale_log2, out);
     else return cudaErrorInvalidValue;
     return cudaGetLastError();
 }

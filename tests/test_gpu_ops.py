@@ -250,7 +250,7 @@ def test_sampler_rejects_unsupported_top_k(native_lib):
 
 # ---------------------------------------------------------------------------------------------------
 # tensor-core GEMM (prefill / batched decode): y[t][n] = sum_k f16(x[t][k]) * W[n][k]
-def _gemm_case(native_lib, tname, K, N, T, accumulate=False, flags=0):
+def _gemm_case(native_lib, tname, K, N, T, accumulate=False, n_splits=0):
     from llama_cpp.synth import random_blocks
     from oracle import ggml_blocks as gb
     t = TYPE_IDS[tname]
@@ -260,7 +260,7 @@ def _gemm_case(native_lib, tname, K, N, T, accumulate=False, flags=0):
     x = (rng.standard_normal((T, K)) * rng.uniform(0.2, 2.0, size=K)).astype(np.float32)
     y_in = rng.standard_normal((T, N)).astype(np.float32) if accumulate else None
     y = np.zeros((T, N), np.float32)
-    rc = native_lib.b2_op_gemm(0, t, ptr(w), N, K, ptr(x), T, ptr(y_in) if accumulate else None, ptr(y), flags)
+    rc = native_lib.b2_op_gemm(0, t, ptr(w), N, K, ptr(x), T, ptr(y_in) if accumulate else None, ptr(y), n_splits)
     lib_check(native_lib, rc)
     W = gb.dequantize(w, t).reshape(N, K).astype(np.float64)
     ref = x.astype(np.float16).astype(np.float64) @ W.T
@@ -281,6 +281,13 @@ def test_gemm_vs_oracle(native_lib, tname, K, N, T):
 
 def test_gemm_accumulates_into_residual(native_lib):
     assert _gemm_case(native_lib, "Q4_K", 1024, 256, 48, accumulate=True) < 2e-3
+
+
+@pytest.mark.parametrize("n_splits", [1, 2, 3, 16])
+def test_gemm_k_splits_add_up(native_lib, n_splits):
+    # K ranges computed by separate CTAs (uneven when K/64 is not a multiple) and added in a fixed order
+    assert _gemm_case(native_lib, "Q6_K", 1280, 200, 40, n_splits=n_splits) < 2e-3
+    assert _gemm_case(native_lib, "Q8_0", 4096, 128, 320, n_splits=n_splits) < 2e-3
 
 
 def test_gemm_rejects_bad_shapes(native_lib):
