@@ -42,12 +42,63 @@ __global__ void __launch_bounds__(AT_THREADS) attn_decode_kernel(const AttnParam
     attn_decode_body<HD, CLUSTER>(p, sh, full, use, blockIdx.x, blockIdx.y, threadIdx.x);
 }
 
+// one launch for several sequences: blockIdx.z picks the sequence
+template <int HD, bool CLUSTER>
+__global__ void __launch_bounds__(AT_THREADS) attn_decode_batch_kernel(const AttnParams p0, const SlotDev* tab, const BatchIdx b) {
+    extern __shared__ __align__(128) uint8_t smem_raw[];
+    AttnShared<HD>& sh = *reinterpret_cast<AttnShared<HD>*>(smem_raw);
+    __shared__ uint64_t full[2];
+    if (threadIdx.x == 0) { mbar_init(&full[0], 1); mbar_init(&full[1], 1); fence_mbar_init(); }
+    __syncthreads();
+    const int z = blockIdx.z;
+    const SlotDev sd = tab[b.slot[z]];
+    AttnParams p = p0;
+    const size_t qd = (size_t)p.n_head * p.head_dim;
+    p.q = p0.q + z * qd; p.out = p0.out + z * qd;
+    p.pos_ptr = sd.ints + 1; p.block_table = sd.block_table;
+    p.scratch = p0.scratch + z * qd / p.head_dim * p.n_splits * (p.head_dim + 2);
+    p.counters = p0.counters + z * p.n_kv;
+    uint32_t use[2] = {0u, 0u};
+    attn_decode_body<HD, CLUSTER>(p, sh, full, use, blockIdx.x, blockIdx.y, threadIdx.x);
+}
+
 cudaError_t attn_init() {
     cudaError_t e;
     if ((e = cudaFuncSetAttribute(attn_decode_kernel<64, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AttnShared<64>))) != cudaSuccess) return e;
     if ((e = cudaFuncSetAttribute(attn_decode_kernel<64, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AttnShared<64>))) != cudaSuccess) return e;
     if ((e = cudaFuncSetAttribute(attn_decode_kernel<128, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AttnShared<128>))) != cudaSuccess) return e;
-    return cudaFuncSetAttribute(attn_decode_kernel<128, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AttnShared<128>));
+    if ((e = cudaFuncSetAttribute(attn_decode_kernel<128, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AttnShared<128>))) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(attn_decode_batch_kernel<64, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AttnShared<64>))) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(attn_decode_batch_kernel<64, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AttnShared<64>))) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(attn_decode_batch_kernel<128, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AttnShared<128>))) != cudaSuccess) return e;
+    return cudaFuncSetAttribute(attn_decode_batch_kernel<128, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AttnShared<128>));
+}
+
+cudaError_t attn_decode_batch_launch(const AttnParams& p, const SlotDev* tab, const BatchIdx& b, cudaStream_t stream) {
+    const int G = p.n_kv > 0 ? p.n_head / p.n_kv : 0;
+    if (p.n_kv <= 0 || p.n_head % p.n_kv || G > AT_GMAX || b.n < 1 || b.n > BATCH_MAX) return cudaErrorInvalidValue;
+    if (p.n_splits < 1 || G * p.n_splits > AT_GMAX * AT_TT) return cudaErrorInvalidValue;
+    const bool cluster = p.n_splits == 2 || p.n_splits == 4 || p.n_splits == 8;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(p.n_splits, p.n_kv, b.n); cfg.blockDim = dim3(AT_THREADS); cfg.stream = stream;
+    cudaLaunchAttribute at[1];
+    int na = 0;
+    if (cluster) {
+        at[na].id = cudaLaunchAttributeClusterDimension;
+        at[na].val.clusterDim.x = p.n_splits; at[na].val.clusterDim.y = 1; at[na].val.clusterDim.z = 1;
+        na++;
+    }
+    cfg.attrs = at; cfg.numAttrs = na;
+    if (p.head_dim == 64) {
+        cfg.dynamicSmemBytes = sizeof(AttnShared<64>);
+        return cluster ? cudaLaunchKernelEx(&cfg, attn_decode_batch_kernel<64, true>, p, tab, b)
+                       : cudaLaunchKernelEx(&cfg, attn_decode_batch_kernel<64, false>, p, tab, b);
+    } else if (p.head_dim == 128) {
+        cfg.dynamicSmemBytes = sizeof(AttnShared<128>);
+        return cluster ? cudaLaunchKernelEx(&cfg, attn_decode_batch_kernel<128, true>, p, tab, b)
+                       : cudaLaunchKernelEx(&cfg, attn_decode_batch_kernel<128, false>, p, tab, b);
+    }
+    return cudaErrorInvalidValue;
 }
 
 cudaError_t attn_decode_launch(const AttnParams& p, cudaStream_t stream, bool pdl) {

@@ -68,6 +68,7 @@ struct Slot {
     int n_decode_nodes = 0, n_pre_step_nodes = 0, n_pre_last_nodes = 0, n_fwd_nodes = 0;
     MvParams* mega_mv = nullptr;   // device tables for the persistent layer kernel (built on first use)
     AttnParams* mega_at = nullptr;
+    const float* logits_view = nullptr;   // where the latest logits of this slot are (own buffer, or a row of the batch output)
     int n_past = 0;                // host mirror of ints[1]
     int n_sampled = 0;             // host mirror of ints[3]
 };
@@ -100,6 +101,12 @@ struct b2_engine {
     size_t pf_part_floats = 0;
     __half *pf_xn = nullptr, *pf_qh = nullptr, *pf_att = nullptr, *pf_h = nullptr;
     int n_sms = 148;
+    // batched decode (several sequences per step through the GEMM path)
+    SlotDev* slot_tab = nullptr;   // device table, one entry per slot
+    float *bd_q = nullptr, *bd_att = nullptr, *bd_scratch = nullptr;
+    unsigned* bd_counters = nullptr;
+    int* bd_out = nullptr;
+    int batch_min = 4;             // fewer sequences than this step one after another through the mat-vec path
     bool gemm_ok = false;          // every layer matrix is a block format the GEMM reads
     int prefill_min = 8;           // prompts chunks shorter than this go token by token through the mat-vec path
     unsigned long long* mega_ts = nullptr;   // B2_MEGA_TS=1: phase timestamps of the last layer-kernel launch
@@ -218,6 +225,16 @@ extern "C" int b2_engine_create(const b2_config* c, b2_engine** out) {
         CK(cudaMalloc(&s.uniforms, sizeof(double) * 8192));
         CK(cudaMemset(s.uniforms, 0, sizeof(double) * 8192));
     }
+    {
+        std::vector<SlotDev> tab(c->max_seqs);
+        for (int i = 0; i < c->max_seqs; i++) {
+            Slot& s = e->slots[i];
+            tab[i].ints = s.ints; tab[i].block_table = s.block_table; tab[i].ring = s.ring;
+            tab[i].sst = s.sst; tab[i].sp = s.sp; tab[i].uniforms = s.uniforms;
+        }
+        CK(cudaMalloc(&e->slot_tab, sizeof(SlotDev) * c->max_seqs));
+        CK(cudaMemcpy(e->slot_tab, tab.data(), sizeof(SlotDev) * c->max_seqs, cudaMemcpyHostToDevice));
+    }
     CK(cudaStreamSynchronize(e->stream));
     *out = e;
     return B2_OK;
@@ -245,6 +262,8 @@ extern "C" int b2_engine_destroy(b2_engine* e) {
     cudaFree(e->mega_bar); cudaFree(e->mega_scratch); cudaFree(e->mega_counters);
     cudaFree(e->k_pool); cudaFree(e->v_pool); cudaFree(e->rope_freq);
     cudaFree(e->attn_scratch); cudaFree(e->attn_counters);
+    cudaFree(e->pf_x); cudaFree(e->pf_part); cudaFree(e->pf_xn); cudaFree(e->pf_qh); cudaFree(e->pf_att); cudaFree(e->pf_h);
+    cudaFree(e->slot_tab); cudaFree(e->bd_q); cudaFree(e->bd_att); cudaFree(e->bd_scratch); cudaFree(e->bd_counters); cudaFree(e->bd_out);
     cudaFreeHost(e->pinned);
     cudaEventDestroy(e->ev0); cudaEventDestroy(e->ev1);
     cudaStreamDestroy(e->stream);
@@ -386,6 +405,7 @@ extern "C" int b2_engine_finalize(b2_engine* e) {
         for (const DevTensor* t : {&L.wq, &L.wk, &L.wv, &L.wo, &L.wgate, &L.wup, &L.wdown})
             if (block_elems(t->type) == 1) e->gemm_ok = false;
     if (const char* s = getenv("B2_PREFILL_MIN")) if (atoi(s) > 0) e->prefill_min = atoi(s);
+    if (const char* s = getenv("B2_BATCH_MIN")) if (atoi(s) > 0) e->batch_min = atoi(s);
     if (e->gemm_ok) CK(gemm_init());
     e->finalized = true;
     return B2_OK;
@@ -524,6 +544,7 @@ static int record_step(b2_engine* e, Slot& s, GraphKind k, bool pdl) {
 
 // run one step of kind k for slot s, through a captured graph when enabled
 static int run_step(b2_engine* e, Slot& s, GraphKind k) {
+    s.logits_view = s.logits;
     cudaGraphExec_t* ge = k == GK_DECODE ? &s.g_decode : k == GK_PRE_STEP ? &s.g_pre_step : k == GK_PRE_LAST ? &s.g_pre_last : &s.g_fwd;
     int* nn = k == GK_DECODE ? &s.n_decode_nodes : k == GK_PRE_STEP ? &s.n_pre_step_nodes : k == GK_PRE_LAST ? &s.n_pre_last_nodes : &s.n_fwd_nodes;
     if (!e->use_graph) return record_step(e, s, k, e->use_pdl);
@@ -712,6 +733,7 @@ extern "C" int b2_prefill(b2_engine* e, int slot, const int32_t* tokens, int n) 
         MvParams h = e->p_head;
         h.x = s.x; h.y = s.logits;
         CK(mv_launch(h, e->n_ctas, e->stream, e->act2, false));
+        s.logits_view = s.logits;
         e->launches += 2;
     } else {
         for (int i = 0; i < n; i++) {
@@ -744,6 +766,69 @@ extern "C" int b2_sample(b2_engine* e, int slot, int32_t* out) {
     return B2_OK;
 }
 
+static int ensure_batch_workspace(b2_engine* e) {
+    int rc = ensure_prefill_workspace(e); if (rc) return rc;
+    if (e->bd_q) return B2_OK;
+    const b2_config& c = e->cfg;
+    const size_t qd = (size_t)c.n_head * c.head_dim;
+    CK(cudaMalloc(&e->bd_q, BATCH_MAX * qd * 4));
+    CK(cudaMalloc(&e->bd_att, BATCH_MAX * qd * 4));
+    CK(cudaMalloc(&e->bd_scratch, BATCH_MAX * attn_scratch_floats(c.n_head, c.n_head_kv, c.head_dim, e->n_splits) * 4));
+    CK(cudaMalloc(&e->bd_counters, sizeof(unsigned) * BATCH_MAX * c.n_head_kv));
+    CK(cudaMemsetAsync(e->bd_counters, 0, sizeof(unsigned) * BATCH_MAX * c.n_head_kv, e->stream));
+    CK(cudaMalloc(&e->bd_out, sizeof(int) * BATCH_MAX));
+    return B2_OK;
+}
+
+// One decode step for b.n sequences at once: the weights are read (and dequantised) once for all of them by the
+// tensor-core GEMM; attention and sampling run one CTA group per sequence from the per-slot device tables.
+static int batch_step(b2_engine* e, const BatchIdx& b) {
+    const b2_config& c = e->cfg;
+    cudaStream_t st = e->stream;
+    const int T = b.n, T_pad = (T + 15) / 16 * 16, E = c.n_embd, F = c.n_ff, hd = c.head_dim, qd = c.n_head * hd;
+    int rc, np = 0;
+    long ps = 0;
+    CK(embed_batch_launch(e->tok_embd.type, e->tok_embd.ptr, E, e->slot_tab, b, e->pf_x, st));
+    e->launches++;
+    for (int l = 0; l < c.n_layer; l++) {
+        Layer& L = e->layers[l];
+        __half* kc = e->k_pool + (size_t)l * e->layer_kv_elems;
+        __half* vc = e->v_pool + (size_t)l * e->layer_kv_elems;
+        CK(resid_norm_half_launch(e->pf_x, e->pf_part, np, ps, (const float*)L.attn_norm.ptr, c.rms_eps, E, T, T_pad, e->pf_xn, st));
+        const DevTensor* qkv[3] = {&L.wq, &L.wk, &L.wv};
+        if ((rc = gemm_call(e, qkv, 3, e->pf_xn, T, &np, &ps))) return rc;
+        CK(rope_store_batch_launch(e->pf_part, np, ps, e->slot_tab, b, c.n_head, c.n_head_kv, hd, c.kv_block_tokens, e->rope_freq,
+                                   e->bd_q, kc, vc, st));
+        AttnParams a = {};
+        a.q = e->bd_q; a.k_cache = kc; a.v_cache = vc; a.out = e->bd_att; a.scratch = e->bd_scratch; a.counters = e->bd_counters;
+        a.n_head = c.n_head; a.n_kv = c.n_head_kv; a.head_dim = hd; a.block_tokens = c.kv_block_tokens;
+        a.n_splits = e->n_splits; a.scale = 1.0f / sqrtf((float)hd); a.err = kernel_error_word(); a.max_pages = e->max_blocks;
+        CK(attn_decode_batch_launch(a, e->slot_tab, b, st));
+        CK(to_half_blocked_launch(e->bd_att, T, T_pad, qd, e->pf_att, st));
+        const DevTensor* wo[1] = {&L.wo};
+        if ((rc = gemm_call(e, wo, 1, e->pf_att, T, &np, &ps))) return rc;
+        CK(resid_norm_half_launch(e->pf_x, e->pf_part, np, ps, (const float*)L.ffn_norm.ptr, c.rms_eps, E, T, T_pad, e->pf_xn, st));
+        const DevTensor* gu[2] = {&L.wgate, &L.wup};
+        if ((rc = gemm_call(e, gu, 2, e->pf_xn, T, &np, &ps))) return rc;
+        CK(silu_mul_half_launch(e->pf_part, np, ps, F, T, T_pad, e->pf_h, st));
+        const DevTensor* wd[1] = {&L.wdown};
+        if ((rc = gemm_call(e, wd, 1, e->pf_h, T, &np, &ps))) return rc;
+        e->launches += 6;
+    }
+    // x += last ffn_down; output norm; lm_head (one K range: the logits are complete rows); sample every sequence
+    CK(resid_norm_half_launch(e->pf_x, e->pf_part, np, ps, (const float*)e->out_norm.ptr, c.rms_eps, E, T, T_pad, e->pf_xn, st));
+    {
+        GemmParams p = {};
+        p.nseg = 1; p.K = E; p.seg[0].w = e->output.ptr; p.seg[0].type = e->output.type; p.seg[0].n_rows = c.n_vocab;
+        p.x = e->pf_xn; p.T = T; p.y = e->pf_part; p.ldy = c.n_vocab; p.split_stride = 0; p.err = kernel_error_word();
+        if (gemm_plan(p, e->n_sms, 1)) return fail(B2_ERR_UNSUPPORTED, "GEMM shape not supported");
+        CK(gemm_launch(p, st));
+    }
+    CK(sample_batch_launch(e->pf_part, c.n_vocab, c.n_vocab, e->slot_tab, b, c.n_ctx + 1, e->bd_out, st));
+    e->launches += 3;
+    return B2_OK;
+}
+
 extern "C" int b2_decode(b2_engine* e, const int32_t* slots, int n, int32_t* out) {
     if (!e || !slots || n <= 0) return fail(B2_ERR_ARG, "bad arguments");
     if (!e->finalized) return fail(B2_ERR_STATE, "engine not finalized");
@@ -752,13 +837,33 @@ extern "C" int b2_decode(b2_engine* e, const int32_t* slots, int n, int32_t* out
     CK(cudaSetDevice(e->cfg.device));
     for (int i = 0; i < n; i++) {
         if (slots[i] < 0 || slots[i] >= (int)e->slots.size()) return fail(B2_ERR_ARG, "slot out of range");
-        Slot& s = e->slots[slots[i]];
-        if (s.n_past + 1 > e->cfg.n_ctx) return fail(B2_ERR_ARG, "context window full");
-        int rc = run_step(e, s, GK_DECODE);
-        if (rc) return rc;
-        CK(cudaMemcpyAsync(e->pinned + i, s.ints + 2, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
-        s.n_past += 1;
-        s.n_sampled += 1;
+        if (e->slots[slots[i]].n_past + 1 > e->cfg.n_ctx) return fail(B2_ERR_ARG, "context window full");
+        for (int j = 0; j < i; j++) if (slots[j] == slots[i]) return fail(B2_ERR_ARG, "slot listed twice");
+    }
+    const bool batched = e->gemm_ok && block_elems(e->output.type) != 1 && n >= e->batch_min &&
+                         (size_t)n * e->cfg.n_vocab <= (e->pf_part_floats ? e->pf_part_floats : (size_t)-1);
+    if (batched) {
+        int rc = ensure_batch_workspace(e); if (rc) return rc;
+        for (int i0 = 0; i0 < n; i0 += BATCH_MAX) {
+            BatchIdx b = {};
+            b.n = n - i0 < BATCH_MAX ? n - i0 : BATCH_MAX;
+            for (int i = 0; i < b.n; i++) b.slot[i] = slots[i0 + i];
+            if ((size_t)b.n * e->cfg.n_vocab > e->pf_part_floats) return fail(B2_ERR_UNSUPPORTED, "vocabulary too large for the batch workspace");
+            if ((rc = batch_step(e, b))) return rc;
+            // logits of this step stay in the batch output until the next GEMM call reuses the buffer
+            for (int i = 0; i < b.n; i++) e->slots[b.slot[i]].logits_view = e->pf_part + (size_t)i * e->cfg.n_vocab;
+            CK(cudaMemcpyAsync(e->pinned + i0, e->bd_out, sizeof(int) * b.n, cudaMemcpyDeviceToHost, e->stream));
+        }
+        for (int i = 0; i < n; i++) { Slot& s = e->slots[slots[i]]; s.n_past += 1; s.n_sampled += 1; }
+    } else {
+        for (int i = 0; i < n; i++) {
+            Slot& s = e->slots[slots[i]];
+            int rc = run_step(e, s, GK_DECODE);
+            if (rc) return rc;
+            CK(cudaMemcpyAsync(e->pinned + i, s.ints + 2, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+            s.n_past += 1;
+            s.n_sampled += 1;
+        }
     }
     CK(cudaStreamSynchronize(e->stream));
     { int rc2 = check_kernel_error(); if (rc2) return rc2; }
@@ -859,7 +964,8 @@ extern "C" int b2_get_logits(b2_engine* e, int slot, float* out) {
     int rc = check_slot(e, slot); if (rc) return rc;
     std::lock_guard<std::mutex> lk(e->mu);
     CK(cudaSetDevice(e->cfg.device));
-    CK(cudaMemcpyAsync(out, e->slots[slot].logits, sizeof(float) * e->cfg.n_vocab, cudaMemcpyDeviceToHost, e->stream));
+    const Slot& s = e->slots[slot];
+    CK(cudaMemcpyAsync(out, s.logits_view ? s.logits_view : s.logits, sizeof(float) * e->cfg.n_vocab, cudaMemcpyDeviceToHost, e->stream));
     CK(cudaStreamSynchronize(e->stream));
     return B2_OK;
 }
@@ -1029,25 +1135,27 @@ extern "C" int b2_op_gemm(int device, int type, const void* w, int n_rows, int K
     int be = block_elems(type), bb = block_bytes(type);
     if (be == 1 || !bb) return fail(B2_ERR_UNSUPPORTED, "weight type must be a quantised block format");
     if (K % 256) return fail(B2_ERR_ARG, "K must be a multiple of 256");
-    if (n_splits < 0 || n_splits > 16 || (n_splits > 0 && K / 64 / n_splits < 1)) return fail(B2_ERR_ARG, "bad n_splits");
+    if (n_splits < 0 || n_splits > 16) return fail(B2_ERR_ARG, "bad n_splits");
     CK(cudaSetDevice(device));
     CK(gemm_init());
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
     const size_t wbytes = (size_t)n_rows * (K / be) * bb, out_n = (size_t)T * n_rows;
+    DevBuf dw, dx, dxh, dpart, dyin, dy;
+    CK(dw.alloc(wbytes + 64));
+    CK(cudaMemcpy(dw.p, w, wbytes, cudaMemcpyHostToDevice));
     GemmParams p = {};
-    p.nseg = 1; p.K = K; p.seg[0].type = type; p.seg[0].n_rows = n_rows; p.seg[0].out_off = 0;
+    p.nseg = 1; p.K = K; p.seg[0].w = dw.as<uint8_t>(); p.seg[0].type = type; p.seg[0].n_rows = n_rows; p.seg[0].out_off = 0;
     p.T = T; p.ldy = n_rows; p.split_stride = (long)out_n; p.err = kernel_error_word();
     if (gemm_plan(p, sms, 16)) return fail(B2_ERR_UNSUPPORTED, "GEMM shape not supported");
     if (n_splits > 0) p.n_splits = n_splits;
-    DevBuf dw, dx, dxh, dpart, dyin, dy;
-    CK(dw.alloc(wbytes + 64)); CK(dx.alloc((size_t)T * K * 4)); CK(dxh.alloc((size_t)p.T_pad * K * 2));
+    if (p.n_splits > K / 256) p.n_splits = K / 256;
+    CK(dx.alloc((size_t)T * K * 4)); CK(dxh.alloc((size_t)p.T_pad * K * 2));
     CK(dpart.alloc(out_n * 4 * p.n_splits)); CK(dy.alloc(out_n * 4));
-    CK(cudaMemcpy(dw.p, w, wbytes, cudaMemcpyHostToDevice));
     CK(cudaMemcpy(dx.p, x, (size_t)T * K * 4, cudaMemcpyHostToDevice));
     CK(to_half_blocked_launch(dx.as<float>(), T, p.T_pad, K, dxh.as<__half>(), 0));
     if (y_in) { CK(dyin.alloc(out_n * 4)); CK(cudaMemcpy(dyin.p, y_in, out_n * 4, cudaMemcpyHostToDevice)); }
-    p.seg[0].w = dw.as<uint8_t>(); p.x = dxh.as<__half>(); p.y = dpart.as<float>();
+    p.x = dxh.as<__half>(); p.y = dpart.as<float>();
     CK(gemm_launch(p, 0));
     sum_parts_kernel<<<(unsigned)((out_n + 255) / 256), 256>>>(dpart.as<float>(), p.n_splits, (long)out_n,
                                                                y_in ? dyin.as<float>() : nullptr, (long)out_n, dy.as<float>());

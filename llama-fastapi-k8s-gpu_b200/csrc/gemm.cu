@@ -27,15 +27,20 @@
 #include "kernels.h"
 #include "ptx.cuh"
 #include "quant_blocks.cuh"
+#include <cuda.h>
 #include <cuda_fp16.h>
+#include <stdlib.h>
+#include <algorithm>
 
 namespace b2 {
 
-constexpr int GM_THREADS = 160;     // 4 dequantising warps + 1 control warp
+constexpr int GM_THREADS = 192;     // 4 dequantising warps + control warp (MMA, activation tiles) + weight-producer warp
 constexpr int GM_BM = 128;          // weight rows per CTA
 constexpr int GM_BK = 64;           // K per stage
 constexpr int GM_HDR = 256;         // barriers at the start of dynamic shared memory
 constexpr int GM_MAX_STAGES = 6;
+constexpr int GM_RAW_STAGES = 2;    // raw weight spans in flight (TMA), at most
+constexpr int GM_SPAN_WORDS = 68;   // largest 256-weight span: Q8_0, 272 bytes
 
 __device__ __forceinline__ void tmem_alloc(uint32_t* smem_dst, uint32_t ncols) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)), "r"(ncols) : "memory");
@@ -256,11 +261,48 @@ __device__ __forceinline__ void dequant_store(int type, const RawKB& r, int k0, 
 
 struct GemmBars {
     uint64_t a_full[GM_MAX_STAGES], b_full[GM_MAX_STAGES], empty[GM_MAX_STAGES];
+    uint64_t raw_full[GM_RAW_STAGES], raw_empty[GM_RAW_STAGES];
     uint32_t tmem_base;
 };
 static_assert(sizeof(GemmBars) <= GM_HDR, "barrier header");
 
-__global__ void __launch_bounds__(GM_THREADS) gemm_q_kernel(const GemmParams p) {
+// 2-D TMA tile load: box (inner = one 256-weight span of a row, outer = 128 rows) -> dense [128][box bytes] in smem
+__device__ __forceinline__ void tma_load_2d(void* dst, const void* tmap, int c0, int c1, uint64_t* bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 ::"r"(smem_u32(dst)), "l"(tmap), "r"(c0), "r"(c1), "r"(smem_u32(bar)) : "memory");
+}
+
+// words of one 64-weight block inside the 256-weight span W (registers; c is a compile-time constant after unrolling)
+template <int C>
+__device__ __forceinline__ void span_block(int type, const uint32_t (&W)[GM_SPAN_WORDS], RawKB& r) {
+    if (type == T_Q4_K) {
+#pragma unroll
+        for (int i = 0; i < 4; i++) r.w[i] = W[i];
+#pragma unroll
+        for (int i = 0; i < 8; i++) r.w[4 + i] = W[4 + 8 * C + i];
+    } else if (type == T_Q5_K) {
+#pragma unroll
+        for (int i = 0; i < 4; i++) r.w[i] = W[i];
+#pragma unroll
+        for (int i = 0; i < 8; i++) { r.w[4 + i] = W[12 + 8 * C + i]; r.w[12 + i] = W[4 + i]; }
+    } else if (type == T_Q6_K) {
+        constexpr int hf = C >> 1, nib = C & 1;
+#pragma unroll
+        for (int i = 0; i < 16; i++) r.w[i] = W[16 * hf + i];
+#pragma unroll
+        for (int i = 0; i < 8; i++) r.w[16 + i] = W[32 + 8 * hf + i];
+        r.w[24] = W[48 + 2 * hf + nib];
+        r.w[25] = W[52];
+    } else if (type == T_Q8_0) {
+#pragma unroll
+        for (int i = 0; i < 17; i++) r.w[i] = W[17 * C + i];
+    } else {
+#pragma unroll
+        for (int i = 0; i < 9; i++) r.w[i] = W[9 * C + i];
+    }
+}
+
+__global__ void __launch_bounds__(GM_THREADS) gemm_q_kernel(const __grid_constant__ GemmParams p) {
     extern __shared__ __align__(128) uint8_t smem_raw[];
     GemmBars& sh = *reinterpret_cast<GemmBars*>(smem_raw);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -268,22 +310,25 @@ __global__ void __launch_bounds__(GM_THREADS) gemm_q_kernel(const GemmParams p) 
     const uint32_t a_bytes = GM_BM * GM_BK * 2, b_bytes = (uint32_t)T * GM_BK * 2;
     const uint32_t stage_bytes = a_bytes + b_bytes;
     uint8_t* stage0 = smem_raw + GM_HDR;
+    uint8_t* raw0 = stage0 + (size_t)S * stage_bytes;                  // raw weight spans: GM_RAW_STAGES x [128][box]
     uint32_t ncols = 32;
     while ((int)ncols < T) ncols <<= 1;
 
-    // ---- which tile / K range
+    // ---- which tile / K range (in 256-weight spans = 4 blocks)
     const int split = blockIdx.x % p.n_splits, tile_g = blockIdx.x / p.n_splits;
     int seg = 0;
     while (seg + 1 < p.nseg && tile_g >= p.seg[seg + 1].tile0) seg++;
     const GemmSeg& sg = p.seg[seg];
     const int m0 = (tile_g - sg.tile0) * GM_BM;
-    const int n_kb_all = p.K / GM_BK;
-    const int kb0 = (int)((long)n_kb_all * split / p.n_splits), kb1 = (int)((long)n_kb_all * (split + 1) / p.n_splits);
-    const int n = kb1 - kb0;
+    const int n_sp_all = p.K / 256;
+    const int sp0 = (int)((long)n_sp_all * split / p.n_splits), sp1 = (int)((long)n_sp_all * (split + 1) / p.n_splits);
+    const int n_sp = sp1 - sp0, kb0 = sp0 * 4, n = n_sp * 4, NR = p.n_raw;
+    const uint32_t box = (uint32_t)sg.box_bytes, raw_stage_bytes = GM_BM * box;
 
     if (warp == 4) {
         if (lane == 0) {
             for (int i = 0; i < S; i++) { mbar_init(&sh.a_full[i], GM_BM); mbar_init(&sh.b_full[i], 1); mbar_init(&sh.empty[i], 1); }
+            for (int i = 0; i < GM_RAW_STAGES; i++) { mbar_init(&sh.raw_full[i], 1); mbar_init(&sh.raw_empty[i], GM_BM); }
             fence_mbar_init();
         }
         __syncwarp();
@@ -298,20 +343,70 @@ __global__ void __launch_bounds__(GM_THREADS) gemm_q_kernel(const GemmParams p) 
 
     if (warp < 4) {
         // ================= dequantising threads: thread <-> weight row
-        const int my_row = min(m0 + tid, sg.n_rows - 1);               // rows past N are computed and dropped
-        const uint8_t* wrow = sg.w + (size_t)my_row * sg.row_bytes;
         const int type = sg.type;
-        RawKB cur, nxt;
-        load_raw(type, wrow, kb0 * GM_BK, cur);
-        for (int i = 0; i < n; i++) {
+        auto emit = [&](const RawKB& r, int i) {           // block i of this CTA's range -> A tile of its stage
             const int s = i % S, use = i / S;
-            if (i + 1 < n) load_raw(type, wrow, (kb0 + i + 1) * GM_BK, nxt);     // in flight while this block is expanded
             if (use > 0) mbar_wait(&sh.empty[s], (use - 1) & 1, p.err, 0x40001u, (unsigned)i);   // MMAs that read the stage are done
             uint8_t* sa = stage0 + (size_t)s * stage_bytes;
-            dequant_store(type, cur, (kb0 + i) * GM_BK, sa + tid * 16, lbo_a);
+            dequant_store(type, r, (i & 3) * GM_BK, sa + tid * 16, lbo_a);
             fence_proxy_async();        // generic-proxy writes -> visible to the tensor core (async proxy)
             mbar_arrive(&sh.a_full[s]);
-            cur = nxt;
+        };
+        if (sg.use_tma) {
+            // raw spans arrive in shared memory by TMA; this thread's row is one box row
+            // the box starts at the 16-byte boundary below the span (TMA needs it); only Q6_K spans (210 B) can be off it
+            const int n16 = type == T_Q6_K ? 15 : (int)((sg.span_bytes + 15) / 16);
+            for (int sp = 0; sp < n_sp; sp++) {
+                const int rs = sp % NR, ruse = sp / NR;
+                mbar_wait(&sh.raw_full[rs], ruse & 1, p.err, 0x40006u, (unsigned)sp);
+                const uint8_t* slot = raw0 + (size_t)rs * raw_stage_bytes + (size_t)tid * box;
+                uint32_t W[GM_SPAN_WORDS];
+#pragma unroll
+                for (int j = 0; j < GM_SPAN_WORDS / 4; j++) {
+                    if (j < n16) {
+                        const uint4 v = *reinterpret_cast<const uint4*>(slot + 16 * j);
+                        W[4 * j] = v.x; W[4 * j + 1] = v.y; W[4 * j + 2] = v.z; W[4 * j + 3] = v.w;
+                    }
+                }
+                mbar_arrive(&sh.raw_empty[rs]);            // the span is in registers: the stage can be refilled
+                if (type == T_Q6_K) {                      // shift the 53 words of the span down by its misalignment (0,2,..14 bytes)
+                    const uint32_t mis = ((uint32_t)(sp0 + sp) * 210u) & 15u, sh16 = (mis & 2u) * 8u;
+                    switch (mis >> 2) {
+                        case 0:
+#pragma unroll
+                            for (int i = 0; i < 53; i++) W[i] = fshr(W[i], W[i + 1], sh16);
+                            break;
+                        case 1:
+#pragma unroll
+                            for (int i = 0; i < 53; i++) W[i] = fshr(W[i + 1], W[i + 2], sh16);
+                            break;
+                        case 2:
+#pragma unroll
+                            for (int i = 0; i < 53; i++) W[i] = fshr(W[i + 2], W[i + 3], sh16);
+                            break;
+                        default:
+#pragma unroll
+                            for (int i = 0; i < 53; i++) W[i] = fshr(W[i + 3], W[i + 4], sh16);
+                            break;
+                    }
+                }
+                RawKB r;
+                span_block<0>(type, W, r); emit(r, sp * 4 + 0);
+                span_block<1>(type, W, r); emit(r, sp * 4 + 1);
+                span_block<2>(type, W, r); emit(r, sp * 4 + 2);
+                span_block<3>(type, W, r); emit(r, sp * 4 + 3);
+            }
+        } else {
+            // rows that are not 16-byte multiples (Q6_K with K % 2048 != 0): direct loads, next block prefetched in registers
+            const int my_row = min(m0 + tid, sg.n_rows - 1);           // rows past N are computed and dropped
+            const uint8_t* wrow = sg.w + (size_t)my_row * sg.row_bytes;
+            RawKB cur, nxt;
+            load_raw(type, wrow, kb0 * GM_BK, cur);
+            for (int i = 0; i < n; i++) {
+                if (i + 1 < n) load_raw(type, wrow, (kb0 + i + 1) * GM_BK, nxt);
+                emit(cur, i);
+                cur = nxt;
+            }
         }
         // ================= epilogue: TMEM lane = tid
         const int last = n - 1;
@@ -329,7 +424,7 @@ __global__ void __launch_bounds__(GM_THREADS) gemm_q_kernel(const GemmParams p) 
                     if (c0 + j < p.T) ybase[(size_t)(c0 + j) * p.ldy] = v[j];
             }
         }
-    } else if (lane == 0) {
+    } else if (warp == 4 && lane == 0) {
         // ================= control thread: B tiles by TMA, MMA issue
         const uint32_t idesc_lo = instr_desc(GM_BM, T > 256 ? 256 : T);
         const uint32_t idesc_hi = T > 256 ? instr_desc(GM_BM, T - 256) : 0u;
@@ -364,6 +459,15 @@ __global__ void __launch_bounds__(GM_THREADS) gemm_q_kernel(const GemmParams p) 
                 load_b(ip + S);
             }
         }
+    } else if (warp == 5 && lane == 0 && sg.use_tma) {
+        // ================= weight producer: one 2-D TMA box (128 rows x one 256-weight span) per stage
+        const void* tmap = &sg.tmap;
+        for (int sp = 0; sp < n_sp; sp++) {
+            const int rs = sp % NR, ruse = sp / NR;
+            if (ruse > 0) mbar_wait(&sh.raw_empty[rs], (ruse - 1) & 1, p.err, 0x40007u, (unsigned)sp);
+            mbar_arrive_expect_tx(&sh.raw_full[rs], raw_stage_bytes);
+            tma_load_2d(raw0 + (size_t)rs * raw_stage_bytes, tmap, (int)((((size_t)(sp0 + sp) * sg.span_bytes) & ~(size_t)15) >> 1), m0, &sh.raw_full[rs]);
+        }
     }
     tc_fence_before();
     __syncthreads();
@@ -371,20 +475,41 @@ __global__ void __launch_bounds__(GM_THREADS) gemm_q_kernel(const GemmParams p) 
 }
 
 // ---------------------------------------------------------------- host side
-size_t gemm_smem_bytes(int T_pad, int n_stages) {
-    return GM_HDR + (size_t)n_stages * ((size_t)GM_BM * GM_BK * 2 + (size_t)T_pad * GM_BK * 2);
+static size_t gemm_raw_bytes(const GemmParams& p) {
+    size_t m = 0;
+    for (int s = 0; s < p.nseg; s++) if (p.seg[s].use_tma) m = std::max(m, (size_t)p.n_raw * GM_BM * p.seg[s].box_bytes);
+    return m;
+}
+size_t gemm_smem_bytes(const GemmParams& p) {
+    return GM_HDR + (size_t)p.n_stages * ((size_t)GM_BM * GM_BK * 2 + (size_t)p.T_pad * GM_BK * 2) + gemm_raw_bytes(p);
 }
 
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn g_encode = nullptr;
+
 cudaError_t gemm_init() {
+    if (!g_encode) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+        if (e != cudaSuccess) return e;
+        if (qres != cudaDriverEntryPointSuccess || !fn) return cudaErrorNotSupported;
+        g_encode = (EncodeTiledFn)fn;
+    }
     return cudaFuncSetAttribute(gemm_q_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
 }
 
-// Fill tile ranges, the stage count and the K split. n_sms: SMs to fill; max_splits: what the partial buffer allows.
+// Fill tile ranges, tensor maps, the stage count and the K split. n_sms: SMs to fill; max_splits: what the partial
+// buffer allows.
 int gemm_plan(GemmParams& p, int n_sms, int max_splits) {
+    static_assert(sizeof(CUtensorMap) == sizeof(p.seg[0].tmap), "tensor map storage");
     if (p.nseg < 1 || p.nseg > 3 || p.K <= 0 || p.K % 256) return -1;
     if (p.T < 1 || p.T > 512) return -2;
     p.T_pad = (p.T + 15) / 16 * 16;
     int tiles = 0;
+    const bool no_tma = getenv("B2_GEMM_NO_TMA") != nullptr;
     for (int s = 0; s < p.nseg; s++) {
         GemmSeg& g = p.seg[s];
         const int be = block_elems(g.type), bb = block_bytes(g.type);
@@ -393,25 +518,51 @@ int gemm_plan(GemmParams& p, int n_sms, int max_splits) {
         g.tile0 = tiles;
         g.n_tiles = (g.n_rows + GM_BM - 1) / GM_BM;
         tiles += g.n_tiles;
+        g.span_bytes = 256 / be * bb;                                  // one 256-weight span of a row
+        // box row = span rounded up to 16 B, and an odd multiple of 16 B so 128-bit shared loads of 8 rows hit 8 bank groups
+        int box = (g.span_bytes + 15) / 16 * 16;
+        if ((box / 16) % 2 == 0 || g.type == T_Q6_K) box = g.type == T_Q6_K ? 240 : box + 16;   // Q6_K: room for the 14-byte misalignment
+        g.box_bytes = box;
+        g.use_tma = 0;
+        if (!no_tma && g_encode && g.row_bytes % 16 == 0 && ((uintptr_t)g.w & 15) == 0 && (g.type != T_Q6_K || !getenv("B2_GEMM_Q6K_DIRECT"))) {
+            const cuuint64_t dims[2] = {(cuuint64_t)g.row_bytes / 2, (cuuint64_t)g.n_rows};
+            const cuuint64_t strides[1] = {(cuuint64_t)g.row_bytes};
+            const cuuint32_t boxd[2] = {(cuuint32_t)box / 2, (cuuint32_t)GM_BM};
+            const cuuint32_t estr[2] = {1, 1};
+            CUresult r = g_encode(reinterpret_cast<CUtensorMap*>(g.tmap), CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, (void*)g.w, dims, strides,
+                                  boxd, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                  CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+            g.use_tma = r == CUDA_SUCCESS ? 1 : 0;
+        }
     }
     p.n_tiles = tiles;
     const size_t stage = (size_t)GM_BM * GM_BK * 2 + (size_t)p.T_pad * GM_BK * 2;
-    // small T: several CTAs per SM hide the weight-load latency; each gets <= ~100 KB
-    const size_t budget = p.T_pad <= 128 ? 100 * 1024 : 227 * 1024 - 1024;
-    int S = (int)((budget - GM_HDR) / stage);
-    if (S > 4) S = 4;
-    if (S < 2) return -4;
+    const size_t cap = 227 * 1024 - 1024;
+    p.n_raw = GM_RAW_STAGES;
+    if (GM_HDR + 2 * stage + gemm_raw_bytes(p) > cap) p.n_raw = 1;       // T near 512 with wide spans: one raw stage
+    if (GM_HDR + 2 * stage + gemm_raw_bytes(p) > cap) for (int s = 0; s < p.nseg; s++) p.seg[s].use_tma = 0;
+    const size_t raw = gemm_raw_bytes(p);
+    // small T: two CTAs per SM (each <= ~112 KB) so one tile's epilogue overlaps the other's main loop
+    int per_sm = 1, S;
+    if (p.T_pad <= 64) { per_sm = 2; S = 2; }
+    else if (p.T_pad <= 128) { per_sm = 1; S = 4; }
+    else S = 4;
+    if (const char* v = getenv("B2_GEMM_PER_SM")) if (atoi(v) > 0) per_sm = atoi(v);
+    if (const char* v = getenv("B2_GEMM_STAGES")) if (atoi(v) > 1) S = atoi(v);
+    if (S > GM_MAX_STAGES) S = GM_MAX_STAGES;
+    while (S > 2 && GM_HDR + (size_t)S * stage + raw > cap) S--;
+    if (GM_HDR + (size_t)S * stage + raw > cap) return -4;
+    if (per_sm > 1 && (GM_HDR + (size_t)S * stage + raw + 1024) * per_sm > 228 * 1024) per_sm = 1;
     p.n_stages = S;
-    const int per_sm = p.T_pad <= 128 ? 2 : 1;
     const int slots = n_sms * per_sm;
-    const int n_kb = p.K / GM_BK;
+    const int n_sp = p.K / 256;
     // choose the K split that minimises (waves) x (blocks per CTA + fixed cost), fixed cost ~ epilogue + ramp
     const int fixed = 6 + p.T_pad / 32;
     long best_cost = -1;
     int best = 1;
-    for (int s = 1; s <= max_splits && s <= 16 && n_kb / s >= 4; s++) {
+    for (int s = 1; s <= max_splits && s <= 16 && s <= n_sp; s++) {
         const long waves = ((long)tiles * s + slots - 1) / slots;
-        const long cost = waves * ((n_kb + s - 1) / s + fixed);
+        const long cost = waves * (4 * ((n_sp + s - 1) / s) + fixed);
         if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = s; }
     }
     p.n_splits = best;
@@ -420,8 +571,8 @@ int gemm_plan(GemmParams& p, int n_sms, int max_splits) {
 
 cudaError_t gemm_launch(const GemmParams& p, cudaStream_t stream) {
     if (p.n_stages < 2 || p.n_stages > GM_MAX_STAGES || p.n_splits < 1 || p.n_tiles < 1) return cudaErrorInvalidValue;
-    if (p.T_pad < 16 || p.T_pad > 512 || p.T_pad % 16 || p.T > p.T_pad) return cudaErrorInvalidValue;
-    gemm_q_kernel<<<p.n_tiles * p.n_splits, GM_THREADS, gemm_smem_bytes(p.T_pad, p.n_stages), stream>>>(p);
+    if (p.T_pad < 16 || p.T_pad > 512 || p.T_pad % 16 || p.T > p.T_pad || p.n_splits > p.K / 256) return cudaErrorInvalidValue;
+    gemm_q_kernel<<<p.n_tiles * p.n_splits, GM_THREADS, gemm_smem_bytes(p), stream>>>(p);
     return cudaGetLastError();
 }
 

@@ -59,6 +59,20 @@ int mv_plan(MvParams& p, int n_ctas);
 size_t mv_smem_bytes(const MvParams& p);
 cudaError_t mv_launch(const MvParams& p, int n_ctas, cudaStream_t stream, bool act2, bool pdl);
 
+// ---------------------------------------------------------------- batched steps: per-slot device state
+struct SamplerState;
+struct SampleParams;
+struct SlotDev {              // one entry per sequence slot, device-resident table
+    int* ints;                // [0]=token [1]=pos [2]=out_token [3]=step ...
+    int* block_table;
+    int* ring;
+    SamplerState* sst;
+    SampleParams* sp;
+    double* uniforms;
+};
+constexpr int BATCH_MAX = 64;
+struct BatchIdx { int n; int slot[BATCH_MAX]; };   // passed by value: which slots take part in this step
+
 // ---------------------------------------------------------------- flash-decode (attention.cu)
 struct AttnParams {
     const float* q;          // [n_head * head_dim] float32 (already rotated)
@@ -77,6 +91,9 @@ struct AttnParams {
 cudaError_t attn_init();
 size_t attn_scratch_floats(int n_head, int n_kv, int head_dim, int n_splits);
 cudaError_t attn_decode_launch(const AttnParams& p, cudaStream_t stream, bool pdl);
+// one launch for b.n sequences: q / out are [b.n][n_head*head_dim]; position and page table come from tab[b.slot[z]];
+// scratch / counters need b.n times the single-sequence size
+cudaError_t attn_decode_batch_launch(const AttnParams& p, const SlotDev* tab, const BatchIdx& b, cudaStream_t stream);
 // allocation-free variant: split partials in a fixed device array inside the library (attention.cu)
 size_t attn_static_scratch_floats();
 cudaError_t attn_static_setup(int device);
@@ -105,6 +122,9 @@ struct GemmSeg {
     int type, n_rows;
     int out_off;            // column offset of this matrix in the output row
     int row_bytes, tile0, n_tiles;   // filled by gemm_plan
+    int span_bytes, box_bytes;       // one 256-weight span of a row; its (padded) row in the shared-memory box
+    int use_tma;                     // 1: spans are staged by 2-D TMA; 0: direct loads (rows not 16-byte multiples)
+    alignas(64) unsigned char tmap[128];   // CUtensorMap over the raw rows (u16 elements)
 };
 struct GemmParams {
     GemmSeg seg[3];         // matrices that share the input (q|k|v, gate|up)
@@ -115,11 +135,11 @@ struct GemmParams {
     int ldy;
     long split_stride;
     unsigned int* err;
-    int n_tiles, n_splits, n_stages;   // filled by gemm_plan
+    int n_tiles, n_splits, n_stages, n_raw;   // filled by gemm_plan
 };
 cudaError_t gemm_init();
 int gemm_plan(GemmParams& p, int n_sms, int max_splits);
-size_t gemm_smem_bytes(int T_pad, int n_stages);
+size_t gemm_smem_bytes(const GemmParams& p);
 cudaError_t gemm_launch(const GemmParams& p, cudaStream_t stream);
 cudaError_t to_half_blocked_launch(const float* x, int T, int T_pad, int K, __half* y, cudaStream_t s);
 
@@ -141,6 +161,11 @@ cudaError_t attn_prefill_launch(const __half* qh, const __half* k_cache, const _
                                 int T, int T_pad, int pos0, int n_head, int n_kv, int hd, int bt, __half* out, cudaStream_t s);
 // gate|up parts [T][2F] -> h = f16(silu(gate) * up) in operand order
 cudaError_t silu_mul_half_launch(const float* parts, int n_parts, long part_stride, int F, int T, int T_pad, __half* h, cudaStream_t s);
+// batched decode step (one token per slot of b)
+cudaError_t embed_batch_launch(int type, const uint8_t* table, int K, const SlotDev* tab, const BatchIdx& b, float* x, cudaStream_t s);
+cudaError_t rope_store_batch_launch(const float* parts, int n_parts, long part_stride, const SlotDev* tab, const BatchIdx& b,
+                                    int n_head, int n_kv, int hd, int bt, const float* rope_freq, float* q_out,
+                                    __half* k_cache, __half* v_cache, cudaStream_t s);
 cudaError_t prefill_finish_launch(const int* prompt, int n, int pos_last, int* ints, SamplerState* st, cudaStream_t s);
 
 // ---------------------------------------------------------------- small kernels (misc.cu)
@@ -170,5 +195,9 @@ struct SamplerState {            // per sequence slot, device resident
 cudaError_t sample_launch(float* logits, int n_vocab, const SampleParams* params_dev, SamplerState* st,
                           const double* uniforms, int* step_ptr, int* out_token, int* next_token_ptr,
                           int* pos_ptr, int* out_ring, int ring_len, cudaStream_t s, bool pdl);
+
+// logits row z (row_stride floats apart) belongs to slot b.slot[z]; also writes the token to out_tokens[z]
+cudaError_t sample_batch_launch(float* logits, long row_stride, int n_vocab, const SlotDev* tab, const BatchIdx& b,
+                                int ring_len, int* out_tokens, cudaStream_t s);
 
 }  // namespace b2

@@ -36,17 +36,23 @@ cudaError_t embed_rows_launch(int type, const uint8_t* table, int K, const int* 
 __device__ __forceinline__ size_t op_index(int t, int k, int T_pad) { return ((size_t)(k >> 3) * T_pad + t) * 8 + (k & 7); }
 
 // ---------------------------------------------------------------- residual add + RMSNorm -> f16
-__global__ void __launch_bounds__(256) resid_norm_half_kernel(float* x, const float* parts, int n_parts, long part_stride,
-                                                              const float* w, float eps, int K, int T_pad, __half* xn) {
-    __shared__ float red[8];
+constexpr int RN_THREADS = 1024;
+__global__ void __launch_bounds__(RN_THREADS) resid_norm_half_kernel(float* x, const float* parts, int n_parts, long part_stride,
+                                                                     const float* w, float eps, int K, int T_pad, __half* xn) {
+    __shared__ float red[RN_THREADS / 32];
     const int t = blockIdx.x;
     float* xr = x + (size_t)t * K;
     float ss = 0.f;
-    for (int i = threadIdx.x; i < K; i += 256) {
-        float v = xr[i];
-        for (int s = 0; s < n_parts; s++) v += parts[(size_t)s * part_stride + (size_t)t * K + i];
-        if (n_parts) xr[i] = v;
-        ss += v * v;
+    for (int i = threadIdx.x; i < K / 4; i += RN_THREADS) {          // float4 per thread: the split sums are independent loads
+        float4 v = *reinterpret_cast<const float4*>(xr + 4 * i);
+        const float* pp = parts + (size_t)t * K + 4 * i;
+#pragma unroll 4
+        for (int s = 0; s < n_parts; s++) {
+            const float4 q = *reinterpret_cast<const float4*>(pp + (size_t)s * part_stride);
+            v.x += q.x; v.y += q.y; v.z += q.z; v.w += q.w;
+        }
+        if (n_parts) *reinterpret_cast<float4*>(xr + 4 * i) = v;
+        ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
     }
     if (!w) return;
     ss = warp_sum(ss);
@@ -54,9 +60,9 @@ __global__ void __launch_bounds__(256) resid_norm_half_kernel(float* x, const fl
     __syncthreads();
     float tot = 0.f;
 #pragma unroll
-    for (int i = 0; i < 8; i++) tot += red[i];
+    for (int i = 0; i < RN_THREADS / 32; i++) tot += red[i];
     const float r = rsqrtf(tot / (float)K + eps);
-    for (int c = threadIdx.x; c < K / 8; c += 256) {                   // 8 consecutive k = one 16-byte run in operand order
+    for (int c = threadIdx.x; c < K / 8; c += RN_THREADS) {            // 8 consecutive k = one 16-byte run in operand order
         const float4 a = *reinterpret_cast<const float4*>(xr + 8 * c), b = *reinterpret_cast<const float4*>(xr + 8 * c + 4);
         const float4 wa = *reinterpret_cast<const float4*>(w + 8 * c), wb = *reinterpret_cast<const float4*>(w + 8 * c + 4);
         const __half2 h0 = __floats2half2_rn(a.x * r * wa.x, a.y * r * wa.y), h1 = __floats2half2_rn(a.z * r * wa.z, a.w * r * wa.w);
@@ -68,7 +74,7 @@ __global__ void __launch_bounds__(256) resid_norm_half_kernel(float* x, const fl
 }
 cudaError_t resid_norm_half_launch(float* x, const float* parts, int n_parts, long part_stride, const float* w, float eps,
                                    int K, int T, int T_pad, __half* xn, cudaStream_t s) {
-    resid_norm_half_kernel<<<T, 256, 0, s>>>(x, parts, n_parts, part_stride, w, eps, K, T_pad, xn);
+    resid_norm_half_kernel<<<T, RN_THREADS, 0, s>>>(x, parts, n_parts, part_stride, w, eps, K, T_pad, xn);
     return cudaGetLastError();
 }
 
@@ -84,6 +90,7 @@ __global__ void rope_store_kernel(const float* parts, int n_parts, long part_str
     for (int pi = threadIdx.x; pi < row_len / 2; pi += blockDim.x) {
         const int e = 2 * pi;
         float v0 = 0.f, v1 = 0.f;
+#pragma unroll 4
         for (int s = 0; s < n_parts; s++) {
             const float2 v = *reinterpret_cast<const float2*>(r + (size_t)s * part_stride + e);
             v0 += v.x; v1 += v.y;
@@ -109,7 +116,7 @@ __global__ void rope_store_kernel(const float* parts, int n_parts, long part_str
 cudaError_t rope_store_launch(const float* parts, int n_parts, long part_stride, int T, int pos0, int n_head, int n_kv, int hd,
                               int bt, const int* block_table, const float* rope_freq, __half* qh, __half* k_cache,
                               __half* v_cache, cudaStream_t s) {
-    rope_store_kernel<<<T, 256, 0, s>>>(parts, n_parts, part_stride, T, pos0, n_head, n_kv, hd, bt, block_table, rope_freq, qh, k_cache, v_cache);
+    rope_store_kernel<<<T, 1024, 0, s>>>(parts, n_parts, part_stride, T, pos0, n_head, n_kv, hd, bt, block_table, rope_freq, qh, k_cache, v_cache);
     return cudaGetLastError();
 }
 
@@ -139,6 +146,62 @@ __global__ void silu_mul_half_kernel(const float* parts, int n_parts, long part_
 cudaError_t silu_mul_half_launch(const float* parts, int n_parts, long part_stride, int F, int T, int T_pad, __half* h, cudaStream_t s) {
     const long n = (long)T * (F / 8);
     silu_mul_half_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(parts, n_parts, part_stride, F, T, T_pad, h);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------- batched decode step: one token per slot
+__global__ void embed_batch_kernel(int type, const uint8_t* table, int K, const SlotDev* tab, const BatchIdx b, float* x) {
+    const int t = blockIdx.x;
+    const int tok = tab[b.slot[t]].ints[0];
+    const int be = block_elems(type), bb = block_bytes(type);
+    const uint8_t* row = table + (size_t)tok * (K / be) * bb;
+    for (int i = threadIdx.x; i < K; i += blockDim.x)
+        x[(size_t)t * K + i] = dequant_elem(type, row + (size_t)(i / be) * bb, i % be);
+}
+cudaError_t embed_batch_launch(int type, const uint8_t* table, int K, const SlotDev* tab, const BatchIdx& b, float* x, cudaStream_t s) {
+    embed_batch_kernel<<<b.n, 256, 0, s>>>(type, table, K, tab, b, x);
+    return cudaGetLastError();
+}
+
+// like rope_store, but row t belongs to slot b.slot[t] at that slot's own position; q stays float32 for flash-decode
+__global__ void rope_store_batch_kernel(const float* parts, int n_parts, long part_stride, const SlotDev* tab, const BatchIdx b,
+                                        int n_head, int n_kv, int hd, int bt, const float* rope_freq, float* q_out,
+                                        __half* k_cache, __half* v_cache) {
+    const int t = blockIdx.x;
+    const SlotDev sd = tab[b.slot[t]];
+    const int pos = sd.ints[1];
+    const int nq = n_head * hd, nk = n_kv * hd, row_len = nq + 2 * nk;
+    const float* r = parts + (size_t)t * row_len;
+    const int page = sd.block_table[pos / bt], slot = pos % bt;
+    for (int pi = threadIdx.x; pi < row_len / 2; pi += blockDim.x) {
+        const int e = 2 * pi;
+        float v0 = 0.f, v1 = 0.f;
+#pragma unroll 4
+        for (int s = 0; s < n_parts; s++) {
+            const float2 v = *reinterpret_cast<const float2*>(r + (size_t)s * part_stride + e);
+            v0 += v.x; v1 += v.y;
+        }
+        if (e < nq + nk) {
+            const int i = (e % hd) >> 1;
+            float sn, cs;
+            sincosf((float)pos * rope_freq[i], &sn, &cs);
+            const float a = v0 * cs - v1 * sn, c = v0 * sn + v1 * cs;
+            v0 = a; v1 = c;
+        }
+        if (e < nq) {
+            *reinterpret_cast<float2*>(q_out + (size_t)t * nq + e) = make_float2(v0, v1);
+        } else {
+            const int ee = e < nq + nk ? e - nq : e - nq - nk;
+            const int kvh = ee / hd, d = ee % hd;
+            const size_t idx = (((size_t)page * n_kv + kvh) * bt + slot) * hd + d;
+            *reinterpret_cast<__half2*>((e < nq + nk ? k_cache : v_cache) + idx) = __floats2half2_rn(v0, v1);
+        }
+    }
+}
+cudaError_t rope_store_batch_launch(const float* parts, int n_parts, long part_stride, const SlotDev* tab, const BatchIdx& b,
+                                    int n_head, int n_kv, int hd, int bt, const float* rope_freq, float* q_out,
+                                    __half* k_cache, __half* v_cache, cudaStream_t s) {
+    rope_store_batch_kernel<<<b.n, 1024, 0, s>>>(parts, n_parts, part_stride, tab, b, n_head, n_kv, hd, bt, rope_freq, q_out, k_cache, v_cache);
     return cudaGetLastError();
 }
 

@@ -58,15 +58,13 @@ __device__ void select_bin(SmShared& sh, int nbins, unsigned k) {
     __syncthreads();
 }
 
-__global__ void __launch_bounds__(SM_THREADS) sample_kernel(float* logits, int V, const SampleParams* prm,
-                                                            SamplerState* st, const double* uniforms,
-                                                            int n_uniform, int* step_ptr, int* out_token,
-                                                            int* next_token_ptr, int* pos_ptr, int* out_ring,
-                                                            int ring_len) {
+__device__ __forceinline__ void sample_body(float* logits, int V, const SampleParams* prm,
+                                            SamplerState* st, const double* uniforms,
+                                            int n_uniform, int* step_ptr, int* out_token,
+                                            int* next_token_ptr, int* pos_ptr, int* out_ring,
+                                            int ring_len, int* out_token2) {
     __shared__ SmShared sh;
     const int t = threadIdx.x, lane = t & 31, w = t >> 5;
-    griddep_launch();
-    griddep_wait();
     const SampleParams P = *prm;
     const int n_hist = st->n_hist;
 
@@ -216,6 +214,7 @@ __global__ void __launch_bounds__(SM_THREADS) sample_kernel(float* logits, int V
     }
     if (t == 0) {
         *out_token = result;
+        if (out_token2) *out_token2 = result;
         *next_token_ptr = result;
         *step_ptr = *step_ptr + 1;      // one uniform consumed per sampled token (greedy too)
         st->history[n_hist & (HISTORY_LEN - 1)] = result;
@@ -226,7 +225,30 @@ __global__ void __launch_bounds__(SM_THREADS) sample_kernel(float* logits, int V
     }
 }
 
-struct SampleLaunchArgs { int dummy; };
+__global__ void __launch_bounds__(SM_THREADS) sample_kernel(float* logits, int V, const SampleParams* prm,
+                                                            SamplerState* st, const double* uniforms,
+                                                            int n_uniform, int* step_ptr, int* out_token,
+                                                            int* next_token_ptr, int* pos_ptr, int* out_ring,
+                                                            int ring_len) {
+    griddep_launch();
+    griddep_wait();
+    sample_body(logits, V, prm, st, uniforms, n_uniform, step_ptr, out_token, next_token_ptr, pos_ptr, out_ring, ring_len, nullptr);
+}
+
+// one CTA per sequence of the batch
+__global__ void __launch_bounds__(SM_THREADS) sample_batch_kernel(float* logits, long row_stride, int V, const SlotDev* tab,
+                                                                  const BatchIdx b, int n_uniform, int ring_len, int* out_tokens) {
+    const int z = blockIdx.x;
+    const SlotDev sd = tab[b.slot[z]];
+    sample_body(logits + (size_t)z * row_stride, V, sd.sp, sd.sst, sd.uniforms, n_uniform, sd.ints + 3, sd.ints + 2, sd.ints + 0,
+                sd.ints + 1, sd.ring, ring_len, out_tokens + z);
+}
+
+cudaError_t sample_batch_launch(float* logits, long row_stride, int n_vocab, const SlotDev* tab, const BatchIdx& b,
+                                int ring_len, int* out_tokens, cudaStream_t s) {
+    sample_batch_kernel<<<b.n, SM_THREADS, 0, s>>>(logits, row_stride, n_vocab, tab, b, 8192, ring_len, out_tokens);
+    return cudaGetLastError();
+}
 
 cudaError_t sample_launch(float* logits, int n_vocab, const SampleParams* params_dev, SamplerState* st,
                           const double* uniforms, int* step_ptr, int* out_token, int* next_token_ptr,

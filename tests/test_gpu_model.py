@@ -241,3 +241,60 @@ def test_tensor_core_prefill_agrees_with_token_by_token(native_lib, tmp_models, 
         eng.close()
     assert np.abs(outs[0][1] - outs[1][1]).max() <= LOGIT_TOL
     assert outs[0][0] == outs[1][0]
+
+
+@pytest.mark.parametrize("arch,ftype,seed", [("tiny", "Q4_K_M", 1), ("tiny128", "Q8_0", 6)])
+def test_batched_decode_matches_oracle_and_serial_path(native_lib, tmp_models, arch, ftype, seed, monkeypatch):
+    """>= 4 sequences per b2_decode call step together through the tensor-core GEMM (weights read once per
+    step), each at its own position with its own pages and sampler state. Greedy continuations must equal the
+    one-sequence-at-a-time path wherever the oracle's top-2 margin is clear, logits within the tolerance."""
+    from oracle.llama_ref import RefModel
+    path = _model(tmp_models, arch, ftype, seed)
+    ref = RefModel(path)
+    rng = np.random.default_rng(11)
+    prompts = [[int(t) for t in rng.integers(3, 700, size=n)] for n in (5, 9, 17, 30, 12, 3)]
+    n_new = 10
+    runs = {}
+    for mode in ("serial", "batched"):
+        monkeypatch.setenv("B2_BATCH_MIN", "100" if mode == "serial" else "4")
+        eng = _engine(path, max_seqs=8, n_ctx=128)
+        for s, pr in enumerate(prompts):
+            eng.ensure_pages(s, len(pr) + n_new + 2)
+            eng.seq_begin(s, 0, [], _greedy())
+            eng.prefill(s, pr)
+        seqs = [[eng.sample(s)] for s in range(len(prompts))]
+        for _ in range(n_new - 1):
+            for s, t in enumerate(eng.decode(list(range(len(prompts))))):
+                seqs[s].append(t)
+        runs[mode] = (seqs, [eng.logits(s).copy() for s in range(len(prompts))])
+        eng.close()
+    for s, pr in enumerate(prompts):
+        serial, batched = runs["serial"][0][s], runs["batched"][0][s]
+        # oracle logits along the serial continuation: tokens must agree wherever the margin is clear
+        full = pr + serial
+        ref.reset()                      # the oracle appends to its own KV cache: one sequence per reset
+        lg = ref.forward(full)
+        for i in range(n_new):
+            row = lg[len(pr) - 1 + i]
+            top2 = np.sort(row)[-2:]
+            if batched[:i] != serial[:i]:
+                break
+            if top2[1] - top2[0] >= 10 * LOGIT_TOL:
+                assert batched[i] == serial[i] == int(np.argmax(row)), (s, i)
+        if batched == serial:
+            assert np.abs(runs["batched"][1][s] - runs["serial"][1][s]).max() <= LOGIT_TOL
+            assert np.abs(runs["batched"][1][s] - lg[len(full) - 2]).max() <= LOGIT_TOL
+
+
+def test_batched_decode_rejects_duplicate_slots(native_lib, tmp_models):
+    from llama_cpp._cabi import B2Error
+    path = _model(tmp_models, "tiny", "Q4_K_M", 1)
+    eng = _engine(path, max_seqs=4)
+    for s in range(2):
+        eng.ensure_pages(s, 16)
+        eng.seq_begin(s, 0, [], _greedy())
+        eng.prefill(s, TOKENS[:4])
+        eng.sample(s)
+    with pytest.raises(B2Error):
+        eng.decode([0, 1, 0])
+    eng.close()
