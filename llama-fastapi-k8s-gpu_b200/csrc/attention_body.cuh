@@ -154,6 +154,7 @@ __device__ __forceinline__ void attn_decode_body(const AttnParams& p, AttnShared
                 if (i < hg3 && g < G) { float pj = sh.sc[0][g][j]; acc[i][0] += pj * vv.x; acc[i][1] += pj * vv.y; }
             }
         }
+        fence_proxy_async();                   // this thread's reads of the tile before the next TMA (async proxy) rewrites it
         named_bar_sync(AT_BAR, AT_THREADS);    // tile buffers and sc[] are free again
     }
 

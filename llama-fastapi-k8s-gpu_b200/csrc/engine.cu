@@ -802,7 +802,11 @@ static int batch_step(b2_engine* e, const BatchIdx& b) {
         AttnParams a = {};
         a.q = e->bd_q; a.k_cache = kc; a.v_cache = vc; a.out = e->bd_att; a.scratch = e->bd_scratch; a.counters = e->bd_counters;
         a.n_head = c.n_head; a.n_kv = c.n_head_kv; a.head_dim = hd; a.block_tokens = c.kv_block_tokens;
-        a.n_splits = e->n_splits; a.scale = 1.0f / sqrtf((float)hd); a.err = kernel_error_word(); a.max_pages = e->max_blocks;
+        // enough CTAs to fill the GPU ~4x over, no more: every extra split of a sequence re-pays the kernel's fixed latency
+        int ns = e->n_splits;
+        while (ns > 1 && (long)ns * c.n_head_kv * T > 4L * e->n_sms) ns >>= 1;
+        if (const char* v = getenv("B2_BATCH_ATTN_SPLITS")) if (atoi(v) > 0 && atoi(v) <= e->n_splits) ns = atoi(v);
+        a.n_splits = ns; a.scale = 1.0f / sqrtf((float)hd); a.err = kernel_error_word(); a.max_pages = e->max_blocks;
         CK(attn_decode_batch_launch(a, e->slot_tab, b, st));
         CK(to_half_blocked_launch(e->bd_att, T, T_pad, qd, e->pf_att, st));
         const DevTensor* wo[1] = {&L.wo};
@@ -1156,6 +1160,8 @@ extern "C" int b2_op_gemm(int device, int type, const void* w, int n_rows, int K
     CK(to_half_blocked_launch(dx.as<float>(), T, p.T_pad, K, dxh.as<__half>(), 0));
     if (y_in) { CK(dyin.alloc(out_n * 4)); CK(cudaMemcpy(dyin.p, y_in, out_n * 4, cudaMemcpyHostToDevice)); }
     p.x = dxh.as<__half>(); p.y = dpart.as<float>();
+    DevBuf ddbg;
+    if (getenv("B2_GEMM_DBG")) { CK(ddbg.alloc(64 * 8 * 8)); CK(cudaMemset(ddbg.p, 0, 64 * 8 * 8)); p.dbg = ddbg.as<long long>(); }
     CK(gemm_launch(p, 0));
     sum_parts_kernel<<<(unsigned)((out_n + 255) / 256), 256>>>(dpart.as<float>(), p.n_splits, (long)out_n,
                                                                y_in ? dyin.as<float>() : nullptr, (long)out_n, dy.as<float>());
@@ -1163,6 +1169,16 @@ extern "C" int b2_op_gemm(int device, int type, const void* w, int n_rows, int K
     CK(cudaDeviceSynchronize());
     if (int rc = check_kernel_error()) return rc;
     CK(cudaMemcpy(y, dy.p, out_n * 4, cudaMemcpyDeviceToHost));
+    if (p.dbg) {      // debugging aid: pipeline timeline of CTA 0, cycles relative to the first record
+        std::vector<long long> t(64 * 8);
+        cudaMemcpy(t.data(), ddbg.p, t.size() * 8, cudaMemcpyDeviceToHost);
+        long long t0 = t[0];
+        fprintf(stderr, "[b2 gemm] stages A %d B %d raw %d splits %d; per K block: deq(wait_empty, got, arrived) mma(b_ok, a_ok, committed) raw(wait, got)\n",
+                p.n_stages, p.n_bstages, p.n_raw, p.n_splits);
+        for (int i = 0; i < 24; i++)
+            fprintf(stderr, "[b2 gemm] kb %2d  deq %7lld %7lld %7lld   mma %7lld %7lld %7lld   raw %7lld %7lld\n", i, t[i * 8] - t0, t[i * 8 + 1] - t0,
+                    t[i * 8 + 2] - t0, t[i * 8 + 3] - t0, t[i * 8 + 4] - t0, t[i * 8 + 5] - t0, t[i * 8 + 6] ? t[i * 8 + 6] - t0 : 0, t[i * 8 + 7] ? t[i * 8 + 7] - t0 : 0);
+    }
     return B2_OK;
 }
 

@@ -34,11 +34,12 @@
 
 namespace b2 {
 
-constexpr int GM_THREADS = 192;     // 4 dequantising warps + control warp (MMA, activation tiles) + weight-producer warp
+constexpr int GM_THREADS = 224;     // 4 dequantising warps + MMA warp + weight-producer warp + activation-producer warp
 constexpr int GM_BM = 128;          // weight rows per CTA
 constexpr int GM_BK = 64;           // K per stage
-constexpr int GM_HDR = 256;         // barriers at the start of dynamic shared memory
-constexpr int GM_MAX_STAGES = 6;
+constexpr int GM_HDR = 512;         // barriers at the start of dynamic shared memory
+constexpr int GM_MAX_STAGES = 6;     // A-tile ring
+constexpr int GM_MAX_BSTAGES = 8;    // activation-tile ring
 constexpr int GM_RAW_STAGES = 2;    // raw weight spans in flight (TMA), at most
 constexpr int GM_SPAN_WORDS = 68;   // largest 256-weight span: Q8_0, 272 bytes
 
@@ -80,6 +81,11 @@ __device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo, uint3
     d |= (uint64_t)((sbo >> 4) & 0x3FFF) << 32;
     d |= (uint64_t)1 << 46;                  // descriptor version (sm_100)
     return d;                                // layout_type = 0: no swizzle
+}
+__device__ __forceinline__ uint64_t desc_join(uint32_t lo, uint32_t hi) {
+    uint64_t d;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "r"(lo), "r"(hi));
+    return d;
 }
 // instruction descriptor: D = f32, A = B = f16, both K-major, M x N
 __device__ __forceinline__ uint32_t instr_desc(int M, int N) {
@@ -260,7 +266,8 @@ __device__ __forceinline__ void dequant_store(int type, const RawKB& r, int k0, 
 }
 
 struct GemmBars {
-    uint64_t a_full[GM_MAX_STAGES], b_full[GM_MAX_STAGES], empty[GM_MAX_STAGES];
+    uint64_t a_full[GM_MAX_STAGES], empty[GM_MAX_STAGES];
+    uint64_t b_full[GM_MAX_BSTAGES], b_empty[GM_MAX_BSTAGES];
     uint64_t raw_full[GM_RAW_STAGES], raw_empty[GM_RAW_STAGES];
     uint32_t tmem_base;
 };
@@ -302,15 +309,102 @@ __device__ __forceinline__ void span_block(int type, const uint32_t (&W)[GM_SPAN
     }
 }
 
+struct DeqCtx {
+    GemmBars* sh;
+    uint8_t* stage0;
+    const uint8_t* raw0;
+    const uint8_t* wrow;
+    int S, NR, tid, n, n_sp, sp0, kb0, use_tma, span_bytes;
+    uint32_t raw_stage_bytes, box;
+    unsigned int* err;
+    long long* dbg;
+};
+
+template <int TYPE>
+__device__ __noinline__ void deq_loop(const DeqCtx cx) {
+    GemmBars& sh = *cx.sh;
+    constexpr uint32_t a_bytes = GM_BM * GM_BK * 2, lbo_a = GM_BM * 16;
+    int st = 0;                 // A stage of the next block and how often the ring has wrapped
+    uint32_t wraps = 0;
+    auto emit = [&](const RawKB& r, int i) {               // block i of this CTA's range -> A tile of its stage
+        if (cx.dbg && i < 64) cx.dbg[i * 8 + 0] = clock64();
+        if (wraps > 0) mbar_wait(&sh.empty[st], (wraps - 1) & 1, cx.err, 0x40001u, (unsigned)i);   // MMAs that read the stage are done
+        if (cx.dbg && i < 64) cx.dbg[i * 8 + 1] = clock64();
+        dequant_store(TYPE, r, (i & 3) * GM_BK, cx.stage0 + (size_t)st * a_bytes + cx.tid * 16, lbo_a);
+        fence_proxy_async();            // generic-proxy writes -> visible to the tensor core (async proxy)
+        mbar_arrive(&sh.a_full[st]);
+        if (cx.dbg && i < 64) cx.dbg[i * 8 + 2] = clock64();
+        if (++st == cx.S) { st = 0; wraps++; }
+    };
+    if (cx.use_tma) {
+        // raw spans arrive in shared memory by TMA; this thread's row is one box row. The box starts at the 16-byte
+        // boundary below the span (TMA needs it); only Q6_K spans (210 B) can be off it.
+        constexpr int span = TYPE == T_Q4_K ? 144 : TYPE == T_Q5_K ? 176 : TYPE == T_Q6_K ? 210 : TYPE == T_Q8_0 ? 272 : 144;
+        constexpr int n16 = TYPE == T_Q6_K ? 15 : (span + 15) / 16;
+        int rs = 0;
+        uint32_t rwraps = 0;
+        for (int sp = 0; sp < cx.n_sp; sp++) {
+            if (cx.dbg && sp < 16) cx.dbg[sp * 4 * 8 + 6] = clock64();
+            mbar_wait(&sh.raw_full[rs], rwraps & 1, cx.err, 0x40006u, (unsigned)sp);
+            if (cx.dbg && sp < 16) cx.dbg[sp * 4 * 8 + 7] = clock64();
+            const uint8_t* slot = cx.raw0 + (size_t)rs * cx.raw_stage_bytes + (size_t)cx.tid * cx.box;
+            uint32_t W[GM_SPAN_WORDS];
+#pragma unroll
+            for (int j = 0; j < n16; j++) {
+                const uint4 v = *reinterpret_cast<const uint4*>(slot + 16 * j);
+                W[4 * j] = v.x; W[4 * j + 1] = v.y; W[4 * j + 2] = v.z; W[4 * j + 3] = v.w;
+            }
+            fence_proxy_async();                           // these generic-proxy reads before the TMA (async proxy) rewrite
+            mbar_arrive(&sh.raw_empty[rs]);                // the span is in registers: the stage can be refilled
+            if (++rs == cx.NR) { rs = 0; rwraps++; }
+            if (TYPE == T_Q6_K) {                          // shift the 53 words of the span down by its misalignment (0,2,..14 bytes)
+                const uint32_t mis = ((uint32_t)(cx.sp0 + sp) * 210u) & 15u, sh16 = (mis & 2u) * 8u;
+                switch (mis >> 2) {
+                    case 0:
+#pragma unroll
+                        for (int i = 0; i < 53; i++) W[i] = fshr(W[i], W[i + 1], sh16);
+                        break;
+                    case 1:
+#pragma unroll
+                        for (int i = 0; i < 53; i++) W[i] = fshr(W[i + 1], W[i + 2], sh16);
+                        break;
+                    case 2:
+#pragma unroll
+                        for (int i = 0; i < 53; i++) W[i] = fshr(W[i + 2], W[i + 3], sh16);
+                        break;
+                    default:
+#pragma unroll
+                        for (int i = 0; i < 53; i++) W[i] = fshr(W[i + 3], W[i + 4], sh16);
+                        break;
+                }
+            }
+            RawKB r;
+            span_block<0>(TYPE, W, r); emit(r, sp * 4 + 0);
+            span_block<1>(TYPE, W, r); emit(r, sp * 4 + 1);
+            span_block<2>(TYPE, W, r); emit(r, sp * 4 + 2);
+            span_block<3>(TYPE, W, r); emit(r, sp * 4 + 3);
+        }
+    } else {
+        // rows that are not 16-byte multiples (Q6_K with K % 2048 != 0): direct loads, next block prefetched in registers
+        RawKB cur, nxt;
+        load_raw(TYPE, cx.wrow, cx.kb0 * GM_BK, cur);
+        for (int i = 0; i < cx.n; i++) {
+            if (i + 1 < cx.n) load_raw(TYPE, cx.wrow, (cx.kb0 + i + 1) * GM_BK, nxt);
+            emit(cur, i);
+            cur = nxt;
+        }
+    }
+}
+
 __global__ void __launch_bounds__(GM_THREADS) gemm_q_kernel(const __grid_constant__ GemmParams p) {
     extern __shared__ __align__(128) uint8_t smem_raw[];
     GemmBars& sh = *reinterpret_cast<GemmBars*>(smem_raw);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int T = p.T_pad, S = p.n_stages;
+    const int T = p.T_pad, S = p.n_stages, SB = p.n_bstages;
     const uint32_t a_bytes = GM_BM * GM_BK * 2, b_bytes = (uint32_t)T * GM_BK * 2;
-    const uint32_t stage_bytes = a_bytes + b_bytes;
-    uint8_t* stage0 = smem_raw + GM_HDR;
-    uint8_t* raw0 = stage0 + (size_t)S * stage_bytes;                  // raw weight spans: GM_RAW_STAGES x [128][box]
+    uint8_t* stage0 = smem_raw + GM_HDR;                               // A tiles: S x 16 KB
+    uint8_t* bst0 = stage0 + (size_t)S * a_bytes;                      // activation tiles: SB x T*128 B
+    uint8_t* raw0 = bst0 + (size_t)SB * b_bytes;                       // raw weight spans: n_raw x [128][box]
     uint32_t ncols = 32;
     while ((int)ncols < T) ncols <<= 1;
 
@@ -327,7 +421,8 @@ __global__ void __launch_bounds__(GM_THREADS) gemm_q_kernel(const __grid_constan
 
     if (warp == 4) {
         if (lane == 0) {
-            for (int i = 0; i < S; i++) { mbar_init(&sh.a_full[i], GM_BM); mbar_init(&sh.b_full[i], 1); mbar_init(&sh.empty[i], 1); }
+            for (int i = 0; i < S; i++) { mbar_init(&sh.a_full[i], GM_BM); mbar_init(&sh.empty[i], 1); }
+            for (int i = 0; i < SB; i++) { mbar_init(&sh.b_full[i], 1); mbar_init(&sh.b_empty[i], 1); }
             for (int i = 0; i < GM_RAW_STAGES; i++) { mbar_init(&sh.raw_full[i], 1); mbar_init(&sh.raw_empty[i], GM_BM); }
             fence_mbar_init();
         }
@@ -342,71 +437,20 @@ __global__ void __launch_bounds__(GM_THREADS) gemm_q_kernel(const __grid_constan
     const uint32_t lbo_a = GM_BM * 16, lbo_b = (uint32_t)T * 16, sbo = 128;
 
     if (warp < 4) {
-        // ================= dequantising threads: thread <-> weight row
-        const int type = sg.type;
-        auto emit = [&](const RawKB& r, int i) {           // block i of this CTA's range -> A tile of its stage
-            const int s = i % S, use = i / S;
-            if (use > 0) mbar_wait(&sh.empty[s], (use - 1) & 1, p.err, 0x40001u, (unsigned)i);   // MMAs that read the stage are done
-            uint8_t* sa = stage0 + (size_t)s * stage_bytes;
-            dequant_store(type, r, (i & 3) * GM_BK, sa + tid * 16, lbo_a);
-            fence_proxy_async();        // generic-proxy writes -> visible to the tensor core (async proxy)
-            mbar_arrive(&sh.a_full[s]);
-        };
-        if (sg.use_tma) {
-            // raw spans arrive in shared memory by TMA; this thread's row is one box row
-            // the box starts at the 16-byte boundary below the span (TMA needs it); only Q6_K spans (210 B) can be off it
-            const int n16 = type == T_Q6_K ? 15 : (int)((sg.span_bytes + 15) / 16);
-            for (int sp = 0; sp < n_sp; sp++) {
-                const int rs = sp % NR, ruse = sp / NR;
-                mbar_wait(&sh.raw_full[rs], ruse & 1, p.err, 0x40006u, (unsigned)sp);
-                const uint8_t* slot = raw0 + (size_t)rs * raw_stage_bytes + (size_t)tid * box;
-                uint32_t W[GM_SPAN_WORDS];
-#pragma unroll
-                for (int j = 0; j < GM_SPAN_WORDS / 4; j++) {
-                    if (j < n16) {
-                        const uint4 v = *reinterpret_cast<const uint4*>(slot + 16 * j);
-                        W[4 * j] = v.x; W[4 * j + 1] = v.y; W[4 * j + 2] = v.z; W[4 * j + 3] = v.w;
-                    }
-                }
-                mbar_arrive(&sh.raw_empty[rs]);            // the span is in registers: the stage can be refilled
-                if (type == T_Q6_K) {                      // shift the 53 words of the span down by its misalignment (0,2,..14 bytes)
-                    const uint32_t mis = ((uint32_t)(sp0 + sp) * 210u) & 15u, sh16 = (mis & 2u) * 8u;
-                    switch (mis >> 2) {
-                        case 0:
-#pragma unroll
-                            for (int i = 0; i < 53; i++) W[i] = fshr(W[i], W[i + 1], sh16);
-                            break;
-                        case 1:
-#pragma unroll
-                            for (int i = 0; i < 53; i++) W[i] = fshr(W[i + 1], W[i + 2], sh16);
-                            break;
-                        case 2:
-#pragma unroll
-                            for (int i = 0; i < 53; i++) W[i] = fshr(W[i + 2], W[i + 3], sh16);
-                            break;
-                        default:
-#pragma unroll
-                            for (int i = 0; i < 53; i++) W[i] = fshr(W[i + 3], W[i + 4], sh16);
-                            break;
-                    }
-                }
-                RawKB r;
-                span_block<0>(type, W, r); emit(r, sp * 4 + 0);
-                span_block<1>(type, W, r); emit(r, sp * 4 + 1);
-                span_block<2>(type, W, r); emit(r, sp * 4 + 2);
-                span_block<3>(type, W, r); emit(r, sp * 4 + 3);
-            }
-        } else {
-            // rows that are not 16-byte multiples (Q6_K with K % 2048 != 0): direct loads, next block prefetched in registers
-            const int my_row = min(m0 + tid, sg.n_rows - 1);           // rows past N are computed and dropped
-            const uint8_t* wrow = sg.w + (size_t)my_row * sg.row_bytes;
-            RawKB cur, nxt;
-            load_raw(type, wrow, kb0 * GM_BK, cur);
-            for (int i = 0; i < n; i++) {
-                if (i + 1 < n) load_raw(type, wrow, (kb0 + i + 1) * GM_BK, nxt);
-                emit(cur, i);
-                cur = nxt;
-            }
+        // ================= dequantising threads: thread <-> weight row. One instantiation per quant type keeps the
+        // loop a CTA actually runs small enough for the instruction cache (all five inlined: ~100 KB of SASS).
+        DeqCtx cx;
+        cx.sh = &sh; cx.stage0 = stage0; cx.raw0 = raw0; cx.S = S; cx.NR = NR; cx.raw_stage_bytes = raw_stage_bytes; cx.box = box;
+        cx.tid = tid; cx.n = n; cx.n_sp = n_sp; cx.sp0 = sp0; cx.kb0 = kb0; cx.err = p.err;
+        cx.dbg = (p.dbg && blockIdx.x == 0 && tid == 0) ? p.dbg : nullptr;
+        cx.use_tma = sg.use_tma; cx.span_bytes = sg.span_bytes;
+        cx.wrow = sg.w + (size_t)min(m0 + tid, sg.n_rows - 1) * sg.row_bytes;      // rows past N are computed and dropped
+        switch (sg.type) {
+            case T_Q4_K: deq_loop<T_Q4_K>(cx); break;
+            case T_Q5_K: deq_loop<T_Q5_K>(cx); break;
+            case T_Q6_K: deq_loop<T_Q6_K>(cx); break;
+            case T_Q8_0: deq_loop<T_Q8_0>(cx); break;
+            default: deq_loop<T_Q4_0>(cx); break;
         }
         // ================= epilogue: TMEM lane = tid
         const int last = n - 1;
@@ -425,45 +469,52 @@ __global__ void __launch_bounds__(GM_THREADS) gemm_q_kernel(const __grid_constan
             }
         }
     } else if (warp == 4 && lane == 0) {
-        // ================= control thread: B tiles by TMA, MMA issue
+        // ================= MMA thread
         const uint32_t idesc_lo = instr_desc(GM_BM, T > 256 ? 256 : T);
         const uint32_t idesc_hi = T > 256 ? instr_desc(GM_BM, T - 256) : 0u;
-        const uint8_t* xb = reinterpret_cast<const uint8_t*>(p.x);     // block kb = 8 chunks x T x 16 B, contiguous
-        auto load_b = [&](int i) {
-            const int s = i % S;
-            mbar_arrive_expect_tx(&sh.b_full[s], b_bytes);
-            tma_load_1d(stage0 + (size_t)s * stage_bytes + a_bytes, xb + (size_t)(kb0 + i) * b_bytes, b_bytes, &sh.b_full[s]);
-        };
-        for (int i = 0; i < S && i < n; i++) load_b(i);
+        int s = 0, sb = 0;
+        uint32_t use = 0, useb = 0;
+        const uint32_t a_lo0 = (smem_u32(stage0) >> 4) | ((lbo_a >> 4) << 16), b_lo0 = (smem_u32(bst0) >> 4) | ((lbo_b >> 4) << 16);
+        const uint32_t desc_hi = (sbo >> 4) | (1u << 14);          // SBO, descriptor version 1, no swizzle
         for (int i = 0; i < n; i++) {
-            const int s = i % S, use = i / S;
-            mbar_wait(&sh.b_full[s], use & 1, p.err, 0x40003u, (unsigned)i);
+            mbar_wait(&sh.b_full[sb], useb & 1, p.err, 0x40003u, (unsigned)i);
+            if (p.dbg && blockIdx.x == 0 && i < 64) p.dbg[i * 8 + 3] = clock64();
             mbar_wait(&sh.a_full[s], use & 1, p.err, 0x40004u, (unsigned)i);
+            if (p.dbg && blockIdx.x == 0 && i < 64) p.dbg[i * 8 + 4] = clock64();
             tc_fence_after();
-            const uint32_t a_addr = smem_u32(stage0 + (size_t)s * stage_bytes), b_addr = a_addr + a_bytes;
+            // descriptors differ only in the 14-bit start-address field (units of 16 B): add, do not rebuild
+            const uint32_t a_lo = a_lo0 + (uint32_t)s * (a_bytes >> 4), b_lo = b_lo0 + (uint32_t)sb * (b_bytes >> 4);
 #pragma unroll
             for (int ks = 0; ks < GM_BK / 16; ks++) {
-                const uint64_t da = smem_desc(a_addr + ks * 2 * lbo_a, lbo_a, sbo);
-                const uint64_t db = smem_desc(b_addr + ks * 2 * lbo_b, lbo_b, sbo);
+                const uint64_t da = desc_join(a_lo + ks * (2 * lbo_a >> 4), desc_hi);
+                const uint64_t db = desc_join(b_lo + ks * (2 * lbo_b >> 4), desc_hi);
                 const uint32_t acc = (i > 0 || ks > 0) ? 1u : 0u;
                 umma_f16(tmem, da, db, idesc_lo, acc);
-                if (T > 256) {
-                    const uint64_t db2 = smem_desc(b_addr + ks * 2 * lbo_b + 256 * 16, lbo_b, sbo);
-                    umma_f16(tmem + 256, da, db2, idesc_hi, acc);
-                }
+                if (T > 256) umma_f16(tmem + 256, da, desc_join(b_lo + ks * (2 * lbo_b >> 4) + 256, desc_hi), idesc_hi, acc);
             }
-            umma_commit(&sh.empty[s]);      // arrives when the MMAs above have finished reading the stage
-            if (i >= 1 && i - 1 + S < n) {  // refill the stage of the previous block as soon as its MMAs retire
-                const int ip = i - 1;
-                mbar_wait(&sh.empty[ip % S], (ip / S) & 1, p.err, 0x40005u, (unsigned)ip);
-                load_b(ip + S);
-            }
+            umma_commit(&sh.empty[s]);      // both arrive when the MMAs above have finished reading their tiles
+            umma_commit(&sh.b_empty[sb]);
+            if (p.dbg && blockIdx.x == 0 && i < 64) p.dbg[i * 8 + 5] = clock64();
+            if (++s == S) { s = 0; use++; }
+            if (++sb == SB) { sb = 0; useb++; }
+        }
+    } else if (warp == 6 && lane == 0) {
+        // ================= activation producer: the tile of a block is one contiguous 1-D bulk copy (operand order in HBM)
+        const uint8_t* xb = reinterpret_cast<const uint8_t*>(p.x);
+        int sb = 0;
+        uint32_t useb = 0;
+        for (int i = 0; i < n; i++) {
+            if (useb > 0) mbar_wait(&sh.b_empty[sb], (useb - 1) & 1, p.err, 0x40005u, (unsigned)i);
+            mbar_arrive_expect_tx(&sh.b_full[sb], b_bytes);
+            tma_load_1d(bst0 + (size_t)sb * b_bytes, xb + (size_t)(kb0 + i) * b_bytes, b_bytes, &sh.b_full[sb]);
+            if (++sb == SB) { sb = 0; useb++; }
         }
     } else if (warp == 5 && lane == 0 && sg.use_tma) {
         // ================= weight producer: one 2-D TMA box (128 rows x one 256-weight span) per stage
         const void* tmap = &sg.tmap;
-        for (int sp = 0; sp < n_sp; sp++) {
-            const int rs = sp % NR, ruse = sp / NR;
+        int rs = 0;
+        uint32_t ruse = 0;
+        for (int sp = 0; sp < n_sp; sp++, rs = (rs + 1 == NR ? 0 : rs + 1), ruse += (rs == 0)) {
             if (ruse > 0) mbar_wait(&sh.raw_empty[rs], (ruse - 1) & 1, p.err, 0x40007u, (unsigned)sp);
             mbar_arrive_expect_tx(&sh.raw_full[rs], raw_stage_bytes);
             tma_load_2d(raw0 + (size_t)rs * raw_stage_bytes, tmap, (int)((((size_t)(sp0 + sp) * sg.span_bytes) & ~(size_t)15) >> 1), m0, &sh.raw_full[rs]);
@@ -481,7 +532,7 @@ static size_t gemm_raw_bytes(const GemmParams& p) {
     return m;
 }
 size_t gemm_smem_bytes(const GemmParams& p) {
-    return GM_HDR + (size_t)p.n_stages * ((size_t)GM_BM * GM_BK * 2 + (size_t)p.T_pad * GM_BK * 2) + gemm_raw_bytes(p);
+    return GM_HDR + (size_t)p.n_stages * GM_BM * GM_BK * 2 + (size_t)p.n_bstages * p.T_pad * GM_BK * 2 + gemm_raw_bytes(p);
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
@@ -536,24 +587,28 @@ int gemm_plan(GemmParams& p, int n_sms, int max_splits) {
         }
     }
     p.n_tiles = tiles;
-    const size_t stage = (size_t)GM_BM * GM_BK * 2 + (size_t)p.T_pad * GM_BK * 2;
+    const size_t a_st = (size_t)GM_BM * GM_BK * 2, b_st = (size_t)p.T_pad * GM_BK * 2;
     const size_t cap = 227 * 1024 - 1024;
-    p.n_raw = GM_RAW_STAGES;
-    if (GM_HDR + 2 * stage + gemm_raw_bytes(p) > cap) p.n_raw = 1;       // T near 512 with wide spans: one raw stage
-    if (GM_HDR + 2 * stage + gemm_raw_bytes(p) > cap) for (int s = 0; s < p.nseg; s++) p.seg[s].use_tma = 0;
-    const size_t raw = gemm_raw_bytes(p);
-    // small T: two CTAs per SM (each <= ~112 KB) so one tile's epilogue overlaps the other's main loop
-    int per_sm = 1, S;
-    if (p.T_pad <= 64) { per_sm = 2; S = 2; }
-    else if (p.T_pad <= 128) { per_sm = 1; S = 4; }
-    else S = 4;
+    // activation ring: deep when the tiles are small (their TMA latency must not gate the MMAs)
+    int SB = p.T_pad <= 32 ? 8 : p.T_pad <= 64 ? 6 : p.T_pad <= 128 ? 4 : p.T_pad <= 256 ? 3 : 2;
+    int S = p.T_pad <= 64 ? 2 : 3;
+    int per_sm = p.T_pad <= 64 ? 2 : 1;       // small T: two CTAs per SM (more dequantising warps per scheduler)
     if (const char* v = getenv("B2_GEMM_PER_SM")) if (atoi(v) > 0) per_sm = atoi(v);
     if (const char* v = getenv("B2_GEMM_STAGES")) if (atoi(v) > 1) S = atoi(v);
+    if (const char* v = getenv("B2_GEMM_BSTAGES")) if (atoi(v) > 1) SB = atoi(v);
     if (S > GM_MAX_STAGES) S = GM_MAX_STAGES;
-    while (S > 2 && GM_HDR + (size_t)S * stage + raw > cap) S--;
-    if (GM_HDR + (size_t)S * stage + raw > cap) return -4;
-    if (per_sm > 1 && (GM_HDR + (size_t)S * stage + raw + 1024) * per_sm > 228 * 1024) per_sm = 1;
-    p.n_stages = S;
+    if (SB > GM_MAX_BSTAGES) SB = GM_MAX_BSTAGES;
+    p.n_raw = GM_RAW_STAGES;
+    if (const char* v = getenv("B2_GEMM_RAW")) if (atoi(v) == 1) p.n_raw = 1;
+    const size_t budget = per_sm > 1 ? (228 * 1024) / per_sm - 1024 : cap;
+    auto total = [&]() { return GM_HDR + S * a_st + SB * b_st + gemm_raw_bytes(p); };
+    if (total() > budget && p.n_raw > 1) p.n_raw = 1;
+    while (total() > budget && SB > 2) SB--;
+    while (total() > budget && S > 2) S--;
+    if (total() > budget && per_sm > 1) per_sm = 1;
+    if (total() > cap) { for (int s = 0; s < p.nseg; s++) p.seg[s].use_tma = 0; }
+    if (total() > cap) return -4;
+    p.n_stages = S; p.n_bstages = SB;
     const int slots = n_sms * per_sm;
     const int n_sp = p.K / 256;
     // choose the K split that minimises (waves) x (blocks per CTA + fixed cost), fixed cost ~ epilogue + ramp
@@ -570,7 +625,8 @@ int gemm_plan(GemmParams& p, int n_sms, int max_splits) {
 }
 
 cudaError_t gemm_launch(const GemmParams& p, cudaStream_t stream) {
-    if (p.n_stages < 2 || p.n_stages > GM_MAX_STAGES || p.n_splits < 1 || p.n_tiles < 1) return cudaErrorInvalidValue;
+    if (p.n_stages < 2 || p.n_stages > GM_MAX_STAGES || p.n_bstages < 2 || p.n_bstages > GM_MAX_BSTAGES || p.n_splits < 1 ||
+        p.n_tiles < 1) return cudaErrorInvalidValue;
     if (p.T_pad < 16 || p.T_pad > 512 || p.T_pad % 16 || p.T > p.T_pad || p.n_splits > p.K / 256) return cudaErrorInvalidValue;
     gemm_q_kernel<<<p.n_tiles * p.n_splits, GM_THREADS, gemm_smem_bytes(p), stream>>>(p);
     return cudaGetLastError();

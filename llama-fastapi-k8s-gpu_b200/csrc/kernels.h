@@ -135,7 +135,8 @@ struct GemmParams {
     int ldy;
     long split_stride;
     unsigned int* err;
-    int n_tiles, n_splits, n_stages, n_raw;   // filled by gemm_plan
+    long long* dbg;         // optional: CTA 0 records clock64() per K block (8 slots each), scripts/gemm_micro.py
+    int n_tiles, n_splits, n_stages, n_bstages, n_raw;   // filled by gemm_plan
 };
 cudaError_t gemm_init();
 int gemm_plan(GemmParams& p, int n_sms, int max_splits);

@@ -326,6 +326,7 @@ __device__ __forceinline__ void consume(const MvParams& p, const CtaWork& work, 
                 for (int r = 0; r < R; r++) acc[r] = out.v[r];
             }
         }
+        fence_proxy_async();    // generic-proxy reads of the stage, ordered before the TMA (async proxy) refill
         __syncwarp();
         if (lane == 0) mbar_arrive(&sh.empty[st]);      // stage can be refilled
         // transposed butterfly over the 4 rows: lanes 0-7 / 8-15 / 16-23 / 24-31 end with row 0 / 1 / 2 / 3
