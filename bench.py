@@ -29,13 +29,50 @@ for p in (ROOT, PKG):
         sys.path.insert(0, p)
 
 WORKLOADS = {
-    # name: (arch, ftype, prompt tokens)   -- BASELINE.json configs
-    "llama3-8b-q4_k_m-bs1": ("llama-3-8b", "Q4_K_M", 512),
-    "tinyllama-1.1b-q4_0-bs1": ("tinyllama-1.1b", "Q4_0", 128),
-    "llama3-8b-q8_0-bs1": ("llama-3-8b", "Q8_0", 512),
-    "mistral-7b-q4_k_m-8k": ("mistral-7b", "Q4_K_M", 8192 - 512),
-    "tiny-q4_k_m": ("tiny", "Q4_K_M", 32),
+    # name: (arch, ftype, prompt tokens, sequences per step)   -- BASELINE.json configs
+    "llama3-8b-q4_k_m-bs1": ("llama-3-8b", "Q4_K_M", 512, 1),
+    "tinyllama-1.1b-q4_0-bs1": ("tinyllama-1.1b", "Q4_0", 128, 1),
+    "llama3-8b-q8_0-bs1": ("llama-3-8b", "Q8_0", 512, 1),
+    "llama3-8b-q8_0-bs32": ("llama-3-8b", "Q8_0", 512, 32),
+    "llama3-8b-q4_k_m-bs32": ("llama-3-8b", "Q4_K_M", 512, 32),
+    "mistral-7b-q4_k_m-8k": ("mistral-7b", "Q4_K_M", 8192 - 512, 1),
+    "tiny-q4_k_m": ("tiny", "Q4_K_M", 32, 1),
+    "tiny-q4_k_m-bs8": ("tiny", "Q4_K_M", 32, 8),
 }
+
+
+def batched_decode_run(path, n_prompt, bs, n_warm, n_steps, device, seed=7):
+    """bs sequences with n_prompt-token prompts resident in the paged KV cache, then n_steps decode steps of all of
+    them at once (b2_decode): CUDA events on the engine stream around the timed steps. Also returns the p50 of the
+    per-prompt prefill times (host-timed synchronous b2_prefill calls) seen while filling the slots."""
+    import numpy as np
+    from llama_cpp.engine import Engine, SamplingSettings
+    from llama_cpp.gguf_file import GGUFFile
+    eng = Engine(GGUFFile(path), n_ctx=n_prompt + n_warm + n_steps + 16, max_seqs=bs, device=device, kv_block_tokens=64)
+    greedy = SamplingSettings(temperature=0.0, repeat_penalty=1.0)
+    rng = np.random.default_rng(seed)
+    pre = []
+    with eng.lock:
+        for s in range(bs):
+            prompt = [int(t) for t in rng.integers(0, eng.dims.n_vocab, size=n_prompt)]
+            eng.ensure_pages(s, n_prompt + n_warm + n_steps + 8)
+            eng.seq_begin(s, 0, [], greedy)
+            t0 = time.perf_counter()
+            eng.prefill(s, prompt)
+            pre.append((time.perf_counter() - t0) * 1e3)
+            eng.sample(s)
+        slots = list(range(bs))
+        for _ in range(n_warm):
+            eng.decode(slots)
+        l0 = eng.launch_count()
+        eng.timer_start()
+        for _ in range(n_steps):
+            eng.decode(slots)
+        ms = eng.timer_stop()
+        launches = eng.launch_count() - l0
+    eng.close()
+    pre = sorted(pre[1:] or pre)            # the first call also allocates the prompt workspace
+    return dict(ms=ms, launches=launches, prefill_p50_ms=pre[len(pre) // 2], prefill_n=len(pre))
 
 
 def model_path(arch, ftype, seed=1):
@@ -153,6 +190,86 @@ def cpu_reference_run(path, n_warm, n_steps, budget_s, prompt_len=16):
                        f"KV reads are <2% of the bytes at the workload's context, weights are streamed in full")
 
 
+def batch_workload(args, cfg, path, n_prompt, batch, rank, world, local_rank, barrier, torch, dist):
+    """Continuous-batching configs: `batch` sequences decode together, one weight pass per step (tensor-core GEMM path)."""
+    import numpy as np
+    from llama_cpp import Llama
+    from llama_cpp.gguf_file import GGUFFile
+    K, W = args.steps, args.warmup
+    clocks = ClockSampler(local_rank)
+    if not args.ncu_mode:
+        clocks.start()
+    barrier()
+    r = batched_decode_run(path, n_prompt, batch, W, K, local_rank)
+    barrier()
+    clk = clocks.result() if not args.ncu_mode else {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+    t = torch.tensor([r["ms"]], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max = float(t.item())
+    value = world * batch * K / (ms_max / 1e3)
+    e2e = None
+    if not args.ncu_mode:
+        # end to end: `batch` concurrent callers of the public API (as /response handlers would be), host ids in, text out
+        os.environ["B200_MAX_SEQS"] = str(batch)
+        n_new = min(K, 64)
+        llm = Llama(model_path=path, n_gpu_layers=-1, n_ctx=n_prompt + n_new + 16, seed=1, verbose=False)
+        rng = np.random.default_rng(99 + rank)
+        prompts = [[int(x) for x in rng.integers(0, llm.n_vocab(), size=n_prompt)] for _ in range(batch)]
+        llm.create_completion(prompts[0][:64], max_tokens=4, temperature=0.0, repeat_penalty=1.0)
+        outs = [None] * batch
+
+        def call(i):
+            outs[i] = llm.create_completion(prompts[i], max_tokens=n_new, temperature=0.0, repeat_penalty=1.0)
+        th = [threading.Thread(target=call, args=(i,)) for i in range(batch)]
+        barrier()
+        t0 = time.perf_counter()
+        for x in th:
+            x.start()
+        for x in th:
+            x.join()
+        wall = time.perf_counter() - t0
+        barrier()
+        n_gen = sum(o["usage"]["completion_tokens"] for o in outs if o)
+        t2 = torch.tensor([wall], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t2, op=dist.ReduceOp.MAX)
+        e2e = {"value": world * n_gen / float(t2.item()), "unit": "tok/s", "h2d_bytes_per_step": round(4.0 * n_prompt * batch / n_new, 1),
+               "d2h_bytes_per_step": 4 * batch, "tokens": n_gen, "wall_s": wall, "max_batch": llm._scheduler.stats["max_batch"],
+               "note": f"{batch} threads call Llama.create_completion(token ids, max_tokens={n_new}, temperature=0) at once; "
+                       "generated tokens / wall time of the whole burst, prompt processing of all requests included"}
+        llm.close()
+    if rank != 0:
+        return 0
+    g = GGUFFile(path)
+    ctx_mean = n_prompt + W + K / 2.0
+    w_read, kv_pos, _ = algorithmic_bytes(g, ctx_mean)
+    step_bytes = w_read + batch * ctx_mean * kv_pos
+    peak, peak_src = measured_peak_gbs()
+    achieved = step_bytes / (ms_max / K / 1e3) / 1e9
+    roof = {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
+            "traffic": None, "peak_source": peak_src, "bytes_per_launch": int(step_bytes),
+            "launch": f"one batched decode step ({batch} sequences): weights once + every sequence's KV; algorithmic bytes = "
+                      "W_read + batch * mean_ctx * KV bytes/position"}
+    line = {"metric": "decode_tokens_per_s", "value": round(value, 2), "unit": "tok/s", "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": round(ms_max / K, 5), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f16 activations x int4/6/8 weights expanded to f16 (tcgen05 kind::f16), f32 accumulate, f16 KV",
+            "data": "synthetic", "config": cfg, "clocks": clk, "e2e": e2e, "gpu_launches": int(r["launches"]), "roofline": roof,
+            "prefill_p50_ms": round(r["prefill_p50_ms"], 2), "prefill_tok_s": round(n_prompt / r["prefill_p50_ms"] * 1e3, 1),
+            "w_read_bytes": int(w_read), "kv_bytes_per_pos": kv_pos, "ctx_mean": ctx_mean}
+    if not args.no_cpu_baseline and not args.ncu_mode:
+        try:
+            c = cpu_reference_run(path, 1, 64, budget_s=args.cpu_budget_s)
+            line["cpu_baseline"] = {"value": round(c["value"], 3), "unit": "tok/s", "cores": c["cores"], "kind": "port",
+                                    "sample": c["sample"] + " (one sequence; the CPU path has no batching)"}
+        except Exception as exc:  # noqa: BLE001
+            line["cpu_baseline"] = {"value": None, "unit": "tok/s", "cores": 0, "kind": "port", "sample": f"failed: {exc}"}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -161,18 +278,19 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="llama3-8b-q4_k_m-bs1", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--batch-extra", type=int, default=32, help="bs1 workloads: also time this many sequences per step (0 = skip)")
     ap.add_argument("--cpu-budget-s", type=float, default=20.0)
     ap.add_argument("--profile-kernels", action="store_true", help="also print a per-kernel-kind breakdown to stderr")
     ap.add_argument("--ncu-mode", action="store_true", help="short run for ncu: skip e2e, cpu baseline, clocks")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3
-    arch, ftype, n_prompt = WORKLOADS[args.workload]
+    arch, ftype, n_prompt, batch = WORKLOADS[args.workload]
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     cfg = {"workload": f"{args.workload}: {arch}-arch {ftype} synthetic GGUF (seed 1), {n_prompt}-token prompt then "
-                       f"batch-1 greedy decode", "prompt_tokens": n_prompt, "batch": 1,
+                       f"batch-{batch} greedy decode", "prompt_tokens": n_prompt, "batch": batch,
            "parallelism": f"replicas x{world}" if world > 1 else "single GPU",
            "l2": "inputs (weights 4.6 GB/step) larger than L2; no flush needed"}
 
@@ -213,6 +331,8 @@ def main():
     from llama_cpp.engine import SamplingSettings
     from llama_cpp.gguf_file import GGUFFile
     K, W = args.steps, args.warmup
+    if batch > 1:
+        return batch_workload(args, cfg, path, n_prompt, batch, rank, world, local_rank, barrier, torch, dist)
     n_ctx = n_prompt + W + K + 16
     t_load = time.perf_counter()
     llm = Llama(model_path=path, n_gpu_layers=-1, n_ctx=n_ctx, seed=1, verbose=False)
@@ -277,6 +397,20 @@ def main():
                "note": "Llama.create_completion(token ids, max_tokens=K, temperature=0): decode phase of the call "
                        "(first token to last), host-timed; includes per-chunk D2H of sampled ids, stop checks, detokenise"}
 
+    # ---- the other headline numbers of BASELINE.json on the same model: prompt p50 and 32 sequences per step
+    extra = None
+    if not args.ncu_mode and args.batch_extra > 0:
+        try:
+            bsteps = min(K, 64)
+            br = batched_decode_run(path, n_prompt, args.batch_extra, 4, bsteps, local_rank)
+            extra = {"bs": args.batch_extra, "value": round(args.batch_extra * bsteps / (br["ms"] / 1e3), 1), "unit": "tok/s",
+                     "ms_per_step": round(br["ms"] / bsteps, 4), "steps": bsteps, "prompt_tokens": n_prompt,
+                     "prefill_p50_ms": round(br["prefill_p50_ms"], 2), "prefill_runs": br["prefill_n"],
+                     "prefill_tok_s": round(n_prompt / br["prefill_p50_ms"] * 1e3, 1),
+                     "note": "per GPU; b2_decode over all slots per step (tensor-core GEMM path), CUDA events on the engine "
+                             "stream; prefill p50 = synchronous b2_prefill calls, host-timed"}
+        except Exception as exc:  # noqa: BLE001
+            extra = {"error": str(exc)}
     if rank != 0:
         return 0
     g = GGUFFile(path)
@@ -299,7 +433,7 @@ def main():
             "config": cfg, "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof,
             "engine": mode, "prefill_ms": round(ttft_ms, 2), "prefill_tok_s": round(n_prompt / ttft_ms * 1e3, 1),
             "prefill_cold_ms": round(ttft_cold_ms, 2), "load_s": round(t_load, 2),
-            "w_read_bytes": int(w_read), "kv_bytes_per_pos": kv_pos, "ctx_mean": ctx_mean}
+            "w_read_bytes": int(w_read), "kv_bytes_per_pos": kv_pos, "ctx_mean": ctx_mean, "batched": extra}
     if not args.no_cpu_baseline and not args.ncu_mode:
         try:
             r = cpu_reference_run(path, 1, 64, budget_s=args.cpu_budget_s)
