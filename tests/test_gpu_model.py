@@ -298,3 +298,30 @@ def test_batched_decode_rejects_duplicate_slots(native_lib, tmp_models):
     with pytest.raises(B2Error):
         eng.decode([0, 1, 0])
     eng.close()
+
+
+def test_long_context_uses_more_attention_splits_and_matches_oracle(native_lib, tmp_models):
+    """n_ctx > 4096 switches flash-decode to 32 splits merged through global scratch, and a 2600-token prompt spans
+    six 512-token GEMM chunks whose causal attention reads the earlier chunks from the paged cache."""
+    from oracle.llama_ref import RefModel
+    path = _model(tmp_models, "tiny128", "Q4_K_M", 9)
+    rng = np.random.default_rng(21)
+    prompt = [int(t) for t in rng.integers(3, 700, size=2600)]
+    ref = RefModel(path)
+    lg = ref.forward(prompt, last_only=True)[-1]
+    eng = _engine(path, n_ctx=5000, bt=64, max_seqs=1)
+    assert eng.mode()["attn_splits"] == 32
+    eng.ensure_pages(0, 2700)
+    eng.seq_begin(0, 0, [], _greedy())
+    eng.prefill(0, prompt)
+    assert np.abs(eng.logits(0) - lg).max() <= LOGIT_TOL
+    tok = eng.sample(0)
+    for _ in range(3):                       # decode steps attend to all 2600+ cached positions
+        nxt = ref.forward([tok], last_only=True)[-1]
+        t2 = eng.decode([0])[0]
+        assert np.abs(eng.logits(0) - nxt).max() <= LOGIT_TOL
+        top2 = np.sort(nxt)[-2:]
+        if top2[1] - top2[0] >= 10 * LOGIT_TOL:
+            assert t2 == int(np.argmax(nxt))
+        tok = t2
+    eng.close()
