@@ -163,6 +163,11 @@ def ncu_traffic_bytes():
 
 def cpu_reference_run(path, n_warm, n_steps, budget_s, prompt_len=16):
     """Time the CPU restatement of the reference's llama.cpp CPU path: decode tokens one at a time."""
+    # torchrun exports OMP_NUM_THREADS=1 to its workers; the CPU arm is meant to use every host core it can
+    if os.environ.get("OMP_NUM_THREADS") in (None, "", "1") and "B2_CPU_THREADS" not in os.environ:
+        os.environ["OMP_NUM_THREADS"] = str(len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else os.cpu_count())
+    elif "B2_CPU_THREADS" in os.environ:
+        os.environ["OMP_NUM_THREADS"] = os.environ["B2_CPU_THREADS"]
     from oracle.cpu_ref import CpuRef
     import numpy as np
     c = CpuRef(path, n_ctx=prompt_len + n_warm + n_steps + 8)
@@ -292,7 +297,7 @@ def main():
     cfg = {"workload": f"{args.workload}: {arch}-arch {ftype} synthetic GGUF (seed 1), {n_prompt}-token prompt then "
                        f"batch-{batch} greedy decode", "prompt_tokens": n_prompt, "batch": batch,
            "parallelism": f"replicas x{world}" if world > 1 else "single GPU",
-           "l2": "inputs (weights 4.6 GB/step) larger than L2; no flush needed"}
+           "l2": "every step streams all weights (0.6-8 GB, larger than the 126 MB L2); no flush needed"}
 
     if args.impl == "reference":
         # the reference's own CPU implementation of the path (restated: llama_cpp is not installable here)
