@@ -288,29 +288,39 @@ __device__ __forceinline__ void consume(const MvParams& p, const CtaWork& work, 
     const int sb = geo.slot_bytes;
     const int tpg = work.tpg;
     const int first = (int)(((uint32_t)warp + (uint32_t)NCW - qbase % (uint32_t)NCW) % (uint32_t)NCW);
+    // tile bookkeeping advances by NCW per iteration: carried incrementally (integer division by a run-time
+    // value is ~20 instructions, and there were six of them per tile)
+    if (first >= work.total || tpg <= 0) return;     // no tile for this warp (tpg is 0 in CTAs without rows)
+    int gi = first / tpg, within = first % tpg;
+    uint32_t st = (qbase + (uint32_t)first) % S, use = (qbase + (uint32_t)first) / S;
+    const int n_sl = p.n_slices;
     for (int q = first; q < work.total; q += NCW) {
-        const int gi = q / tpg, within = q % tpg;
-        const int m = gateup ? within / p.n_slices : 0;
+        const int m = (gateup && within >= n_sl) ? 1 : 0;
         const int seg = gateup ? m : work.seg;
-        const int sl = within % p.n_slices;
+        const int sl = within - m * n_sl;
         const MvSeg& sg = p.seg[seg];
         const int type = sg.type;
         const int row0 = work.r0 + gi * R, nrows = min(R, work.r1 - row0);
         const uint32_t row_bytes = (uint32_t)sg.row_bytes;
         const uint32_t row_lo = (uint32_t)(uintptr_t)sg.w + (uint32_t)row0 * row_bytes + (uint32_t)sl * (uint32_t)slice_bytes(type);
-        const uint32_t g = qbase + (uint32_t)q, st = g % S, use = g / S;
+        const uint32_t g = qbase + (uint32_t)q;
+        const int gi_cur = gi;
+        // next iteration's values
+        within += NCW; while (within >= tpg) { within -= tpg; gi++; }
+        const uint32_t st_cur = st, use_cur = use;
+        st += NCW; while (st >= S) { st -= S; use++; }
         {   // the producer has armed this use of the stage (see the protocol note at the top)
             uint32_t spins = 0;
-            while (*reinterpret_cast<volatile unsigned int*>(&sh.issued[st]) != use + 1) {
+            while (*reinterpret_cast<volatile unsigned int*>(&sh.issued[st_cur]) != use_cur + 1) {
                 if (++spins > (1u << 26)) {
                     volatile unsigned int* e = reinterpret_cast<volatile unsigned int*>(p.err);
-                    if (e && e[0] == 0) { e[1] = blockIdx.x; e[2] = threadIdx.x; e[3] = g; e[4] = use; e[0] = 0x10003u; }
+                    if (e && e[0] == 0) { e[1] = blockIdx.x; e[2] = threadIdx.x; e[3] = g; e[4] = use_cur; e[0] = 0x10003u; }
                     break;
                 }
             }
         }
-        mbar_wait(&sh.full[st], use & 1, p.err, 0x10002u, g);
-        const uint8_t* stage = ring + (size_t)st * geo.stage_bytes;
+        mbar_wait(&sh.full[st_cur], use_cur & 1, p.err, 0x10002u, g);
+        const uint8_t* stage = ring + (size_t)st_cur * geo.stage_bytes;
         float acc[R];
 #pragma unroll
         for (int r = 0; r < R; r++) acc[r] = 0.f;
@@ -328,7 +338,7 @@ __device__ __forceinline__ void consume(const MvParams& p, const CtaWork& work, 
         }
         fence_proxy_async();    // generic-proxy reads of the stage, ordered before the TMA (async proxy) refill
         __syncwarp();
-        if (lane == 0) mbar_arrive(&sh.empty[st]);      // stage can be refilled
+        if (lane == 0) mbar_arrive(&sh.empty[st_cur]);      // stage can be refilled
         // transposed butterfly over the 4 rows: lanes 0-7 / 8-15 / 16-23 / 24-31 end with row 0 / 1 / 2 / 3
         const bool hi16 = lane & 16, hi8 = lane & 8;
         float s0 = hi16 ? acc[0] : acc[2], s1 = hi16 ? acc[1] : acc[3];
@@ -343,7 +353,7 @@ __device__ __forceinline__ void consume(const MvParams& p, const CtaWork& work, 
         float v0, v1, g0 = 0.f, g1 = 0.f;                   // lanes 0 / 16 finish pair 0 / 1 of the group
         bool finish = true;
         if (tpg > 1) {
-            const int slot = gi % MV_GSLOTS;
+            const int slot = gi_cur % MV_GSLOTS;
             if ((lane & 7) == 0) atomicAdd(&sh.gacc[slot][m][lane >> 3], kp);
             __syncwarp();
             unsigned int old = 0;

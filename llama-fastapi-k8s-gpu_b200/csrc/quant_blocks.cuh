@@ -282,9 +282,10 @@ B2_D float row_dot_q4k(const uint8_t* row, int lane, const LaneAct& act) {
     uint32_t qw[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
     uint32_t sh = (c & 1) * 16;
     uint32_t w0 = h.y >> sh, w1 = h.z >> sh, w2 = h.w >> sh;
-    uint32_t scp, mp;
-    if (c < 2) { scp = w0 & 0x3F3Fu; mp = w1 & 0x3F3Fu; }
-    else { scp = (w2 & 0x0F0Fu) | ((w0 >> 2) & 0x3030u); mp = ((w2 >> 4) & 0x0F0Fu) | ((w1 >> 2) & 0x3030u); }
+    // both layouts of the 6-bit fields, then a select: lanes of one warp differ in c, a branch would diverge
+    const uint32_t sc_a = w0 & 0x3F3Fu, m_a = w1 & 0x3F3Fu;
+    const uint32_t sc_b = (w2 & 0x0F0Fu) | ((w0 >> 2) & 0x3030u), m_b = ((w2 >> 4) & 0x0F0Fu) | ((w1 >> 2) & 0x3030u);
+    const uint32_t scp = c < 2 ? sc_a : sc_b, mp = c < 2 ? m_a : m_b;
     float d = h2f(h.x & 0xffffu), dmin = h2f(h.x >> 16);
     int Alo = 0, Blo = 0, Ahi = 0, Bhi = 0;
 #pragma unroll
@@ -314,9 +315,10 @@ B2_D float row_dot_q5k(const uint8_t* row, int lane, const LaneAct& act) {
     uint32_t hw[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
     uint32_t sh = (c & 1) * 16;
     uint32_t w0 = h.y >> sh, w1 = h.z >> sh, w2 = h.w >> sh;
-    uint32_t scp, mp;
-    if (c < 2) { scp = w0 & 0x3F3Fu; mp = w1 & 0x3F3Fu; }
-    else { scp = (w2 & 0x0F0Fu) | ((w0 >> 2) & 0x3030u); mp = ((w2 >> 4) & 0x0F0Fu) | ((w1 >> 2) & 0x3030u); }
+    // both layouts of the 6-bit fields, then a select: lanes of one warp differ in c, a branch would diverge
+    const uint32_t sc_a = w0 & 0x3F3Fu, m_a = w1 & 0x3F3Fu;
+    const uint32_t sc_b = (w2 & 0x0F0Fu) | ((w0 >> 2) & 0x3030u), m_b = ((w2 >> 4) & 0x0F0Fu) | ((w1 >> 2) & 0x3030u);
+    const uint32_t scp = c < 2 ? sc_a : sc_b, mp = c < 2 ? m_a : m_b;
     float d = h2f(h.x & 0xffffu), dmin = h2f(h.x >> 16);
     int Alo = 0, Blo = 0, Ahi = 0, Bhi = 0;
 #pragma unroll
