@@ -34,7 +34,6 @@
 
 namespace b2 {
 
-constexpr int GM_THREADS = 224;     // 4 dequantising warps + MMA warp + weight-producer warp + activation-producer warp
 constexpr int GM_BM = 128;          // weight rows per CTA
 constexpr int GM_BK = 64;           // K per stage
 constexpr int GM_HDR = 512;         // barriers at the start of dynamic shared memory
@@ -315,7 +314,7 @@ struct DeqCtx {
     const uint8_t* raw0;
     const uint8_t* wrow;
     int S, NR, tid, n, n_sp, sp0, kb0, use_tma, span_bytes;
-    uint32_t raw_stage_bytes, box;
+    uint32_t raw_stage_bytes, box, a_bytes, lbo_a;      // weight tile: rows * 128 B per stage, rows * 16 B between K chunks
     unsigned int* err;
     long long* dbg;
 };
@@ -323,7 +322,7 @@ struct DeqCtx {
 template <int TYPE>
 __device__ __noinline__ void deq_loop(const DeqCtx cx) {
     GemmBars& sh = *cx.sh;
-    constexpr uint32_t a_bytes = GM_BM * GM_BK * 2, lbo_a = GM_BM * 16;
+    const uint32_t a_bytes = cx.a_bytes, lbo_a = cx.lbo_a;
     int st = 0;                 // A stage of the next block and how often the ring has wrapped
     uint32_t wraps = 0;
     auto emit = [&](const RawKB& r, int i) {               // block i of this CTA's range -> A tile of its stage
@@ -396,34 +395,41 @@ __device__ __noinline__ void deq_loop(const DeqCtx cx) {
     }
 }
 
-__global__ void __launch_bounds__(GM_THREADS) gemm_q_kernel(const __grid_constant__ GemmParams p) {
+// ROWS weight rows per CTA, ROWS / 32 dequantising warps + 3 service warps.
+// SWAP = false (T > 128): weights are the MMA's A operand (M = 128 rows = TMEM lanes), tokens its N (TMEM columns).
+// SWAP = true  (T <= 128): tokens are the A operand (M = 128, rows past T are don't-care), 256 weight rows are the N:
+//   with few tokens an instruction costs ~130 cycles whatever N is (measured), so each MMA should cover as many
+//   weight rows as an instruction can: 256.
+template <int ROWS, bool SWAP>
+__global__ void __launch_bounds__((ROWS / 32 + 3) * 32) gemm_q_kernel(const __grid_constant__ GemmParams p) {
+    constexpr int DW = ROWS / 32;          // dequantising warps; then: MMA warp, weight producer, activation producer
     extern __shared__ __align__(128) uint8_t smem_raw[];
     GemmBars& sh = *reinterpret_cast<GemmBars*>(smem_raw);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int T = p.T_pad, S = p.n_stages, SB = p.n_bstages;
-    const uint32_t a_bytes = GM_BM * GM_BK * 2, b_bytes = (uint32_t)T * GM_BK * 2;
+    const uint32_t a_bytes = ROWS * GM_BK * 2, b_bytes = (uint32_t)T * GM_BK * 2;
     uint8_t* stage0 = smem_raw + GM_HDR;                               // A tiles: S x 16 KB
     uint8_t* bst0 = stage0 + (size_t)S * a_bytes;                      // activation tiles: SB x T*128 B
     uint8_t* raw0 = bst0 + (size_t)SB * b_bytes;                       // raw weight spans: n_raw x [128][box]
     uint32_t ncols = 32;
-    while ((int)ncols < T) ncols <<= 1;
+    while ((int)ncols < (SWAP ? ROWS : T)) ncols <<= 1;
 
     // ---- which tile / K range (in 256-weight spans = 4 blocks)
     const int split = blockIdx.x % p.n_splits, tile_g = blockIdx.x / p.n_splits;
     int seg = 0;
     while (seg + 1 < p.nseg && tile_g >= p.seg[seg + 1].tile0) seg++;
     const GemmSeg& sg = p.seg[seg];
-    const int m0 = (tile_g - sg.tile0) * GM_BM;
+    const int m0 = (tile_g - sg.tile0) * ROWS;
     const int n_sp_all = p.K / 256;
     const int sp0 = (int)((long)n_sp_all * split / p.n_splits), sp1 = (int)((long)n_sp_all * (split + 1) / p.n_splits);
     const int n_sp = sp1 - sp0, kb0 = sp0 * 4, n = n_sp * 4, NR = p.n_raw;
-    const uint32_t box = (uint32_t)sg.box_bytes, raw_stage_bytes = GM_BM * box;
+    const uint32_t box = (uint32_t)sg.box_bytes, raw_stage_bytes = ROWS * box;
 
-    if (warp == 4) {
+    if (warp == DW) {
         if (lane == 0) {
-            for (int i = 0; i < S; i++) { mbar_init(&sh.a_full[i], GM_BM); mbar_init(&sh.empty[i], 1); }
+            for (int i = 0; i < S; i++) { mbar_init(&sh.a_full[i], ROWS); mbar_init(&sh.empty[i], 1); }
             for (int i = 0; i < SB; i++) { mbar_init(&sh.b_full[i], 1); mbar_init(&sh.b_empty[i], 1); }
-            for (int i = 0; i < GM_RAW_STAGES; i++) { mbar_init(&sh.raw_full[i], 1); mbar_init(&sh.raw_empty[i], GM_BM); }
+            for (int i = 0; i < GM_RAW_STAGES; i++) { mbar_init(&sh.raw_full[i], 1); mbar_init(&sh.raw_empty[i], ROWS); }
             fence_mbar_init();
         }
         __syncwarp();
@@ -434,14 +440,14 @@ __global__ void __launch_bounds__(GM_THREADS) gemm_q_kernel(const __grid_constan
     tc_fence_after();
     const uint32_t tmem = sh.tmem_base;
     // K-major, no swizzle: element (r, k) of a tile with R rows sits at (k/8) * (R*16) + r*16 + (k%8)*2
-    const uint32_t lbo_a = GM_BM * 16, lbo_b = (uint32_t)T * 16, sbo = 128;
+    const uint32_t lbo_a = ROWS * 16, lbo_b = (uint32_t)T * 16, sbo = 128;
 
-    if (warp < 4) {
+    if (warp < DW) {
         // ================= dequantising threads: thread <-> weight row. One instantiation per quant type keeps the
         // loop a CTA actually runs small enough for the instruction cache (all five inlined: ~100 KB of SASS).
         DeqCtx cx;
         cx.sh = &sh; cx.stage0 = stage0; cx.raw0 = raw0; cx.S = S; cx.NR = NR; cx.raw_stage_bytes = raw_stage_bytes; cx.box = box;
-        cx.tid = tid; cx.n = n; cx.n_sp = n_sp; cx.sp0 = sp0; cx.kb0 = kb0; cx.err = p.err;
+        cx.tid = tid; cx.n = n; cx.n_sp = n_sp; cx.sp0 = sp0; cx.kb0 = kb0; cx.err = p.err; cx.a_bytes = a_bytes; cx.lbo_a = lbo_a;
         cx.dbg = (p.dbg && blockIdx.x == 0 && tid == 0) ? p.dbg : nullptr;
         cx.use_tma = sg.use_tma; cx.span_bytes = sg.span_bytes;
         cx.wrow = sg.w + (size_t)min(m0 + tid, sg.n_rows - 1) * sg.row_bytes;      // rows past N are computed and dropped
@@ -452,26 +458,45 @@ __global__ void __launch_bounds__(GM_THREADS) gemm_q_kernel(const __grid_constan
             case T_Q8_0: deq_loop<T_Q8_0>(cx); break;
             default: deq_loop<T_Q4_0>(cx); break;
         }
-        // ================= epilogue: TMEM lane = tid
+        // ================= epilogue
         const int last = n - 1;
         mbar_wait(&sh.empty[last % S], (last / S) & 1, p.err, 0x40002u, (unsigned)last);
         tc_fence_after();
-        const int row = m0 + tid;
-        const uint32_t lane_addr = tmem + ((uint32_t)(warp * 32) << 16);
-        float* ybase = p.y + (size_t)split * p.split_stride + sg.out_off + row;
-        for (int c0 = 0; c0 < T; c0 += 16) {
-            float v[16];
-            tmem_ld16(lane_addr + c0, v);
-            if (row < sg.n_rows) {
+        if (!SWAP) {                               // TMEM lane = weight row, columns = tokens
+            const int row = m0 + tid;
+            const uint32_t lane_addr = tmem + ((uint32_t)(warp * 32) << 16);
+            float* ybase = p.y + (size_t)split * p.split_stride + sg.out_off + row;
+            for (int c0 = 0; c0 < T; c0 += 16) {
+                float v[16];
+                tmem_ld16(lane_addr + c0, v);
+                if (row < sg.n_rows) {
 #pragma unroll
-                for (int j = 0; j < 16; j++)
-                    if (c0 + j < p.T) ybase[(size_t)(c0 + j) * p.ldy] = v[j];
+                    for (int j = 0; j < 16; j++)
+                        if (c0 + j < p.T) ybase[(size_t)(c0 + j) * p.ldy] = v[j];
+                }
+            }
+        } else if (warp < 4 && warp * 32 < p.T) {  // TMEM lane = token (warps 0-3 own the 128 lanes), columns = weight rows
+            const uint32_t lane_addr = tmem + ((uint32_t)(warp * 32) << 16);
+            float* yrow = p.y + (size_t)split * p.split_stride + (size_t)tid * p.ldy + sg.out_off + m0;
+            const int n_valid = min(ROWS, sg.n_rows - m0);
+            for (int c0 = 0; c0 < ROWS; c0 += 16) {
+                float v[16];
+                tmem_ld16(lane_addr + c0, v);      // warp-wide: every lane takes part, only tokens < T store
+                if (tid < p.T) {
+                    if (c0 + 16 <= n_valid) {
+#pragma unroll
+                        for (int j = 0; j < 16; j += 4) *reinterpret_cast<float4*>(yrow + c0 + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 16; j++) if (c0 + j < n_valid) yrow[c0 + j] = v[j];
+                    }
+                }
             }
         }
-    } else if (warp == 4 && lane == 0) {
+    } else if (warp == DW && lane == 0) {
         // ================= MMA thread
-        const uint32_t idesc_lo = instr_desc(GM_BM, T > 256 ? 256 : T);
-        const uint32_t idesc_hi = T > 256 ? instr_desc(GM_BM, T - 256) : 0u;
+        const uint32_t idesc_lo = SWAP ? instr_desc(128, ROWS) : instr_desc(ROWS, T > 256 ? 256 : T);
+        const uint32_t idesc_hi = (!SWAP && T > 256) ? instr_desc(ROWS, T - 256) : 0u;
         int s = 0, sb = 0;
         uint32_t use = 0, useb = 0;
         const uint32_t a_lo0 = (smem_u32(stage0) >> 4) | ((lbo_a >> 4) << 16), b_lo0 = (smem_u32(bst0) >> 4) | ((lbo_b >> 4) << 16);
@@ -489,8 +514,12 @@ __global__ void __launch_bounds__(GM_THREADS) gemm_q_kernel(const __grid_constan
                 const uint64_t da = desc_join(a_lo + ks * (2 * lbo_a >> 4), desc_hi);
                 const uint64_t db = desc_join(b_lo + ks * (2 * lbo_b >> 4), desc_hi);
                 const uint32_t acc = (i > 0 || ks > 0) ? 1u : 0u;
-                umma_f16(tmem, da, db, idesc_lo, acc);
-                if (T > 256) umma_f16(tmem + 256, da, desc_join(b_lo + ks * (2 * lbo_b >> 4) + 256, desc_hi), idesc_hi, acc);
+                if (SWAP) {
+                    umma_f16(tmem, db, da, idesc_lo, acc);          // A = tokens (rows past T read whatever follows: dropped), B = weights
+                } else {
+                    umma_f16(tmem, da, db, idesc_lo, acc);
+                    if (T > 256) umma_f16(tmem + 256, da, desc_join(b_lo + ks * (2 * lbo_b >> 4) + 256, desc_hi), idesc_hi, acc);
+                }
             }
             umma_commit(&sh.empty[s]);      // both arrive when the MMAs above have finished reading their tiles
             umma_commit(&sh.b_empty[sb]);
@@ -498,7 +527,7 @@ __global__ void __launch_bounds__(GM_THREADS) gemm_q_kernel(const __grid_constan
             if (++s == S) { s = 0; use++; }
             if (++sb == SB) { sb = 0; useb++; }
         }
-    } else if (warp == 6 && lane == 0) {
+    } else if (warp == DW + 2 && lane == 0) {
         // ================= activation producer: the tile of a block is one contiguous 1-D bulk copy (operand order in HBM)
         const uint8_t* xb = reinterpret_cast<const uint8_t*>(p.x);
         int sb = 0;
@@ -509,7 +538,7 @@ __global__ void __launch_bounds__(GM_THREADS) gemm_q_kernel(const __grid_constan
             tma_load_1d(bst0 + (size_t)sb * b_bytes, xb + (size_t)(kb0 + i) * b_bytes, b_bytes, &sh.b_full[sb]);
             if (++sb == SB) { sb = 0; useb++; }
         }
-    } else if (warp == 5 && lane == 0 && sg.use_tma) {
+    } else if (warp == DW + 1 && lane == 0 && sg.use_tma) {
         // ================= weight producer: one 2-D TMA box (128 rows x one 256-weight span) per stage
         const void* tmap = &sg.tmap;
         int rs = 0;
@@ -522,17 +551,20 @@ __global__ void __launch_bounds__(GM_THREADS) gemm_q_kernel(const __grid_constan
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 4) tmem_dealloc(tmem, ncols);
+    if (warp == DW) tmem_dealloc(tmem, ncols);
 }
 
 // ---------------------------------------------------------------- host side
+static int gemm_rows(const GemmParams& p) { return p.swap ? 256 : GM_BM; }
 static size_t gemm_raw_bytes(const GemmParams& p) {
     size_t m = 0;
-    for (int s = 0; s < p.nseg; s++) if (p.seg[s].use_tma) m = std::max(m, (size_t)p.n_raw * GM_BM * p.seg[s].box_bytes);
+    for (int s = 0; s < p.nseg; s++) if (p.seg[s].use_tma) m = std::max(m, (size_t)p.n_raw * gemm_rows(p) * p.seg[s].box_bytes);
     return m;
 }
 size_t gemm_smem_bytes(const GemmParams& p) {
-    return GM_HDR + (size_t)p.n_stages * GM_BM * GM_BK * 2 + (size_t)p.n_bstages * p.T_pad * GM_BK * 2 + gemm_raw_bytes(p);
+    // swap: the MMA reads 128 token rows per K chunk whatever T is; the rows past the tile must still be shared memory
+    return GM_HDR + (size_t)p.n_stages * gemm_rows(p) * GM_BK * 2 + (size_t)p.n_bstages * p.T_pad * GM_BK * 2 + gemm_raw_bytes(p) +
+           (p.swap ? 4096 : 0);
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
@@ -549,7 +581,9 @@ cudaError_t gemm_init() {
         if (qres != cudaDriverEntryPointSuccess || !fn) return cudaErrorNotSupported;
         g_encode = (EncodeTiledFn)fn;
     }
-    return cudaFuncSetAttribute(gemm_q_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(gemm_q_kernel<GM_BM, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(gemm_q_kernel<256, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
 }
 
 // Fill tile ranges, tensor maps, the stage count and the K split. n_sms: SMs to fill; max_splits: what the partial
@@ -559,6 +593,8 @@ int gemm_plan(GemmParams& p, int n_sms, int max_splits) {
     if (p.nseg < 1 || p.nseg > 3 || p.K <= 0 || p.K % 256) return -1;
     if (p.T < 1 || p.T > 512) return -2;
     p.T_pad = (p.T + 15) / 16 * 16;
+    p.swap = (p.T_pad <= 128 && !getenv("B2_GEMM_NOSWAP")) ? 1 : 0;
+    const int ROWS = gemm_rows(p);
     int tiles = 0;
     const bool no_tma = getenv("B2_GEMM_NO_TMA") != nullptr;
     for (int s = 0; s < p.nseg; s++) {
@@ -567,7 +603,7 @@ int gemm_plan(GemmParams& p, int n_sms, int max_splits) {
         if (be == 1 || !bb || g.n_rows <= 0) return -3;
         g.row_bytes = p.K / be * bb;
         g.tile0 = tiles;
-        g.n_tiles = (g.n_rows + GM_BM - 1) / GM_BM;
+        g.n_tiles = (g.n_rows + ROWS - 1) / ROWS;
         tiles += g.n_tiles;
         g.span_bytes = 256 / be * bb;                                  // one 256-weight span of a row
         // box row = span rounded up to 16 B, and an odd multiple of 16 B so 128-bit shared loads of 8 rows hit 8 bank groups
@@ -578,7 +614,7 @@ int gemm_plan(GemmParams& p, int n_sms, int max_splits) {
         if (!no_tma && g_encode && g.row_bytes % 16 == 0 && ((uintptr_t)g.w & 15) == 0 && (g.type != T_Q6_K || !getenv("B2_GEMM_Q6K_DIRECT"))) {
             const cuuint64_t dims[2] = {(cuuint64_t)g.row_bytes / 2, (cuuint64_t)g.n_rows};
             const cuuint64_t strides[1] = {(cuuint64_t)g.row_bytes};
-            const cuuint32_t boxd[2] = {(cuuint32_t)box / 2, (cuuint32_t)GM_BM};
+            const cuuint32_t boxd[2] = {(cuuint32_t)box / 2, (cuuint32_t)ROWS};
             const cuuint32_t estr[2] = {1, 1};
             CUresult r = g_encode(reinterpret_cast<CUtensorMap*>(g.tmap), CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, (void*)g.w, dims, strides,
                                   boxd, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
@@ -587,12 +623,12 @@ int gemm_plan(GemmParams& p, int n_sms, int max_splits) {
         }
     }
     p.n_tiles = tiles;
-    const size_t a_st = (size_t)GM_BM * GM_BK * 2, b_st = (size_t)p.T_pad * GM_BK * 2;
+    const size_t a_st = (size_t)ROWS * GM_BK * 2, b_st = (size_t)p.T_pad * GM_BK * 2;
     const size_t cap = 227 * 1024 - 1024;
     // activation ring: deep when the tiles are small (their TMA latency must not gate the MMAs)
     int SB = p.T_pad <= 32 ? 8 : p.T_pad <= 64 ? 6 : p.T_pad <= 128 ? 4 : p.T_pad <= 256 ? 3 : 2;
-    int S = p.T_pad <= 64 ? 2 : 3;
-    int per_sm = p.T_pad <= 64 ? 2 : 1;       // small T: two CTAs per SM (more dequantising warps per scheduler)
+    int S = p.swap ? 3 : (p.T_pad <= 64 ? 2 : 3);
+    int per_sm = (!p.swap && p.T_pad <= 64) ? 2 : 1;   // 128-row variant at small T: two CTAs per SM
     if (const char* v = getenv("B2_GEMM_PER_SM")) if (atoi(v) > 0) per_sm = atoi(v);
     if (const char* v = getenv("B2_GEMM_STAGES")) if (atoi(v) > 1) S = atoi(v);
     if (const char* v = getenv("B2_GEMM_BSTAGES")) if (atoi(v) > 1) SB = atoi(v);
@@ -601,7 +637,7 @@ int gemm_plan(GemmParams& p, int n_sms, int max_splits) {
     p.n_raw = GM_RAW_STAGES;
     if (const char* v = getenv("B2_GEMM_RAW")) if (atoi(v) == 1) p.n_raw = 1;
     const size_t budget = per_sm > 1 ? (228 * 1024) / per_sm - 1024 : cap;
-    auto total = [&]() { return GM_HDR + S * a_st + SB * b_st + gemm_raw_bytes(p); };
+    auto total = [&]() { return GM_HDR + S * a_st + SB * b_st + gemm_raw_bytes(p) + (p.swap ? 4096 : 0); };
     if (total() > budget && p.n_raw > 1) p.n_raw = 1;
     while (total() > budget && SB > 2) SB--;
     while (total() > budget && S > 2) S--;
@@ -628,7 +664,8 @@ cudaError_t gemm_launch(const GemmParams& p, cudaStream_t stream) {
     if (p.n_stages < 2 || p.n_stages > GM_MAX_STAGES || p.n_bstages < 2 || p.n_bstages > GM_MAX_BSTAGES || p.n_splits < 1 ||
         p.n_tiles < 1) return cudaErrorInvalidValue;
     if (p.T_pad < 16 || p.T_pad > 512 || p.T_pad % 16 || p.T > p.T_pad || p.n_splits > p.K / 256) return cudaErrorInvalidValue;
-    gemm_q_kernel<<<p.n_tiles * p.n_splits, GM_THREADS, gemm_smem_bytes(p), stream>>>(p);
+    if (p.swap) gemm_q_kernel<256, true><<<p.n_tiles * p.n_splits, (256 / 32 + 3) * 32, gemm_smem_bytes(p), stream>>>(p);
+    else gemm_q_kernel<GM_BM, false><<<p.n_tiles * p.n_splits, (GM_BM / 32 + 3) * 32, gemm_smem_bytes(p), stream>>>(p);
     return cudaGetLastError();
 }
 

@@ -136,7 +136,7 @@ struct GemmParams {
     long split_stride;
     unsigned int* err;
     long long* dbg;         // optional: CTA 0 records clock64() per K block (8 slots each), scripts/gemm_micro.py
-    int n_tiles, n_splits, n_stages, n_bstages, n_raw;   // filled by gemm_plan
+    int n_tiles, n_splits, n_stages, n_bstages, n_raw, swap;   // filled by gemm_plan (swap: 256-row variant, tokens as the MMA's M)
 };
 cudaError_t gemm_init();
 int gemm_plan(GemmParams& p, int n_sms, int max_splits);
