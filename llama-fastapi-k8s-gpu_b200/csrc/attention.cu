@@ -50,6 +50,8 @@ __global__ void __launch_bounds__(AT_THREADS) attn_decode_batch_kernel(const Att
     __shared__ uint64_t full[2];
     if (threadIdx.x == 0) { mbar_init(&full[0], 1); mbar_init(&full[1], 1); fence_mbar_init(); }
     __syncthreads();
+    griddep_launch();
+    griddep_wait();
     const int z = blockIdx.z;
     const SlotDev sd = tab[b.slot[z]];
     AttnParams p = p0;
@@ -81,8 +83,13 @@ cudaError_t attn_decode_batch_launch(const AttnParams& p, const SlotDev* tab, co
     const bool cluster = p.n_splits == 2 || p.n_splits == 4 || p.n_splits == 8;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(p.n_splits, p.n_kv, b.n); cfg.blockDim = dim3(AT_THREADS); cfg.stream = stream;
-    cudaLaunchAttribute at[1];
+    cudaLaunchAttribute at[2];
     int na = 0;
+    if (g_chain_pdl) {
+        at[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[na].val.programmaticStreamSerializationAllowed = 1;
+        na++;
+    }
     if (cluster) {
         at[na].id = cudaLaunchAttributeClusterDimension;
         at[na].val.clusterDim.x = p.n_splits; at[na].val.clusterDim.y = 1; at[na].val.clusterDim.z = 1;

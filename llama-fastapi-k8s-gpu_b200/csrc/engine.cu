@@ -675,7 +675,14 @@ static int gemm_call(b2_engine* e, const DevTensor* const* ws, int nw, const __h
 
 // One chunk of T <= PF_T prompt tokens (device ids at `tokens`) at positions pos0.. through every layer:
 // tensor-core GEMMs over all T tokens at once, so each weight is read and dequantised once per chunk.
+struct ChainPdl {      // programmatic dependent launch for every kernel launched while this is alive
+    bool prev;
+    explicit ChainPdl(bool on) : prev(g_chain_pdl) { g_chain_pdl = on; }
+    ~ChainPdl() { g_chain_pdl = prev; }
+};
+
 static int prefill_chunk(b2_engine* e, Slot& s, const int* tokens, int T, int pos0) {
+    ChainPdl chain(e->use_pdl && !getenv("B2_NO_CHAIN_PDL"));
     const b2_config& c = e->cfg;
     cudaStream_t st = e->stream;
     const int E = c.n_embd, F = c.n_ff, hd = c.head_dim, T_pad = (T + 15) / 16 * 16;
@@ -785,6 +792,7 @@ static int ensure_batch_workspace(b2_engine* e) {
 // One decode step for b.n sequences at once: the weights are read (and dequantised) once for all of them by the
 // tensor-core GEMM; attention and sampling run one CTA group per sequence from the per-slot device tables.
 static int batch_step(b2_engine* e, const BatchIdx& b) {
+    ChainPdl chain(e->use_pdl && !getenv("B2_NO_CHAIN_PDL"));
     const b2_config& c = e->cfg;
     cudaStream_t st = e->stream;
     const int T = b.n, T_pad = (T + 15) / 16 * 16, E = c.n_embd, F = c.n_ff, hd = c.head_dim, qd = c.n_head * hd;

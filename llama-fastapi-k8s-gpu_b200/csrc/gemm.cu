@@ -438,6 +438,10 @@ __global__ void __launch_bounds__((ROWS / 32 + 3) * 32) gemm_q_kernel(const __gr
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
+    // Programmatic dependent launch: the next kernel of the chain may start now. In THIS kernel only the threads that
+    // touch the previous kernel's data wait for it (the activation producer; the epilogue, which overwrites the planes
+    // the previous consumer read): weights stream and dequantise while the predecessor is still running.
+    griddep_launch();
     const uint32_t tmem = sh.tmem_base;
     // K-major, no swizzle: element (r, k) of a tile with R rows sits at (k/8) * (R*16) + r*16 + (k%8)*2
     const uint32_t lbo_a = ROWS * 16, lbo_b = (uint32_t)T * 16, sbo = 128;
@@ -462,6 +466,7 @@ __global__ void __launch_bounds__((ROWS / 32 + 3) * 32) gemm_q_kernel(const __gr
         const int last = n - 1;
         mbar_wait(&sh.empty[last % S], (last / S) & 1, p.err, 0x40002u, (unsigned)last);
         tc_fence_after();
+        griddep_wait();
         if (!SWAP) {                               // TMEM lane = weight row, columns = tokens
             const int row = m0 + tid;
             const uint32_t lane_addr = tmem + ((uint32_t)(warp * 32) << 16);
@@ -532,6 +537,7 @@ __global__ void __launch_bounds__((ROWS / 32 + 3) * 32) gemm_q_kernel(const __gr
         const uint8_t* xb = reinterpret_cast<const uint8_t*>(p.x);
         int sb = 0;
         uint32_t useb = 0;
+        griddep_wait();                 // the activations come from the previous kernel
         for (int i = 0; i < n; i++) {
             if (useb > 0) mbar_wait(&sh.b_empty[sb], (useb - 1) & 1, p.err, 0x40005u, (unsigned)i);
             mbar_arrive_expect_tx(&sh.b_full[sb], b_bytes);
@@ -664,13 +670,14 @@ cudaError_t gemm_launch(const GemmParams& p, cudaStream_t stream) {
     if (p.n_stages < 2 || p.n_stages > GM_MAX_STAGES || p.n_bstages < 2 || p.n_bstages > GM_MAX_BSTAGES || p.n_splits < 1 ||
         p.n_tiles < 1) return cudaErrorInvalidValue;
     if (p.T_pad < 16 || p.T_pad > 512 || p.T_pad % 16 || p.T > p.T_pad || p.n_splits > p.K / 256) return cudaErrorInvalidValue;
-    if (p.swap) gemm_q_kernel<256, true><<<p.n_tiles * p.n_splits, (256 / 32 + 3) * 32, gemm_smem_bytes(p), stream>>>(p);
-    else gemm_q_kernel<GM_BM, false><<<p.n_tiles * p.n_splits, (GM_BM / 32 + 3) * 32, gemm_smem_bytes(p), stream>>>(p);
-    return cudaGetLastError();
+    if (p.swap) return launch_chain(gemm_q_kernel<256, true>, dim3(p.n_tiles * p.n_splits), dim3((256 / 32 + 3) * 32), gemm_smem_bytes(p), stream, p);
+    return launch_chain(gemm_q_kernel<GM_BM, false>, dim3(p.n_tiles * p.n_splits), dim3((GM_BM / 32 + 3) * 32), gemm_smem_bytes(p), stream, p);
 }
 
 // x [T][K] float32 -> f16 in the MMA operand order [K/8][T_pad][8] (rows >= T zero)
 __global__ void to_half_blocked_kernel(const float* x, int T, int T_pad, int K, __half* y) {
+    griddep_launch();
+    griddep_wait();
     const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;      // one output element
     if (i >= (long)T_pad * K) return;
     const int e = (int)(i & 7);
@@ -680,8 +687,7 @@ __global__ void to_half_blocked_kernel(const float* x, int T, int T_pad, int K, 
 }
 cudaError_t to_half_blocked_launch(const float* x, int T, int T_pad, int K, __half* y, cudaStream_t s) {
     const long n = (long)T_pad * K;
-    to_half_blocked_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(x, T, T_pad, K, y);
-    return cudaGetLastError();
+    return launch_chain(to_half_blocked_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, s, x, T, T_pad, K, y);
 }
 
 }  // namespace b2

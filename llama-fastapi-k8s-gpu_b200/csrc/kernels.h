@@ -5,7 +5,24 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <utility>
+
 namespace b2 {
+
+// Kernels of the prompt / batched-decode chains are launched with programmatic dependent launch while this is set
+// (engine.cu sets it around a chain): a kernel may start while its predecessor still runs and must execute
+// griddepcontrol.wait before it touches anything the predecessor writes (or reads, if it overwrites it).
+extern thread_local bool g_chain_pdl;
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_chain(void (*k)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = g_chain_pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, k, std::forward<Args>(args)...);
+}
 
 // ---------------------------------------------------------------- mat-vec (matvec.cu)
 enum MvMode { MV_STORE = 0, MV_RESID = 1, MV_QKV = 2, MV_GATEUP = 3 };

@@ -7,6 +7,8 @@
 
 namespace b2 {
 
+thread_local bool g_chain_pdl = false;
+
 unsigned int* kernel_error_word() {
     static unsigned int* w = nullptr;
     if (!w) {

@@ -22,6 +22,8 @@ namespace b2 {
 
 // ---------------------------------------------------------------- embedding rows
 __global__ void embed_rows_kernel(int type, const uint8_t* table, int K, const int* tokens, float* x) {
+    griddep_launch();
+    griddep_wait();
     const int t = blockIdx.x;
     const int be = block_elems(type), bb = block_bytes(type);
     const uint8_t* row = table + (size_t)tokens[t] * (K / be) * bb;
@@ -29,8 +31,7 @@ __global__ void embed_rows_kernel(int type, const uint8_t* table, int K, const i
         x[(size_t)t * K + i] = dequant_elem(type, row + (size_t)(i / be) * bb, i % be);
 }
 cudaError_t embed_rows_launch(int type, const uint8_t* table, int K, const int* tokens, int T, float* x, cudaStream_t s) {
-    embed_rows_kernel<<<T, 256, 0, s>>>(type, table, K, tokens, x);
-    return cudaGetLastError();
+    return launch_chain(embed_rows_kernel, dim3(T), dim3(256), 0, s, type, table, K, tokens, x);
 }
 
 __device__ __forceinline__ size_t op_index(int t, int k, int T_pad) { return ((size_t)(k >> 3) * T_pad + t) * 8 + (k & 7); }
@@ -39,6 +40,8 @@ __device__ __forceinline__ size_t op_index(int t, int k, int T_pad) { return ((s
 constexpr int RN_THREADS = 1024;
 __global__ void __launch_bounds__(RN_THREADS) resid_norm_half_kernel(float* x, const float* parts, int n_parts, long part_stride,
                                                                      const float* w, float eps, int K, int T_pad, __half* xn) {
+    griddep_launch();
+    griddep_wait();
     __shared__ float red[RN_THREADS / 32];
     const int t = blockIdx.x;
     float* xr = x + (size_t)t * K;
@@ -74,8 +77,7 @@ __global__ void __launch_bounds__(RN_THREADS) resid_norm_half_kernel(float* x, c
 }
 cudaError_t resid_norm_half_launch(float* x, const float* parts, int n_parts, long part_stride, const float* w, float eps,
                                    int K, int T, int T_pad, __half* xn, cudaStream_t s) {
-    resid_norm_half_kernel<<<T, RN_THREADS, 0, s>>>(x, parts, n_parts, part_stride, w, eps, K, T_pad, xn);
-    return cudaGetLastError();
+    return launch_chain(resid_norm_half_kernel, dim3(T), dim3(RN_THREADS), 0, s, x, parts, n_parts, part_stride, w, eps, K, T_pad, xn);
 }
 
 // ---------------------------------------------------------------- RoPE + KV store
@@ -83,6 +85,8 @@ cudaError_t resid_norm_half_launch(float* x, const float* parts, int n_parts, lo
 __global__ void rope_store_kernel(const float* parts, int n_parts, long part_stride, int T, int pos0, int n_head, int n_kv,
                                   int hd, int bt, const int* block_table, const float* rope_freq, __half* qh,
                                   __half* k_cache, __half* v_cache) {
+    griddep_launch();
+    griddep_wait();
     const int t = blockIdx.x, pos = pos0 + t;
     const int nq = n_head * hd, nk = n_kv * hd, row_len = nq + 2 * nk;
     const float* r = parts + (size_t)t * row_len;
@@ -116,12 +120,13 @@ __global__ void rope_store_kernel(const float* parts, int n_parts, long part_str
 cudaError_t rope_store_launch(const float* parts, int n_parts, long part_stride, int T, int pos0, int n_head, int n_kv, int hd,
                               int bt, const int* block_table, const float* rope_freq, __half* qh, __half* k_cache,
                               __half* v_cache, cudaStream_t s) {
-    rope_store_kernel<<<T, 1024, 0, s>>>(parts, n_parts, part_stride, T, pos0, n_head, n_kv, hd, bt, block_table, rope_freq, qh, k_cache, v_cache);
-    return cudaGetLastError();
+    return launch_chain(rope_store_kernel, dim3(T), dim3(1024), 0, s, parts, n_parts, part_stride, T, pos0, n_head, n_kv, hd, bt, block_table, rope_freq, qh, k_cache, v_cache);
 }
 
 // ---------------------------------------------------------------- SiLU(gate) * up -> f16
 __global__ void silu_mul_half_kernel(const float* parts, int n_parts, long part_stride, int F, int T, int T_pad, __half* h) {
+    griddep_launch();
+    griddep_wait();
     // thread <-> (8 consecutive f, token): one 16-byte store in operand order
     const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
     const int t = (int)(i % T), ch = (int)(i / T);
@@ -145,12 +150,13 @@ __global__ void silu_mul_half_kernel(const float* parts, int n_parts, long part_
 }
 cudaError_t silu_mul_half_launch(const float* parts, int n_parts, long part_stride, int F, int T, int T_pad, __half* h, cudaStream_t s) {
     const long n = (long)T * (F / 8);
-    silu_mul_half_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(parts, n_parts, part_stride, F, T, T_pad, h);
-    return cudaGetLastError();
+    return launch_chain(silu_mul_half_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, s, parts, n_parts, part_stride, F, T, T_pad, h);
 }
 
 // ---------------------------------------------------------------- batched decode step: one token per slot
 __global__ void embed_batch_kernel(int type, const uint8_t* table, int K, const SlotDev* tab, const BatchIdx b, float* x) {
+    griddep_launch();
+    griddep_wait();
     const int t = blockIdx.x;
     const int tok = tab[b.slot[t]].ints[0];
     const int be = block_elems(type), bb = block_bytes(type);
@@ -159,14 +165,15 @@ __global__ void embed_batch_kernel(int type, const uint8_t* table, int K, const 
         x[(size_t)t * K + i] = dequant_elem(type, row + (size_t)(i / be) * bb, i % be);
 }
 cudaError_t embed_batch_launch(int type, const uint8_t* table, int K, const SlotDev* tab, const BatchIdx& b, float* x, cudaStream_t s) {
-    embed_batch_kernel<<<b.n, 256, 0, s>>>(type, table, K, tab, b, x);
-    return cudaGetLastError();
+    return launch_chain(embed_batch_kernel, dim3(b.n), dim3(256), 0, s, type, table, K, tab, b, x);
 }
 
 // like rope_store, but row t belongs to slot b.slot[t] at that slot's own position; q stays float32 for flash-decode
 __global__ void rope_store_batch_kernel(const float* parts, int n_parts, long part_stride, const SlotDev* tab, const BatchIdx b,
                                         int n_head, int n_kv, int hd, int bt, const float* rope_freq, float* q_out,
                                         __half* k_cache, __half* v_cache) {
+    griddep_launch();
+    griddep_wait();
     const int t = blockIdx.x;
     const SlotDev sd = tab[b.slot[t]];
     const int pos = sd.ints[1];
@@ -201,12 +208,13 @@ __global__ void rope_store_batch_kernel(const float* parts, int n_parts, long pa
 cudaError_t rope_store_batch_launch(const float* parts, int n_parts, long part_stride, const SlotDev* tab, const BatchIdx& b,
                                     int n_head, int n_kv, int hd, int bt, const float* rope_freq, float* q_out,
                                     __half* k_cache, __half* v_cache, cudaStream_t s) {
-    rope_store_batch_kernel<<<b.n, 1024, 0, s>>>(parts, n_parts, part_stride, tab, b, n_head, n_kv, hd, bt, rope_freq, q_out, k_cache, v_cache);
-    return cudaGetLastError();
+    return launch_chain(rope_store_batch_kernel, dim3(b.n), dim3(1024), 0, s, parts, n_parts, part_stride, tab, b, n_head, n_kv, hd, bt, rope_freq, q_out, k_cache, v_cache);
 }
 
 // ---------------------------------------------------------------- slot registers after a prompt chunk
 __global__ void prefill_finish_kernel(const int* prompt, int n, int pos_last, int* ints, SamplerState* st) {
+    griddep_launch();
+    griddep_wait();
     int nh = st->n_hist;
     for (int i = 0; i < n; i++) { st->history[nh & (HISTORY_LEN - 1)] = prompt[i]; nh++; }
     st->n_hist = nh;
@@ -214,8 +222,7 @@ __global__ void prefill_finish_kernel(const int* prompt, int n, int pos_last, in
     ints[1] = pos_last;
 }
 cudaError_t prefill_finish_launch(const int* prompt, int n, int pos_last, int* ints, SamplerState* st, cudaStream_t s) {
-    prefill_finish_kernel<<<1, 1, 0, s>>>(prompt, n, pos_last, ints, st);
-    return cudaGetLastError();
+    return launch_chain(prefill_finish_kernel, dim3(1), dim3(1), 0, s, prompt, n, pos_last, ints, st);
 }
 
 // ---------------------------------------------------------------- causal attention for T queries
@@ -239,6 +246,8 @@ template <int HD>
 __global__ void __launch_bounds__(256) attn_prefill_kernel(const __half* qh, const __half* k_cache, const __half* v_cache,
                                                            const int* block_table, int T, int T_pad, int pos0, int n_head,
                                                            int n_kv, int bt, int QW, float scale_log2, __half* out) {
+    griddep_launch();
+    griddep_wait();
     constexpr int LD = HD + 8;                                  // padded row: conflict-free fragment loads
     extern __shared__ __align__(16) uint8_t smem_raw[];
     __half* ks = reinterpret_cast<__half*>(smem_raw);           // [PA_KT][LD]
@@ -367,10 +376,9 @@ cudaError_t attn_prefill_launch(const __half* qh, const __half* k_cache, const _
     dim3 grid((T + q_tile - 1) / q_tile, n_kv), block(32 * G * QW);
     const float scale_log2 = 1.4426950408889634f / sqrtf((float)hd);
     const size_t smem = (size_t)2 * PA_KT * (hd + 8) * 2;
-    if (hd == 64) attn_prefill_kernel<64><<<grid, block, smem, s>>>(qh, k_cache, v_cache, block_table, T, T_pad, pos0, n_head, n_kv, bt, QW, scale_log2, out);
-    else if (hd == 128) attn_prefill_kernel<128><<<grid, block, smem, s>>>(qh, k_cache, v_cache, block_table, T, T_pad, pos0, n_head, n_kv, bt, QW, scale_log2, out);
-    else return cudaErrorInvalidValue;
-    return cudaGetLastError();
+    if (hd == 64) return launch_chain(attn_prefill_kernel<64>, grid, block, smem, s, qh, k_cache, v_cache, block_table, T, T_pad, pos0, n_head, n_kv, bt, QW, scale_log2, out);
+    if (hd == 128) return launch_chain(attn_prefill_kernel<128>, grid, block, smem, s, qh, k_cache, v_cache, block_table, T, T_pad, pos0, n_head, n_kv, bt, QW, scale_log2, out);
+    return cudaErrorInvalidValue;
 }
 
 }  // namespace b2

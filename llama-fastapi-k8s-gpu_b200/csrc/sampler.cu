@@ -238,6 +238,8 @@ __global__ void __launch_bounds__(SM_THREADS) sample_kernel(float* logits, int V
 // one CTA per sequence of the batch
 __global__ void __launch_bounds__(SM_THREADS) sample_batch_kernel(float* logits, long row_stride, int V, const SlotDev* tab,
                                                                   const BatchIdx b, int n_uniform, int ring_len, int* out_tokens) {
+    griddep_launch();
+    griddep_wait();
     const int z = blockIdx.x;
     const SlotDev sd = tab[b.slot[z]];
     sample_body(logits + (size_t)z * row_stride, V, sd.sp, sd.sst, sd.uniforms, n_uniform, sd.ints + 3, sd.ints + 2, sd.ints + 0,
@@ -246,8 +248,7 @@ __global__ void __launch_bounds__(SM_THREADS) sample_batch_kernel(float* logits,
 
 cudaError_t sample_batch_launch(float* logits, long row_stride, int n_vocab, const SlotDev* tab, const BatchIdx& b,
                                 int ring_len, int* out_tokens, cudaStream_t s) {
-    sample_batch_kernel<<<b.n, SM_THREADS, 0, s>>>(logits, row_stride, n_vocab, tab, b, 8192, ring_len, out_tokens);
-    return cudaGetLastError();
+    return launch_chain(sample_batch_kernel, dim3(b.n), dim3(SM_THREADS), 0, s, logits, row_stride, n_vocab, tab, b, 8192, ring_len, out_tokens);
 }
 
 cudaError_t sample_launch(float* logits, int n_vocab, const SampleParams* params_dev, SamplerState* st,
