@@ -432,6 +432,15 @@ def main():
         roof["kernels"] = {k: {"ms": round(v["ms"], 4), "launches": v["launches"],
                                "GBps": round(v["bytes"] / max(v["ms"], 1e-9) / 1e6, 1)} for k, v in kinds.items()}
         roof["kernels_note"] = "one un-graphed decode step with events around every launch (no overlap between kernels)"
+        top = max((k for k in kinds if kinds[k]["bytes"] > 0), key=lambda k: kinds[k]["ms"])
+        kv = kinds[top]
+        roof["dominant_kernel"] = {"name": f"matvec_kernel, {top} launches" if top != "attention" else "attn_decode_kernel",
+                                   "launches_per_step": kv["launches"], "bytes_per_launch": int(kv["bytes"] / kv["launches"]),
+                                   "us_per_launch": round(kv["ms"] / kv["launches"] * 1e3, 2),
+                                   "achieved": round(kv["bytes"] / max(kv["ms"], 1e-9) / 1e6, 1), "unit": "GB/s",
+                                   "frac": round(kv["bytes"] / max(kv["ms"], 1e-9) / 1e6 / peak, 4),
+                                   "note": "CUDA events around each launch of this kind in one un-graphed step (cold start of every "
+                                           "launch included); the whole-step figure above is the graph replay"}
     line = {"metric": "decode_tokens_per_s", "value": round(value, 2), "unit": "tok/s", "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": round(ms_max / K, 5), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "int8x2 activations x int4/6 weights (dp4a), f32 accumulate, f16 KV", "data": "synthetic",
