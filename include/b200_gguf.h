@@ -158,7 +158,7 @@ int b2_op_gemm(int device, int type, const void* host_w, int n_rows, int K, cons
 int b2_op_rmsnorm(int device, const float* host_x, const float* host_w, float eps, int K, int rows, float* host_y);
 /* Decode attention for one sequence: q [n_head*head_dim] f32 (already rotated), K/V as f16
  * [n_ctx_tokens][n_kv][head_dim] (token-major; the op scatters them into pages in the order
- * host_blocks gives), attends to all n_ctx_tokens. out [n_head*head_dim] f32. */
+ * host_blocks gives), attends to all n_ctx_tokens. out [n_head*head_dim] f32. * n_splits < 0 selects the tensor-core kernel (attention_mma.cu, q rounded to f16) with -n_splits splits. */
 int b2_op_attention_decode(int device, const float* host_q, const uint16_t* host_k, const uint16_t* host_v,
                            int n_ctx_tokens, int n_head, int n_kv, int head_dim, int block_tokens,
                            const int32_t* host_blocks, int n_blocks_total, int n_splits, float* host_out);

@@ -14,7 +14,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "lib")
-CUDA_SOURCES = ["engine.cu", "matvec.cu", "attention.cu", "mega.cu", "gemm.cu", "prefill.cu", "misc.cu", "sampler.cu"]
+CUDA_SOURCES = ["engine.cu", "matvec.cu", "attention.cu", "attention_mma.cu", "mega.cu", "gemm.cu", "prefill.cu", "misc.cu", "sampler.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xptxas", "-v", "--expt-relaxed-constexpr"]
 

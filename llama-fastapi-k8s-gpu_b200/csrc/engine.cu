@@ -106,6 +106,7 @@ struct b2_engine {
     float *bd_q = nullptr, *bd_att = nullptr, *bd_scratch = nullptr;
     unsigned* bd_counters = nullptr;
     int* bd_out = nullptr;
+    int attn_mma = -1;             // tensor-core flash-decode: -1 = batched steps and > 8 splits (long contexts); 0 never; 1 always
     int batch_min = 3;             // fewer sequences than this step one after another through the mat-vec path (measured: 3 slots 4.1 vs 6.3 ms)
     bool gemm_ok = false;          // every layer matrix is a block format the GEMM reads
     int prefill_min = 8;           // prompts chunks shorter than this go token by token through the mat-vec path
@@ -160,6 +161,7 @@ extern "C" int b2_engine_create(const b2_config* c, b2_engine** out) {
     CK(cudaSetDevice(c->device));
     CK(mv_init());
     CK(attn_init());
+    CK(attn_mma_init());
     CK(mega_init());
     b2_engine* e = new b2_engine();
     e->cfg = *c;
@@ -408,6 +410,7 @@ extern "C" int b2_engine_finalize(b2_engine* e) {
             if (block_elems(t->type) == 1) e->gemm_ok = false;
     if (const char* s = getenv("B2_PREFILL_MIN")) if (atoi(s) > 0) e->prefill_min = atoi(s);
     if (const char* s = getenv("B2_BATCH_MIN")) if (atoi(s) > 0) e->batch_min = atoi(s);
+    if (const char* s = getenv("B2_ATTN_MMA")) e->attn_mma = atoi(s) ? 1 : 0;
     if (e->gemm_ok) CK(gemm_init());
     e->finalized = true;
     return B2_OK;
@@ -497,7 +500,8 @@ static int forward_launches(b2_engine* e, Slot& s, bool with_head, bool with_sam
         a.n_splits = e->n_splits; a.scale = 1.0f / sqrtf((float)c.head_dim); a.err = kernel_error_word();
         a.max_pages = e->max_blocks;
         tick(2, &ye);
-        CK(attn_decode_launch(a, st, pdl));
+        if (e->attn_mma == 1 || (e->attn_mma < 0 && e->n_splits > 8)) CK(attn_decode_mma_launch(a, nullptr, nullptr, st, pdl));
+        else CK(attn_decode_launch(a, st, pdl));
         tock(ye);
         MvParams o = L.p_o;
         o.x = s.att; o.y = s.x; o.resid = s.x;
@@ -817,7 +821,8 @@ static int batch_step(b2_engine* e, const BatchIdx& b) {
         while (ns > 1 && (long)ns * c.n_head_kv * T > 2L * e->n_sms) ns >>= 1;
         if (const char* v = getenv("B2_BATCH_ATTN_SPLITS")) if (atoi(v) > 0 && atoi(v) <= e->n_splits) ns = atoi(v);
         a.n_splits = ns; a.scale = 1.0f / sqrtf((float)hd); a.err = kernel_error_word(); a.max_pages = e->max_blocks;
-        CK(attn_decode_batch_launch(a, e->slot_tab, b, st));
+        if (e->attn_mma != 0) CK(attn_decode_mma_launch(a, e->slot_tab, &b, st, false));
+        else CK(attn_decode_batch_launch(a, e->slot_tab, b, st));
         CK(to_half_blocked_launch(e->bd_att, T, T_pad, qd, e->pf_att, st));
         const DevTensor* wo[1] = {&L.wo};
         if ((rc = gemm_call(e, wo, 1, e->pf_att, T, &np, &ps))) return rc;
@@ -1214,6 +1219,8 @@ extern "C" int b2_op_attention_decode(int device, const float* q, const uint16_t
     if (n_head % n_kv || n_head / n_kv > 8) return fail(B2_ERR_UNSUPPORTED, "n_head / n_kv must be an integer <= 8");
     if (bt <= 0 || bt % 16) return fail(B2_ERR_ARG, "block_tokens must be a multiple of 16");
     int need = (T + bt - 1) / bt;
+    const bool use_mma = n_splits < 0;      // negative: the tensor-core kernel with -n_splits splits
+    if (use_mma) n_splits = -n_splits;
     if (n_splits < 1) n_splits = 1;
     for (int i = 0; i < need; i++) if (blocks[i] < 0 || blocks[i] >= nblk_total) return fail(B2_ERR_ARG, "page id out of range");
     CK(cudaSetDevice(device));
@@ -1243,7 +1250,8 @@ extern "C" int b2_op_attention_decode(int device, const float* q, const uint16_t
     a.pos_ptr = dpos.as<int>(); a.out = dout.as<float>(); a.scratch = dscr.as<float>(); a.counters = dcnt.as<unsigned>();
     a.n_head = n_head; a.n_kv = n_kv; a.head_dim = hd; a.block_tokens = bt; a.n_splits = n_splits;
     a.scale = 1.0f / sqrtf((float)hd); a.err = kernel_error_word(); a.max_pages = need;
-    CK(attn_decode_launch(a, 0, false));
+    if (use_mma) { CK(attn_mma_init()); CK(attn_decode_mma_launch(a, nullptr, nullptr, 0, false)); }
+    else CK(attn_decode_launch(a, 0, false));
     CK(cudaDeviceSynchronize());
     { int rc2 = check_kernel_error(); if (rc2) return rc2; }
     CK(cudaMemcpy(out, dout.p, (size_t)n_head * hd * 4, cudaMemcpyDeviceToHost));

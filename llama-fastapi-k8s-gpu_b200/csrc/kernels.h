@@ -111,6 +111,9 @@ cudaError_t attn_decode_launch(const AttnParams& p, cudaStream_t stream, bool pd
 // one launch for b.n sequences: q / out are [b.n][n_head*head_dim]; position and page table come from tab[b.slot[z]];
 // scratch / counters need b.n times the single-sequence size
 cudaError_t attn_decode_batch_launch(const AttnParams& p, const SlotDev* tab, const BatchIdx& b, cudaStream_t stream);
+// tensor-core flash-decode (attention_mma.cu): same scratch / counters protocol; tab == nullptr: the one sequence p describes
+cudaError_t attn_mma_init();
+cudaError_t attn_decode_mma_launch(const AttnParams& p, const SlotDev* tab, const BatchIdx* b, cudaStream_t stream, bool pdl);
 // allocation-free variant: split partials in a fixed device array inside the library (attention.cu)
 size_t attn_static_scratch_floats();
 cudaError_t attn_static_setup(int device);

@@ -165,6 +165,27 @@ def test_attention_decode_vs_oracle(native_lib, n_head, n_kv, hd, T):
         assert np.abs(out - ref).max() < 2e-4, (n_head, n_kv, hd, T, bt, n_splits, np.abs(out - ref).max())
 
 
+@pytest.mark.parametrize("n_head,n_kv,hd", [(8, 2, 64), (4, 2, 128), (32, 8, 128), (32, 4, 64), (4, 4, 128), (8, 1, 128)])
+@pytest.mark.parametrize("T", [1, 15, 64, 65, 200, 1000, 3000])
+def test_attention_decode_tensor_core_vs_oracle(native_lib, n_head, n_kv, hd, T):
+    """attention_mma.cu (negative n_splits selects it): q and the probabilities are rounded to f16 for the MMA, so the
+    reference uses the f16-rounded q and the bar is 2e-3 absolute on O(1) outputs (f16 P: 2^-11 relative per term)."""
+    rng = np.random.default_rng(T * 11 + n_head)
+    q = rng.standard_normal(n_head * hd).astype(np.float32)
+    k = (rng.standard_normal((T, n_kv, hd)) * 0.7).astype(np.float16)
+    v = rng.standard_normal((T, n_kv, hd)).astype(np.float16)
+    ref = _attn_ref(q.astype(np.float16).astype(np.float32), k.astype(np.float32), v.astype(np.float32), n_head, n_kv, hd)
+    for bt, n_splits in ((16, 1), (16, 5), (64, 32), (64, 8), (32, 3)):
+        nblk = (T + bt - 1) // bt
+        total = nblk + 3
+        blocks = rng.permutation(total)[:nblk].astype(np.int32)
+        out = np.zeros(n_head * hd, np.float32)
+        rc = native_lib.b2_op_attention_decode(0, ptr(q), ptr(k.view(np.uint16)), ptr(v.view(np.uint16)), T, n_head,
+                                               n_kv, hd, bt, ptr(blocks), total, -n_splits, ptr(out))
+        lib_check(native_lib, rc)
+        assert np.abs(out - ref).max() < 2e-3, (n_head, n_kv, hd, T, bt, n_splits, np.abs(out - ref).max())
+
+
 def test_attention_rejects_bad_config(native_lib):
     q = np.zeros(96 * 2, np.float32)
     k = np.zeros((4, 2, 96), np.uint16)
