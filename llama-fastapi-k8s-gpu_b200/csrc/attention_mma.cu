@@ -195,21 +195,37 @@ __global__ void __launch_bounds__(AM_THREADS) attn_decode_mma_kernel(const AttnP
     __syncthreads();
     if (s_ticket != (unsigned)(p.n_splits - 1)) return;
     __threadfence();
+    // (m, l) of every split with independent loads, weights once per (head, split), then the outputs
+    float* msp = reinterpret_cast<float*>(smem_raw);             // [G][n_splits]; the tile buffers are free again
+    float* lsp = msp + 8 * p.n_splits;
+    float* wsp = lsp + 8 * p.n_splits;
+    float* inv = wsp + 8 * p.n_splits;                           // [G]
+    for (int i = tid; i < G * p.n_splits; i += AM_THREADS) {
+        const int gg = i / p.n_splits, s2 = i % p.n_splits;
+        const float* r = p.scratch + (((size_t)h * p.n_splits + s2) * G + gg) * rec;
+        msp[i] = __ldcg(r + HD);
+        lsp[i] = __ldcg(r + HD + 1);
+    }
+    __syncthreads();
+    if (tid < G) {
+        float M = -INFINITY, den = 0.f;
+        for (int s2 = 0; s2 < p.n_splits; s2++) M = fmaxf(M, msp[tid * p.n_splits + s2]);
+        for (int s2 = 0; s2 < p.n_splits; s2++) {
+            const float ms = msp[tid * p.n_splits + s2];
+            const float wt = ms == -INFINITY ? 0.f : exp2f(ms - M);
+            wsp[tid * p.n_splits + s2] = wt;
+            den += wt * lsp[tid * p.n_splits + s2];
+        }
+        inv[tid] = 1.0f / den;
+    }
+    __syncthreads();
     for (int e = tid; e < G * HD; e += AM_THREADS) {
         const int gg = e / HD, d = e % HD;
-        const float* base = p.scratch + ((size_t)h * p.n_splits * G + gg) * rec;
-        float M = -INFINITY;
-        for (int s2 = 0; s2 < p.n_splits; s2++) M = fmaxf(M, __ldcg(base + (size_t)s2 * G * rec + HD));
-        float num = 0.f, den = 0.f;
-#pragma unroll 4
-        for (int s2 = 0; s2 < p.n_splits; s2++) {
-            const float* r = base + (size_t)s2 * G * rec;
-            const float ms = __ldcg(r + HD);
-            const float wt = ms == -INFINITY ? 0.f : exp2f(ms - M);
-            num += wt * __ldcg(r + d);
-            den += wt * __ldcg(r + HD + 1);
-        }
-        p.out[((size_t)h * G + gg) * HD + d] = num / den;
+        const float* base = p.scratch + ((size_t)h * p.n_splits * G + gg) * rec + d;
+        float num = 0.f;
+#pragma unroll 8
+        for (int s2 = 0; s2 < p.n_splits; s2++) num += wsp[gg * p.n_splits + s2] * __ldcg(base + (size_t)s2 * G * rec);
+        p.out[((size_t)h * G + gg) * HD + d] = num * inv[gg];
     }
     if (tid == 0) p.counters[h] = 0;                             // ready for the next launch
 }
@@ -226,7 +242,7 @@ cudaError_t attn_mma_init() {
 // [b.n][n_head*head_dim] and scratch / counters hold b.n times the single-sequence size.
 cudaError_t attn_decode_mma_launch(const AttnParams& p, const SlotDev* tab, const BatchIdx* b, cudaStream_t stream, bool pdl) {
     const int G = p.n_kv > 0 ? p.n_head / p.n_kv : 0;
-    if (p.n_kv <= 0 || p.n_head % p.n_kv || G > 8 || p.n_splits < 1) return cudaErrorInvalidValue;
+    if (p.n_kv <= 0 || p.n_head % p.n_kv || G > 8 || p.n_splits < 1 || p.n_splits > 256) return cudaErrorInvalidValue;
     if (tab && (!b || b->n < 1 || b->n > BATCH_MAX)) return cudaErrorInvalidValue;
     BatchIdx none = {};
     cudaLaunchConfig_t cfg = {};
