@@ -53,7 +53,6 @@ typedef struct b2_config {
 #define B2_FLAG_NO_GRAPH 1      /* launch kernels directly instead of replaying CUDA graphs */
 #define B2_FLAG_NO_PDL 2        /* no programmatic dependent launch between kernels */
 #define B2_FLAG_ACT8 4          /* single int8 activation plane (faster, ~0.5% noise) */
-#define B2_FLAG_NO_MEGA 8       /* one kernel per operation instead of the persistent layer kernel */
 
 typedef struct b2_sampling {
     float temperature;        /* <= 0: greedy */
@@ -134,6 +133,13 @@ int b2_engine_mode(b2_engine* e, int* graph, int* pdl, int* act_planes, int* n_c
 int b2_profile_decode_step(b2_engine* e, int slot, float* ms_out, int32_t* launches_out,
                            int64_t* bytes_out);
 
+/* Streaming rate of the decode mat-vec kernel alone (scripts/mv_micro.py): synthetic weight bytes made on the
+ * device, `iters` launches back to back on one stream cycling through n_copies weight sets (size them past the
+ * L2), chained by programmatic dependent launch when pdl != 0. mode: 0 store, 1 residual add, 3 fused gate|up
+ * (two matrices of n_rows). us_per_launch_out = mean device time per launch (CUDA events). */
+int b2_bench_matvec(int device, int mode, int ggml_type, int n_rows, int K, int n_copies, int iters, int n_ctas,
+                    int act_planes, int pdl, float* us_per_launch_out);
+
 /* ---- single-operator entry points (parity tests call the kernels through these).
  *      All pointers are HOST memory; the call stages data through device scratch. ---------- */
 /* ggml dequantize_row_* / gguf.quants.dequantize */
@@ -181,13 +187,19 @@ int b2_op_sample(int device, const float* host_logits, int n_vocab, const b2_sam
  * V pools [page][n_kv][block_tokens][head_dim] f16, the page table (max_pages entries), *dev_pos
  * = index of the newest token (attends to 0..pos), out [n_head*head_dim] f32. `stream` is a
  * cudaStream_t (NULL = default stream); the call only enqueues work.
- * Limits: n_splits >= 2, n_head * n_splits * (head_dim + 2) <= 262144 floats, n_kv <= 64,
- * max_pages <= 512; anything larger is rejected with B2_ERR_ARG and a message naming the limit.
+ * Limits: n_splits >= 2, (n_head / n_kv) * n_splits <= 512, n_head * n_splits * (head_dim + 2) <= 262144 floats,
+ * n_kv <= 64, max_pages <= 512; anything larger is rejected with B2_ERR_ARG and a message naming the limit.
+ * The K and V pools must be 16-byte aligned (the kernel reads them with bulk copies), the other pointers 4-byte
+ * aligned; misaligned pointers are rejected. *dev_pos must be < max_pages * block_tokens: the kernel reads the
+ * position on the device and attends to at most max_pages * block_tokens positions whatever it says.
+ * The caller's current CUDA device is left as it was.
  * The first call on each device also looks up the array's device address (cudaGetSymbolAddress)
  * and sets a kernel attribute; make that first call before starting any stream capture.
  * Every call uses the same array: it clears the tickets, the partials are overwritten before they
  * are read, and two calls that overlap on the GPU (different streams) race with each other.
- * No cudaMalloc, cudaFree or allocating library routine is called. */
+ * No cudaMalloc, cudaFree or allocating library routine is called, also when this is the very first call
+ * into the library. The engine paths report a kernel that timed out on a barrier through a pinned host word;
+ * creating that word allocates, so this entry point does without it and cannot report such a time-out. */
 int b2_attention_decode_static(int device, const float* dev_q, const uint16_t* dev_k_pool,
                                const uint16_t* dev_v_pool, const int32_t* dev_block_table, int max_pages,
                                const int32_t* dev_pos, int n_head, int n_kv, int head_dim, int block_tokens,

@@ -13,8 +13,8 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-LIB = os.path.join(HERE, "lib")
-CUDA_SOURCES = ["engine.cu", "matvec.cu", "attention.cu", "attention_mma.cu", "mega.cu", "gemm.cu", "prefill.cu", "misc.cu", "sampler.cu"]
+LIB = os.environ.get("B2_LIB_DIR") or os.path.join(HERE, "lib")   # B2_LIB_DIR: experiment builds (with B2_NVCC_EXTRA)
+CUDA_SOURCES = ["engine.cu", "matvec.cu", "attention.cu", "attention_mma.cu", "gemm.cu", "prefill.cu", "misc.cu", "sampler.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xptxas", "-v", "--expt-relaxed-constexpr"]
 
@@ -32,18 +32,30 @@ def build(force: bool = False, verbose: bool = False) -> str:
     deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(HERE, "..", "include", "b200_gguf.h")]
     out = os.path.join(LIB, "libb200gguf.so")
     if force or _newer(out, deps):
-        objs = []
-        for src in CUDA_SOURCES:
+        extra = os.environ.get("B2_NVCC_EXTRA", "").split()
+        headers = [d for d in deps if not d.endswith(".cu")]
+
+        def compile_one(src):
             obj = os.path.join(LIB, src.replace(".cu", ".o"))
-            extra = os.environ.get("B2_NVCC_EXTRA", "").split()
-            cmd = [nvcc, *NVCC_FLAGS, *extra, "-c", os.path.join(CSRC, src), "-o", obj]
+            path = os.path.join(CSRC, src)
+            if not force and not extra and not _newer(obj, [path, *headers]):
+                return obj, 0, ""
+            cmd = [nvcc, *NVCC_FLAGS, *extra, "-c", path, "-o", obj]
             r = subprocess.run(cmd, capture_output=True, text=True)
-            if verbose or r.returncode:
-                sys.stderr.write(r.stdout + r.stderr)
-            if r.returncode:
+            if r.returncode == 0:
+                with open(os.path.join(LIB, src + ".ptxas.log"), "w") as f:
+                    f.write(r.stderr)
+            return obj, r.returncode, r.stdout + r.stderr
+
+        from concurrent.futures import ThreadPoolExecutor
+        with ThreadPoolExecutor(max_workers=min(len(CUDA_SOURCES), os.cpu_count() or 4)) as ex:
+            results = list(ex.map(compile_one, CUDA_SOURCES))
+        objs = []
+        for src, (obj, rc, log) in zip(CUDA_SOURCES, results):
+            if verbose or rc:
+                sys.stderr.write(log)
+            if rc:
                 raise RuntimeError(f"nvcc failed on {src}")
-            with open(os.path.join(LIB, src + ".ptxas.log"), "w") as f:
-                f.write(r.stderr)
             objs.append(obj)
         cmd = [nvcc, "-shared", "-o", out, *objs, "-gencode", "arch=compute_100a,code=sm_100a"]
         r = subprocess.run(cmd, capture_output=True, text=True)

@@ -21,6 +21,7 @@
 // Roofline: HBM; algorithmic bytes per launch = 2 * n_kv * head_dim * 2 B * (pos + 1). At chat
 // context lengths the kernel is latency bound (three dependent memory round trips).
 #include "attention_body.cuh"
+#include <mutex>
 
 namespace b2 {
 
@@ -166,7 +167,8 @@ static __device__ __align__(256) unsigned int g_static_tickets[STATIC_MAX_KV_HEA
 
 static float* g_scratch_addr[STATIC_MAX_DEVICES];
 static unsigned int* g_ticket_addr[STATIC_MAX_DEVICES];
-static bool g_static_ready[STATIC_MAX_DEVICES];
+static cudaError_t g_static_status[STATIC_MAX_DEVICES];
+static std::once_flag g_static_once[STATIC_MAX_DEVICES];      // calls may come from any host thread
 
 size_t attn_static_scratch_floats() { return STATIC_SCRATCH_FLOATS; }
 
@@ -174,17 +176,18 @@ size_t attn_static_scratch_floats() { return STATIC_SCRATCH_FLOATS; }
 // and raise the kernel's dynamic shared-memory limit. Nothing here allocates.
 cudaError_t attn_static_setup(int device) {
     if (device < 0 || device >= STATIC_MAX_DEVICES) return cudaErrorInvalidDevice;
-    if (g_static_ready[device]) return cudaSuccess;
-    cudaError_t e;
-    float* s = nullptr;
-    unsigned int* t = nullptr;
-    if ((e = cudaGetSymbolAddress((void**)&s, g_static_scratch)) != cudaSuccess) return e;
-    if ((e = cudaGetSymbolAddress((void**)&t, g_static_tickets)) != cudaSuccess) return e;
-    if ((e = attn_init()) != cudaSuccess) return e;
-    g_scratch_addr[device] = s;
-    g_ticket_addr[device] = t;
-    g_static_ready[device] = true;
-    return cudaSuccess;
+    std::call_once(g_static_once[device], [device]() {
+        cudaError_t e;
+        float* sp = nullptr;
+        unsigned int* t = nullptr;
+        if ((e = cudaGetSymbolAddress((void**)&sp, g_static_scratch)) == cudaSuccess &&
+            (e = cudaGetSymbolAddress((void**)&t, g_static_tickets)) == cudaSuccess && (e = attn_init()) == cudaSuccess) {
+            g_scratch_addr[device] = sp;
+            g_ticket_addr[device] = t;
+        }
+        g_static_status[device] = e;
+    });
+    return g_static_status[device];
 }
 
 // Launch the scratch-merging kernel on the built-in arrays. All pointers in `p` except scratch and
@@ -193,7 +196,7 @@ cudaError_t attn_static_setup(int device) {
 // call left and are fully rewritten before they are read. Two calls that overlap on the GPU
 // (different streams) would race on both arrays.
 cudaError_t attn_decode_launch_static(AttnParams p, int device, cudaStream_t stream) {
-    if (device < 0 || device >= STATIC_MAX_DEVICES || !g_static_ready[device]) return cudaErrorNotReady;
+    if (device < 0 || device >= STATIC_MAX_DEVICES || !g_scratch_addr[device]) return cudaErrorNotReady;
     p.scratch = g_scratch_addr[device];
     p.counters = g_ticket_addr[device];
     cudaError_t e = cudaMemsetAsync(p.counters, 0, sizeof(unsigned int) * STATIC_MAX_KV_HEADS, stream);

@@ -46,7 +46,8 @@ __device__ __forceinline__ void attn_decode_body(const AttnParams& p, AttnShared
     const int pos = *p.pos_ptr;
     for (int i = tid; i < p.max_pages && i < AT_MAX_PAGES; i += AT_THREADS) sh.pages[i] = p.block_table[i];
     for (int i = tid; i < G * HD; i += AT_THREADS) sh.q[i / HD][i % HD] = __ldcg(p.q + (size_t)h * G * HD + i);   // written by other SMs
-    const int ctx = pos + 1;
+    // never index past the page ids that were staged above, whatever the caller's position says
+    const int ctx = min(pos + 1, min(p.max_pages, AT_MAX_PAGES) * bt);
     int chunk = (ctx + p.n_splits - 1) / p.n_splits;
     chunk = (chunk + 15) & ~15;
     const int p0 = min(ctx, sp * chunk), p1 = min(ctx, p0 + chunk);

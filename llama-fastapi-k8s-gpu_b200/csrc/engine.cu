@@ -66,8 +66,6 @@ struct Slot {
     double* uniforms = nullptr;    // [8192]
     cudaGraphExec_t g_decode = nullptr, g_pre_step = nullptr, g_pre_last = nullptr, g_fwd = nullptr;
     int n_decode_nodes = 0, n_pre_step_nodes = 0, n_pre_last_nodes = 0, n_fwd_nodes = 0;
-    MvParams* mega_mv = nullptr;   // device tables for the persistent layer kernel (built on first use)
-    AttnParams* mega_at = nullptr;
     const float* logits_view = nullptr;   // where the latest logits of this slot are (own buffer, or a row of the batch output)
     int n_past = 0;                // host mirror of ints[1]
     int n_sampled = 0;             // host mirror of ints[3]
@@ -90,12 +88,8 @@ struct b2_engine {
     int32_t* pinned = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     int64_t launches = 0, weight_bytes = 0, kv_bytes = 0;
-    bool use_graph = true, use_pdl = true, act2 = true, finalized = false, use_mega = true;
-    MegaParams mega = {};
-    unsigned int* mega_bar = nullptr;
-    int mega_splits = 1;
-    float* mega_scratch = nullptr;
-    unsigned* mega_counters = nullptr;
+    bool use_graph = true, use_pdl = true, act2 = true, finalized = false, chain_pdl = true;
+    int batch_attn_splits = 0;     // B2_BATCH_ATTN_SPLITS (tuning), read once at create
     // prompt (GEMM) workspace, allocated on the first long prompt: PF_T tokens per chunk
     float *pf_x = nullptr, *pf_part = nullptr;     // residual stream [PF_T][n_embd]; K-split partial sums of the last GEMM
     size_t pf_part_floats = 0;
@@ -110,7 +104,6 @@ struct b2_engine {
     int batch_min = 3;             // fewer sequences than this step one after another through the mat-vec path (measured: 3 slots 4.1 vs 6.3 ms)
     bool gemm_ok = false;          // every layer matrix is a block format the GEMM reads
     int prefill_min = 8;           // prompts chunks shorter than this go token by token through the mat-vec path
-    unsigned long long* mega_ts = nullptr;   // B2_MEGA_TS=1: phase timestamps of the last layer-kernel launch
     std::mutex mu;
 };
 
@@ -147,6 +140,7 @@ extern "C" int b2_device_count(int* n) {
     return B2_OK;
 }
 
+static int engine_create_impl(b2_engine* e, const b2_config* c);
 extern "C" int b2_engine_create(const b2_config* c, b2_engine** out) {
     if (!c || !out) return fail(B2_ERR_ARG, "null argument");
     if (c->n_layer <= 0 || c->n_embd <= 0 || c->n_head <= 0 || c->n_head_kv <= 0 || c->n_vocab <= 0 ||
@@ -158,22 +152,29 @@ extern "C" int b2_engine_create(const b2_config* c, b2_engine** out) {
     if (c->n_embd % 256 || c->n_ff % 256 || (c->n_head * c->head_dim) % 256)
         return fail(B2_ERR_UNSUPPORTED, "n_embd, n_ff and n_head*head_dim must be multiples of 256");
     if (c->kv_block_tokens % 16) return fail(B2_ERR_ARG, "kv_block_tokens must be a multiple of 16");
+    b2_engine* e = new b2_engine();
+    e->cfg = *c;
+    const int rc = engine_create_impl(e, c);
+    if (rc) { b2_engine_destroy(e); return rc; }     // frees whatever was allocated before the failure (e.g. KV pool OOM)
+    *out = e;
+    return B2_OK;
+}
+
+static int engine_create_impl(b2_engine* e, const b2_config* c) {
     CK(cudaSetDevice(c->device));
     CK(mv_init());
     CK(attn_init());
     CK(attn_mma_init());
-    CK(mega_init());
-    b2_engine* e = new b2_engine();
-    e->cfg = *c;
     e->use_graph = !(c->flags & B2_FLAG_NO_GRAPH);
     e->use_pdl = !(c->flags & B2_FLAG_NO_PDL);
     e->act2 = !(c->flags & B2_FLAG_ACT8);
-    // The persistent layer kernel is opt-in (B2_MEGA=1): measured slower than the per-kernel graph on B200
-    // (a 148-CTA grid barrier costs ~5 us, as much as a kernel boundary).
-    e->use_mega = getenv("B2_MEGA") && !(c->flags & B2_FLAG_NO_MEGA) && !getenv("B2_NO_MEGA");
+    // tuning knobs are read here, once; the hot path never calls getenv
+    e->chain_pdl = e->use_pdl && !getenv("B2_NO_CHAIN_PDL");
+    if (const char* s = getenv("B2_BATCH_ATTN_SPLITS")) e->batch_attn_splits = atoi(s);
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
-    int per = mv_ctas_per_sm_default();
+    // one mat-vec CTA per SM: the second CTA slot of every SM is for the NEXT kernel's CTAs (matvec.cu)
+    int per = 1;
     if (const char* s = getenv("B2_CTAS_PER_SM")) per = atoi(s) > 0 ? atoi(s) : per;
     e->n_ctas = sms * per;
     e->n_sms = sms;
@@ -240,7 +241,6 @@ extern "C" int b2_engine_create(const b2_config* c, b2_engine** out) {
         CK(cudaMemcpy(e->slot_tab, tab.data(), sizeof(SlotDev) * c->max_seqs, cudaMemcpyHostToDevice));
     }
     CK(cudaStreamSynchronize(e->stream));
-    *out = e;
     return B2_OK;
 }
 
@@ -255,22 +255,23 @@ static void free_slot_graphs(Slot& s) {
 extern "C" int b2_engine_destroy(b2_engine* e) {
     if (!e) return B2_OK;
     cudaSetDevice(e->cfg.device);
-    cudaStreamSynchronize(e->stream);
+    if (e->stream) cudaStreamSynchronize(e->stream);
     for (auto& kv : e->tensors) cudaFree(kv.second.ptr);
     for (auto& s : e->slots) {
         free_slot_graphs(s);
         cudaFree(s.x); cudaFree(s.q); cudaFree(s.att); cudaFree(s.h); cudaFree(s.logits);
         cudaFree(s.ints); cudaFree(s.block_table); cudaFree(s.prompt); cudaFree(s.ring); cudaFree(s.sst); cudaFree(s.sp);
-        cudaFree(s.uniforms); cudaFree(s.mega_mv); cudaFree(s.mega_at);
+        cudaFree(s.uniforms);
     }
-    cudaFree(e->mega_bar); cudaFree(e->mega_scratch); cudaFree(e->mega_counters);
     cudaFree(e->k_pool); cudaFree(e->v_pool); cudaFree(e->rope_freq);
     cudaFree(e->attn_scratch); cudaFree(e->attn_counters);
     cudaFree(e->pf_x); cudaFree(e->pf_part); cudaFree(e->pf_xn); cudaFree(e->pf_qh); cudaFree(e->pf_att); cudaFree(e->pf_h);
     cudaFree(e->slot_tab); cudaFree(e->bd_q); cudaFree(e->bd_att); cudaFree(e->bd_scratch); cudaFree(e->bd_counters); cudaFree(e->bd_out);
-    cudaFreeHost(e->pinned);
-    cudaEventDestroy(e->ev0); cudaEventDestroy(e->ev1);
-    cudaStreamDestroy(e->stream);
+    if (e->pinned) cudaFreeHost(e->pinned);
+    if (e->ev0) cudaEventDestroy(e->ev0);
+    if (e->ev1) cudaEventDestroy(e->ev1);
+    if (e->stream) cudaStreamDestroy(e->stream);
+    cudaGetLastError();
     delete e;
     return B2_OK;
 }
@@ -319,7 +320,7 @@ static MvSeg make_seg(const DevTensor& t, int out_off = 0) {
 static int plan_or_fail(MvParams& p, int n_ctas, const char* what) {
     int rc = mv_plan(p, n_ctas);
     if (rc) return fail(B2_ERR_UNSUPPORTED, std::string("cannot plan mat-vec for ") + what + " (code " + std::to_string(rc) +
-                                               (rc == -2 ? ": K > 16384 not supported yet)" : ")"));
+                                               (rc == -2 ? ": K > 65536 not supported)" : ")"));
     return B2_OK;
 }
 
@@ -381,29 +382,6 @@ extern "C" int b2_engine_finalize(b2_engine* e) {
     h.norm_w = (const float*)e->out_norm.ptr; h.eps = c.rms_eps; h.err = kernel_error_word();
     if ((rc = plan_or_fail(h, e->n_ctas, "output"))) return rc;
     e->p_head = h;
-    if (e->use_mega) {
-        // one ring geometry for the whole layer stack; attention inside it merges splits through global scratch
-        std::vector<MvParams> all;
-        for (auto& L : e->layers) { all.push_back(L.p_qkv); all.push_back(L.p_o); all.push_back(L.p_gu); all.push_back(L.p_down); }
-        int sms = e->n_ctas;
-        int G = c.n_head / c.n_head_kv;
-        int ns = sms / c.n_head_kv;
-        if (ns > 32) ns = 32;
-        while (ns > 1 && (G * ns > 512 || (ns - 1) * 16 >= c.n_ctx)) ns--;
-        if (ns < 1) ns = 1;
-        e->mega_splits = ns;
-        int prc = mega_plan(e->mega, all.data(), (int)all.size(), c.head_dim, c.n_head_kv, ns, sms);
-        if (prc != 0 || mv_ctas_per_sm_default() != 1) e->use_mega = false;    // shapes do not fit: per-kernel path
-        else {
-            e->mega.n_layer = c.n_layer; e->mega.err = kernel_error_word();
-            CK(cudaMalloc(&e->mega_bar, sizeof(unsigned int)));
-            CK(cudaMalloc(&e->mega_scratch, attn_scratch_floats(c.n_head, c.n_head_kv, c.head_dim, ns) * 4));
-            CK(cudaMalloc(&e->mega_counters, sizeof(unsigned) * c.n_head_kv));
-            CK(cudaMemset(e->mega_counters, 0, sizeof(unsigned) * c.n_head_kv));
-            e->mega.bar = e->mega_bar;
-            if (getenv("B2_MEGA_TS")) { CK(cudaMalloc(&e->mega_ts, sizeof(unsigned long long) * (5 * c.n_layer + 2 + 16 * c.n_layer))); e->mega.ts = e->mega_ts; }
-        }
-    }
     e->gemm_ok = !getenv("B2_NO_GEMM_PREFILL");
     for (auto& L : e->layers)
         for (const DevTensor* t : {&L.wq, &L.wk, &L.wv, &L.wo, &L.wgate, &L.wup, &L.wdown})
@@ -429,38 +407,6 @@ struct KindTimer {
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev[8];
 };
 
-// per-slot phase tables of the persistent layer kernel: the engine's plans with this slot's buffers filled in
-static int ensure_mega_tables(b2_engine* e, Slot& s) {
-    if (!e->use_mega || s.mega_mv) return B2_OK;
-    const b2_config& c = e->cfg;
-    cudaStream_t st = e->stream;
-    int* pos = s.ints + 1;
-            std::vector<MvParams> mv; std::vector<AttnParams> at;
-            for (int l = 0; l < c.n_layer; l++) {
-                Layer& L = e->layers[l];
-                MvParams q = L.p_qkv; q.x = s.x; q.q_out = s.q; q.pos_ptr = pos; q.block_table = s.block_table;
-                MvParams o = L.p_o; o.x = s.att; o.y = s.x; o.resid = s.x;
-                MvParams g = L.p_gu; g.x = s.x; g.y = s.h;
-                MvParams d = L.p_down; d.x = s.h; d.y = s.x; d.resid = s.x;
-                mv.push_back(q); mv.push_back(o); mv.push_back(g); mv.push_back(d);
-                AttnParams a = {};
-                a.q = s.q; a.k_cache = q.k_cache; a.v_cache = q.v_cache; a.block_table = s.block_table; a.pos_ptr = pos;
-                a.out = s.att; a.scratch = e->mega_scratch; a.counters = e->mega_counters;
-                a.n_head = c.n_head; a.n_kv = c.n_head_kv; a.head_dim = c.head_dim; a.block_tokens = c.kv_block_tokens;
-                a.n_splits = e->mega_splits; a.scale = 1.0f / sqrtf((float)c.head_dim); a.err = kernel_error_word();
-                a.max_pages = e->max_blocks;
-                at.push_back(a);
-            }
-            cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
-            cudaStreamIsCapturing(st, &cs);
-            if (cs != cudaStreamCaptureStatusNone) return fail(B2_ERR_STATE, "phase tables must be built outside stream capture");
-            CK(cudaMalloc(&s.mega_mv, sizeof(MvParams) * mv.size()));
-            CK(cudaMalloc(&s.mega_at, sizeof(AttnParams) * at.size()));
-            CK(cudaMemcpy(s.mega_mv, mv.data(), sizeof(MvParams) * mv.size(), cudaMemcpyHostToDevice));
-            CK(cudaMemcpy(s.mega_at, at.data(), sizeof(AttnParams) * at.size(), cudaMemcpyHostToDevice));
-            return B2_OK;
-}
-
 static int forward_launches(b2_engine* e, Slot& s, bool with_head, bool with_sample, bool pdl, KindTimer* kt) {
     const b2_config& c = e->cfg;
     cudaStream_t st = e->stream;
@@ -479,13 +425,6 @@ static int forward_launches(b2_engine* e, Slot& s, bool with_head, bool with_sam
     CK(embed_row_launch(e->tok_embd.type, e->tok_embd.ptr, c.n_embd, tok, s.x, st, pdl));
     tock(ye);
     e->launches++;
-    if (e->use_mega && !kt) {
-        { int rc0 = ensure_mega_tables(e, s); if (rc0) return rc0; }
-        MegaParams mp = e->mega;
-        mp.mv = s.mega_mv; mp.at = s.mega_at;
-        CK(mega_launch(mp, e->n_ctas, st, e->act2));
-        e->launches++;
-    } else
     for (int l = 0; l < c.n_layer; l++) {
         Layer& L = e->layers[l];
         MvParams q = L.p_qkv;
@@ -555,7 +494,6 @@ static int run_step(b2_engine* e, Slot& s, GraphKind k) {
     int* nn = k == GK_DECODE ? &s.n_decode_nodes : k == GK_PRE_STEP ? &s.n_pre_step_nodes : k == GK_PRE_LAST ? &s.n_pre_last_nodes : &s.n_fwd_nodes;
     if (!e->use_graph) return record_step(e, s, k, e->use_pdl);
     if (!*ge) {
-        { int rc0 = ensure_mega_tables(e, s); if (rc0) return rc0; }    // cudaMalloc: outside the capture
         for (int attempt = 0; attempt < 2 && !*ge; attempt++) {
             bool pdl = e->use_pdl && attempt == 0;
             int64_t before = e->launches;
@@ -686,7 +624,7 @@ struct ChainPdl {      // programmatic dependent launch for every kernel launche
 };
 
 static int prefill_chunk(b2_engine* e, Slot& s, const int* tokens, int T, int pos0) {
-    ChainPdl chain(e->use_pdl && !getenv("B2_NO_CHAIN_PDL"));
+    ChainPdl chain(e->chain_pdl && e->use_pdl);
     const b2_config& c = e->cfg;
     cudaStream_t st = e->stream;
     const int E = c.n_embd, F = c.n_ff, hd = c.head_dim, T_pad = (T + 15) / 16 * 16;
@@ -796,7 +734,7 @@ static int ensure_batch_workspace(b2_engine* e) {
 // One decode step for b.n sequences at once: the weights are read (and dequantised) once for all of them by the
 // tensor-core GEMM; attention and sampling run one CTA group per sequence from the per-slot device tables.
 static int batch_step(b2_engine* e, const BatchIdx& b) {
-    ChainPdl chain(e->use_pdl && !getenv("B2_NO_CHAIN_PDL"));
+    ChainPdl chain(e->chain_pdl && e->use_pdl);
     const b2_config& c = e->cfg;
     cudaStream_t st = e->stream;
     const int T = b.n, T_pad = (T + 15) / 16 * 16, E = c.n_embd, F = c.n_ff, hd = c.head_dim, qd = c.n_head * hd;
@@ -819,7 +757,7 @@ static int batch_step(b2_engine* e, const BatchIdx& b) {
         // enough CTAs to fill the GPU ~2x over, no more (8 sequences: 4 splits 4.36 ms/step, 8 splits 4.81): every extra split of a sequence re-pays the kernel's fixed latency
         int ns = e->n_splits;
         while (ns > 1 && (long)ns * c.n_head_kv * T > 2L * e->n_sms) ns >>= 1;
-        if (const char* v = getenv("B2_BATCH_ATTN_SPLITS")) if (atoi(v) > 0 && atoi(v) <= e->n_splits) ns = atoi(v);
+        if (e->batch_attn_splits > 0 && e->batch_attn_splits <= e->n_splits) ns = e->batch_attn_splits;
         a.n_splits = ns; a.scale = 1.0f / sqrtf((float)hd); a.err = kernel_error_word(); a.max_pages = e->max_blocks;
         if (e->attn_mma != 0) CK(attn_decode_mma_launch(a, e->slot_tab, &b, st, false));
         else CK(attn_decode_batch_launch(a, e->slot_tab, b, st));
@@ -905,25 +843,6 @@ extern "C" int b2_decode_n(b2_engine* e, int slot, int n, int32_t* out) {
     CK(cudaMemcpyAsync(e->pinned, s.ring + s.n_past + 1, sizeof(int) * n, cudaMemcpyDeviceToHost, e->stream));
     CK(cudaStreamSynchronize(e->stream));
     if ((rc = check_kernel_error())) return rc;
-    if (e->mega_ts && e->use_mega) {      // debugging aid: per-phase-kind time of the last token's layer kernel
-        int L = e->cfg.n_layer;
-        std::vector<unsigned long long> ts(5 * L + 2 + 16 * L);
-        cudaMemcpy(ts.data(), e->mega_ts, sizeof(unsigned long long) * ts.size(), cudaMemcpyDeviceToHost);
-        double kind[5] = {0, 0, 0, 0, 0};
-        for (int i = 0; i < 5 * L; i++) kind[i % 5] += (double)(ts[i + 1] - ts[i]) * 1e-3;
-        fprintf(stderr, "[b2 mega] us per token: qkv %.1f attention %.1f attn_out %.1f gate_up %.1f ffn_down %.1f total %.1f\n",
-                kind[0], kind[1], kind[2], kind[3], kind[4], (double)(ts[5 * L] - ts[0]) * 1e-3);
-        // CTA 0, thread 0 inside each mat-vec phase: [params+sync, input quantisation, tiles, grid barrier is the rest]
-        const char* nm[4] = {"qkv", "attn_out", "gate_up", "ffn_down"};
-        for (int k = 0; k < 4; k++) {
-            double a = 0, b = 0, cc = 0;
-            for (int l = 0; l < L; l++) {
-                const unsigned long long* t2 = &ts[5 * L + 2 + (l * 4 + k) * 4];
-                a += (double)(t2[1] - t2[0]); b += (double)(t2[2] - t2[1]); cc += (double)(t2[3] - t2[2]);
-            }
-            fprintf(stderr, "[b2 mega]   %-8s per layer (us): params %.2f  quantise %.2f  tiles %.2f\n", nm[k], a / L * 1e-3, b / L * 1e-3, cc / L * 1e-3);
-        }
-    }
     if (out) memcpy(out, e->pinned, sizeof(int) * n);
     s.n_past += n;
     s.n_sampled += n;
@@ -1089,7 +1008,7 @@ extern "C" int b2_op_dequantize(int device, int type, const void* blocks, int64_
 
 static int op_matvec_common(int device, MvParams& p, const void* w0, const void* w1, int n_rows, int K,
                             const float* x, const float* nw, const float* resid, float* y, int planes, int n_ctas) {
-    if (n_ctas <= 0) { int sms = 148; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device); n_ctas = sms * mv_ctas_per_sm_default(); }
+    if (n_ctas <= 0) { int sms = 148; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device); n_ctas = sms; }
     CK(mv_init());
     int rc = mv_plan(p, n_ctas);
     if (rc) return fail(B2_ERR_UNSUPPORTED, "mat-vec shape/type not supported (plan code " + std::to_string(rc) + ")");
@@ -1137,6 +1056,60 @@ extern "C" int b2_op_gate_up(int device, int tg, const void* wg, int tu, const v
     p.nseg = 2; p.seg[0].type = tg; p.seg[0].n_rows = n_rows; p.seg[1].type = tu; p.seg[1].n_rows = n_rows;
     p.K = K; p.mode = MV_GATEUP; p.eps = eps;
     return op_matvec_common(device, p, wg, wu, n_rows, K, x, nw, nullptr, y, 2, n_ctas);
+}
+
+// ------------------------------------------------------------------------------------------
+// measurement aid: streaming rate of the mat-vec kernel alone, on synthetic weight bytes
+__global__ void fill_hash_kernel(uint32_t* p, size_t n_words, uint32_t seed) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n_words; i += (size_t)gridDim.x * blockDim.x) {
+        uint32_t v = (uint32_t)i * 2654435761u + seed;
+        v ^= v >> 15; v *= 2246822519u; v ^= v >> 13; v *= 3266489917u; v ^= v >> 16;
+        p[i] = v & 0x3BFF3BFFu;        // clears the top exponent bit of every f16 that may sit here: scale fields stay finite
+    }
+}
+
+extern "C" int b2_bench_matvec(int device, int mode, int type, int n_rows, int K, int n_copies, int iters, int n_ctas,
+                               int planes, int pdl, float* us_out) {
+    if (!us_out || n_rows <= 0 || K <= 0 || n_copies <= 0 || iters <= 0) return fail(B2_ERR_ARG, "bad arguments");
+    if (mode != MV_STORE && mode != MV_RESID && mode != MV_GATEUP) return fail(B2_ERR_ARG, "mode must be 0, 1 or 3");
+    CK(cudaSetDevice(device));
+    CK(mv_init());
+    if (n_ctas <= 0) { int sms = 148; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device); n_ctas = sms; }
+    MvParams p = {};
+    const int nmat = mode == MV_GATEUP ? 2 : 1;
+    p.nseg = nmat; p.K = K; p.mode = mode;
+    for (int m = 0; m < nmat; m++) { p.seg[m].type = type; p.seg[m].n_rows = n_rows; }
+    int rc = mv_plan(p, n_ctas);
+    if (rc) return fail(B2_ERR_UNSUPPORTED, "mat-vec shape/type not supported (plan code " + std::to_string(rc) + ")");
+    const size_t wb = (size_t)n_rows * p.seg[0].row_bytes, wpad = (wb + 64 + 255) / 256 * 256;
+    DevBuf dw, dx, dy;
+    CK(dw.alloc(wpad * nmat * n_copies)); CK(dx.alloc((size_t)K * 4)); CK(dy.alloc((size_t)n_rows * 4));
+    fill_hash_kernel<<<1184, 256>>>(dw.as<uint32_t>(), wpad * nmat * n_copies / 4, 12345u);
+    fill_hash_kernel<<<64, 256>>>(dx.as<uint32_t>(), (size_t)K, 777u);       // finite floats of mixed magnitude
+    CK(cudaMemset(dy.p, 0, (size_t)n_rows * 4));
+    CK(cudaGetLastError());
+    p.x = dx.as<float>(); p.y = dy.as<float>(); p.resid = dy.as<float>(); p.err = kernel_error_word();
+    cudaStream_t st;
+    CK(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    CK(cudaDeviceSynchronize());
+    float ms = 0.f;
+    for (int pass = 0; pass < 2; pass++) {          // pass 0 warms up
+        if (pass) CK(cudaEventRecord(e0, st));
+        for (int i = 0; i < iters; i++) {
+            const uint8_t* base = dw.as<uint8_t>() + (size_t)(i % n_copies) * wpad * nmat;
+            for (int m = 0; m < nmat; m++) p.seg[m].w = base + (size_t)m * wpad;
+            CK(mv_launch(p, n_ctas, st, planes != 1, pdl != 0));
+        }
+        if (pass) CK(cudaEventRecord(e1, st));
+        CK(cudaStreamSynchronize(st));
+    }
+    CK(cudaEventElapsedTime(&ms, e0, e1));
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaStreamDestroy(st);
+    if (int rc2 = check_kernel_error()) return rc2;
+    *us_out = ms * 1000.f / (float)iters;
+    return B2_OK;
 }
 
 __global__ void sum_parts_kernel(const float* parts, int n_parts, long stride, const float* y_in, long n, float* y) {
@@ -1307,13 +1280,25 @@ extern "C" int b2_attention_decode_static(int device, const float* dev_q, const 
     if (need > attn_static_scratch_floats())
         return fail(B2_ERR_ARG, "split partials need " + std::to_string(need * 4) + " bytes, the built-in scratch holds " +
                                     std::to_string(attn_static_scratch_floats() * 4) + " (n_head * n_splits * (head_dim + 2) floats)");
-    CK(cudaSetDevice(device));
-    CK(attn_static_setup(device));      // first call on a device resolves the symbol addresses
-    AttnParams a = {};
-    a.q = dev_q; a.k_cache = (const __half*)dev_k_pool; a.v_cache = (const __half*)dev_v_pool;
-    a.block_table = dev_block_table; a.pos_ptr = dev_pos; a.out = dev_out;
-    a.n_head = n_head; a.n_kv = n_kv; a.head_dim = head_dim; a.block_tokens = block_tokens; a.n_splits = n_splits;
-    a.max_pages = max_pages; a.scale = 1.0f / sqrtf((float)head_dim); a.err = kernel_error_word();
-    CK(attn_decode_launch_static(a, device, (cudaStream_t)stream));
+    if (((uintptr_t)dev_k_pool | (uintptr_t)dev_v_pool) & 15)
+        return fail(B2_ERR_ARG, "the K and V pools must be 16-byte aligned (bulk copies read them)");
+    if (((uintptr_t)dev_q | (uintptr_t)dev_out | (uintptr_t)dev_block_table | (uintptr_t)dev_pos) & 3)
+        return fail(B2_ERR_ARG, "q, out, the page table and the position must be 4-byte aligned");
+    int prev_device = -1;
+    CK(cudaGetDevice(&prev_device));
+    if (prev_device != device) CK(cudaSetDevice(device));
+    // first call on a device: resolve the symbol addresses (no allocation). Never touches the host-mapped watchdog word
+    // the engine paths use (creating it allocates pinned memory): a barrier time-out in this call is not reported.
+    cudaError_t ce = attn_static_setup(device);
+    if (ce == cudaSuccess) {
+        AttnParams a = {};
+        a.q = dev_q; a.k_cache = (const __half*)dev_k_pool; a.v_cache = (const __half*)dev_v_pool;
+        a.block_table = dev_block_table; a.pos_ptr = dev_pos; a.out = dev_out;
+        a.n_head = n_head; a.n_kv = n_kv; a.head_dim = head_dim; a.block_tokens = block_tokens; a.n_splits = n_splits;
+        a.max_pages = max_pages; a.scale = 1.0f / sqrtf((float)head_dim); a.err = nullptr;
+        ce = attn_decode_launch_static(a, device, (cudaStream_t)stream);
+    }
+    if (prev_device != device) cudaSetDevice(prev_device);      // leave the caller's current device as it was
+    if (ce != cudaSuccess) return fail(B2_ERR_CUDA, std::string("b2_attention_decode_static: ") + cudaGetErrorString(ce));
     return B2_OK;
 }

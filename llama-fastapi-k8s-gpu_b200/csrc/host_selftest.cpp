@@ -45,8 +45,11 @@ int b2_host_matvec(int type, const uint8_t* w, int n_rows, int K, const float* x
     memset(abuf, 0, 2 * Kp + 64);
     uint8_t* aa = (uint8_t*)(((uintptr_t)abuf + 15) & ~(uintptr_t)15);
     uint8_t* ab = aa + Kp;
-    float* dx = new float[K / 32 + 4];
-    float* s16 = new float[K / 16 + 4];
+    // packed per-block scales exactly as the mat-vec prologue stores them (quant_blocks.cuh ActView)
+    float* fbuf = new float[K / 16 + K / 16 + 16];
+    float* f = (float*)(((uintptr_t)fbuf + 15) & ~(uintptr_t)15);
+    float* g = f + K / 16;
+    const float fs = act2 ? 1.0f / B2_ACT_RES : 1.0f;
     const int layout = b2::act_layout_of(type);
     for (int b = 0; b < K / 32; b++) {
         int qa[8], qb[8]; float lo, hi;
@@ -56,9 +59,16 @@ int b2_host_matvec(int type, const uint8_t* w, int n_rows, int K, const float* x
             memcpy(aa + sl * B2_SLICE + 16 * pos, qa + 4 * h2, 16);
             memcpy(ab + sl * B2_SLICE + 16 * pos, qb + 4 * h2, 16);
         }
-        dx[b] = amax / 127.0f; s16[2 * b] = lo; s16[2 * b + 1] = hi;
+        if (layout == 0) {
+            f[4 * (b >> 1) + (b & 1)] = amax / 127.0f * fs;
+            f[4 * (b >> 1) + 2 + (b & 1)] = lo + hi;
+        } else {
+            f[b] = amax / 127.0f * fs;
+            g[b2::act_s16p_index(2 * b)] = 32.0f * lo;
+            g[b2::act_s16p_index(2 * b + 1)] = 32.0f * hi;
+        }
     }
-    b2::ActView v; v.a = aa; v.b = ab; v.dx = dx; v.s16 = s16;
+    b2::ActView v; v.a = aa; v.b = ab; v.f = f; v.g = g;
     uintptr_t base = ((uintptr_t)buf + 15) & ~(uintptr_t)15;
     uint8_t* rowp = (uint8_t*)base + misalign;
     int rc = 0;
@@ -73,7 +83,7 @@ int b2_host_matvec(int type, const uint8_t* w, int n_rows, int K, const float* x
             default: rc = -2;
         }
     }
-    delete[] buf; delete[] abuf; delete[] dx; delete[] s16;
+    delete[] buf; delete[] abuf; delete[] fbuf;
     return rc;
 }
 

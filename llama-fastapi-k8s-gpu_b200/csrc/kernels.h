@@ -26,16 +26,20 @@ inline cudaError_t launch_chain(void (*k)(KArgs...), dim3 grid, dim3 block, size
 
 // ---------------------------------------------------------------- mat-vec (matvec.cu)
 enum MvMode { MV_STORE = 0, MV_RESID = 1, MV_QKV = 2, MV_GATEUP = 3 };
-constexpr int MV_MAX_STAGES = 40;
-constexpr int MV_MAX_PROD = 4;               // TMA producer warps per CTA (upper bound)
-constexpr int MV_SHARED_HDR = 4096;          // barriers + reduction scratch at the start of dynamic smem
-constexpr int MV_ROWS = 4;                 // rows per group (one warp, one ring stage)
+#ifndef B2_MV_NCW
+#define B2_MV_NCW 8
+#endif
+constexpr int MV_NCW = B2_MV_NCW;            // warps per CTA
+constexpr int MV_ROWS = 2;                   // rows per row group (one RoPE pair)
+constexpr int MV_MAX_STAGES = 32;            // ring stages (upper bound)
+constexpr int MV_SHARED_HDR = 2048;          // barriers + reduction scratch at the start of dynamic smem
 
 struct MvSeg {
     const uint8_t* w;   // quantised rows, unchanged GGUF bytes
     int type;           // ggml type id
     int n_rows;
     int row_bytes;      // filled by mv_plan
+    int parts, chunk;   // tiles per row pair and K-slices per tile (mv_plan): parts == 1 -> the pair is one bulk copy
     int cta0, ncta;     // CTA range that works on this segment (filled by mv_plan)
     int out_off;        // element offset into y / resid
 };
@@ -59,19 +63,19 @@ struct MvParams {
     const float* rope_freq; // [head_dim / 2]
     int head_dim, n_kv, block_tokens;
     unsigned int* err;      // host-mapped error word (kernel watchdogs)
+    int trigger_late;       // 1: let the next kernel launch only after this one's own dependency wait (its prologue
+                            //    may then read what this kernel's predecessors wrote, e.g. the token position)
     // plan (mv_plan)
     int n_slices;           // K-slices of 2048 elements per row
-    int slot_bytes;         // one row-slice slot in a stage
-    int stage_bytes, n_stages;
-    int n_prod;             // producer warps
-    int skip_compute;       // experiment knob (B2_MV_SKIP_COMPUTE): stream tiles, skip the dot products
-    int whole_rows;         // 1: a ring tile is R full rows (one bulk copy); 0: R row-slices (R copies)
-    int act_layout, act_dual; // activation plane layout (quant_blocks.cuh); both layouts present?
+    int slot_bytes;         // one row's slot in a stage (rows cut into parts)
+    int stage_bytes, n_stages; // ring: tile q of a CTA lives in stage q % n_stages
+    int act_dual;           // gate/up pair of different quant families: activation planes in both layouts
+    int act_plane;          // bytes of one int8 activation plane (K padded to whole slices)
+    int act_off[2];         // byte offset in dynamic shared memory of the activation block of layout 0 / 1
     int ring_off;           // byte offset of the ring in dynamic shared memory (after the activations)
 };
 
 cudaError_t mv_init();   // once per device, outside stream capture
-int mv_ctas_per_sm_default();   // 2 with 8 consumer warps per CTA, 1 with 16 or 20 (env B2_MV_WARPS)
 int mv_plan(MvParams& p, int n_ctas);
 size_t mv_smem_bytes(const MvParams& p);
 cudaError_t mv_launch(const MvParams& p, int n_ctas, cudaStream_t stream, bool act2, bool pdl);
@@ -118,23 +122,6 @@ cudaError_t attn_decode_mma_launch(const AttnParams& p, const SlotDev* tab, cons
 size_t attn_static_scratch_floats();
 cudaError_t attn_static_setup(int device);
 cudaError_t attn_decode_launch_static(AttnParams p, int device, cudaStream_t stream);
-
-// ---------------------------------------------------------------- persistent decode kernel (mega.cu)
-constexpr int MEGA_SMEM_MAX = 227 * 1024;
-struct MegaParams {
-    const MvParams* mv;      // device: 4 phases per layer (qkv, attn_out, gate_up, ffn_down)
-    const AttnParams* at;    // device: one per layer (global-scratch split merge)
-    int n_layer;
-    unsigned int* bar;       // grid-barrier counter (zeroed before every launch)
-    unsigned int* err;
-    int slot_bytes, stage_bytes, n_stages, ring_off, n_prod;   // one ring geometry for all phases
-    int attn_items;          // n_kv * n_splits CTAs take part in the attention phase
-    unsigned long long* ts;  // optional: CTA 0 records %globaltimer at every phase boundary (5 per layer + 1)
-};
-cudaError_t mega_init();
-int mega_plan(MegaParams& mp, const MvParams* host_mv, int n_phase, int head_dim, int n_kv, int n_splits, int n_sms);
-size_t mega_smem_bytes(const MegaParams& mp);
-cudaError_t mega_launch(const MegaParams& mp, int n_ctas, cudaStream_t stream, bool act2);
 
 // ---------------------------------------------------------------- tensor-core GEMM (gemm.cu)
 struct GemmSeg {

@@ -4,6 +4,7 @@
 #include "kernels.h"
 #include "ptx.cuh"
 #include "quant_blocks.cuh"
+#include <mutex>
 
 namespace b2 {
 
@@ -11,10 +12,13 @@ thread_local bool g_chain_pdl = false;
 
 unsigned int* kernel_error_word() {
     static unsigned int* w = nullptr;
-    if (!w) {
-        if (cudaHostAlloc(&w, 8 * sizeof(unsigned int), cudaHostAllocMapped | cudaHostAllocPortable) != cudaSuccess) return nullptr;
-        for (int i = 0; i < 8; i++) w[i] = 0;
-    }
+    static std::once_flag once;               // first use may come from any host thread
+    std::call_once(once, []() {
+        unsigned int* p = nullptr;
+        if (cudaHostAlloc(&p, 8 * sizeof(unsigned int), cudaHostAllocMapped | cudaHostAllocPortable) != cudaSuccess) return;
+        for (int i = 0; i < 8; i++) p[i] = 0;
+        w = p;
+    });
     return w;
 }
 

@@ -52,6 +52,7 @@ B2_HD int block_bytes(int t) {
 // ---------------------------------------------------------------- primitives
 #if defined(__CUDA_ARCH__) && !defined(B2_HOST_EMU)
 B2_D float h2f(uint32_t h) { return __half2float(__ushort_as_half((unsigned short)h)); }
+B2_D float u2f(uint32_t u) { return __uint_as_float(u); }
 B2_D int dp4a(int a, int b, int c) { return __dp4a(a, b, c); }
 B2_D int dp4a_us(uint32_t a, int b, int c) {
     int d;
@@ -78,6 +79,7 @@ inline float h2f(uint32_t h) {
     else o = (s << 31) | ((e + 112) << 23) | (m << 13);
     float f; memcpy(&f, &o, 4); return f;
 }
+inline float u2f(uint32_t u) { float f; memcpy(&f, &u, 4); return f; }
 inline int dp4a(int a, int b, int c) {
     for (int i = 0; i < 4; i++) c += (int)(int8_t)(a >> (8 * i)) * (int)(int8_t)(b >> (8 * i));
     return c;
@@ -173,9 +175,15 @@ B2_D float dequant_elem(int type, const uint8_t* blk, int e) {
 struct ActView {
     const uint8_t* a;            // [K] int8
     const uint8_t* b;            // [K] int8
-    const float* dx;             // [K/32]
-    const float* s16;            // [K/16]
+    // per-block scales, packed so a lane fetches what it needs with one or two 16-byte loads:
+    //   layout 0: f[4c .. 4c+3] = {dx'(2c), dx'(2c+1), sum32(2c), sum32(2c+1)} for the 64-element chunk c
+    //   layout 1: f[blk] = dx'(blk);  g[act_s16p_index(u)] = 32 * sum16(u)
+    // dx' = dx (one plane) or dx / 252 (two planes: the scale of the folded integer 252 a + b)
+    const float* f;
+    const float* g;
 };
+// index of 16-element unit u in the layout-1 sum array: lane (j, hf, qt) reads its four kq values as one float4
+B2_HD int act_s16p_index(int u) { return (u & ~15) + 8 * ((u >> 3) & 1) + 4 * (u & 1) + ((u >> 1) & 3); }
 // What one lane keeps in registers for one K-slice: 64 activations (16+16 words) and their scales.
 // Q4_0/Q8_0/Q4_K/Q5_K: the contiguous chunk [64*lane, 64*lane+64): f[0..1] = dx of its two
 // 32-blocks, f[2..3] = float sums of the two 32-blocks.
@@ -253,19 +261,15 @@ B2_D void load_act(LaneAct& r, const ActView& v, int e0 /* first element of the 
         }
     }
     if (T == T_Q6_K) {
-        int eb = e0 + 256 * (lane >> 2) + 128 * ((lane >> 1) & 1) + 16 * (lane & 1);
-#pragma unroll
-        for (int kq = 0; kq < 4; kq++) {
-            int e = eb + 32 * kq;
-            r.f[kq] = v.dx[e >> 5] * (ACT2 ? 1.0f / B2_ACT_RES : 1.0f);     // scale of the folded integer T
-            r.f[4 + kq] = 32.0f * v.s16[e >> 4];
-        }
+        const int b0 = (e0 >> 5) + 8 * (lane >> 2) + 4 * ((lane >> 1) & 1);      // first of the lane's four 32-blocks
+        const int u0 = (e0 >> 4) + 16 * (lane >> 2) + 8 * ((lane >> 1) & 1) + 4 * (lane & 1);
+        U4 d4 = ld128(reinterpret_cast<const uint8_t*>(v.f + b0));
+        U4 s4 = ld128(reinterpret_cast<const uint8_t*>(v.g + u0));
+        r.f[0] = u2f(d4.x); r.f[1] = u2f(d4.y); r.f[2] = u2f(d4.z); r.f[3] = u2f(d4.w);
+        r.f[4] = u2f(s4.x); r.f[5] = u2f(s4.y); r.f[6] = u2f(s4.z); r.f[7] = u2f(s4.w);
     } else {
-        int e = e0 + 64 * lane;
-        r.f[0] = v.dx[e >> 5] * (ACT2 ? 1.0f / B2_ACT_RES : 1.0f);           // scale of the folded integer T
-        r.f[1] = v.dx[(e >> 5) + 1] * (ACT2 ? 1.0f / B2_ACT_RES : 1.0f);
-        r.f[2] = v.s16[e >> 4] + v.s16[(e >> 4) + 1];
-        r.f[3] = v.s16[(e >> 4) + 2] + v.s16[(e >> 4) + 3];
+        U4 f4 = ld128(reinterpret_cast<const uint8_t*>(v.f + 4 * ((e0 >> 6) + lane)));
+        r.f[0] = u2f(f4.x); r.f[1] = u2f(f4.y); r.f[2] = u2f(f4.z); r.f[3] = u2f(f4.w);
     }
 }
 

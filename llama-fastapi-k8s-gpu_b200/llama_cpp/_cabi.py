@@ -13,7 +13,7 @@ from ctypes import POINTER, c_char_p, c_double, c_float, c_int, c_int32, c_int64
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libb200gguf.so")
 
-B2_FLAG_NO_GRAPH, B2_FLAG_NO_PDL, B2_FLAG_ACT8, B2_FLAG_NO_MEGA = 1, 2, 4, 8
+B2_FLAG_NO_GRAPH, B2_FLAG_NO_PDL, B2_FLAG_ACT8 = 1, 2, 4
 
 
 class B2Config(ctypes.Structure):
@@ -54,6 +54,7 @@ SIGNATURES = {
     "b2_kernel_launch_count": (c_int, [c_void_p, POINTER(c_int64)]),
     "b2_engine_mode": (c_int, [c_void_p, POINTER(c_int), POINTER(c_int), POINTER(c_int), POINTER(c_int), POINTER(c_int)]),
     "b2_profile_decode_step": (c_int, [c_void_p, c_int, POINTER(c_float), POINTER(c_int32), POINTER(c_int64)]),
+    "b2_bench_matvec": (c_int, [c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, POINTER(c_float)]),
     "b2_op_dequantize": (c_int, [c_int, c_int, c_void_p, c_int64, c_void_p]),
     "b2_op_matvec": (c_int, [c_int, c_int, c_void_p, c_int, c_int, c_void_p, c_void_p, c_float, c_void_p, c_void_p, c_int, c_int]),
     "b2_op_gate_up": (c_int, [c_int, c_int, c_void_p, c_int, c_void_p, c_int, c_int, c_void_p, c_void_p, c_float, c_void_p, c_int]),

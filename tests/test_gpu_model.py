@@ -168,28 +168,6 @@ def test_engine_rejects_bad_input(native_lib, tmp_models):
     eng.close()
 
 
-def test_persistent_layer_kernel_matches_per_kernel_path(native_lib, tmp_models, monkeypatch):
-    """B2_MEGA=1: all layers of a token in one persistent kernel (grid barriers between phases).
-    Same arithmetic as the per-kernel path except the attention split count, so tokens must agree and
-    logits must be within the logit tolerance of each other."""
-    path = _model(tmp_models, "tiny128", "Q4_0", 2)
-    outs = []
-    for mega in (False, True):
-        if mega:
-            monkeypatch.setenv("B2_MEGA", "1")
-        else:
-            monkeypatch.delenv("B2_MEGA", raising=False)
-        eng = _engine(path)
-        eng.ensure_pages(0, 64)
-        eng.seq_begin(0, 0, [], _greedy())
-        eng.prefill(0, TOKENS[:10])
-        toks = [eng.sample(0)] + [eng.decode([0])[0] for _ in range(12)]
-        outs.append((toks, eng.logits(0).copy()))
-        eng.close()
-    assert outs[0][0] == outs[1][0]
-    assert np.abs(outs[0][1] - outs[1][1]).max() < LOGIT_TOL
-
-
 @pytest.mark.parametrize("arch,ftype,seed", MODELS)
 def test_tensor_core_prefill_matches_oracle(native_lib, tmp_models, arch, ftype, seed):
     """Prompt chunks of >= 8 tokens go through the tcgen05 GEMM path (f16 activations, f32 accumulate): logits
