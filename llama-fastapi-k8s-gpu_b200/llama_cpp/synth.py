@@ -45,6 +45,11 @@ ARCHS: Dict[str, Arch] = {
     # tiny test architectures (CPU oracle finishes in well under a second)
     "tiny": Arch("tiny", 2, 512, 8, 2, 1536, 1024, 10000.0, 1e-5, 2048, "bpe"),
     "tiny128": Arch("tiny128", 2, 512, 4, 2, 1024, 768, 500000.0, 1e-5, 2048, "bpe"),
+    # one layer of the benchmark geometries: the launch shapes the 8B / 70B runs use (row counts per CTA, K slices,
+    # the Q6_K attn_v / ffn_down / output of the Q4_K_M mix, a 128256-row output head) at a size the float32
+    # oracle still handles (tests/test_gpu_wide.py)
+    "wide-1l": Arch("wide-1l", 1, 4096, 32, 8, 14336, 128256, 500000.0, 1e-5, 8192, "bpe"),
+    "wide70-1l": Arch("wide70-1l", 1, 8192, 64, 8, 28672, 16384, 500000.0, 1e-5, 8192, "bpe"),
     "tinyllama-1.1b": Arch("tinyllama-1.1b", 22, 2048, 32, 4, 5632, 32000, 10000.0, 1e-5, 2048, "spm"),
     "llama-3-8b": Arch("llama-3-8b", 32, 4096, 32, 8, 14336, 128256, 500000.0, 1e-5, 8192, "bpe"),
     "mistral-7b": Arch("mistral-7b", 32, 4096, 32, 8, 14336, 32000, 10000.0, 1e-5, 32768, "spm"),

@@ -40,10 +40,7 @@ def build(force: bool = False) -> str:
 
 class CpuRef:
     def __init__(self, gguf_path: str, n_ctx: int):
-        pkg = os.path.join(os.path.dirname(HERE), "llama-fastapi-k8s-gpu_b200")
-        if pkg not in sys.path:
-            sys.path.insert(0, pkg)
-        from llama_cpp.gguf_file import GGUFFile   # container format only
+        from .gguf_load import OracleGGUF          # gguf-py reader, independent of the product's
         try:
             self.lib = ctypes.CDLL(build())
         except OSError:
@@ -55,7 +52,7 @@ class CpuRef:
         self.lib.cr_reset.argtypes = [c_void_p]
         self.lib.cr_destroy.argtypes = [c_void_p]
         self.lib.cr_threads.restype = c_int
-        self.g = GGUFFile(gguf_path)
+        self.g = OracleGGUF(gguf_path)
         md = self.g.metadata
 
         def T(name):

@@ -85,14 +85,10 @@ class RefModel:
     """Float32 weights dequantised with the block oracle + a growing KV cache."""
 
     def __init__(self, gguf_path: str):
-        # the oracle parses the file with the product's reader only for the container
-        # format (header walk); every number comes from oracle/ggml_blocks.py
-        here = os.path.dirname(os.path.abspath(__file__))
-        pkg = os.path.join(os.path.dirname(here), "llama-fastapi-k8s-gpu_b200")
-        if pkg not in sys.path:
-            sys.path.insert(0, pkg)
-        from llama_cpp.gguf_file import GGUFFile
-        g = GGUFFile(gguf_path)
+        # container format: ggml's own gguf-py reader (oracle/gguf_load.py), not the product's;
+        # every number comes from oracle/ggml_blocks.py
+        from .gguf_load import OracleGGUF
+        g = OracleGGUF(gguf_path)
         md = g.metadata
         self.cfg = RefConfig(
             n_layer=int(md["llama.block_count"]), n_embd=int(md["llama.embedding_length"]),

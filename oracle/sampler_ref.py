@@ -9,6 +9,14 @@ presence_penalty=0.8)` (/root/reference/api.py:55-63): `Llama.sample` ->
 REFERENCE: no llama_cpp here and no golden vectors in the reference repo; this restates the
 published algorithm (tfs_z = typical_p = 1.0 are no-ops and are not modelled).
 
+Independent artefacts that pin this module (tests/test_oracle_sampler.py):
+  * `draw` + `MT19937Uniforms`: libstdc++'s own std::mt19937 + std::discrete_distribution<>, the two objects
+    llama_sample_token uses, run by oracle/draw_ref.cpp -> tests/golden/sampler_draws.json (bit-exact indices).
+    One difference is deliberate and documented: with a single candidate libstdc++ returns 0 WITHOUT drawing from
+    the generator, while this restatement (and the device sampler) always spends one uniform per token.
+  * penalties / top-k / top-p / min-p / temperature: hand-worked known-answer vectors, including the fixed
+    settings of api.py:59-62.
+
 Order: penalties over the last `penalty_last_n` tokens -> (temperature <= 0: arg-max, first
 maximum) | top-k -> softmax -> top-p (smallest prefix with cumulative p >= top_p) -> min-p
 (keep logit >= max_logit + log(min_p)) -> logits / temperature -> softmax ->

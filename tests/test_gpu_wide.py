@@ -1,0 +1,109 @@
+"""Parity at the launch geometry the benchmark runs (GPU only).
+
+The toy models of test_gpu_model.py never give a mat-vec CTA more than a handful of rows. These one-layer models have
+the real Llama-3-8B / 70B matrix shapes -- d = 4096 (8192), n_ff = 14336 (28672), a 128256-row output head, the Q6_K
+attn_v / ffn_down / output of the Q4_K_M mix -- so every kernel runs with the row counts per CTA, K-slice counts, ring
+wrap-arounds and tile splits of the timed configuration, and is compared with the float32 oracle (logits max-abs
+<= 1e-2, BASELINE.json north_star). The oracle dequantises ~1 G weights: tens of seconds per model.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from util import TYPE_IDS, lib_check, ptr
+
+pytestmark = pytest.mark.gpu
+LOGIT_TOL = 1e-2
+
+
+def _model(tmp_models, arch, ftype, seed):
+    from llama_cpp import synth
+    path = os.path.join(tmp_models, f"{arch}_{ftype}_{seed}.gguf")
+    if not os.path.exists(path):
+        synth.write_synthetic_model(path, arch, ftype, seed=seed, output_std=0.1, with_vocab=False)
+    return path
+
+
+def _engine(path, max_seqs=1, n_ctx=128, flags=0):
+    from llama_cpp.engine import Engine
+    from llama_cpp.gguf_file import GGUFFile
+    return Engine(GGUFFile(path), n_ctx=n_ctx, max_seqs=max_seqs, kv_block_tokens=16, flags=flags)
+
+
+def _greedy():
+    from llama_cpp.engine import SamplingSettings
+    return SamplingSettings(temperature=0.0, repeat_penalty=1.0)
+
+
+@pytest.mark.parametrize("arch,ftype,seed", [("wide-1l", "Q4_K_M", 11), ("wide-1l", "Q8_0", 12), ("wide-1l", "Q4_0", 13),
+                                             ("wide70-1l", "Q4_K_M", 14)])
+def test_wide_model_logits_on_every_path(native_lib, tmp_models, arch, ftype, seed):
+    """mat-vec decode (CUDA-graph replay and plain launches), tensor-core prompt pass, batched step at 32 slots."""
+    from llama_cpp import _cabi
+    from oracle.llama_ref import RefModel
+    path = _model(tmp_models, arch, ftype, seed)
+    ref = RefModel(path)
+    V = ref.cfg.n_vocab
+    rng = np.random.default_rng(seed)
+    tokens = [int(t) for t in rng.integers(0, V, 28)]
+    want = ref.forward(tokens)                                   # [T, V]
+    worst = {}
+    for name, flags in (("graph", 0), ("plain", _cabi.B2_FLAG_NO_GRAPH | _cabi.B2_FLAG_NO_PDL)):
+        eng = _engine(path, flags=flags)
+        eng.ensure_pages(0, len(tokens) + 1)
+        eng.seq_begin(0, 0, [], _greedy())
+        eng.prefill(0, tokens[:4])                               # < 8 tokens: token by token through the mat-vec kernels
+        w = np.abs(eng.logits(0) - want[3]).max()
+        for i in range(4, 12):
+            eng.set_token(0, tokens[i])
+            eng.forward_pending(0)
+            w = max(w, np.abs(eng.logits(0) - want[i]).max())
+        worst[name] = w
+        if name == "graph":
+            eng.prefill(0, tokens[12:28])                        # 16 tokens: tcgen05 GEMM path, attends to the 12 before
+            worst["prompt"] = np.abs(eng.logits(0) - want[27]).max()
+        eng.close()
+    # batched step: 32 sequences of different lengths share one weight pass
+    n_seq = 32
+    eng = _engine(path, max_seqs=n_seq)
+    seqs = [[int(t) for t in rng.integers(0, V, 3 + (s % 7))] for s in range(n_seq)]
+    for s, sq in enumerate(seqs):
+        eng.ensure_pages(s, len(sq) + 2)
+        eng.seq_begin(s, 0, [], _greedy())
+        eng.prefill(s, sq[:-1])
+        eng.set_token(s, sq[-1])
+    eng.decode(list(range(n_seq)))
+    wb = 0.0
+    for s, sq in enumerate(seqs):
+        ref.reset()
+        wb = max(wb, np.abs(eng.logits(s) - ref.forward(sq, last_only=True)[0]).max())
+    worst["batched32"] = wb
+    eng.close()
+    assert all(v <= LOGIT_TOL for v in worst.values()), (arch, ftype, worst)
+
+
+@pytest.mark.parametrize("tname,N,K", [("Q6_K", 128256, 4096), ("Q4_K", 28672, 8192), ("Q6_K", 8192, 28672)])
+def test_matvec_many_row_groups_per_cta(native_lib, tname, N, K):
+    """The 8B output head gives every CTA ~433 row pairs (the ring wraps dozens of times); the 70B shapes are the ones
+    whose rows are cut into parts / that take the SM alone. Same bar as the small op tests: 1e-3 of the output rms."""
+    from llama_cpp.synth import random_blocks
+    from oracle import ggml_blocks as gb
+    t = TYPE_IDS[tname]
+    rng = np.random.default_rng(N + K)
+    w = random_blocks(tname, N * K // 256, 0.02, seed=N + 7 * K).reshape(-1)
+    x = (rng.standard_normal(K) * rng.uniform(0.2, 2.0, size=K)).astype(np.float32)
+    nw = rng.uniform(0.5, 1.5, size=K).astype(np.float32)
+    y = np.zeros(N, np.float32)
+    lib_check(native_lib, native_lib.b2_op_matvec(0, t, ptr(w), N, K, ptr(x), ptr(nw), 1e-5, None, ptr(y), 2, 0))
+    xx = x.astype(np.float64)
+    xx = xx / np.sqrt((xx ** 2).mean() + 1e-5) * nw.astype(np.float64)
+    ref = np.empty(N, np.float64)
+    rows = 8192
+    blk_bytes = gb.BLOCK[t][1]
+    wb = w.reshape(N, K // 256 * blk_bytes)
+    for r0 in range(0, N, rows):
+        W = gb.dequantize(wb[r0:r0 + rows].reshape(-1), t).reshape(-1, K)
+        ref[r0:r0 + rows] = W.astype(np.float64) @ xx
+    err = np.abs(y - ref).max() / np.sqrt((ref ** 2).mean())
+    assert err < 1e-3, (tname, N, K, err)
