@@ -53,10 +53,12 @@ struct DevTensor {
 struct Layer {
     DevTensor attn_norm, wq, wk, wv, wo, ffn_norm, wgate, wup, wdown;
     MvParams p_qkv, p_o, p_gu, p_down;
+    MvParams p_gate, p_up;         // un-fused pair when ffn_gate and ffn_up have different quant types
+    bool gu_fused = true;
 };
 
 struct Slot {
-    float *x = nullptr, *q = nullptr, *att = nullptr, *h = nullptr, *logits = nullptr;
+    float *x = nullptr, *q = nullptr, *att = nullptr, *h = nullptr, *hg = nullptr, *logits = nullptr;
     int* ints = nullptr;           // [0]=token [1]=pos [2]=out_token [3]=step [4]=cursor [5]=pos_base
     int* block_table = nullptr;
     int* prompt = nullptr;         // [n_ctx]
@@ -215,6 +217,7 @@ static int engine_create_impl(b2_engine* e, const b2_config* c) {
         CK(cudaMalloc(&s.q, sizeof(float) * c->n_head * c->head_dim));
         CK(cudaMalloc(&s.att, sizeof(float) * c->n_head * c->head_dim));
         CK(cudaMalloc(&s.h, sizeof(float) * c->n_ff));
+        CK(cudaMalloc(&s.hg, sizeof(float) * c->n_ff));
         CK(cudaMalloc(&s.logits, sizeof(float) * c->n_vocab));
         CK(cudaMalloc(&s.ints, sizeof(int) * 8));
         CK(cudaMemset(s.ints, 0, sizeof(int) * 8));
@@ -259,7 +262,7 @@ extern "C" int b2_engine_destroy(b2_engine* e) {
     for (auto& kv : e->tensors) cudaFree(kv.second.ptr);
     for (auto& s : e->slots) {
         free_slot_graphs(s);
-        cudaFree(s.x); cudaFree(s.q); cudaFree(s.att); cudaFree(s.h); cudaFree(s.logits);
+        cudaFree(s.x); cudaFree(s.q); cudaFree(s.att); cudaFree(s.h); cudaFree(s.hg); cudaFree(s.logits);
         cudaFree(s.ints); cudaFree(s.block_table); cudaFree(s.prompt); cudaFree(s.ring); cudaFree(s.sst); cudaFree(s.sp);
         cudaFree(s.uniforms);
     }
@@ -320,7 +323,7 @@ static MvSeg make_seg(const DevTensor& t, int out_off = 0) {
 static int plan_or_fail(MvParams& p, int n_ctas, const char* what) {
     int rc = mv_plan(p, n_ctas);
     if (rc) return fail(B2_ERR_UNSUPPORTED, std::string("cannot plan mat-vec for ") + what + " (code " + std::to_string(rc) +
-                                               (rc == -2 ? ": K > 65536 not supported)" : ")"));
+                                               (rc == -2 ? ": K > 32768 not supported)" : ")"));
     return B2_OK;
 }
 
@@ -370,8 +373,19 @@ extern "C" int b2_engine_finalize(b2_engine* e) {
         MvParams g = {};
         g.nseg = 2; g.seg[0] = make_seg(L.wgate); g.seg[1] = make_seg(L.wup); g.K = c.n_embd; g.mode = MV_GATEUP;
         g.norm_w = (const float*)L.ffn_norm.ptr; g.eps = c.rms_eps; g.err = kernel_error_word();
-        if ((rc = plan_or_fail(g, e->n_ctas, "ffn_gate/up"))) return rc;
-        L.p_gu = g;
+        if (L.wgate.type == L.wup.type) {
+            if ((rc = plan_or_fail(g, e->n_ctas, "ffn_gate/up"))) return rc;
+            L.p_gu = g;
+        } else {          // mixed pair: two plain mat-vecs (each with the fused norm) and a SiLU-multiply
+            L.gu_fused = false;
+            MvParams a = {}, b = {};
+            a.nseg = 1; a.seg[0] = make_seg(L.wgate); a.K = c.n_embd; a.mode = MV_STORE;
+            a.norm_w = (const float*)L.ffn_norm.ptr; a.eps = c.rms_eps; a.err = kernel_error_word();
+            b = a; b.seg[0] = make_seg(L.wup);
+            if ((rc = plan_or_fail(a, e->n_ctas, "ffn_gate"))) return rc;
+            if ((rc = plan_or_fail(b, e->n_ctas, "ffn_up"))) return rc;
+            L.p_gate = a; L.p_up = b;
+        }
         MvParams d = {};
         d.nseg = 1; d.seg[0] = make_seg(L.wdown); d.K = c.n_ff; d.mode = MV_RESID; d.err = kernel_error_word();
         if ((rc = plan_or_fail(d, e->n_ctas, "ffn_down"))) return rc;
@@ -447,10 +461,19 @@ static int forward_launches(b2_engine* e, Slot& s, bool with_head, bool with_sam
         tick(3, &ye);
         CK(mv_launch(o, e->n_ctas, st, e->act2, pdl));
         tock(ye);
-        MvParams g = L.p_gu;
-        g.x = s.x; g.y = s.h;
         tick(4, &ye);
-        CK(mv_launch(g, e->n_ctas, st, e->act2, pdl));
+        if (L.gu_fused) {
+            MvParams g = L.p_gu;
+            g.x = s.x; g.y = s.h;
+            CK(mv_launch(g, e->n_ctas, st, e->act2, pdl));
+        } else {
+            MvParams a = L.p_gate, b = L.p_up;
+            a.x = s.x; a.y = s.hg; b.x = s.x; b.y = s.h;
+            CK(mv_launch(a, e->n_ctas, st, e->act2, pdl));
+            CK(mv_launch(b, e->n_ctas, st, e->act2, pdl));
+            CK(silu_mul_launch(s.hg, s.h, c.n_ff, st, pdl));
+            e->launches += 2;
+        }
         tock(ye);
         MvParams d = L.p_down;
         d.x = s.h; d.y = s.x; d.resid = s.x;
@@ -973,7 +996,7 @@ extern "C" int b2_profile_decode_step(b2_engine* e, int slot, float* ms, int32_t
     bytes[0] = (int64_t)c.n_embd / be * bb;
     for (auto& L : e->layers) {
         bytes[1] += seg_bytes(L.p_qkv); bytes[3] += seg_bytes(L.p_o);
-        bytes[4] += seg_bytes(L.p_gu); bytes[5] += seg_bytes(L.p_down);
+        bytes[4] += L.gu_fused ? seg_bytes(L.p_gu) : seg_bytes(L.p_gate) + seg_bytes(L.p_up); bytes[5] += seg_bytes(L.p_down);
     }
     bytes[2] = (int64_t)c.n_layer * 2 * c.n_head_kv * c.head_dim * 2 * (s.n_past + 1);
     bytes[6] = seg_bytes(e->p_head);
@@ -1052,6 +1075,19 @@ extern "C" int b2_op_gate_up(int device, int tg, const void* wg, int tu, const v
     if (!wg || !wu || !x || !y || n_rows <= 0 || K <= 0) return fail(B2_ERR_ARG, "bad arguments");
     if (n_rows % 2) return fail(B2_ERR_ARG, "n_rows must be even");
     CK(cudaSetDevice(device));
+    if (tg != tu) {     // what the engine does for a mixed pair: two plain mat-vecs with the fused norm, then SiLU-multiply
+        std::vector<float> g(n_rows);
+        int rc = b2_op_matvec(device, tg, wg, n_rows, K, x, nw, eps, nullptr, g.data(), 2, n_ctas);
+        if (rc) return rc;
+        if ((rc = b2_op_matvec(device, tu, wu, n_rows, K, x, nw, eps, nullptr, y, 2, n_ctas))) return rc;
+        DevBuf dg, dh;
+        CK(dg.alloc((size_t)n_rows * 4)); CK(dh.alloc((size_t)n_rows * 4));
+        CK(cudaMemcpy(dg.p, g.data(), (size_t)n_rows * 4, cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(dh.p, y, (size_t)n_rows * 4, cudaMemcpyHostToDevice));
+        CK(silu_mul_launch(dg.as<float>(), dh.as<float>(), n_rows, 0, false));
+        CK(cudaMemcpy(y, dh.p, (size_t)n_rows * 4, cudaMemcpyDeviceToHost));
+        return B2_OK;
+    }
     MvParams p = {};
     p.nseg = 2; p.seg[0].type = tg; p.seg[0].n_rows = n_rows; p.seg[1].type = tu; p.seg[1].n_rows = n_rows;
     p.K = K; p.mode = MV_GATEUP; p.eps = eps;

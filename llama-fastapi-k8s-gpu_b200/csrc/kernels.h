@@ -27,19 +27,18 @@ inline cudaError_t launch_chain(void (*k)(KArgs...), dim3 grid, dim3 block, size
 // ---------------------------------------------------------------- mat-vec (matvec.cu)
 enum MvMode { MV_STORE = 0, MV_RESID = 1, MV_QKV = 2, MV_GATEUP = 3 };
 #ifndef B2_MV_NCW
-#define B2_MV_NCW 8
+#define B2_MV_NCW 16
 #endif
 constexpr int MV_NCW = B2_MV_NCW;            // warps per CTA
 constexpr int MV_ROWS = 2;                   // rows per row group (one RoPE pair)
-constexpr int MV_MAX_STAGES = 32;            // ring stages (upper bound)
-constexpr int MV_SHARED_HDR = 2048;          // barriers + reduction scratch at the start of dynamic smem
+constexpr int MV_MAX_STAGES = 48;            // ring stages (upper bound)
+constexpr int MV_SHARED_HDR = 6144;          // barriers + reduction scratch at the start of dynamic smem
 
 struct MvSeg {
     const uint8_t* w;   // quantised rows, unchanged GGUF bytes
     int type;           // ggml type id
     int n_rows;
     int row_bytes;      // filled by mv_plan
-    int parts, chunk;   // tiles per row pair and K-slices per tile (mv_plan): parts == 1 -> the pair is one bulk copy
     int cta0, ncta;     // CTA range that works on this segment (filled by mv_plan)
     int out_off;        // element offset into y / resid
 };
@@ -66,12 +65,12 @@ struct MvParams {
     int trigger_late;       // 1: let the next kernel launch only after this one's own dependency wait (its prologue
                             //    may then read what this kernel's predecessors wrote, e.g. the token position)
     // plan (mv_plan)
-    int n_slices;           // K-slices of 2048 elements per row
-    int slot_bytes;         // one row's slot in a stage (rows cut into parts)
+    int n_slices;           // K-slices of 2048 elements per row = warp teams
+    int nrows;              // rows per tile: 2 (a pair), or 1 for very long rows
     int stage_bytes, n_stages; // ring: tile q of a CTA lives in stage q % n_stages
-    int act_dual;           // gate/up pair of different quant families: activation planes in both layouts
+    unsigned int inv_stages;   // 2^32 / n_stages rounded up: q / n_stages == umulhi(q, inv_stages)
     int act_plane;          // bytes of one int8 activation plane (K padded to whole slices)
-    int act_off[2];         // byte offset in dynamic shared memory of the activation block of layout 0 / 1
+    int act_off;            // byte offset of the activation block in dynamic shared memory
     int ring_off;           // byte offset of the ring in dynamic shared memory (after the activations)
 };
 
@@ -183,6 +182,7 @@ cudaError_t dequantize_launch(int type, const uint8_t* raw, long n_elems, float*
 // x[0..K) = dequantised row `*token_ptr` of the embedding table
 cudaError_t embed_row_launch(int type, const uint8_t* table, int K, const int* token_ptr, float* x,
                              cudaStream_t s, bool pdl);
+cudaError_t silu_mul_launch(const float* g, float* h, int n, cudaStream_t s, bool pdl);   // h = silu(g) * h
 cudaError_t rmsnorm_launch(const float* x, const float* w, float eps, int K, int rows, float* y, cudaStream_t s);
 
 // ---------------------------------------------------------------- sampler (sampler.cu)

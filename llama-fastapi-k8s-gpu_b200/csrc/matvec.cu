@@ -3,34 +3,33 @@
 // mul_mat_vec_q + the separate rms_norm / rope / cpy / silu / add launches that the reference
 // runs under llm.create_chat_completion (/root/reference/api.py:55-63; SURVEY.md 2.3 K2-K7,K11).
 //
-// Structure: 148 CTAs of 8 warps and at most 112 KB of shared memory, so that TWO CTAs fit an SM:
-// with programmatic dependent launch the CTAs of the next kernel in the stream become resident
-// beside the running ones and fill their rings with weights while this kernel still computes --
-// HBM keeps streaming across the kernel boundary.
-//   * Tiles. A CTA's rows are cut into groups of R=2 consecutive rows (one RoPE pair); a group is
-//     one tile when the two rows fit a ring stage (they are contiguous in memory: ONE bulk copy of
-//     4-13 KB), else `parts` tiles of a few K-slices each (one copy per row). Measured on B200: a
-//     warp issues a cp.async.bulk every ~110 cycles, so copies of 1-2 KB cap a CTA at ~3 TB/s chip
-//     rate no matter how deep the ring is; copies of >= 4 KB do not.
-//   * Ring. Tile q of the CTA lives in stage q % S. There is no producer warp and there are no
-//     "empty" barriers: the warp that has just read stage s refills it itself with tile q + S
-//     (self-refill; eight issuers in parallel). An mbarrier only exposes the parity of its phase and
-//     consecutive uses of a stage belong to different warps, so a warp that looked at a stage before
-//     the previous use had even landed would read "complete" for the wrong phase: the refilling warp
-//     therefore publishes `issued[s] = use + 1` (release) after arming the barrier, and a reader
-//     waits for that value (acquire; by then the previous use has been consumed, hence landed)
-//     before it waits on the parity.
-//   * Warps. Warp w owns the row groups g = w, w+8, ... for ALL of K: sums stay in registers over
-//     the whole row, one lane reduction (5 shuffles per row pair) per group, no shared-memory
-//     atomics. Per slice a lane loads its 64 quantised activations (two int8 planes) once and
-//     reuses them for both rows; weights stay packed and go through dp4a.
-//   * The first S tiles are requested BEFORE griddepcontrol.wait (weights do not depend on the
-//     previous kernel).
-//   * prologue (after the wait): x -> optional fused RMSNorm weight -> two int8 planes + packed
-//     per-block scales in shared memory; the loads of x are issued in one batch (one L2 round
-//     trip), the norm weights were prefetched to L1 before the wait.
-//   * epilogue (lane 0 of the owning warp, a row pair): plain store, residual add, RoPE +
-//     paged-KV store for the fused QKV projection, or SiLU(gate) * up for the fused FFN projection.
+// Structure: one CTA of 16 warps per SM, all of the SM's shared memory as a ring of weight tiles.
+//   * Tiles. A tile is a row pair (one RoPE pair; a single row when two very long rows would not leave four
+//     ring stages). Rows are contiguous in memory, so a tile is ONE bulk copy of 4-30 KB (cp.async.bulk +
+//     mbarrier complete_tx). Measured on B200: a warp issues a cp.async.bulk only every ~110 cycles, so
+//     copies of 1-2 KB cap a CTA at ~3 TB/s chip rate however deep the ring is; copies of >= 4 KB do not.
+//   * Teams. K is cut into slices of 2048 elements; team t = the warps with warp % n_slices == t owns slice t
+//     for the whole kernel and keeps that slice's 64 quantised activations per lane (two int8 planes +
+//     scales, 40 registers) in REGISTERS: activations are read from shared memory once per kernel, not once
+//     per tile (re-reading them per row pair took most of the shared-memory bandwidth and of the issue slots).
+//     The row pairs of the CTA are dealt round-robin to the members of each team, so every tile is read by
+//     exactly one warp of every team.
+//   * Ring. Tile q of the CTA lives in stage q % S. There is no producer warp: the LAST of a tile's readers
+//     (mbarrier `empty[s]` with one arrival per team; the arrival that finds one pending is the last) refills
+//     the stage with tile q + S -- sixteen potential issuers. An mbarrier only exposes the parity of its
+//     phase and consecutive uses of a stage belong to different warps, so a warp that looked at a stage
+//     before the previous use had even landed would read "complete" for the wrong phase: the refilling warp
+//     publishes `issued[s] = use + 1` after arming the barrier, and a reader waits for that value (by then
+//     the previous use has been consumed, hence landed) before it waits on the parity.
+//   * Row sums. Each warp reduces its slice of the row pair over its lanes (5 shuffles) and drops the partial
+//     sums in a shared-memory slot; the warp that brings the last partial (mbarrier again) adds them in team
+//     order -- the result does not depend on timing -- and runs the epilogue.
+//   * The first S tiles are requested BEFORE griddepcontrol.wait (weights do not depend on the previous kernel).
+//   * prologue (after the wait): x -> optional fused RMSNorm weight -> two int8 planes + packed per-block
+//     scales in shared memory (loads of x in one batch: one L2 round trip; norm weights prefetched to L1
+//     before the wait), then every warp loads its slice into registers.
+//   * epilogue (lane 0 of the finishing warp): plain store, residual add, RoPE + paged-KV store for the fused
+//     QKV projection, or SiLU(gate) * up for the fused FFN projection.
 //
 // Roofline: HBM. Algorithmic bytes per launch = sum of the weight bytes of its segments.
 #include "kernels.h"
@@ -49,23 +48,27 @@ constexpr int NCW = MV_NCW;
 constexpr int R = MV_ROWS;
 static_assert(R == 2, "a row group is one RoPE pair");
 constexpr int MV_THREADS = NCW * 32;
-constexpr int MV_SMEM_CO = 112 * 1024;      // two CTAs per SM
-constexpr int MV_SMEM_SOLO = 224 * 1024;    // shapes whose activations leave too little ring: one CTA per SM
-constexpr int MV_TILE_MAX = 14 * 1024;      // largest tile (both rows)
+constexpr int MV_SMEM_MAX = 224 * 1024;
+constexpr int MV_GSLOTS = 16;               // row pairs whose partial sums can be in flight at once
 
 struct __align__(16) MvShared {
-    uint64_t full[MV_MAX_STAGES];
+    uint64_t full[MV_MAX_STAGES];           // a tile's bytes have landed (expect_tx)
+    uint64_t empty[MV_MAX_STAGES];          // one arrival per team: the tile has been read
+    uint64_t gbar[MV_GSLOTS];               // one arrival per team: the row pair's partial sums are in
     unsigned int issued[MV_MAX_STAGES];     // use number + 1 last armed on each stage
+    unsigned int gen[MV_GSLOTS];            // slot i serves row pair g with g % MV_GSLOTS == i and g / MV_GSLOTS == gen[i]
     float red[NCW];
+    uint64_t probe;                         // scratch barrier: what does pending_count report for the last arrival?
+    unsigned int last_cnt;                  // ... this value (measured once per CTA instead of trusting a reading of the PTX manual)
+    float4 part[MV_GSLOTS][NCW];            // per team: {row0, row1, gate row0, gate row1}
 };
 static_assert(sizeof(MvShared) <= MV_SHARED_HDR, "header does not fit");
 
 struct CtaWork {
     int seg;            // segment (non gate/up modes)
     int r0, r1;         // row range [r0, r1), both even
-    int ng;             // row groups of R rows
-    int parts0;         // tiles per group of the first (or only) matrix
-    int tpg;            // tiles per group (all matrices)
+    int ng;             // row groups of p.nrows rows
+    int tpg;            // tiles per group: 1, or 2 for gate/up (gate tile, up tile)
 };
 
 __device__ __forceinline__ CtaWork cta_work(const MvParams& p, int cta, int nctas) {
@@ -82,18 +85,18 @@ __device__ __forceinline__ CtaWork cta_work(const MvParams& p, int cta, int ncta
     const int i = cta - c0;
     const long u0 = (long)units * i / nc, u1 = (long)units * (i + 1) / nc;
     w.r0 = (int)u0 * 2; w.r1 = (int)u1 * 2;
-    w.ng = (w.r1 - w.r0) / R;
-    w.parts0 = p.seg[s].parts;
-    w.tpg = gu ? p.seg[0].parts + p.seg[1].parts : p.seg[s].parts;
+    w.ng = (w.r1 - w.r0) / p.nrows;
+    w.tpg = gu ? 2 : 1;
     return w;
 }
 
-// lane 0 of the owning warp finishes a row pair
-__device__ __forceinline__ void epilogue_pair(const MvParams& p, int seg, int row, float v0, float v1, float2 res) {
+// lane 0 of the finishing warp completes a row pair
+__device__ __forceinline__ void epilogue_pair(const MvParams& p, int seg, int row, float v0, float v1) {
     const MvSeg& sg = p.seg[seg];
     if (p.mode == MV_STORE) {
         *reinterpret_cast<float2*>(p.y + sg.out_off + row) = make_float2(v0, v1);
     } else if (p.mode == MV_RESID) {
+        const float2 res = __ldcg(reinterpret_cast<const float2*>(p.resid + sg.out_off + row));   // written by other SMs
         *reinterpret_cast<float2*>(p.y + sg.out_off + row) = make_float2(res.x + v0, res.y + v1);
     } else if (p.mode == MV_QKV) {
         const int hd = p.head_dim;
@@ -119,100 +122,42 @@ __device__ __forceinline__ void epilogue_pair(const MvParams& p, int seg, int ro
     }
 }
 
-// One K-slice of a tile: both rows against the lane's 64 activations of that slice. row[r] points at the first
-// byte of row r's slice in the ring stage (Q6_K rows may sit off a 4-byte boundary: row_dot copes).
-template <int T, bool ACT2>
-__device__ __forceinline__ void slice_dots(const uint8_t* row0, const uint8_t* row1, int slice, int lane, const ActView& av,
-                                           float (&acc)[R]) {
-    LaneAct la;
-    load_act<T, ACT2>(la, av, slice * B2_SLICE, lane);
-#pragma unroll ROW_UNROLL
-    for (int r = 0; r < R; r++) {
-        const float d = row_dot<T, ACT2>(r ? row1 : row0, lane, la);
-#pragma unroll
-        for (int k = 0; k < R; k++) if (k == r) acc[k] += d;
-    }
-}
-
-// cold path: second matrix of a gate/up pair whose quant type differs from the first
-struct AccR { float v[R]; };
-template <bool ACT2>
-__device__ __noinline__ AccR slice_dots_any(int type, const uint8_t* row0, const uint8_t* row1, int slice, int lane, ActView av, AccR in) {
-    float acc[R];
-#pragma unroll
-    for (int r = 0; r < R; r++) acc[r] = in.v[r];
-    switch (type) {
-        case T_Q4_K: slice_dots<T_Q4_K, ACT2>(row0, row1, slice, lane, av, acc); break;
-        case T_Q6_K: slice_dots<T_Q6_K, ACT2>(row0, row1, slice, lane, av, acc); break;
-        case T_Q8_0: slice_dots<T_Q8_0, ACT2>(row0, row1, slice, lane, av, acc); break;
-        case T_Q4_0: slice_dots<T_Q4_0, ACT2>(row0, row1, slice, lane, av, acc); break;
-        case T_Q5_K: slice_dots<T_Q5_K, ACT2>(row0, row1, slice, lane, av, acc); break;
-    }
-    AccR out;
-#pragma unroll
-    for (int r = 0; r < R; r++) out.v[r] = acc[r];
-    return out;
-}
-
-// Where tile t of group g comes from (global) and how it is laid out in its stage.
-struct TileGeo {
-    int seg, sl0, nsl;          // matrix, first K-slice, number of K-slices
-    uint32_t off[R];            // byte offset of row r's first slice inside the stage
-};
-__device__ __forceinline__ TileGeo tile_geo(const MvParams& p, const CtaWork& w, int g, int t) {
-    TileGeo tg;
-    const bool second = (p.mode == MV_GATEUP) && t >= w.parts0;
-    tg.seg = (p.mode == MV_GATEUP) ? (second ? 1 : 0) : w.seg;
-    const int part = second ? t - w.parts0 : t;
-    const MvSeg& sg = p.seg[tg.seg];
-    tg.sl0 = part * sg.chunk;
-    tg.nsl = min(sg.chunk, p.n_slices - tg.sl0);
-    const uint32_t row_lo = (uint32_t)(uintptr_t)sg.w + (uint32_t)(w.r0 + g * R) * (uint32_t)sg.row_bytes;   // low address bits of row 0
-    if (sg.parts == 1) {        // both rows in one copy that started at the 16-byte boundary below row 0
-        tg.off[0] = row_lo & 15u; tg.off[1] = tg.off[0] + (uint32_t)sg.row_bytes;
-    } else {                    // one copy per row into its own slot, each from the 16-byte boundary below its start
-        const uint32_t s_lo = row_lo + (uint32_t)tg.sl0 * (uint32_t)slice_bytes(sg.type);
-        tg.off[0] = s_lo & 15u; tg.off[1] = (uint32_t)p.slot_bytes + ((s_lo + (uint32_t)sg.row_bytes) & 15u);
-    }
-    return tg;
-}
-
-// Request tile t of group g into `stage` (lanes 0..R-1 of the calling warp take part; call with the warp converged).
+// ---------------------------------------------------------------- small PTX helpers of the ring protocol
 __device__ __forceinline__ void st_release_shared(unsigned int* p, unsigned int v) {
     asm volatile("st.release.cta.shared::cta.u32 [%0], %1;" ::"r"(smem_u32(p)), "r"(v) : "memory");
 }
-__device__ __forceinline__ unsigned int ld_acquire_shared(const unsigned int* p) {
+__device__ __forceinline__ unsigned int ld_volatile_shared(const unsigned int* p) {
     unsigned int v;
-    asm volatile("ld.acquire.cta.shared::cta.u32 %0, [%1];" : "=r"(v) : "r"(smem_u32(p)) : "memory");
+    asm volatile("ld.volatile.shared::cta.u32 %0, [%1];" : "=r"(v) : "r"(smem_u32(p)) : "memory");
     return v;
 }
+__device__ __forceinline__ void st_volatile_shared(unsigned int* p, unsigned int v) {
+    asm volatile("st.volatile.shared::cta.u32 [%0], %1;" ::"r"(smem_u32(p)), "r"(v) : "memory");
+}
+// arrive on an mbarrier and report the pending-arrival count of the state the arrive returns
+__device__ __forceinline__ uint32_t mbar_arrive_pending(uint64_t* bar, uint64_t& state) {
+    uint32_t cnt;
+    asm volatile("{\n\tmbarrier.arrive.shared::cta.b64 %0, [%2];\n\tmbarrier.pending_count.b64 %1, %0;\n\t}"
+                 : "=l"(state), "=r"(cnt) : "r"(smem_u32(bar)) : "memory");
+    return cnt;
+}
+__device__ __forceinline__ bool mbar_test_wait_state(uint64_t* bar, uint64_t state) {
+    uint32_t ok;
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.test_wait.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(smem_u32(bar)), "l"(state) : "memory");
+    return ok != 0;
+}
+
+// Request tile t (0, or 1 = the second matrix of gate/up) of group g into `stage`: ONE bulk copy (lane 0 of the calling warp).
 __device__ __forceinline__ void tile_issue(const MvParams& p, const CtaWork& w, int g, int t, uint8_t* stage, uint64_t* bar,
                                            unsigned int* issued, unsigned int use, int lane) {
-    const bool second = (p.mode == MV_GATEUP) && t >= w.parts0;
-    const int seg = (p.mode == MV_GATEUP) ? (second ? 1 : 0) : w.seg;
-    const int part = second ? t - w.parts0 : t;
-    const MvSeg& sg = p.seg[seg];
-    const int row0 = w.r0 + g * R;
-    if (sg.parts == 1) {
-        if (lane == 0) {
-            const uintptr_t start = (uintptr_t)sg.w + (size_t)row0 * sg.row_bytes;
-            const uintptr_t a0 = start & ~(uintptr_t)15, a1 = (start + (size_t)R * sg.row_bytes + 15) & ~(uintptr_t)15;
-            mbar_arrive_expect_tx(bar, (uint32_t)(a1 - a0));
-            st_release_shared(issued, use + 1);
-            tma_load_1d(stage, (const void*)a0, (uint32_t)(a1 - a0), bar);
-        }
-    } else {
-        const int sb = slice_bytes(sg.type), sl0 = part * sg.chunk;
-        const int len = min(sg.chunk * sb, sg.row_bytes - sl0 * sb);            // the last part may be shorter
-        const uintptr_t start = (uintptr_t)sg.w + (size_t)(row0 + (lane & (R - 1))) * sg.row_bytes + (size_t)sl0 * sb;
-        const uintptr_t a0 = start & ~(uintptr_t)15, a1 = (start + len + 15) & ~(uintptr_t)15;
-        uint32_t bytes = (uint32_t)(a1 - a0), tot = bytes;
-#pragma unroll
-        for (int o = 1; o < R; o <<= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
-        if (lane == 0) { mbar_arrive_expect_tx(bar, tot); st_release_shared(issued, use + 1); }
-        __syncwarp();
-        if (lane < R) tma_load_1d(stage + lane * p.slot_bytes, (const void*)a0, bytes, bar);
-    }
+    if (lane != 0) return;
+    const MvSeg& sg = p.seg[(p.mode == MV_GATEUP) ? t : w.seg];
+    const uintptr_t start = (uintptr_t)sg.w + (size_t)(w.r0 + g * p.nrows) * sg.row_bytes;
+    const uintptr_t a0 = start & ~(uintptr_t)15, a1 = (start + (size_t)p.nrows * sg.row_bytes + 15) & ~(uintptr_t)15;
+    mbar_arrive_expect_tx(bar, (uint32_t)(a1 - a0));
+    st_volatile_shared(issued, use + 1);
+    tma_load_1d(stage, (const void*)a0, (uint32_t)(a1 - a0), bar);
 }
 
 // Consumer prologue: x (float32, global) -> optional RMSNorm weight -> two int8 planes + packed per-block
@@ -227,8 +172,8 @@ __device__ __forceinline__ void mv_quantize_input(const MvParams& p, MvShared& s
     const int nblk = p.K / 32;                         // a multiple of 8: a warp's 8 quads are in or out together
     const float MAGIC = 12582912.0f;                   // 1.5 * 2^23: float add rounds to nearest integer
     const float fs = ACT2 ? 1.0f / B2_ACT_RES : 1.0f;
-    uint8_t* const lay0 = smem + p.act_off[0];
-    uint8_t* const lay1 = smem + p.act_off[1];
+    uint8_t* const lay0 = smem + p.act_off;
+    uint8_t* const lay1 = smem + p.act_off;
     constexpr int U = 8;                               // blocks per thread whose loads are in flight together
     constexpr int QUADS = NCW * 8;
     float ssq = 0.f;
@@ -308,8 +253,8 @@ __device__ __forceinline__ float mv_rms_scale(const MvParams& p, const MvShared&
     return rsqrtf(tot / (float)p.K + p.eps);
 }
 
-__device__ __forceinline__ ActView act_view(const MvParams& p, uint8_t* smem, int layout) {
-    uint8_t* base = smem + p.act_off[layout];
+__device__ __forceinline__ ActView act_view(const MvParams& p, uint8_t* smem) {
+    uint8_t* base = smem + p.act_off;
     ActView v;
     v.a = base; v.b = base + p.act_plane;
     v.f = reinterpret_cast<const float*>(base + 2 * p.act_plane);
@@ -331,98 +276,123 @@ __device__ __forceinline__ void pair_reduce(const float (&acc)[R], int lane, flo
     v1 = __shfl_sync(0xffffffffu, keep, 16);
 }
 
-// One warp: its row groups, every tile of a group in ring order, sums in registers; after reading a stage the
-// warp refills it with the tile S places further on in the CTA's tile order.
+// One warp = (team, member): K-slice `team` of the row groups g = member, member + team size, ...
 template <int T, bool ACT2>
 __device__ __forceinline__ void consume(const MvParams& p, const CtaWork& work, MvShared& sh, uint8_t* ring,
-                                        const ActView& av0, const ActView& av1, float rs, int warp, int lane) {
+                                        const ActView& av, float rs, int warp, int lane) {
     const bool gateup = (p.mode == MV_GATEUP);
-    const int S = p.n_stages, tpg = work.tpg, ng = work.ng;
-    if (warp >= ng) return;
-    // ring position of this warp's current tile q = g * tpg + t, and the tile q + S that will replace it
-    int s, u, g2, t2;
-    { const int q = warp * tpg; s = q % S; u = q / S; g2 = warp + S / tpg; t2 = S % tpg; }
-    const int jump = (NCW - 1) * tpg + 1, jump_s = jump % S, jump_u = jump / S;     // last tile of a group -> first of the next
-    for (int g = warp; g < ng; g += NCW) {
-        const int row0 = work.r0 + g * R;
-        float2 res = make_float2(0.f, 0.f);
-        if (p.mode == MV_RESID && lane == 0)           // early: the round trip hides behind the group's tiles
-            res = __ldcg(reinterpret_cast<const float2*>(p.resid + p.seg[work.seg].out_off + row0));
+    const int S = p.n_stages, tpg = work.tpg, ng = work.ng, n_teams = p.n_slices, nrows = p.nrows;
+    const int team = warp % n_teams, member = warp / n_teams;
+    const int team_size = (NCW - 1 - team) / n_teams + 1;
+    const unsigned int n_tiles = (unsigned)(ng * tpg);
+    const unsigned int last_cnt = sh.last_cnt;
+    const bool active = team * B2_SLICE + lane * 64 < p.K;              // lanes past K in a partial last slice idle
+    LaneAct la;
+    if (active) load_act<T, ACT2>(la, av, team * B2_SLICE, lane);       // this warp's activations, for the whole kernel
+    const int sb = slice_bytes(T);
+    for (int g = member; g < ng; g += team_size) {
+        const int row0 = work.r0 + g * nrows;
         float acc[R], gacc[R];
 #pragma unroll
         for (int r = 0; r < R; r++) { acc[r] = 0.f; gacc[r] = 0.f; }
-        int seg = work.seg;
         for (int t = 0; t < tpg; t++) {
-            if (gateup && t == work.parts0) {          // gate done: keep its sums, go on with up
-#pragma unroll
-                for (int r = 0; r < R; r++) { gacc[r] = acc[r]; acc[r] = 0.f; }
-            }
-            const TileGeo tg = tile_geo(p, work, g, t);
-            seg = tg.seg;
-            const int type = p.seg[seg].type;
-            const int sb = slice_bytes(type);
+            const MvSeg& sg = p.seg[gateup ? t : work.seg];
+            const unsigned int q = (unsigned)(g * tpg + t);
+            const unsigned int u = __umulhi(q, p.inv_stages);
+            const int s = (int)(q - u * (unsigned)S);
             uint8_t* stage = ring + (size_t)s * p.stage_bytes;
             {   // this use of the stage has been armed (see the ring note at the top), then: its bytes have landed
                 uint32_t spins = 0;
-                while (ld_acquire_shared(&sh.issued[s]) != (unsigned)u + 1u) {
-                    __nanosleep(64);
-                    if (++spins > (1u << 22)) {
+                while (ld_volatile_shared(&sh.issued[s]) != u + 1u) {
+                    __nanosleep(20);
+                    if (++spins > (1u << 23)) {
                         volatile unsigned int* e = reinterpret_cast<volatile unsigned int*>(p.err);
-                        if (e && e[0] == 0) { e[1] = blockIdx.x; e[2] = threadIdx.x; e[3] = (unsigned)g; e[4] = (unsigned)u; e[0] = 0x10003u; }
+                        if (e && e[0] == 0) { e[1] = blockIdx.x; e[2] = threadIdx.x; e[3] = (unsigned)g; e[4] = u; e[0] = 0x10003u; }
                         break;
                     }
                 }
             }
-            mbar_wait(&sh.full[s], u & 1, p.err, 0x10002u, (unsigned)g);
-            const uint8_t* r0p = stage + tg.off[0];
-            const uint8_t* r1p = stage + tg.off[1];
-            for (int i = 0; i < tg.nsl; i++, r0p += sb, r1p += sb) {
-                const int sl = tg.sl0 + i;
+            mbar_wait(&sh.full[s], u & 1u, p.err, 0x10002u, (unsigned)g);
+            // the copy started at the 16-byte boundary below row 0 (only Q6_K rows can sit off one: row_dot copes)
+            const uint32_t off0 = ((uint32_t)(uintptr_t)sg.w + (uint32_t)row0 * (uint32_t)sg.row_bytes) & 15u;
+            const uint8_t* r0p = stage + off0 + team * sb;
 #ifndef B2_MV_SKIP_COMPUTE      // experiment builds only (scripts/mv_variants.sh): stream the tiles, skip the dot products
-                if (sl * B2_SLICE + lane * 64 < p.K)
-#else
-                if (false)
-#endif
-                {
-                    if (type == T) slice_dots<T, ACT2>(r0p, r1p, sl, lane, av0, acc);
-                    else {
-                        AccR in;
+            if (active) {
+                if (nrows == 2) {
+                    const uint8_t* r1p = r0p + sg.row_bytes;
+#pragma unroll ROW_UNROLL
+                    for (int r = 0; r < R; r++) {
+                        const float d = row_dot<T, ACT2>(r ? r1p : r0p, lane, la);
 #pragma unroll
-                        for (int r = 0; r < R; r++) in.v[r] = acc[r];
-                        const AccR out = slice_dots_any<ACT2>(type, r0p, r1p, sl, lane,
-                                                              act_layout_of(type) == act_layout_of(T) ? av0 : av1, in);
-#pragma unroll
-                        for (int r = 0; r < R; r++) acc[r] = out.v[r];
+                        for (int k = 0; k < R; k++) if (k == r) acc[k] += d;
                     }
+                } else {
+                    acc[0] += row_dot<T, ACT2>(r0p, lane, la);
                 }
             }
+#endif
+            if (gateup && t == 0) {                    // gate done: keep its sums, go on with up
+#pragma unroll
+                for (int r = 0; r < R; r++) { gacc[r] = acc[r]; acc[r] = 0.f; }
+            }
+            // done with the stage: the last of its readers (one warp per team) refills it
             fence_proxy_async();    // generic-proxy reads of the stage, ordered before the TMA (async proxy) refill
             __syncwarp();
-            if (g2 < ng) tile_issue(p, work, g2, t2, stage, &sh.full[s], &sh.issued[s], (unsigned)u + 1u, lane);
-            // next tile of this warp (and the tile S places after it)
-            if (t + 1 < tpg) { if (++s == S) { s = 0; u++; } }
-            else { s += jump_s; u += jump_u; if (s >= S) { s -= S; u++; } g2 += NCW - 1; }
-            if (++t2 == tpg) { t2 = 0; g2++; }
+            bool last = false;
+            if (lane == 0) { uint64_t st; last = mbar_arrive_pending(&sh.empty[s], st) == last_cnt; }
+            last = __shfl_sync(0xffffffffu, last, 0);
+            if (last && q + (unsigned)S < n_tiles) {
+                const unsigned int q2 = q + (unsigned)S;
+                const int g2 = (int)(tpg == 2 ? q2 >> 1 : q2), t2 = (int)(tpg == 2 ? q2 & 1u : 0u);
+                tile_issue(p, work, g2, t2, stage, &sh.full[s], &sh.issued[s], u + 1u, lane);
+            }
         }
         float v0, v1, g0 = 0.f, g1 = 0.f;
-        pair_reduce(acc, lane, v0, v1);
-        if (gateup) pair_reduce(gacc, lane, g0, g1);
+        if (nrows == 2) {
+            pair_reduce(acc, lane, v0, v1);
+            if (gateup) pair_reduce(gacc, lane, g0, g1);
+        } else {
+            v0 = warp_sum(acc[0]); v1 = 0.f;
+        }
         if (lane == 0) {
-            v0 *= rs; v1 *= rs;                            // fused RMSNorm factor (a scalar: applied to the sums)
-            if (gateup) {
-                g0 *= rs; g1 *= rs;
-                const float h0 = g0 / (1.0f + __expf(-g0)) * v0;
-                const float h1 = g1 / (1.0f + __expf(-g1)) * v1;
-                *reinterpret_cast<float2*>(p.y + row0) = make_float2(h0, h1);
-            } else {
-                epilogue_pair(p, seg, row0, v0, v1, res);
+            bool finish = true;
+            if (n_teams > 1) {     // hand this team's partial sums in; the team that completes the group adds them in team order
+                const int slot = g % MV_GSLOTS;
+                const unsigned int gen = (unsigned)(g / MV_GSLOTS);
+                while (ld_volatile_shared(&sh.gen[slot]) != gen) __nanosleep(20);     // the group MV_GSLOTS back is done with the slot
+                sh.part[slot][team] = make_float4(v0, v1, g0, g1);
+                uint64_t st;
+                finish = mbar_arrive_pending(&sh.gbar[slot], st) == last_cnt;         // release: our partial sums are visible ...
+                if (finish) {
+                    while (!mbar_test_wait_state(&sh.gbar[slot], st)) {}              // ... acquire: and so are everybody else's
+                    v0 = v1 = g0 = g1 = 0.f;
+                    for (int i = 0; i < n_teams; i++) {
+                        const float4 c = sh.part[slot][i];
+                        v0 += c.x; v1 += c.y; g0 += c.z; g1 += c.w;
+                    }
+                    st_release_shared(&sh.gen[slot], gen + 1u);
+                }
+            }
+            if (finish) {
+                v0 *= rs; v1 *= rs;                        // fused RMSNorm factor (a scalar: applied to the sums)
+                if (gateup) {
+                    g0 *= rs; g1 *= rs;
+                    const float h0 = g0 / (1.0f + __expf(-g0)) * v0;
+                    const float h1 = g1 / (1.0f + __expf(-g1)) * v1;
+                    *reinterpret_cast<float2*>(p.y + row0) = make_float2(h0, h1);
+                } else if (nrows == 2) {
+                    epilogue_pair(p, work.seg, row0, v0, v1);
+                } else {                                   // single rows: plain store / residual add only (mv_plan)
+                    float* y = p.y + p.seg[work.seg].out_off + row0;
+                    *y = (p.mode == MV_RESID ? __ldcg(p.resid + p.seg[work.seg].out_off + row0) : 0.f) + v0;
+                }
             }
         }
     }
 }
 
 template <bool ACT2>
-__global__ void __launch_bounds__(MV_THREADS, 2) matvec_kernel(const MvParams p) {
+__global__ void __launch_bounds__(MV_THREADS, 1) matvec_kernel(const MvParams p) {
     extern __shared__ __align__(128) uint8_t smem_raw[];
     MvShared& sh = *reinterpret_cast<MvShared*>(smem_raw);
     uint8_t* ring = smem_raw + p.ring_off;
@@ -430,20 +400,20 @@ __global__ void __launch_bounds__(MV_THREADS, 2) matvec_kernel(const MvParams p)
     const CtaWork work = cta_work(p, blockIdx.x, gridDim.x);
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < p.n_stages; s++) { mbar_init(&sh.full[s], 1); sh.issued[s] = 0; }
+        for (int s = 0; s < p.n_stages; s++) { mbar_init(&sh.full[s], 1); mbar_init(&sh.empty[s], p.n_slices); sh.issued[s] = 0; }
+        for (int i = 0; i < MV_GSLOTS; i++) { mbar_init(&sh.gbar[i], p.n_slices); sh.gen[i] = 0; }
+        mbar_init(&sh.probe, 1);
         fence_mbar_init();
+        uint64_t st;
+        sh.last_cnt = mbar_arrive_pending(&sh.probe, st);    // the only (= last) arrival of a one-arrival barrier
     }
     __syncthreads();
-    if (!p.trigger_late) griddep_launch();   // the next kernel's CTAs may move in beside us and prefetch their weights
+    if (!p.trigger_late) griddep_launch();   // the next kernel may start (it will prefetch its own weights)
     {   // first pass over the ring: weights do not depend on the previous kernel, so this runs ahead of the wait
         const int n_first = min(p.n_stages, work.ng * work.tpg);
-        int g = 0, t = warp;
-        while (t >= work.tpg && work.tpg > 0) { t -= work.tpg; g++; }
-        for (int q = warp; q < n_first; q += NCW) {
-            tile_issue(p, work, g, t, ring + (size_t)q * p.stage_bytes, &sh.full[q], &sh.issued[q], 0u, lane);
-            t += NCW;
-            while (t >= work.tpg) { t -= work.tpg; g++; }
-        }
+        for (int q = warp; q < n_first; q += NCW)
+            tile_issue(p, work, work.tpg == 2 ? q >> 1 : q, work.tpg == 2 ? q & 1 : 0, ring + (size_t)q * p.stage_bytes,
+                       &sh.full[q], &sh.issued[q], 0u, lane);
     }
     if (p.norm_w) {     // weights, not activations: warm L1 while the previous kernel finishes
         for (int i = threadIdx.x * 32; i < p.K; i += MV_THREADS * 32)
@@ -451,105 +421,72 @@ __global__ void __launch_bounds__(MV_THREADS, 2) matvec_kernel(const MvParams p)
     }
     griddep_wait();     // activations written by the previous kernel are visible from here on
     if (p.trigger_late) griddep_launch();
-    // plane layout follows the quant type this CTA reads (gate/up: seg 0's, plus the other if the pair is mixed)
+    // plane layout follows the quant type this CTA reads (a gate/up pair has one type: mv_plan)
     const int type0 = (p.mode == MV_GATEUP) ? p.seg[0].type : p.seg[work.seg].type;
-    const int lay = act_layout_of(type0);
-    const int layouts = (p.act_dual ? 3 : (1 << lay));
-    mv_quantize_input<ACT2>(p, sh, smem_raw, layouts, warp, lane);
-    const ActView av0 = act_view(p, smem_raw, lay), av1 = act_view(p, smem_raw, p.act_dual ? 1 - lay : lay);
+    mv_quantize_input<ACT2>(p, sh, smem_raw, 1 << act_layout_of(type0), warp, lane);
+    const ActView av = act_view(p, smem_raw);
     const float rs = mv_rms_scale(p, sh);
     switch (type0) {
-        case T_Q4_K: consume<T_Q4_K, ACT2>(p, work, sh, ring, av0, av1, rs, warp, lane); break;
-        case T_Q6_K: consume<T_Q6_K, ACT2>(p, work, sh, ring, av0, av1, rs, warp, lane); break;
-        case T_Q8_0: consume<T_Q8_0, ACT2>(p, work, sh, ring, av0, av1, rs, warp, lane); break;
-        case T_Q4_0: consume<T_Q4_0, ACT2>(p, work, sh, ring, av0, av1, rs, warp, lane); break;
-        case T_Q5_K: consume<T_Q5_K, ACT2>(p, work, sh, ring, av0, av1, rs, warp, lane); break;
+        case T_Q4_K: consume<T_Q4_K, ACT2>(p, work, sh, ring, av, rs, warp, lane); break;
+        case T_Q6_K: consume<T_Q6_K, ACT2>(p, work, sh, ring, av, rs, warp, lane); break;
+        case T_Q8_0: consume<T_Q8_0, ACT2>(p, work, sh, ring, av, rs, warp, lane); break;
+        case T_Q4_0: consume<T_Q4_0, ACT2>(p, work, sh, ring, av, rs, warp, lane); break;
+        case T_Q5_K: consume<T_Q5_K, ACT2>(p, work, sh, ring, av, rs, warp, lane); break;
     }
 }
 
 // ---------------------------------------------------------------- host side
 static int g_stage_cap = 0;      // B2_MV_STAGES (tuning): read once in mv_init
-static int g_solo = 0;           // B2_MV_SOLO=1: always one CTA per SM (224 KB of shared memory)
-static int g_tile_max = MV_TILE_MAX;   // B2_MV_TILE (tuning): largest tile in bytes
 
-cudaError_t mv_init() {   // per device: allow > 48 KB dynamic shared memory; read the tuning knobs once
+cudaError_t mv_init() {   // per device: allow > 48 KB dynamic shared memory; read the tuning knob once
     static bool env_read = false;
     if (!env_read) {
         if (const char* s = getenv("B2_MV_STAGES")) g_stage_cap = atoi(s);
-        if (const char* s = getenv("B2_MV_SOLO")) g_solo = atoi(s);
-        if (const char* s = getenv("B2_MV_TILE")) { int v = atoi(s); if (v >= 2048 && v <= 65536) g_tile_max = v; }
         env_read = true;
     }
-    cudaError_t e = cudaFuncSetAttribute(matvec_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, MV_SMEM_SOLO);
+    cudaError_t e = cudaFuncSetAttribute(matvec_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, MV_SMEM_MAX);
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(matvec_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, MV_SMEM_SOLO);
+    return cudaFuncSetAttribute(matvec_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, MV_SMEM_MAX);
 }
 
 int mv_plan(MvParams& p, int n_ctas) {
     if (p.K % 256 || p.K <= 0) return -1;
-    if (p.K > 65536) return -2;
     p.n_slices = (p.K + B2_SLICE - 1) / B2_SLICE;
+    if (p.n_slices > NCW) return -2;                       // one warp team per K-slice: K <= 32768
+    int max_row = 0;
     for (int s = 0; s < p.nseg; s++) {
         MvSeg& sg = p.seg[s];
         const int be = block_elems(sg.type), bb = block_bytes(sg.type);
         if (!bb || be == 1) return -3;
         sg.row_bytes = p.K / be * bb;
         if (sg.n_rows % 2) return -4;
+        max_row = sg.row_bytes > max_row ? sg.row_bytes : max_row;
     }
-    p.act_dual = 0;
-    for (int s = 1; s < p.nseg; s++)
-        if (p.mode == MV_GATEUP && act_layout_of(p.seg[s].type) != act_layout_of(p.seg[0].type)) p.act_dual = 1;
-    // one activation block per layout in use: [plane a][plane b][K/8 floats of packed scales]
+    if (p.mode == MV_GATEUP) {
+        if (p.nseg != 2 || p.seg[0].n_rows != p.seg[1].n_rows) return -6;
+        if (p.seg[0].type != p.seg[1].type) return -8;     // a mixed pair is run unfused by the caller
+    }
+    // activation block: [plane a][plane b][K/8 floats of packed scales]
     p.act_plane = p.n_slices * B2_SLICE;
     const int act_block = (2 * p.act_plane + p.K / 2 + 127) / 128 * 128;
-    p.act_off[0] = MV_SHARED_HDR;
-    p.act_off[1] = p.act_dual ? MV_SHARED_HDR + act_block : MV_SHARED_HDR;
-    p.ring_off = MV_SHARED_HDR + (p.act_dual ? 2 : 1) * act_block;
-    // Tile geometry for a given cap on the tile size. A row pair is one contiguous run of 2 * row_bytes: one tile
-    // (ONE copy) if that fits, else the rows are cut into `parts` runs of `chunk` K-slices, one copy per row and run.
-    auto geometry = [&](int tile_cap) {
-        int max_tile = 0, max_slot = 0;
-        for (int s = 0; s < p.nseg; s++) {
-            MvSeg& sg = p.seg[s];
-            if (R * sg.row_bytes + 32 <= tile_cap) {
-                sg.parts = 1; sg.chunk = p.n_slices;
-                const int tile = (R * sg.row_bytes + 32 + 15) / 16 * 16;      // + slack: the copy starts / ends on 16-byte boundaries
-                max_tile = tile > max_tile ? tile : max_tile;
-            } else {
-                const int sb = slice_bytes(sg.type);
-                int chunk = (tile_cap / R - 32) / sb;
-                if (chunk < 1) chunk = 1;
-                sg.parts = (p.n_slices + chunk - 1) / chunk;
-                sg.chunk = (p.n_slices + sg.parts - 1) / sg.parts;             // even parts
-                sg.parts = (p.n_slices + sg.chunk - 1) / sg.chunk;
-                const int slot = (sg.chunk * sb + 32 + 15) / 16 * 16;
-                max_slot = slot > max_slot ? slot : max_slot;
-                max_tile = R * slot > max_tile ? R * slot : max_tile;
-            }
-        }
-        p.slot_bytes = max_slot;
-        p.stage_bytes = (max_tile + 127) / 128 * 128;
-    };
-    // Prefer two CTAs per SM (112 KB each) with at least one stage per warp; shrink the tiles (down to ~4 KB copies)
-    // before giving that up; shapes that still leave < 6 stages take the SM alone (224 KB).
-    int S = 0;
-    if (!g_solo) {
-        for (int cap = g_tile_max; cap >= 8192 && S < NCW; cap -= 2048) {
-            geometry(cap);
-            S = (MV_SMEM_CO - p.ring_off) / p.stage_bytes;
-        }
-    }
-    if (S < 6) {
-        geometry(g_tile_max);
-        S = (MV_SMEM_SOLO - p.ring_off) / p.stage_bytes;
+    p.act_off = MV_SHARED_HDR;
+    p.ring_off = MV_SHARED_HDR + act_block;
+    // a tile = a row pair (ONE copy of 2 * row_bytes); single rows when pairs of very long rows would leave < 4 stages
+    p.nrows = 2;
+    p.stage_bytes = (2 * max_row + 32 + 127) / 128 * 128;  // + slack: the copy starts / ends on 16-byte boundaries
+    int S = (MV_SMEM_MAX - p.ring_off) / p.stage_bytes;
+    if (S < 4 && (p.mode == MV_STORE || p.mode == MV_RESID)) {
+        p.nrows = 1;
+        p.stage_bytes = (max_row + 32 + 127) / 128 * 128;
+        S = (MV_SMEM_MAX - p.ring_off) / p.stage_bytes;
     }
     if (S > MV_MAX_STAGES) S = MV_MAX_STAGES;
     if (g_stage_cap >= 2 && g_stage_cap < S) S = g_stage_cap;
     if (S < 2) return -5;
     p.n_stages = S;
+    p.inv_stages = 0xFFFFFFFFu / (unsigned)S + 1u;
     // CTA split proportional to bytes (gate/up: every CTA handles both matrices)
     if (p.mode == MV_GATEUP) {
-        if (p.nseg != 2 || p.seg[0].n_rows != p.seg[1].n_rows) return -6;
         p.seg[0].cta0 = p.seg[1].cta0 = 0; p.seg[0].ncta = p.seg[1].ncta = n_ctas;
     } else {
         if (n_ctas < p.nseg) return -7;

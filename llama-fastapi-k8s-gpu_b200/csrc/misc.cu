@@ -59,6 +59,26 @@ cudaError_t embed_row_launch(int type, const uint8_t* table, int K, const int* t
     return cudaLaunchKernelEx(&cfg, embed_row_kernel, type, table, K, token_ptr, x);
 }
 
+// h[i] = silu(g[i]) * h[i]: the un-fused tail of a gate/up pair whose two matrices have different quant types
+__global__ void silu_mul_kernel(const float* __restrict__ g, float* __restrict__ h, int n) {
+    griddep_launch();
+    griddep_wait();
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const float a = g[i];
+        h[i] = a / (1.0f + __expf(-a)) * h[i];
+    }
+}
+
+cudaError_t silu_mul_launch(const float* g, float* h, int n, cudaStream_t s, bool pdl) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((n + 255) / 256); cfg.blockDim = dim3(256); cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, silu_mul_kernel, g, h, n);
+}
+
 // y[r,:] = x[r,:] * rsqrt(mean(x[r,:]^2) + eps) * w      (one CTA per row)
 __global__ void rmsnorm_kernel(const float* __restrict__ x, const float* __restrict__ w, float eps, int K,
                                float* __restrict__ y) {
