@@ -37,10 +37,12 @@ __global__ void __launch_bounds__(AT_THREADS) attn_decode_kernel(const AttnParam
     __shared__ uint64_t full[2];
     if (threadIdx.x == 0) { mbar_init(&full[0], 1); mbar_init(&full[1], 1); fence_mbar_init(); }
     __syncthreads();
+    if (threadIdx.x == 0) tl_stamp(p.tl, 0);
     griddep_launch();
-    griddep_wait();     // q and this token's K/V come from the QKV kernel just before us
+    if (!p.early) griddep_wait();     // q and this token's K/V come from the QKV kernel just before us
     uint32_t use[2] = {0u, 0u};
-    attn_decode_body<HD, CLUSTER>(p, sh, full, use, blockIdx.x, blockIdx.y, threadIdx.x);
+    attn_decode_body<HD, CLUSTER>(p, sh, full, use, blockIdx.x, blockIdx.y, threadIdx.x, p.early != 0);
+    if (p.tl) { __syncthreads(); if (threadIdx.x == 0) tl_stamp(p.tl, 3); }
 }
 
 // one launch for several sequences: blockIdx.z picks the sequence

@@ -21,7 +21,8 @@ struct __align__(16) AttnShared {
     __half k[2][AT_TT][HD];
     __half v[2][AT_TT][HD];
     float q[AT_GMAX][HD];
-    float part[AT_GMAX][HD];           // this split's un-normalised output (cluster merge reads it)
+    float part[AT_GMAX * HD + 8];      // cluster merge: slice [r * per, (r+1) * per) = what split r sent us (its un-normalised outputs of OUR elements)
+    float part_ml[8][AT_GMAX][2];      // cluster merge: (running max, running sum) of every head from every split
     float sc[4][AT_GMAX][AT_TT];       // per head_dim-quarter partial scores; sc[0] then holds p
     float m_run[AT_GMAX], l_run[AT_GMAX], alpha[AT_GMAX];
     int pages[AT_MAX_PAGES];
@@ -33,19 +34,24 @@ struct __align__(16) AttnShared {
 // synchronise on named barrier AT_BAR, so it can be a kernel of its own or a phase of the persistent
 // decode kernel (mega.cu). `full` are two mbarriers that live across calls; `use` counts how often
 // each has completed (the caller keeps it; every thread holds the same value).
+// `early`: the body is entered BEFORE griddepcontrol.wait (programmatic dependent launch). Position and page table are
+// already valid then (the kernel that writes q and this token's K/V row lets us start only after ITS dependency wait,
+// MvParams::trigger_late), so the K/V tiles of the older positions are requested first and the wait happens inside,
+// just before q and the newest row are needed: the copies overlap the tail of the QKV kernel.
 template <int HD, bool CLUSTER>
 __device__ __forceinline__ void attn_decode_body(const AttnParams& p, AttnShared<HD>& sh, uint64_t* full, uint32_t (&use)[2],
-                                                 int sp, int h, int tid) {
+                                                 int sp, int h, int tid, bool early = false) {
     const int warp = tid >> 5, lane = tid & 31;
     const int G = p.n_head / p.n_kv;
     const int bt = p.block_tokens;
 
     if (tid < AT_GMAX) { sh.m_run[tid] = -INFINITY; sh.l_run[tid] = 0.f; sh.alpha[tid] = 0.f; }
 
-    // one round trip: position, page table and q are fetched together
+    // one round trip: position and page table (and q, unless it is still being written)
     const int pos = *p.pos_ptr;
     for (int i = tid; i < p.max_pages && i < AT_MAX_PAGES; i += AT_THREADS) sh.pages[i] = p.block_table[i];
-    for (int i = tid; i < G * HD; i += AT_THREADS) sh.q[i / HD][i % HD] = __ldcg(p.q + (size_t)h * G * HD + i);   // written by other SMs
+    if (!early)
+        for (int i = tid; i < G * HD; i += AT_THREADS) sh.q[i / HD][i % HD] = __ldcg(p.q + (size_t)h * G * HD + i);   // written by other SMs
     // never index past the page ids that were staged above, whatever the caller's position says
     const int ctx = min(pos + 1, min(p.max_pages, AT_MAX_PAGES) * bt);
     int chunk = (ctx + p.n_splits - 1) / p.n_splits;
@@ -54,14 +60,12 @@ __device__ __forceinline__ void attn_decode_body(const AttnParams& p, AttnShared
     const int ntile = (p1 - p0 + AT_TT - 1) / AT_TT;
     named_bar_sync(AT_BAR, AT_THREADS);
 
-    auto issue = [&](int ti) {      // thread 0 only
-        int st = ti & 1;
-        int t0 = p0 + ti * AT_TT, t1 = min(p1, t0 + AT_TT);
-        mbar_arrive_expect_tx(&full[st], (uint32_t)(t1 - t0) * HD * 2 * 2);
-        int a = t0;
-        while (a < t1) {
+    // thread 0: arm the tile's barrier for ALL its bytes, copy the positions [lo, hi) of it (whole page runs)
+    auto copy_rows = [&](int st, int t0, int lo, int hi) {
+        int a = lo;
+        while (a < hi) {
             int pg = a / bt, in = a % bt;
-            int b = min(t1, (pg + 1) * bt);
+            int b = min(hi, (pg + 1) * bt);
             int page = sh.pages[pg];
             size_t off = (((size_t)page * p.n_kv + h) * bt + in) * HD;
             uint32_t bytes = (uint32_t)(b - a) * HD * 2;
@@ -70,7 +74,25 @@ __device__ __forceinline__ void attn_decode_body(const AttnParams& p, AttnShared
             a = b;
         }
     };
-    if (tid == 0 && ntile > 0) issue(0);
+    auto issue = [&](int ti, int excl) {      // positions >= excl are left for a later copy_rows on the same barrier
+        int st = ti & 1;
+        int t0 = p0 + ti * AT_TT, t1 = min(p1, t0 + AT_TT);
+        mbar_arrive_expect_tx(&full[st], (uint32_t)(t1 - t0) * HD * 2 * 2);
+        copy_rows(st, t0, t0, min(t1, excl));
+    };
+    const int n_early = early ? min(ntile, 2) : min(ntile, 1);      // tiles requested up front
+    if (tid == 0)
+        for (int ti = 0; ti < n_early; ti++) issue(ti, early ? pos : 0x7fffffff);
+    if (early) {
+        griddep_wait();     // q and the newest K/V row (position pos) are complete from here on
+        if (tid == 0) tl_stamp(p.tl, 1);
+        for (int i = tid; i < G * HD; i += AT_THREADS) sh.q[i / HD][i % HD] = __ldcg(p.q + (size_t)h * G * HD + i);
+        if (tid == 0 && pos >= p0 && pos < min(p1, p0 + n_early * AT_TT)) {
+            const int ti = (pos - p0) / AT_TT;
+            copy_rows(ti & 1, p0 + ti * AT_TT, pos, pos + 1);
+        }
+        named_bar_sync(AT_BAR, AT_THREADS);
+    }
 
     // phase-3 ownership: a pair of output dims for a set of heads
     constexpr int NSET3 = AT_THREADS / (HD / 2);
@@ -84,7 +106,7 @@ __device__ __forceinline__ void attn_decode_body(const AttnParams& p, AttnShared
     for (int ti = 0; ti < ntile; ti++) {
         const int st = ti & 1;
         const int t0 = p0 + ti * AT_TT, tl = min(p1, t0 + AT_TT) - t0;
-        if (tid == 0 && ti + 1 < ntile) issue(ti + 1);
+        if (tid == 0 && ti + 1 < ntile && ti + 1 >= n_early) issue(ti + 1, 0x7fffffff);
         mbar_wait(&full[st], use[st] & 1, p.err, 0x20001u, (unsigned)ti);
         use[st]++;
 
@@ -173,38 +195,48 @@ __device__ __forceinline__ void attn_decode_body(const AttnParams& p, AttnShared
         return;
     }
     if (CLUSTER) {
+        // Every CTA of the cluster merges a slice of the G * HD outputs. Each split PUSHES its contribution to the
+        // owner of every element (remote shared-memory stores), then ONE cluster barrier, then the owners merge from
+        // their own shared memory: no remote loads, and nobody has to wait for its peers before leaving.
         cg::cluster_group cluster = cg::this_cluster();
-#pragma unroll
-        for (int i = 0; i < HG3; i++) {
-            int g = set3 * hg3 + i;
-            if (i < hg3 && g < G) { sh.part[g][2 * dpair] = acc[i][0]; sh.part[g][2 * dpair + 1] = acc[i][1]; }
-        }
-        cluster.sync();                                   // every split's partial is in its CTA's smem
         const int ns = p.n_splits;
         const int per = (G * HD + ns - 1) / ns;           // outputs merged by each CTA of the cluster
         const int rank = (int)cluster.block_rank();
-        for (int e = rank * per + tid; e < min(G * HD, (rank + 1) * per); e += AT_THREADS) {
-            int g = e / HD, d = e % HD;
-            float ms[8], ls[8], as[8];
 #pragma unroll
-            for (int r = 0; r < 8; r++) {
-                if (r < ns) {
-                    const AttnShared<HD>* rs = cluster.map_shared_rank(&sh, r);
-                    ms[r] = rs->m_run[g]; ls[r] = rs->l_run[g]; as[r] = rs->part[g][d];
-                } else { ms[r] = -INFINITY; ls[r] = 0.f; as[r] = 0.f; }
+        for (int i = 0; i < HG3; i++) {
+            int g = set3 * hg3 + i;
+            if (i < hg3 && g < G) {
+#pragma unroll
+                for (int k = 0; k < 2; k++) {
+                    const int e = g * HD + 2 * dpair + k, r = e / per;
+                    AttnShared<HD>* rs = cluster.map_shared_rank(&sh, r);
+                    rs->part[rank * per + (e - r * per)] = acc[i][k];
+                }
             }
+        }
+        for (int i = tid; i < G * ns; i += AT_THREADS) {
+            const int g = i / ns, r = i % ns;
+            AttnShared<HD>* rs = cluster.map_shared_rank(&sh, r);
+            rs->part_ml[rank][g][0] = sh.m_run[g];
+            rs->part_ml[rank][g][1] = sh.l_run[g];
+        }
+        cluster.sync();                                   // every split's contribution has landed in its owner's smem
+        for (int e = rank * per + tid; e < min(G * HD, (rank + 1) * per); e += AT_THREADS) {
+            const int g = e / HD;
             float M = -INFINITY;
 #pragma unroll
-            for (int r = 0; r < 8; r++) M = fmaxf(M, ms[r]);
+            for (int r = 0; r < 8; r++) if (r < ns) M = fmaxf(M, sh.part_ml[r][g][0]);
             float num = 0.f, den = 0.f;
 #pragma unroll
             for (int r = 0; r < 8; r++) {
-                float w = (ms[r] == -INFINITY) ? 0.f : expf(ms[r] - M);
-                num += w * as[r]; den += w * ls[r];
+                if (r < ns) {
+                    const float ms = sh.part_ml[r][g][0];
+                    const float w = (ms == -INFINITY) ? 0.f : expf(ms - M);
+                    num += w * sh.part[r * per + (e - rank * per)]; den += w * sh.part_ml[r][g][1];
+                }
             }
             p.out[(size_t)h * G * HD + e] = num / den;
         }
-        cluster.sync();                                   // nobody leaves while its smem is still being read
         return;
     }
     // ---- global-scratch merge (n_splits > 8)

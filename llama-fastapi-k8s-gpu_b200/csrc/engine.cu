@@ -92,6 +92,8 @@ struct b2_engine {
     int64_t launches = 0, weight_bytes = 0, kv_bytes = 0;
     bool use_graph = true, use_pdl = true, act2 = true, finalized = false, chain_pdl = true;
     int batch_attn_splits = 0;     // B2_BATCH_ATTN_SPLITS (tuning), read once at create
+    unsigned long long* tl = nullptr;   // B2_TIMELINE=1: 4 time stamps per kernel of a decode step (debugging aid)
+    int tl_n = 0;                  // kernels recorded by the last forward_launches
     // prompt (GEMM) workspace, allocated on the first long prompt: PF_T tokens per chunk
     float *pf_x = nullptr, *pf_part = nullptr;     // residual stream [PF_T][n_embd]; K-split partial sums of the last GEMM
     size_t pf_part_floats = 0;
@@ -173,10 +175,11 @@ static int engine_create_impl(b2_engine* e, const b2_config* c) {
     // tuning knobs are read here, once; the hot path never calls getenv
     e->chain_pdl = e->use_pdl && !getenv("B2_NO_CHAIN_PDL");
     if (const char* s = getenv("B2_BATCH_ATTN_SPLITS")) e->batch_attn_splits = atoi(s);
+    if (getenv("B2_TIMELINE")) CK(cudaMalloc(&e->tl, sizeof(unsigned long long) * 4 * 1024));
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
     // one mat-vec CTA per SM: the second CTA slot of every SM is for the NEXT kernel's CTAs (matvec.cu)
-    int per = 1;
+    int per = mv_ctas_per_sm();
     if (const char* s = getenv("B2_CTAS_PER_SM")) per = atoi(s) > 0 ? atoi(s) : per;
     e->n_ctas = sms * per;
     e->n_sms = sms;
@@ -266,6 +269,7 @@ extern "C" int b2_engine_destroy(b2_engine* e) {
         cudaFree(s.ints); cudaFree(s.block_table); cudaFree(s.prompt); cudaFree(s.ring); cudaFree(s.sst); cudaFree(s.sp);
         cudaFree(s.uniforms);
     }
+    cudaFree(e->tl);
     cudaFree(e->k_pool); cudaFree(e->v_pool); cudaFree(e->rope_freq);
     cudaFree(e->attn_scratch); cudaFree(e->attn_counters);
     cudaFree(e->pf_x); cudaFree(e->pf_part); cudaFree(e->pf_xn); cudaFree(e->pf_qh); cudaFree(e->pf_att); cudaFree(e->pf_h);
@@ -435,6 +439,8 @@ static int forward_launches(b2_engine* e, Slot& s, bool with_head, bool with_sam
     auto tock = [&](cudaEvent_t y) { if (kt) cudaEventRecord(y, st); };
     cudaEvent_t ye = nullptr;
     int* tok = s.ints + 0; int* pos = s.ints + 1;
+    int tl_k = 0;
+    auto next_tl = [&]() -> unsigned long long* { return (e->tl && !kt && tl_k < 1024) ? e->tl + 4 * (tl_k++) : nullptr; };
     tick(0, &ye);
     CK(embed_row_launch(e->tok_embd.type, e->tok_embd.ptr, c.n_embd, tok, s.x, st, pdl));
     tock(ye);
@@ -443,6 +449,9 @@ static int forward_launches(b2_engine* e, Slot& s, bool with_head, bool with_sam
         Layer& L = e->layers[l];
         MvParams q = L.p_qkv;
         q.x = s.x; q.q_out = s.q; q.pos_ptr = pos; q.block_table = s.block_table;
+        const bool attn_plain = !(e->attn_mma == 1 || (e->attn_mma < 0 && e->n_splits > 8));
+        q.trigger_late = pdl && attn_plain;      // attention may start once we are past our own wait: it prefetches old K/V rows
+        q.tl = next_tl();
         tick(1, &ye);
         CK(mv_launch(q, e->n_ctas, st, e->act2, pdl));
         tock(ye);
@@ -452,19 +461,21 @@ static int forward_launches(b2_engine* e, Slot& s, bool with_head, bool with_sam
         a.n_head = c.n_head; a.n_kv = c.n_head_kv; a.head_dim = c.head_dim; a.block_tokens = c.kv_block_tokens;
         a.n_splits = e->n_splits; a.scale = 1.0f / sqrtf((float)c.head_dim); a.err = kernel_error_word();
         a.max_pages = e->max_blocks;
+        a.early = q.trigger_late;
+        a.tl = next_tl();
         tick(2, &ye);
-        if (e->attn_mma == 1 || (e->attn_mma < 0 && e->n_splits > 8)) CK(attn_decode_mma_launch(a, nullptr, nullptr, st, pdl));
+        if (!attn_plain) CK(attn_decode_mma_launch(a, nullptr, nullptr, st, pdl));
         else CK(attn_decode_launch(a, st, pdl));
         tock(ye);
         MvParams o = L.p_o;
-        o.x = s.att; o.y = s.x; o.resid = s.x;
+        o.x = s.att; o.y = s.x; o.resid = s.x; o.tl = next_tl();
         tick(3, &ye);
         CK(mv_launch(o, e->n_ctas, st, e->act2, pdl));
         tock(ye);
         tick(4, &ye);
         if (L.gu_fused) {
             MvParams g = L.p_gu;
-            g.x = s.x; g.y = s.h;
+            g.x = s.x; g.y = s.h; g.tl = next_tl();
             CK(mv_launch(g, e->n_ctas, st, e->act2, pdl));
         } else {
             MvParams a = L.p_gate, b = L.p_up;
@@ -476,7 +487,7 @@ static int forward_launches(b2_engine* e, Slot& s, bool with_head, bool with_sam
         }
         tock(ye);
         MvParams d = L.p_down;
-        d.x = s.h; d.y = s.x; d.resid = s.x;
+        d.x = s.h; d.y = s.x; d.resid = s.x; d.tl = next_tl();
         tick(5, &ye);
         CK(mv_launch(d, e->n_ctas, st, e->act2, pdl));
         tock(ye);
@@ -484,12 +495,13 @@ static int forward_launches(b2_engine* e, Slot& s, bool with_head, bool with_sam
     }
     if (with_head) {
         MvParams h = e->p_head;
-        h.x = s.x; h.y = s.logits;
+        h.x = s.x; h.y = s.logits; h.tl = next_tl();
         tick(6, &ye);
         CK(mv_launch(h, e->n_ctas, st, e->act2, pdl));
         tock(ye);
         e->launches++;
     }
+    if (!kt) e->tl_n = tl_k;
     if (with_sample) {
         tick(7, &ye);
         CK(sample_launch(s.logits, c.n_vocab, s.sp, s.sst, s.uniforms, s.ints + 3, s.ints + 2, tok, pos, s.ring, c.n_ctx + 1, st, pdl));
@@ -859,8 +871,37 @@ extern "C" int b2_decode_n(b2_engine* e, int slot, int n, int32_t* out) {
     if (s.n_past + n > e->cfg.n_ctx) return fail(B2_ERR_ARG, "context window full");
     CK(cudaSetDevice(e->cfg.device));
     for (int i = 0; i < n; i++) {
+        if (e->tl && i == n - 1) {      // debugging aid: record the last step of the call
+            std::vector<unsigned long long> init(4 * 1024, 0ull);
+            for (int k = 0; k < 1024; k++) init[4 * k] = ~0ull;
+            CK(cudaMemcpyAsync(e->tl, init.data(), init.size() * 8, cudaMemcpyHostToDevice, e->stream));
+            CK(cudaStreamSynchronize(e->stream));
+        }
         rc = run_step(e, s, GK_DECODE);
         if (rc) return rc;
+    }
+    if (e->tl) {
+        CK(cudaStreamSynchronize(e->stream));
+        std::vector<unsigned long long> t(4 * 1024);
+        CK(cudaMemcpy(t.data(), e->tl, t.size() * 8, cudaMemcpyDeviceToHost));
+        const int nk = e->tl_n;
+        const char* names[5] = {"qkv", "attn", "o", "gate_up", "down"};
+        double sum[6][4] = {};
+        for (int k = 0; k < nk; k++) {
+            const unsigned long long* r = &t[4 * k];
+            const int kind = k < nk - 1 ? k % 5 : 5;
+            const double prev_end = k ? (double)t[4 * (k - 1) + 3] : (double)r[0];
+            sum[kind][0] += ((double)r[0] - prev_end) * 1e-3;                 // first CTA in, relative to the previous kernel's end
+            sum[kind][1] += r[1] ? ((double)r[1] - (double)r[0]) * 1e-3 : 0;  // in -> past the dependency wait
+            sum[kind][2] += r[2] ? ((double)r[2] - (double)r[1]) * 1e-3 : 0;  // wait -> prologue done
+            sum[kind][3] += ((double)r[3] - (double)r[0]) * 1e-3;             // in -> out
+        }
+        const int L = e->cfg.n_layer;
+        fprintf(stderr, "[b2 timeline] one decode step, us per launch (mean over layers): start-prev_end | in->wait | wait->prologue | in->out\n");
+        for (int kind = 0; kind < 5; kind++)
+            fprintf(stderr, "[b2 timeline] %-8s %7.2f %7.2f %7.2f %7.2f\n", names[kind], sum[kind][0] / L, sum[kind][1] / L, sum[kind][2] / L, sum[kind][3] / L);
+        fprintf(stderr, "[b2 timeline] %-8s %7.2f %7.2f %7.2f %7.2f\n", "lm_head", sum[5][0], sum[5][1], sum[5][2], sum[5][3]);
+        fprintf(stderr, "[b2 timeline] step span %.1f us\n", ((double)t[4 * (nk - 1) + 3] - (double)t[0]) * 1e-3);
     }
     // step i forwards the token at position n_past+i and its sample lands at ring[n_past+i+1]
     CK(cudaMemcpyAsync(e->pinned, s.ring + s.n_past + 1, sizeof(int) * n, cudaMemcpyDeviceToHost, e->stream));
@@ -1110,7 +1151,7 @@ extern "C" int b2_bench_matvec(int device, int mode, int type, int n_rows, int K
     if (mode != MV_STORE && mode != MV_RESID && mode != MV_GATEUP) return fail(B2_ERR_ARG, "mode must be 0, 1 or 3");
     CK(cudaSetDevice(device));
     CK(mv_init());
-    if (n_ctas <= 0) { int sms = 148; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device); n_ctas = sms; }
+    if (n_ctas <= 0) { int sms = 148; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device); n_ctas = sms * mv_ctas_per_sm(); }
     MvParams p = {};
     const int nmat = mode == MV_GATEUP ? 2 : 1;
     p.nseg = nmat; p.K = K; p.mode = mode;

@@ -62,6 +62,8 @@ struct MvParams {
     const float* rope_freq; // [head_dim / 2]
     int head_dim, n_kv, block_tokens;
     unsigned int* err;      // host-mapped error word (kernel watchdogs)
+    unsigned long long* tl; // optional timeline record of this launch (B2_TIMELINE=1): [0] first CTA in, [1] last CTA past its
+                            // dependency wait, [2] last CTA done with its prologue, [3] last CTA out (%globaltimer, ns)
     int trigger_late;       // 1: let the next kernel launch only after this one's own dependency wait (its prologue
                             //    may then read what this kernel's predecessors wrote, e.g. the token position)
     // plan (mv_plan)
@@ -75,6 +77,7 @@ struct MvParams {
 };
 
 cudaError_t mv_init();   // once per device, outside stream capture
+int mv_ctas_per_sm();    // 1 (default build)
 int mv_plan(MvParams& p, int n_ctas);
 size_t mv_smem_bytes(const MvParams& p);
 cudaError_t mv_launch(const MvParams& p, int n_ctas, cudaStream_t stream, bool act2, bool pdl);
@@ -107,6 +110,8 @@ struct AttnParams {
     int max_pages;           // entries of block_table that may be read
     float scale;             // 1 / sqrt(head_dim)
     unsigned int* err;       // host-mapped error word (kernel watchdogs)
+    unsigned long long* tl;  // optional timeline record (see MvParams::tl)
+    int early;               // 1: launched with programmatic dependent launch behind a kernel that triggers late (attention_body.cuh)
 };
 cudaError_t attn_init();
 size_t attn_scratch_floats(int n_head, int n_kv, int head_dim, int n_splits);

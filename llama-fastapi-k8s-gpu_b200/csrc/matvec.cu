@@ -48,7 +48,11 @@ constexpr int NCW = MV_NCW;
 constexpr int R = MV_ROWS;
 static_assert(R == 2, "a row group is one RoPE pair");
 constexpr int MV_THREADS = NCW * 32;
-constexpr int MV_SMEM_MAX = 224 * 1024;
+#ifndef B2_MV_CTAS_PER_SM
+#define B2_MV_CTAS_PER_SM 1
+#endif
+constexpr int MV_CTAS_PER_SM = B2_MV_CTAS_PER_SM;      // experiment knob: 2 = two 8-warp CTAs per SM (build with -DB2_MV_NCW=8)
+constexpr int MV_SMEM_MAX = (MV_CTAS_PER_SM == 1 ? 224 : 112) * 1024;
 constexpr int MV_GSLOTS = 16;               // row pairs whose partial sums can be in flight at once
 
 struct __align__(16) MvShared {
@@ -91,19 +95,19 @@ __device__ __forceinline__ CtaWork cta_work(const MvParams& p, int cta, int ncta
 }
 
 // lane 0 of the finishing warp completes a row pair
-__device__ __forceinline__ void epilogue_pair(const MvParams& p, int seg, int row, float v0, float v1) {
+// (pos, page: position of the token and its KV page, fetched once per thread at kernel start; res: the residual pair,
+// fetched when the warp started on the row pair -- no global round trip is left on this path)
+__device__ __forceinline__ void epilogue_pair(const MvParams& p, int seg, int row, float v0, float v1, int pos, int page, float2 res) {
     const MvSeg& sg = p.seg[seg];
     if (p.mode == MV_STORE) {
         *reinterpret_cast<float2*>(p.y + sg.out_off + row) = make_float2(v0, v1);
     } else if (p.mode == MV_RESID) {
-        const float2 res = __ldcg(reinterpret_cast<const float2*>(p.resid + sg.out_off + row));   // written by other SMs
         *reinterpret_cast<float2*>(p.y + sg.out_off + row) = make_float2(res.x + v0, res.y + v1);
     } else if (p.mode == MV_QKV) {
         const int hd = p.head_dim;
-        const int pos = *p.pos_ptr;
         if (seg < 2) {                      // Q or K: rotate the adjacent pair (ggml "norm" RoPE)
             const int i = (row % hd) >> 1;
-            const float ang = (float)pos * p.rope_freq[i];
+            const float ang = (float)pos * __ldg(p.rope_freq + i);
             float s, c;
             sincosf(ang, &s, &c);
             const float a = v0 * c - v1 * s, b = v0 * s + v1 * c;
@@ -113,7 +117,7 @@ __device__ __forceinline__ void epilogue_pair(const MvParams& p, int seg, int ro
             *reinterpret_cast<float2*>(p.q_out + row) = make_float2(v0, v1);
         } else {
             const int bt = p.block_tokens;
-            const int page = p.block_table[pos / bt], slot = pos % bt;
+            const int slot = pos % bt;
             const int kvh = row / hd, d = row % hd;
             const size_t idx = (((size_t)page * p.n_kv + kvh) * bt + slot) * hd + d;
             __half* dst = (seg == 1 ? p.k_cache : p.v_cache) + idx;
@@ -174,7 +178,7 @@ __device__ __forceinline__ void mv_quantize_input(const MvParams& p, MvShared& s
     const float fs = ACT2 ? 1.0f / B2_ACT_RES : 1.0f;
     uint8_t* const lay0 = smem + p.act_off;
     uint8_t* const lay1 = smem + p.act_off;
-    constexpr int U = 8;                               // blocks per thread whose loads are in flight together
+    constexpr int U = 4;                               // blocks per thread whose loads are in flight together (16 warps: K = 16384 per pass)
     constexpr int QUADS = NCW * 8;
     float ssq = 0.f;
     for (int b0 = quad; b0 < nblk; b0 += QUADS * U) {
@@ -279,7 +283,7 @@ __device__ __forceinline__ void pair_reduce(const float (&acc)[R], int lane, flo
 // One warp = (team, member): K-slice `team` of the row groups g = member, member + team size, ...
 template <int T, bool ACT2>
 __device__ __forceinline__ void consume(const MvParams& p, const CtaWork& work, MvShared& sh, uint8_t* ring,
-                                        const ActView& av, float rs, int warp, int lane) {
+                                        const ActView& av, float rs, int pos, int page, int warp, int lane) {
     const bool gateup = (p.mode == MV_GATEUP);
     const int S = p.n_stages, tpg = work.tpg, ng = work.ng, n_teams = p.n_slices, nrows = p.nrows;
     const int team = warp % n_teams, member = warp / n_teams;
@@ -292,6 +296,11 @@ __device__ __forceinline__ void consume(const MvParams& p, const CtaWork& work, 
     const int sb = slice_bytes(T);
     for (int g = member; g < ng; g += team_size) {
         const int row0 = work.r0 + g * nrows;
+        float2 res = make_float2(0.f, 0.f);
+        if (p.mode == MV_RESID && lane == 0) {         // early: the round trip hides behind the tile (any team may end up finishing the group)
+            const float* rp = p.resid + p.seg[work.seg].out_off + row0;
+            if (nrows == 2) res = __ldcg(reinterpret_cast<const float2*>(rp)); else res.x = __ldcg(rp);
+        }
         float acc[R], gacc[R];
 #pragma unroll
         for (int r = 0; r < R; r++) { acc[r] = 0.f; gacc[r] = 0.f; }
@@ -381,10 +390,10 @@ __device__ __forceinline__ void consume(const MvParams& p, const CtaWork& work, 
                     const float h1 = g1 / (1.0f + __expf(-g1)) * v1;
                     *reinterpret_cast<float2*>(p.y + row0) = make_float2(h0, h1);
                 } else if (nrows == 2) {
-                    epilogue_pair(p, work.seg, row0, v0, v1);
+                    epilogue_pair(p, work.seg, row0, v0, v1, pos, page, res);
                 } else {                                   // single rows: plain store / residual add only (mv_plan)
                     float* y = p.y + p.seg[work.seg].out_off + row0;
-                    *y = (p.mode == MV_RESID ? __ldcg(p.resid + p.seg[work.seg].out_off + row0) : 0.f) + v0;
+                    *y = res.x + v0;
                 }
             }
         }
@@ -392,21 +401,25 @@ __device__ __forceinline__ void consume(const MvParams& p, const CtaWork& work, 
 }
 
 template <bool ACT2>
-__global__ void __launch_bounds__(MV_THREADS, 1) matvec_kernel(const MvParams p) {
+__global__ void __launch_bounds__(MV_THREADS, MV_CTAS_PER_SM) matvec_kernel(const MvParams p) {
     extern __shared__ __align__(128) uint8_t smem_raw[];
     MvShared& sh = *reinterpret_cast<MvShared*>(smem_raw);
     uint8_t* ring = smem_raw + p.ring_off;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const CtaWork work = cta_work(p, blockIdx.x, gridDim.x);
+    if (threadIdx.x == 0) tl_stamp(p.tl, 0);
 
-    if (threadIdx.x == 0) {
-        for (int s = 0; s < p.n_stages; s++) { mbar_init(&sh.full[s], 1); mbar_init(&sh.empty[s], p.n_slices); sh.issued[s] = 0; }
-        for (int i = 0; i < MV_GSLOTS; i++) { mbar_init(&sh.gbar[i], p.n_slices); sh.gen[i] = 0; }
+    // barrier set-up spread over the threads (one thread doing ~110 mbarrier.init in a row cost over a microsecond per launch)
+    if ((int)threadIdx.x < p.n_stages) {
+        mbar_init(&sh.full[threadIdx.x], 1); mbar_init(&sh.empty[threadIdx.x], p.n_slices); sh.issued[threadIdx.x] = 0;
+    } else if (threadIdx.x >= 64 && threadIdx.x < 64 + MV_GSLOTS) {
+        mbar_init(&sh.gbar[threadIdx.x - 64], p.n_slices); sh.gen[threadIdx.x - 64] = 0;
+    } else if (threadIdx.x == 96) {
         mbar_init(&sh.probe, 1);
-        fence_mbar_init();
         uint64_t st;
         sh.last_cnt = mbar_arrive_pending(&sh.probe, st);    // the only (= last) arrival of a one-arrival barrier
     }
+    fence_mbar_init();
     __syncthreads();
     if (!p.trigger_late) griddep_launch();   // the next kernel may start (it will prefetch its own weights)
     {   // first pass over the ring: weights do not depend on the previous kernel, so this runs ahead of the wait
@@ -420,19 +433,24 @@ __global__ void __launch_bounds__(MV_THREADS, 1) matvec_kernel(const MvParams p)
             asm volatile("prefetch.global.L1 [%0];" ::"l"(p.norm_w + i));
     }
     griddep_wait();     // activations written by the previous kernel are visible from here on
+    if (threadIdx.x == 0) tl_stamp(p.tl, 1);
     if (p.trigger_late) griddep_launch();
     // plane layout follows the quant type this CTA reads (a gate/up pair has one type: mv_plan)
     const int type0 = (p.mode == MV_GATEUP) ? p.seg[0].type : p.seg[work.seg].type;
     mv_quantize_input<ACT2>(p, sh, smem_raw, 1 << act_layout_of(type0), warp, lane);
     const ActView av = act_view(p, smem_raw);
     const float rs = mv_rms_scale(p, sh);
+    int pos = 0, page = 0;      // QKV epilogue inputs: fetched here, consumed only after the first tile (no round trip left in the epilogue)
+    if (p.mode == MV_QKV) { pos = *p.pos_ptr; page = p.block_table[pos / p.block_tokens]; }
+    if (threadIdx.x == 0) tl_stamp(p.tl, 2);
     switch (type0) {
-        case T_Q4_K: consume<T_Q4_K, ACT2>(p, work, sh, ring, av, rs, warp, lane); break;
-        case T_Q6_K: consume<T_Q6_K, ACT2>(p, work, sh, ring, av, rs, warp, lane); break;
-        case T_Q8_0: consume<T_Q8_0, ACT2>(p, work, sh, ring, av, rs, warp, lane); break;
-        case T_Q4_0: consume<T_Q4_0, ACT2>(p, work, sh, ring, av, rs, warp, lane); break;
-        case T_Q5_K: consume<T_Q5_K, ACT2>(p, work, sh, ring, av, rs, warp, lane); break;
+        case T_Q4_K: consume<T_Q4_K, ACT2>(p, work, sh, ring, av, rs, pos, page, warp, lane); break;
+        case T_Q6_K: consume<T_Q6_K, ACT2>(p, work, sh, ring, av, rs, pos, page, warp, lane); break;
+        case T_Q8_0: consume<T_Q8_0, ACT2>(p, work, sh, ring, av, rs, pos, page, warp, lane); break;
+        case T_Q4_0: consume<T_Q4_0, ACT2>(p, work, sh, ring, av, rs, pos, page, warp, lane); break;
+        case T_Q5_K: consume<T_Q5_K, ACT2>(p, work, sh, ring, av, rs, pos, page, warp, lane); break;
     }
+    if (p.tl) { __syncthreads(); if (threadIdx.x == 0) tl_stamp(p.tl, 3); }
 }
 
 // ---------------------------------------------------------------- host side
@@ -509,6 +527,7 @@ int mv_plan(MvParams& p, int n_ctas) {
     return 0;
 }
 
+int mv_ctas_per_sm() { return MV_CTAS_PER_SM; }
 size_t mv_smem_bytes(const MvParams& p) { return (size_t)p.ring_off + (size_t)p.n_stages * p.stage_bytes; }
 
 cudaError_t mv_launch(const MvParams& p, int n_ctas, cudaStream_t stream, bool act2, bool pdl) {

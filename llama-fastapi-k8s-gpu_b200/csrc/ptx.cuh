@@ -72,6 +72,14 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
+// timeline records (debugging aid, B2_TIMELINE=1): slot 0 keeps the earliest time, the others the latest
+__device__ __forceinline__ void tl_stamp(unsigned long long* tl, int slot) {
+    if (!tl) return;
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    if (slot == 0) atomicMin(tl, t); else atomicMax(tl + slot, t);
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
