@@ -56,12 +56,13 @@ def test_logits_prefill_and_teacher_forced_decode(native_lib, tmp_models, arch, 
 
 @pytest.mark.parametrize("arch,ftype,seed", MODELS[:3])
 def test_greedy_sequence_matches_oracle(native_lib, tmp_models, arch, ftype, seed):
+    """128 greedy tokens. The oracle runs teacher-forced over the ENGINE's tokens, so after a legitimate near-tie flip
+    the comparison re-synchronises and keeps checking the remaining steps instead of stopping at the first difference:
+    every step whose oracle top-2 margin is >= 10x the logit tolerance must carry the oracle's arg-max."""
     from oracle.llama_ref import RefModel
     path = _model(tmp_models, arch, ftype, seed)
-    n_new = 48
+    n_new = 128
     prompt = TOKENS[:12]
-    ref = RefModel(path)
-    want, ref_logits = ref.greedy(prompt, n_new)
     eng = _engine(path)
     eng.ensure_pages(0, len(prompt) + n_new + 1)
     eng.seq_begin(0, 0, [], _greedy())
@@ -69,15 +70,15 @@ def test_greedy_sequence_matches_oracle(native_lib, tmp_models, arch, ftype, see
     got = [eng.sample(0)]
     for _ in range(n_new - 1):
         got.append(eng.decode([0])[0])
-    for i, (g, w) in enumerate(zip(got, want)):
-        if g != w:
-            top2 = np.sort(ref_logits[i])[-2:]
-            margin = top2[1] - top2[0]
-            assert margin < 10 * LOGIT_TOL, f"step {i}: engine {g} != oracle {w} with margin {margin}"
-            break   # a legitimate near-tie flip: the sequences diverge from here
-    else:
-        assert got == want
     eng.close()
+    want = RefModel(path).forward(prompt + got[:-1])[len(prompt) - 1:]     # logits behind each generated token
+    top2 = np.partition(want, -2, axis=1)[:, -2:]
+    margin = top2[:, 1] - top2[:, 0]
+    flips = [i for i in range(n_new) if int(want[i].argmax()) != got[i]]
+    for i in flips:
+        assert margin[i] < 10 * LOGIT_TOL, f"step {i}: engine {got[i]} != oracle {int(want[i].argmax())} with margin {margin[i]}"
+    checked = int((margin >= 10 * LOGIT_TOL).sum())
+    assert checked >= n_new // 2, f"only {checked} of {n_new} steps have a clear margin: pick another seed"
 
 
 def test_graph_pdl_and_plain_launches_agree_bitwise(native_lib, tmp_models):
