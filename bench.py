@@ -152,25 +152,25 @@ def measured_peak_gbs():
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def ncu_traffic_bytes():
-    """dram read+write bytes per decode step from the committed ncu capture, if there is one."""
+def ncu_traffic_bytes(workload):
+    """dram read+write bytes per decode step from the committed ncu capture of THIS workload, else None (a figure
+    captured on another model says nothing about this one)."""
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            return json.load(f).get("dram_bytes_per_step")
+            t = json.load(f)
+        return t.get("dram_bytes_per_step") if t.get("workload") == workload else None
     except Exception:
         return None
 
 
 def cpu_reference_run(path, n_warm, n_steps, budget_s, prompt_len=16):
     """Time the CPU restatement of the reference's llama.cpp CPU path: decode tokens one at a time."""
-    # torchrun exports OMP_NUM_THREADS=1 to its workers; the CPU arm is meant to use every host core it can
-    if os.environ.get("OMP_NUM_THREADS") in (None, "", "1") and "B2_CPU_THREADS" not in os.environ:
-        os.environ["OMP_NUM_THREADS"] = str(len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else os.cpu_count())
-    elif "B2_CPU_THREADS" in os.environ:
-        os.environ["OMP_NUM_THREADS"] = os.environ["B2_CPU_THREADS"]
+    # torchrun exports OMP_NUM_THREADS=1 to its workers and the OpenMP runtime may already be up (torch): the thread count
+    # is set through the library's own entry point. The CPU arm is meant to use every host core it can.
+    n_threads = int(os.environ.get("B2_CPU_THREADS", "0")) or (len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else os.cpu_count())
     from oracle.cpu_ref import CpuRef
     import numpy as np
-    c = CpuRef(path, n_ctx=prompt_len + n_warm + n_steps + 8)
+    c = CpuRef(path, n_ctx=prompt_len + n_warm + n_steps + 8, n_threads=n_threads)
     rng = np.random.default_rng(0)
     toks = rng.integers(0, c.n_vocab, size=prompt_len + n_warm + n_steps)
     t0 = time.perf_counter()
@@ -188,11 +188,54 @@ def cpu_reference_run(path, n_warm, n_steps, budget_s, prompt_len=16):
     for _ in range(n_steps):
         c.eval(int(toks[i])); i += 1
     dt = time.perf_counter() - t0
-    threads = c.threads
+    threads, simd = c.threads, c.simd
     c.close()
     return dict(value=n_steps / dt, ms_per_step=dt / n_steps * 1e3, steps=n_steps, warmup=n_warm, cores=threads,
-                sample=f"{n_steps} single-token decode steps (all layers + lm_head) after a {prompt_len}-token context; "
-                       f"KV reads are <2% of the bytes at the workload's context, weights are streamed in full")
+                sample=f"{n_steps} single-token decode steps (all layers + lm_head) after a {prompt_len}-token context, "
+                       f"{simd} integer dots on {threads} OpenMP threads; KV reads are <2% of the bytes at the workload's "
+                       f"context, weights are streamed in full")
+
+
+def parity_check(eng, path, n_vocab, n_prompt=6, n_new=8, seed=5):
+    """Run a short greedy generation on the TIMED engine instance (same weights in HBM, same CUDA graphs) and teacher-force
+    the C restatement of the reference's CPU path (oracle/cpu_ref.c, int8 activations) over the same tokens: the whole
+    32-layer graph at the benchmark geometry, checked in the benchmark process. Raises if it is off."""
+    import numpy as np
+    from llama_cpp.engine import SamplingSettings
+    from oracle.cpu_ref import CpuRef
+    rng = np.random.default_rng(seed)
+    prompt = [int(t) for t in rng.integers(0, n_vocab, size=n_prompt)]
+    slot = 0
+    with eng.lock:
+        eng.pages.release(slot)
+        eng.ensure_pages(slot, n_prompt + n_new + 2)
+        eng.seq_begin(slot, 0, [], SamplingSettings(temperature=0.0, repeat_penalty=1.0))
+        eng.prefill(slot, prompt)                 # < 8 tokens: through the mat-vec kernels, like the timed decode steps
+        gpu_logits, toks = [eng.logits(slot)], [eng.sample(slot)]
+        for _ in range(n_new - 1):
+            toks.append(eng.decode([slot])[0])
+            gpu_logits.append(eng.logits(slot))
+    c = CpuRef(path, n_ctx=n_prompt + n_new + 4, n_threads=len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else 0)
+    for t in prompt[:-1]:
+        c.eval(t, want_logits=False)
+    seq = [prompt[-1]] + toks[:-1]
+    worst, agree, clear, std = 0.0, 0, 0, 0.0
+    for t, g in zip(seq, gpu_logits):
+        r = c.eval(int(t))
+        worst = max(worst, float(np.abs(g - r).max()))
+        std = max(std, float(r.std()))
+        top2 = np.partition(r, -2)[-2:]
+        if top2[1] - top2[0] > 0.2 * r.std():     # a clear margin for int8-activation noise
+            clear += 1
+            agree += int(np.argmax(r) == np.argmax(g))
+    c.close()
+    ok = worst < 0.05 * std * 4 + 0.05 and agree == clear      # the bar of tests/test_cpu_ref.py (int8 activations)
+    out = {"max_abs_logit_diff": round(worst, 4), "logit_std": round(std, 3), "argmax_agree": f"{agree}/{clear}", "steps": n_new,
+           "against": "oracle/cpu_ref.c (int8-activation restatement of the reference CPU path), teacher-forced on the engine's tokens",
+           "ok": bool(ok)}
+    if not ok:
+        raise RuntimeError(f"parity check failed: {out}")
+    return out
 
 
 def batch_workload(args, cfg, path, n_prompt, batch, rank, world, local_rank, barrier, torch, dist):
@@ -283,6 +326,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="llama3-8b-q4_k_m-bs1", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-parity-check", action="store_true")
     ap.add_argument("--batch-extra", type=int, default=32, help="bs1 workloads: also time this many sequences per step (0 = skip)")
     ap.add_argument("--cpu-budget-s", type=float, default=20.0)
     ap.add_argument("--profile-kernels", action="store_true", help="also print a per-kernel-kind breakdown to stderr")
@@ -392,15 +436,16 @@ def main():
         barrier()
         tm = llm.last_timings
         n_gen = out["usage"]["completion_tokens"]
-        dec_s = tm["decode_ms"] / 1e3
-        t2 = torch.tensor([dec_s, tm["ttft_ms"]], dtype=torch.float64, device="cuda")
+        t2 = torch.tensor([wall, tm["ttft_ms"], tm["decode_ms"] / 1e3], dtype=torch.float64, device="cuda")
         if world > 1:
             dist.all_reduce(t2, op=dist.ReduceOp.MAX)
-        e2e = {"value": world * max(n_gen - 1, 1) / float(t2[0].item()), "unit": "tok/s",
+        e2e = {"value": world * n_gen / float(t2[0].item()), "unit": "tok/s",
                "h2d_bytes_per_step": round(4 * n_prompt / max(n_gen, 1), 2), "d2h_bytes_per_step": 4,
                "tokens": n_gen, "ttft_ms": float(t2[1].item()), "wall_s": wall,
-               "note": "Llama.create_completion(token ids, max_tokens=K, temperature=0): decode phase of the call "
-                       "(first token to last), host-timed; includes per-chunk D2H of sampled ids, stop checks, detokenise"}
+               "decode_phase_tok_s": world * max(n_gen - 1, 1) / float(t2[2].item()),
+               "note": "WHOLE Llama.create_completion(token ids, max_tokens=K, temperature=0) call, host-timed: H2D of the "
+                       f"{n_prompt} prompt ids, the prompt pass, K decode steps with per-chunk D2H of the sampled ids, stop "
+                       "checks, detokenise; generated tokens / wall time (decode_phase_tok_s = first token to last only)"}
 
     # ---- the other headline numbers of BASELINE.json on the same model: prompt p50 and 32 sequences per step
     extra = None
@@ -424,7 +469,7 @@ def main():
     peak, peak_src = measured_peak_gbs()
     achieved = step_bytes / (ms_max / K / 1e3) / 1e9
     roof = {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
-            "traffic": ncu_traffic_bytes(), "peak_source": peak_src, "bytes_per_launch": int(step_bytes),
+            "traffic": ncu_traffic_bytes(args.workload), "peak_source": peak_src, "bytes_per_launch": int(step_bytes),
             "launch": "one decode step = one CUDA-graph launch (embed, 32 x [qkv, attention, attn_out, gate_up, ffn_down], "
                       "lm_head, sampler); algorithmic bytes = W_read + mean_ctx * KV bytes/position",
             "frac_of_8TBs_nominal": round(achieved / 8000.0, 4)}
@@ -455,6 +500,8 @@ def main():
                                     "sample": r["sample"]}
         except Exception as exc:  # noqa: BLE001
             line["cpu_baseline"] = {"value": None, "unit": "tok/s", "cores": 0, "kind": "port", "sample": f"failed: {exc}"}
+    if not args.ncu_mode and not args.no_parity_check:
+        line["parity_check"] = parity_check(eng, path, eng.dims.n_vocab)      # raises (no JSON line) if the timed engine is off
     print(json.dumps(line))
     llm.close()
     if world > 1:

@@ -21,6 +21,13 @@
 #ifdef _OPENMP
 #include <omp.h>
 #endif
+#if defined(__AVX512VNNI__) && defined(__AVX512VL__) && defined(__AVX512BW__) && defined(__AVX2__)
+#include <immintrin.h>
+#define CR_VNNI 1      /* integer dots on vpdpbusd, as ggml's x86 CPU kernels do them (SURVEY.md 8(d) "CPU baseline") */
+#else
+#define CR_VNNI 0
+#endif
+static int g_simd = CR_VNNI;   /* cr_set_simd(0) forces the scalar loops (tests compare the two) */
 
 enum { T_F32 = 0, T_F16 = 1, T_Q4_0 = 2, T_Q8_0 = 8, T_Q4_K = 12, T_Q5_K = 13, T_Q6_K = 14 };
 
@@ -137,6 +144,68 @@ static void quant_q8_K(const float* x, int K, int8_t* q, float* d, int16_t* bs) 
     }
 }
 
+#if CR_VNNI
+/* Integer block dots on AVX-512 VNNI (vpdpbusd: 4 x u8*s8 -> s32 per lane). Same integers as the scalar loops below. */
+static inline int hsum256(__m256i v) {
+    __m128i s = _mm_add_epi32(_mm256_castsi256_si128(v), _mm256_extracti128_si256(v, 1));
+    s = _mm_add_epi32(s, _mm_shuffle_epi32(s, 0x4e));
+    s = _mm_add_epi32(s, _mm_shuffle_epi32(s, 0xb1));
+    return _mm_cvtsi128_si32(s);
+}
+/* Q4_0 block (16 nibble bytes) x 32 int8: sum (q - 8) * a */
+static inline int dot_q4_0_vnni(const uint8_t* qs, const int8_t* a) {
+    const __m128i b = _mm_loadu_si128((const __m128i*)qs), m4 = _mm_set1_epi8(15);
+    const __m256i q = _mm256_set_m128i(_mm_and_si128(_mm_srli_epi16(b, 4), m4), _mm_and_si128(b, m4));   /* [0..15 | 16..31] */
+    const __m256i av = _mm256_loadu_si256((const __m256i*)a);
+    const __m256i qa = _mm256_dpbusd_epi32(_mm256_setzero_si256(), q, av);
+    const __m256i sa = _mm256_dpbusd_epi32(_mm256_setzero_si256(), _mm256_set1_epi8(8), av);              /* 8 * sum a */
+    return hsum256(_mm256_sub_epi32(qa, sa));
+}
+/* Q8_0 block (32 int8) x 32 int8 */
+static inline int dot_q8_0_vnni(const int8_t* w, const int8_t* a) {
+    const __m256i wv = _mm256_loadu_si256((const __m256i*)w), av = _mm256_loadu_si256((const __m256i*)a);
+    return hsum256(_mm256_dpbusd_epi32(_mm256_setzero_si256(), _mm256_sign_epi8(wv, wv), _mm256_sign_epi8(av, wv)));
+}
+/* Q4_K super-block: sum_is sc[is] * sum_l q[is][l] * a[is*32+l]  (qs: 128 nibble bytes, sc: the 8 unpacked 6-bit scales) */
+static inline int dot_q4_K_vnni(const uint8_t* qs, const int8_t* a, const int* sc) {
+    const __m256i m4 = _mm256_set1_epi8(15);
+    __m512i acc = _mm512_setzero_si512();
+    for (int c = 0; c < 4; c++) {
+        const __m256i b = _mm256_loadu_si256((const __m256i*)(qs + 32 * c));
+        const __m512i q = _mm512_inserti64x4(_mm512_castsi256_si512(_mm256_and_si256(b, m4)),
+                                             _mm256_and_si256(_mm256_srli_epi16(b, 4), m4), 1);     /* sub-block 2c | sub-block 2c+1 */
+        const __m512i p = _mm512_dpbusd_epi32(_mm512_setzero_si512(), q, _mm512_loadu_si512((const void*)(a + 64 * c)));
+        const __m512i scv = _mm512_inserti64x4(_mm512_castsi256_si512(_mm256_set1_epi32(sc[2 * c])), _mm256_set1_epi32(sc[2 * c + 1]), 1);
+        acc = _mm512_add_epi32(acc, _mm512_mullo_epi32(p, scv));
+    }
+    return _mm512_reduce_add_epi32(acc);
+}
+/* Q6_K super-block: sum over the 16 groups of 16: sc[g] * sum_l (q - 32) * a */
+static inline int dot_q6_K_vnni(const uint8_t* p, const int8_t* a) {
+    const __m256i m4 = _mm256_set1_epi8(15), m2 = _mm256_set1_epi8(0x30);
+    const __m512i expand = _mm512_set_epi32(3, 3, 3, 3, 2, 2, 2, 2, 1, 1, 1, 1, 0, 0, 0, 0);
+    const __m512i sc_all = _mm512_cvtepi8_epi32(_mm_loadu_si128((const __m128i*)(p + 192)));        /* 16 int8 scales */
+    __m512i acc = _mm512_setzero_si512();
+    for (int hf = 0; hf < 2; hf++) {
+        const __m256i l0 = _mm256_loadu_si256((const __m256i*)(p + 64 * hf)), l1 = _mm256_loadu_si256((const __m256i*)(p + 64 * hf + 32));
+        const __m256i qh = _mm256_loadu_si256((const __m256i*)(p + 128 + 32 * hf));
+        const __m256i q1 = _mm256_or_si256(_mm256_and_si256(l0, m4), _mm256_and_si256(_mm256_slli_epi16(qh, 4), m2));
+        const __m256i q2 = _mm256_or_si256(_mm256_and_si256(l1, m4), _mm256_and_si256(_mm256_slli_epi16(qh, 2), m2));
+        const __m256i q3 = _mm256_or_si256(_mm256_and_si256(_mm256_srli_epi16(l0, 4), m4), _mm256_and_si256(qh, m2));
+        const __m256i q4 = _mm256_or_si256(_mm256_and_si256(_mm256_srli_epi16(l1, 4), m4), _mm256_and_si256(_mm256_srli_epi16(qh, 2), m2));
+        for (int k = 0; k < 2; k++) {          /* elements 64k .. 64k+63 of this half: groups 4k .. 4k+3 */
+            const __m512i q = _mm512_inserti64x4(_mm512_castsi256_si512(k ? q3 : q1), k ? q4 : q2, 1);
+            const __m512i av = _mm512_loadu_si512((const void*)(a + 128 * hf + 64 * k));
+            __m512i pr = _mm512_dpbusd_epi32(_mm512_setzero_si512(), q, av);
+            pr = _mm512_sub_epi32(pr, _mm512_dpbusd_epi32(_mm512_setzero_si512(), _mm512_set1_epi8(32), av));   /* - 32 * a */
+            const __m512i idx = _mm512_add_epi32(expand, _mm512_set1_epi32(8 * hf + 4 * k));
+            acc = _mm512_add_epi32(acc, _mm512_mullo_epi32(pr, _mm512_permutexvar_epi32(idx, sc_all)));
+        }
+    }
+    return _mm512_reduce_add_epi32(acc);
+}
+#endif
+
 /* y[n] = W[n,:] . x  with x pre-quantised; rows split across OpenMP threads */
 static void matvec(const cr_tensor* w, const int8_t* q8, const float* q8d, const int16_t* q8s, float* y) {
     const int K = (int)w->ne0, N = (int)w->ne1, t = w->type;
@@ -147,11 +216,17 @@ static void matvec(const cr_tensor* w, const int8_t* q8, const float* q8d, const
         if (t == T_Q4_0) {
             for (int b = 0; b < K / 32; b++) { const uint8_t* p = r + b * 18; uint16_t dh; memcpy(&dh, p, 2);
                 const int8_t* a = q8 + b * 32; int s = 0;
+#if CR_VNNI
+                if (g_simd) s = dot_q4_0_vnni(p + 2, a); else
+#endif
                 for (int j = 0; j < 16; j++) s += ((p[2 + j] & 15) - 8) * a[j] + ((p[2 + j] >> 4) - 8) * a[16 + j];
                 acc += h2f(dh) * q8d[b] * s; }
         } else if (t == T_Q8_0) {
             for (int b = 0; b < K / 32; b++) { const uint8_t* p = r + b * 34; uint16_t dh; memcpy(&dh, p, 2);
                 const int8_t* a = q8 + b * 32; const int8_t* wq = (const int8_t*)(p + 2); int s = 0;
+#if CR_VNNI
+                if (g_simd) s = dot_q8_0_vnni(wq, a); else
+#endif
                 for (int j = 0; j < 32; j++) s += wq[j] * a[j];
                 acc += h2f(dh) * q8d[b] * s; }
         } else if (t == T_Q4_K || t == T_Q5_K) {
@@ -159,6 +234,13 @@ static void matvec(const cr_tensor* w, const int8_t* q8, const float* q8d, const
             for (int b = 0; b < K / 256; b++) { const uint8_t* p = r + b * bb; uint16_t dh, mh; memcpy(&dh, p, 2); memcpy(&mh, p + 2, 2);
                 const uint8_t* qs = p + (t == T_Q4_K ? 16 : 48); const int8_t* a = q8 + b * 256; const int16_t* bs = q8s + b * 16;
                 int sumi = 0, summ = 0;
+#if CR_VNNI
+                if (g_simd && t == T_Q4_K) {
+                    int scs[8];
+                    for (int is = 0; is < 8; is++) { int m; k_scale_min(p + 4, is, &scs[is], &m); summ += m * (bs[2 * is] + bs[2 * is + 1]); }
+                    sumi = dot_q4_K_vnni(qs, a, scs);
+                } else
+#endif
                 for (int is = 0; is < 8; is++) { int sc, m; k_scale_min(p + 4, is, &sc, &m);
                     const uint8_t* qq = qs + (is >> 1) * 32; int s = 0;
                     if (t == T_Q4_K) { if (is & 1) for (int l = 0; l < 32; l++) s += (qq[l] >> 4) * a[is * 32 + l];
@@ -169,6 +251,9 @@ static void matvec(const cr_tensor* w, const int8_t* q8, const float* q8d, const
         } else if (t == T_Q6_K) {
             for (int b = 0; b < K / 256; b++) { const uint8_t* p = r + b * 210; uint16_t dh; memcpy(&dh, p + 208, 2);
                 const int8_t* a = q8 + b * 256; const int8_t* sc = (const int8_t*)(p + 192); int sumi = 0;
+#if CR_VNNI
+                if (g_simd) sumi = dot_q6_K_vnni(p, a); else
+#endif
                 for (int hf = 0; hf < 2; hf++) { const uint8_t* ql = p + 64 * hf; const uint8_t* qh = p + 128 + 32 * hf; const int8_t* aa = a + 128 * hf;
                     int s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
                     for (int l = 0; l < 32; l++) { int g = l >> 4;
@@ -227,6 +312,18 @@ void cr_destroy(cr_ctx* c) {
     free(c->g); free(c->u); free(c->logits); free(c->scores); free(c->q8); free(c->q8d); free(c->q8s); free(c->freq); free(c);
 }
 void cr_reset(cr_ctx* c) { c->n_past = 0; }
+/* OpenMP thread count for the mat-vecs and attention (torchrun exports OMP_NUM_THREADS=1, and the variable is only read
+ * when the OpenMP runtime starts: the bench sets the count through this call instead) */
+void cr_set_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+int cr_simd(void) { return g_simd; }          /* 1: AVX-512 VNNI integer dots, 0: scalar loops */
+int cr_has_vnni(void) { return CR_VNNI; }
+void cr_set_simd(int on) { g_simd = on && CR_VNNI; }
 int cr_threads(void) {
 #ifdef _OPENMP
     return omp_get_max_threads();

@@ -39,7 +39,7 @@ def build(force: bool = False) -> str:
 
 
 class CpuRef:
-    def __init__(self, gguf_path: str, n_ctx: int):
+    def __init__(self, gguf_path: str, n_ctx: int, n_threads: int = 0):
         from .gguf_load import OracleGGUF          # gguf-py reader, independent of the product's
         try:
             self.lib = ctypes.CDLL(build())
@@ -52,6 +52,11 @@ class CpuRef:
         self.lib.cr_reset.argtypes = [c_void_p]
         self.lib.cr_destroy.argtypes = [c_void_p]
         self.lib.cr_threads.restype = c_int
+        self.lib.cr_set_threads.argtypes = [c_int]
+        self.lib.cr_set_simd.argtypes = [c_int]
+        self.lib.cr_simd.restype = c_int
+        if n_threads:
+            self.lib.cr_set_threads(int(n_threads))
         self.g = OracleGGUF(gguf_path)
         md = self.g.metadata
 
@@ -78,6 +83,17 @@ class CpuRef:
                              T("output_norm.weight"), T(out), self._layers)
         self.ctx = self.lib.cr_create(ctypes.byref(self.model))
         self.threads = self.lib.cr_threads()
+
+    @property
+    def simd(self) -> str:
+        return "avx512-vnni" if self.lib.cr_simd() else "scalar"
+
+    @property
+    def has_vnni(self) -> bool:
+        return bool(self.lib.cr_has_vnni())
+
+    def set_simd(self, on: bool):
+        self.lib.cr_set_simd(1 if on else 0)
 
     def reset(self):
         self.lib.cr_reset(self.ctx)

@@ -22,3 +22,26 @@ def test_cpu_ref_close_to_float_oracle(tmp_models, arch, ftype, seed):
         assert np.abs(lg - ref[i]).max() < 0.05 * ref[i].std() * 4 + 0.05, i
     assert c.threads >= 1
     c.close()
+
+
+@pytest.mark.parametrize("arch,ftype,seed", [("tiny", "Q4_K_M", 1), ("tiny128", "Q4_0", 2), ("tiny", "Q8_0", 3)])
+def test_vnni_dots_equal_the_scalar_loops(tmp_models, arch, ftype, seed):
+    """The AVX-512 VNNI block dots compute the same integers as the scalar loops: logits identical bit for bit."""
+    from llama_cpp import synth
+    from oracle.cpu_ref import CpuRef
+    path = os.path.join(tmp_models, f"cr_{arch}_{ftype}.gguf")
+    if not os.path.exists(path):
+        synth.write_synthetic_model(path, arch, ftype, seed=seed, output_std=0.1)
+    c = CpuRef(path, 32)
+    if not c.has_vnni:
+        c.close()
+        pytest.skip("no AVX-512 VNNI on this CPU: only the scalar loops are built")
+    toks = [int(t) for t in np.random.default_rng(1).integers(0, 700, size=6)]
+    out = {}
+    for mode in (True, False):
+        c.set_simd(mode)
+        c.reset()
+        out[mode] = np.stack([c.eval(t) for t in toks])
+    c.set_simd(True)
+    c.close()
+    assert np.array_equal(out[True].view(np.uint32), out[False].view(np.uint32))
