@@ -251,11 +251,9 @@ def batch_workload(args, cfg, path, n_prompt, batch, rank, world, local_rank, ba
     r = batched_decode_run(path, n_prompt, batch, W, K, local_rank)
     barrier()
     clk = clocks.result() if not args.ncu_mode else {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
-    t = torch.tensor([r["ms"]], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_max = float(t.item())
-    value = world * batch * K / (ms_max / 1e3)
+    from llama_cpp import replicas
+    agg = replicas.aggregate_throughput(batch * K, r["ms"])       # all ranks' tokens / the slowest rank's device time
+    ms_max, value = agg["ms"], agg["value"]
     e2e = None
     if not args.ncu_mode:
         # end to end: `batch` concurrent callers of the public API (as /response handlers would be), host ids in, text out
@@ -279,10 +277,8 @@ def batch_workload(args, cfg, path, n_prompt, batch, rank, world, local_rank, ba
         wall = time.perf_counter() - t0
         barrier()
         n_gen = sum(o["usage"]["completion_tokens"] for o in outs if o)
-        t2 = torch.tensor([wall], dtype=torch.float64, device="cuda")
-        if world > 1:
-            dist.all_reduce(t2, op=dist.ReduceOp.MAX)
-        e2e = {"value": world * n_gen / float(t2.item()), "unit": "tok/s", "h2d_bytes_per_step": round(4.0 * n_prompt * batch / n_new, 1),
+        agg2 = replicas.aggregate_throughput(n_gen, wall * 1e3)
+        e2e = {"value": agg2["value"], "unit": "tok/s", "h2d_bytes_per_step": round(4.0 * n_prompt * batch / n_new, 1),
                "d2h_bytes_per_step": 4 * batch, "tokens": n_gen, "wall_s": wall, "max_batch": llm._scheduler.stats["max_batch"],
                "note": f"{batch} threads call Llama.create_completion(token ids, max_tokens={n_new}, temperature=0) at once; "
                        "generated tokens / wall time of the whole burst, prompt processing of all requests included"}
@@ -417,11 +413,9 @@ def main():
         clk = clocks.result() if not args.ncu_mode else {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
         kinds = eng.profile_decode_step(0) if (args.profile_kernels or not args.ncu_mode) else None
         mode = eng.mode()
-    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_max = float(t.item())
-    value = world * K / (ms_max / 1e3)
+    from llama_cpp import replicas
+    agg = replicas.aggregate_throughput(K, ms)                    # all ranks' tokens / the slowest rank's device time
+    ms_max, value = agg["ms"], agg["value"]
 
     # ---- end to end through the public API: host token ids in, host text out -------------------
     e2e = None
@@ -436,13 +430,12 @@ def main():
         barrier()
         tm = llm.last_timings
         n_gen = out["usage"]["completion_tokens"]
-        t2 = torch.tensor([wall, tm["ttft_ms"], tm["decode_ms"] / 1e3], dtype=torch.float64, device="cuda")
-        if world > 1:
-            dist.all_reduce(t2, op=dist.ReduceOp.MAX)
-        e2e = {"value": world * n_gen / float(t2[0].item()), "unit": "tok/s",
+        t2 = replicas.dist_max([wall, tm["ttft_ms"], tm["decode_ms"] / 1e3])
+        n_gen_all = replicas.dist_sum([float(n_gen)])[0]
+        e2e = {"value": n_gen_all / t2[0], "unit": "tok/s",
                "h2d_bytes_per_step": round(4 * n_prompt / max(n_gen, 1), 2), "d2h_bytes_per_step": 4,
-               "tokens": n_gen, "ttft_ms": float(t2[1].item()), "wall_s": wall,
-               "decode_phase_tok_s": world * max(n_gen - 1, 1) / float(t2[2].item()),
+               "tokens": n_gen, "ttft_ms": t2[1], "wall_s": wall,
+               "decode_phase_tok_s": world * max(n_gen - 1, 1) / t2[2],
                "note": "WHOLE Llama.create_completion(token ids, max_tokens=K, temperature=0) call, host-timed: H2D of the "
                        f"{n_prompt} prompt ids, the prompt pass, K decode steps with per-chunk D2H of the sampled ids, stop "
                        "checks, detokenise; generated tokens / wall time (decode_phase_tok_s = first token to last only)"}

@@ -11,6 +11,8 @@ on top of the B200 engine: no CPU path (`n_gpu_layers=0` raises), concurrent cal
 from __future__ import annotations
 
 import os
+import queue
+import threading
 import time
 import uuid
 from typing import Any, Dict, Iterator, List, Optional, Sequence, Union
@@ -57,6 +59,7 @@ class Llama:
         self._vocab = Vocab(self._gguf.metadata, self._engine.dims.n_vocab)
         self._scheduler = Scheduler(self._engine, self._vocab)
         self._stream = UniformStream(seed)
+        self._stream_lock = threading.Lock()
         # chat format selection (upstream Llama.__init__)
         self.chat_format = chat_format
         self._chat_formatter = None
@@ -166,8 +169,8 @@ class Llama:
                                 frequency_penalty=float(frequency_penalty), presence_penalty=float(presence_penalty),
                                 penalty_last_n=self.last_n_tokens_size)
 
-    def _run(self, prompt_tokens: List[int], max_tokens: Optional[int], sampling: SamplingSettings,
-             stop: List[bytes], seed: Optional[int], on_token=None) -> Request:
+    def _make_request(self, prompt_tokens: List[int], max_tokens: Optional[int], sampling: SamplingSettings,
+                      stop: List[bytes], seed: Optional[int], on_token=None, cancel_event=None) -> Request:
         if len(prompt_tokens) == 0:
             prompt_tokens = [self._vocab.bos_id if self._vocab.bos_id >= 0 else 0]
         if len(prompt_tokens) >= self._n_ctx:
@@ -176,12 +179,21 @@ class Llama:
             max_tokens = self._n_ctx - len(prompt_tokens)
         if max_tokens + len(prompt_tokens) >= self._n_ctx:
             max_tokens = self._n_ctx - len(prompt_tokens)
-        stream = UniformStream(seed) if seed is not None else self._stream
-        uniforms = stream.take(min(max_tokens + 1, 8192)) if sampling.temperature > 0 else None
+        uniforms = None
+        if sampling.temperature > 0:
+            if seed is not None:
+                uniforms = UniformStream(seed).take(min(max_tokens + 1, 8192))
+            else:
+                with self._stream_lock:       # concurrent callers share the object's generator
+                    uniforms = self._stream.take(min(max_tokens + 1, 8192))
         self._direct_open = False
         self._input_ids = []
-        req = Request(prompt=list(prompt_tokens), max_tokens=int(max_tokens), sampling=sampling, stop=stop,
-                      uniforms=uniforms, on_token=on_token)
+        return Request(prompt=list(prompt_tokens), max_tokens=int(max_tokens), sampling=sampling, stop=stop,
+                       uniforms=uniforms, on_token=on_token, cancel_event=cancel_event)
+
+    def _run(self, prompt_tokens: List[int], max_tokens: Optional[int], sampling: SamplingSettings,
+             stop: List[bytes], seed: Optional[int], on_token=None, cancel_event=None) -> Request:
+        req = self._make_request(prompt_tokens, max_tokens, sampling, stop, seed, on_token, cancel_event)
         self._scheduler.submit(req).wait()
         n = len(req.completion_tokens)
         self.last_timings = dict(
@@ -199,7 +211,9 @@ class Llama:
                           mirostat_tau: float = 5.0, mirostat_eta: float = 0.1, model: Optional[str] = None,
                           stopping_criteria=None, logits_processor=None, grammar=None,
                           logit_bias: Optional[Dict[str, float]] = None, _add_bos: bool = True,
-                          _special: bool = False, **kwargs: Any):
+                          _special: bool = False, cancel_event: Optional[threading.Event] = None, **kwargs: Any):
+        """`cancel_event` (not in upstream): set it from another thread to abandon the generation; the call then returns
+        what was produced so far with finish_reason "cancelled" and the sequence slot is free again."""
         if logprobs is not None:
             raise NotImplementedError("logprobs are not implemented")
         if stopping_criteria is not None:
@@ -219,8 +233,8 @@ class Llama:
         created = int(time.time())
         model_name = model if model is not None else self.model_path
         if stream:
-            return self._stream_completion(tokens, max_tokens, sampling, stop_b, seed, cid, created, model_name)
-        req = self._run(tokens, max_tokens, sampling, stop_b, seed)
+            return self._stream_completion(tokens, max_tokens, sampling, stop_b, seed, cid, created, model_name, cancel_event)
+        req = self._run(tokens, max_tokens, sampling, stop_b, seed, cancel_event=cancel_event)
         text = req.text.decode("utf-8", errors="ignore")
         if echo and prompt_text is not None:
             text = prompt_text + text
@@ -231,17 +245,60 @@ class Llama:
                       "total_tokens": len(req.prompt) + len(req.completion_tokens)},
         }
 
-    def _stream_completion(self, tokens, max_tokens, sampling, stop_b, seed, cid, created, model_name) -> Iterator[dict]:
-        # Non-incremental streaming: the text is produced, then replayed in chunks. The reference
-        # never streams (api.py:58 passes stream=False); the call shape is kept for compatibility.
-        req = self._run(tokens, max_tokens, sampling, stop_b, seed)
-        text = req.text.decode("utf-8", errors="ignore")
-        step = 16
-        for i in range(0, len(text), step):
-            yield {"id": cid, "object": "text_completion", "created": created, "model": model_name,
-                   "choices": [{"text": text[i:i + step], "index": 0, "logprobs": None, "finish_reason": None}]}
-        yield {"id": cid, "object": "text_completion", "created": created, "model": model_name,
-               "choices": [{"text": "", "index": 0, "logprobs": None, "finish_reason": req.finish_reason}]}
+    def _stream_completion(self, tokens, max_tokens, sampling, stop_b, seed, cid, created, model_name,
+                           cancel_event=None) -> Iterator[dict]:
+        """Incremental streaming (upstream `_create_completion(stream=True)`): a chunk goes out as soon as its text can no
+        longer change -- bytes that could still turn out to be the start of a stop string, or that end in the middle of a
+        UTF-8 character, are held back. Closing the generator early cancels the generation."""
+        q: "queue.Queue[Optional[int]]" = queue.Queue()
+        cancel_event = cancel_event or threading.Event()
+        req = self._make_request(tokens, max_tokens, sampling, stop_b, seed, on_token=q.put, cancel_event=cancel_event)
+        self._scheduler.submit(req)
+
+        def chunk(text, finish=None):
+            return {"id": cid, "object": "text_completion", "created": created, "model": model_name,
+                    "choices": [{"text": text, "index": 0, "logprobs": None, "finish_reason": finish}]}
+
+        toks: List[int] = []
+        sent = 0            # bytes of the completion already emitted
+        try:
+            while not req.done.is_set() or not q.empty():
+                try:
+                    t = q.get(timeout=0.05)
+                except queue.Empty:
+                    continue
+                toks.append(t)
+                raw = self._vocab.detokenize(toks)
+                safe = len(raw)
+                for sstr in stop_b:                     # nothing from a stop string on, and hold back a possible stop-string prefix
+                    at = raw.find(sstr)
+                    if at >= 0:
+                        safe = min(safe, at)
+                        continue
+                    for i in range(min(len(sstr) - 1, len(raw)), 0, -1):
+                        if raw.endswith(sstr[:i]):
+                            safe = min(safe, len(raw) - i)
+                            break
+                while safe > sent:                      # hold back an incomplete UTF-8 character
+                    try:
+                        raw[sent:safe].decode("utf-8")
+                        break
+                    except UnicodeDecodeError as exc:
+                        if exc.end < safe - sent and exc.reason != "unexpected end of data":
+                            break                       # invalid bytes in the middle: emit with replacement below
+                        safe = sent + exc.start
+                if safe > sent:
+                    yield chunk(raw[sent:safe].decode("utf-8", errors="ignore"))
+                    sent = safe
+            if req.error is not None:
+                raise req.error
+            tail = req.text[sent:] if len(req.text) > sent else b""
+            if tail:
+                yield chunk(tail.decode("utf-8", errors="ignore"))
+            yield chunk("", req.finish_reason)
+        finally:
+            if not req.done.is_set():                   # the consumer went away: stop generating for it
+                self._scheduler.cancel(req)
 
     __call__ = create_completion
 
@@ -253,9 +310,10 @@ class Llama:
                                frequency_penalty: float = 0.0, repeat_penalty: float = 1.1, tfs_z: float = 1.0,
                                mirostat_mode: int = 0, mirostat_tau: float = 5.0, mirostat_eta: float = 0.1,
                                model: Optional[str] = None, logits_processor=None, grammar=None, logit_bias=None,
-                               logprobs: Optional[bool] = None, top_logprobs: Optional[int] = None, **kwargs: Any):
+                               logprobs: Optional[bool] = None, top_logprobs: Optional[int] = None,
+                               cancel_event: Optional[threading.Event] = None, **kwargs: Any):
         """OpenAI-shaped chat completion; `messages` is not modified (the caller already owns and
-        mutates it: api.py:39,44)."""
+        mutates it: api.py:39,44). `cancel_event` (not in upstream) abandons the generation when set."""
         if functions or tools or response_format is not None:
             raise NotImplementedError("functions / tools / response_format are not implemented")
         fmt = self._chat_formatter if self._chat_formatter is not None else cf.FORMATS[self.chat_format]
@@ -269,7 +327,8 @@ class Llama:
                                      presence_penalty=presence_penalty, frequency_penalty=frequency_penalty,
                                      repeat_penalty=repeat_penalty, tfs_z=tfs_z, mirostat_mode=mirostat_mode,
                                      mirostat_tau=mirostat_tau, mirostat_eta=mirostat_eta, model=model,
-                                     logits_processor=logits_processor, grammar=grammar, logit_bias=logit_bias)
+                                     logits_processor=logits_processor, grammar=grammar, logit_bias=logit_bias,
+                                     cancel_event=cancel_event)
         if stream:
             return self._chat_chunks(out)
         return {

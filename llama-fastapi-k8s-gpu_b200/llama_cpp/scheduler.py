@@ -35,6 +35,7 @@ class Request:
     stop: List[bytes] = field(default_factory=list)
     uniforms: Optional[np.ndarray] = None
     on_token: Optional[Callable[[int], None]] = None     # streaming hook (scheduler thread)
+    cancel_event: Optional[threading.Event] = None       # set by the caller to abandon the request (e.g. after a 408)
     # results
     completion_tokens: List[int] = field(default_factory=list)
     text: bytes = b""
@@ -45,6 +46,9 @@ class Request:
     t_done: float = 0.0
     n_reused: int = 0
     done: threading.Event = field(default_factory=threading.Event)
+
+    def cancelled(self) -> bool:
+        return self.cancel_event is not None and self.cancel_event.is_set()
 
     def wait(self):
         self.done.wait()
@@ -86,6 +90,7 @@ def check_token(req: Request, vocab: Vocab, tok: int) -> bool:
 
 class Scheduler:
     RUN_AHEAD = 8
+    ADMIT_PER_STEP = 2     # while sequences are decoding, at most this many new prompts are processed between two decode steps
 
     def __init__(self, engine: Engine, vocab: Vocab):
         self.engine = engine
@@ -95,7 +100,7 @@ class Scheduler:
         self.cv = threading.Condition()
         self.thread: Optional[threading.Thread] = None
         self.stopping = False
-        self.stats = dict(steps=0, tokens=0, max_batch=0, prefill_tokens=0, reused_tokens=0)
+        self.stats = dict(steps=0, tokens=0, max_batch=0, prefill_tokens=0, reused_tokens=0, cancelled=0)
 
     # ------------------------------------------------------------------ public
     def submit(self, req: Request) -> Request:
@@ -117,6 +122,16 @@ class Scheduler:
         if self.thread is not None:
             self.thread.join(timeout=30)
 
+    def cancel(self, req: Request):
+        """Abandon a request: still queued -> it never starts; running -> its slot is freed at the next step (the caller's
+        `wait()` returns with finish_reason "cancelled" and the text so far). The reference cannot do this: after a 408 its
+        worker thread generates to the end while holding the semaphore (/root/reference/api.py:162-170)."""
+        if req.cancel_event is None:
+            req.cancel_event = threading.Event()
+        req.cancel_event.set()
+        with self.cv:
+            self.cv.notify_all()
+
     def drop_cache(self):
         """Forget cached prefixes (used by Llama.reset / direct eval)."""
         for s in self.slots:
@@ -133,10 +148,22 @@ class Scheduler:
                     return
                 admitted = []
                 n_free = sum(1 for s in self.slots if s.req is None)
-                while self.queue and len(admitted) < n_free:
-                    admitted.append(self.queue.popleft())
+                n_live = len(self.slots) - n_free
+                # prompts are interleaved with decode steps: a burst of arrivals does not stall the running sequences
+                # behind all of its prompt passes
+                limit = n_free if n_live == 0 else min(n_free, self.ADMIT_PER_STEP)
+                while self.queue and len(admitted) < limit:
+                    req = self.queue.popleft()
+                    if req.cancelled():
+                        self._cancelled(req)
+                        continue
+                    admitted.append(req)
                 waiting = len(self.queue)
             with self.engine.lock:
+                for s in self.slots:
+                    if s.req is not None and s.req.cancelled():
+                        self._cancelled(s.req)
+                        s.req = None
                 for req in admitted:
                     self._admit(req)
                 self._step(waiting)
@@ -149,6 +176,13 @@ class Scheduler:
             req.error = exc
             req.t_done = time.perf_counter()
             req.done.set()
+
+    def _cancelled(self, req: Request):
+        req.text = self.vocab.detokenize(req.completion_tokens)
+        req.finish_reason = "cancelled"
+        req.t_done = time.perf_counter()
+        self.stats["cancelled"] += 1
+        req.done.set()
 
     def _finish(self, slot: _Slot):
         req = slot.req
