@@ -108,6 +108,10 @@ struct b2_engine {
     int batch_min = 3;             // fewer sequences than this step one after another through the mat-vec path (measured: 3 slots 4.1 vs 6.3 ms)
     bool gemm_ok = false;          // every layer matrix is a block format the GEMM reads
     int prefill_min = 8;           // prompts chunks shorter than this go token by token through the mat-vec path
+    // GEMM launch plans (tile split, K splits, tensor maps) are built once per (first weight matrix, token count) and reused:
+    // re-planning -- cuTensorMapEncodeTiled and a handful of getenv per call -- for each of the 129 GEMMs of every batched
+    // step cost more host time than the step takes on the GPU
+    std::unordered_map<uint64_t, GemmParams> gemm_plans;
     std::mutex mu;
 };
 
@@ -633,17 +637,24 @@ static int ensure_prefill_workspace(b2_engine* e) {
 
 // One GEMM over up to three matrices that share the input; returns the number of K-split partial sums in pf_part.
 static int gemm_call(b2_engine* e, const DevTensor* const* ws, int nw, const __half* x, int T, int* n_parts, long* part_stride) {
-    GemmParams p = {};
-    p.nseg = nw; p.K = (int)ws[0]->ne0;
-    int off = 0;
-    for (int i = 0; i < nw; i++) {
-        p.seg[i].w = ws[i]->ptr; p.seg[i].type = ws[i]->type; p.seg[i].n_rows = (int)ws[i]->ne1; p.seg[i].out_off = off;
-        off += (int)ws[i]->ne1;
+    const uint64_t key = ((uint64_t)(uintptr_t)ws[0]->ptr << 10) ^ (uint64_t)T;     // the first matrix identifies the call site
+    auto it = e->gemm_plans.find(key);
+    if (it == e->gemm_plans.end()) {
+        GemmParams p = {};
+        p.nseg = nw; p.K = (int)ws[0]->ne0;
+        int off = 0;
+        for (int i = 0; i < nw; i++) {
+            p.seg[i].w = ws[i]->ptr; p.seg[i].type = ws[i]->type; p.seg[i].n_rows = (int)ws[i]->ne1; p.seg[i].out_off = off;
+            off += (int)ws[i]->ne1;
+        }
+        p.x = x; p.T = T; p.y = e->pf_part; p.ldy = off; p.split_stride = (long)T * off;
+        p.err = kernel_error_word();
+        const int max_splits = (int)std::min<size_t>(16, e->pf_part_floats / ((size_t)T * off));
+        if (gemm_plan(p, e->n_sms, max_splits)) return fail(B2_ERR_UNSUPPORTED, "GEMM shape not supported");
+        it = e->gemm_plans.emplace(key, p).first;
     }
-    p.x = x; p.T = T; p.y = e->pf_part; p.ldy = off; p.split_stride = (long)T * off;
-    p.err = kernel_error_word();
-    const int max_splits = (int)std::min<size_t>(16, e->pf_part_floats / ((size_t)T * off));
-    if (gemm_plan(p, e->n_sms, max_splits)) return fail(B2_ERR_UNSUPPORTED, "GEMM shape not supported");
+    GemmParams& p = it->second;
+    if (p.x != x || p.y != e->pf_part) return fail(B2_ERR_STATE, "GEMM plan cache: workspace moved");
     CK(gemm_launch(p, e->stream));
     e->launches++;
     *n_parts = p.n_splits; *part_stride = p.split_stride;
@@ -810,11 +821,16 @@ static int batch_step(b2_engine* e, const BatchIdx& b) {
     // x += last ffn_down; output norm; lm_head (one K range: the logits are complete rows); sample every sequence
     CK(resid_norm_half_launch(e->pf_x, e->pf_part, np, ps, (const float*)e->out_norm.ptr, c.rms_eps, E, T, T_pad, e->pf_xn, st));
     {
-        GemmParams p = {};
-        p.nseg = 1; p.K = E; p.seg[0].w = e->output.ptr; p.seg[0].type = e->output.type; p.seg[0].n_rows = c.n_vocab;
-        p.x = e->pf_xn; p.T = T; p.y = e->pf_part; p.ldy = c.n_vocab; p.split_stride = 0; p.err = kernel_error_word();
-        if (gemm_plan(p, e->n_sms, 1)) return fail(B2_ERR_UNSUPPORTED, "GEMM shape not supported");
-        CK(gemm_launch(p, st));
+        const uint64_t key = (((uint64_t)(uintptr_t)e->output.ptr << 10) ^ (uint64_t)T) + 1;    // + 1: not a gemm_call site (one K range)
+        auto it = e->gemm_plans.find(key);
+        if (it == e->gemm_plans.end()) {
+            GemmParams p = {};
+            p.nseg = 1; p.K = E; p.seg[0].w = e->output.ptr; p.seg[0].type = e->output.type; p.seg[0].n_rows = c.n_vocab;
+            p.x = e->pf_xn; p.T = T; p.y = e->pf_part; p.ldy = c.n_vocab; p.split_stride = 0; p.err = kernel_error_word();
+            if (gemm_plan(p, e->n_sms, 1)) return fail(B2_ERR_UNSUPPORTED, "GEMM shape not supported");
+            it = e->gemm_plans.emplace(key, p).first;
+        }
+        CK(gemm_launch(it->second, st));
     }
     CK(sample_batch_launch(e->pf_part, c.n_vocab, c.n_vocab, e->slot_tab, b, c.n_ctx + 1, e->bd_out, st));
     e->launches += 3;

@@ -38,6 +38,7 @@ class Request:
     cancel_event: Optional[threading.Event] = None       # set by the caller to abandon the request (e.g. after a 408)
     # results
     completion_tokens: List[int] = field(default_factory=list)
+    raw: bytearray = field(default_factory=bytearray)     # bytes of the completion so far (stop-string search window)
     text: bytes = b""
     finish_reason: Optional[str] = None
     error: Optional[BaseException] = None
@@ -66,7 +67,9 @@ class _Slot:
 
 
 def check_token(req: Request, vocab: Vocab, tok: int) -> bool:
-    """Account for one sampled token; returns True when the request is finished."""
+    """Account for one sampled token; returns True when the request is finished. The bytes generated so far are kept in
+    `req.raw` and only their tail is searched for stop strings: re-detokenising the whole completion for every token made
+    a batched step of 32 long sequences cost more on the host than on the GPU."""
     if vocab.is_eog(tok):
         req.text = vocab.detokenize(req.completion_tokens)
         req.finish_reason = "stop"
@@ -75,12 +78,17 @@ def check_token(req: Request, vocab: Vocab, tok: int) -> bool:
     if req.on_token is not None:
         req.on_token(tok)
     if req.stop:
-        all_text = vocab.detokenize(req.completion_tokens)
-        hits = [s for s in req.stop if s in all_text]
-        if hits:
-            req.text = all_text[:all_text.index(hits[0])]
-            req.finish_reason = "stop"
-            return True
+        piece = vocab.token_to_piece(tok, False) if vocab.model != "none" else b"<%d>" % tok
+        req.raw += piece
+        reach = len(piece) + max(len(s) for s in req.stop) - 1
+        tail = bytes(req.raw[-reach:]) if reach < len(req.raw) else bytes(req.raw)
+        if any(s in tail for s in req.stop):
+            all_text = vocab.detokenize(req.completion_tokens)
+            hits = [s for s in req.stop if s in all_text]
+            if hits:
+                req.text = all_text[:all_text.index(hits[0])]
+                req.finish_reason = "stop"
+                return True
     if len(req.completion_tokens) >= req.max_tokens:
         req.text = vocab.detokenize(req.completion_tokens)
         req.finish_reason = "length"

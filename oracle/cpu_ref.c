@@ -28,6 +28,9 @@
 #define CR_VNNI 0
 #endif
 static int g_simd = CR_VNNI;   /* cr_set_simd(0) forces the scalar loops (tests compare the two) */
+static int g_exact = 0;        /* cr_set_exact(1): float activations against dequantised weights, double accumulation: not what
+                                  the reference computes (it quantises activations to int8), but a sharp checker for deep models,
+                                  where the int8 noise of 100+ mat-vecs adds up to ~10% of the logit spread */
 
 enum { T_F32 = 0, T_F16 = 1, T_Q4_0 = 2, T_Q8_0 = 8, T_Q4_K = 12, T_Q5_K = 13, T_Q6_K = 14 };
 
@@ -93,33 +96,35 @@ static int blk_bytes(int t) {
     return 0;
 }
 
+/* dequantise one block (block_elems(type) values) */
+static void dequant_block(int type, const uint8_t* p, float* o) {
+    switch (type) {
+        case T_F32: memcpy(o, p, 4); break;
+        case T_F16: { uint16_t hh; memcpy(&hh, p, 2); o[0] = h2f(hh); } break;
+        case T_Q4_0: { uint16_t dh; memcpy(&dh, p, 2); float d = h2f(dh);
+            for (int j = 0; j < 16; j++) { o[j] = d * ((p[2 + j] & 15) - 8); o[16 + j] = d * ((p[2 + j] >> 4) - 8); } } break;
+        case T_Q8_0: { uint16_t dh; memcpy(&dh, p, 2); float d = h2f(dh);
+            for (int j = 0; j < 32; j++) o[j] = d * (int8_t)p[2 + j]; } break;
+        case T_Q4_K: case T_Q5_K: {
+            uint16_t dh, mh; memcpy(&dh, p, 2); memcpy(&mh, p + 2, 2); float d = h2f(dh), dm = h2f(mh);
+            const uint8_t* qs = p + (type == T_Q4_K ? 16 : 48);
+            for (int is = 0; is < 8; is++) { int sc, m; k_scale_min(p + 4, is, &sc, &m);
+                for (int l = 0; l < 32; l++) { int by = qs[(is >> 1) * 32 + l]; int q = (is & 1) ? by >> 4 : by & 15;
+                    if (type == T_Q5_K) q |= ((p[16 + l] >> is) & 1) << 4;
+                    o[is * 32 + l] = d * sc * q - dm * m; } } } break;
+        case T_Q6_K: { uint16_t dh; memcpy(&dh, p + 208, 2); float d = h2f(dh);
+            for (int e = 0; e < 256; e++) { int hf = e >> 7, ep = e & 127, nib = ep >> 6, kq = ep >> 5, l = ep & 31;
+                int lo = p[64 * hf + (ep & 63)]; lo = nib ? lo >> 4 : lo & 15;
+                int hi = (p[128 + 32 * hf + l] >> (2 * kq)) & 3;
+                o[e] = d * (int8_t)p[192 + (e >> 4)] * ((lo | (hi << 4)) - 32); } } break;
+    }
+}
+
 /* dequantise one row (embedding lookup) */
 static void dequant_row(const cr_tensor* t, int64_t row, float* out) {
     int K = (int)t->ne0, be = blk_elems(t->type), bb = blk_bytes(t->type);
     const uint8_t* r = t->data + row * (int64_t)(K / be * bb);
-    for (int b = 0; b < K / be; b++) {
-        const uint8_t* p = r + (size_t)b * bb; float* o = out + (size_t)b * be;
-        switch (t->type) {
-            case T_F32: memcpy(o, p, 4); break;
-            case T_F16: { uint16_t hh; memcpy(&hh, p, 2); o[0] = h2f(hh); } break;
-            case T_Q4_0: { uint16_t dh; memcpy(&dh, p, 2); float d = h2f(dh);
-                for (int j = 0; j < 16; j++) { o[j] = d * ((p[2 + j] & 15) - 8); o[16 + j] = d * ((p[2 + j] >> 4) - 8); } } break;
-            case T_Q8_0: { uint16_t dh; memcpy(&dh, p, 2); float d = h2f(dh);
-                for (int j = 0; j < 32; j++) o[j] = d * (int8_t)p[2 + j]; } break;
-            case T_Q4_K: case T_Q5_K: {
-                uint16_t dh, mh; memcpy(&dh, p, 2); memcpy(&mh, p + 2, 2); float d = h2f(dh), dm = h2f(mh);
-                const uint8_t* qs = p + (t->type == T_Q4_K ? 16 : 48);
-                for (int is = 0; is < 8; is++) { int sc, m; k_scale_min(p + 4, is, &sc, &m);
-                    for (int l = 0; l < 32; l++) { int by = qs[(is >> 1) * 32 + l]; int q = (is & 1) ? by >> 4 : by & 15;
-                        if (t->type == T_Q5_K) q |= ((p[16 + l] >> is) & 1) << 4;
-                        o[is * 32 + l] = d * sc * q - dm * m; } } } break;
-            case T_Q6_K: { uint16_t dh; memcpy(&dh, p + 208, 2); float d = h2f(dh);
-                for (int e = 0; e < 256; e++) { int hf = e >> 7, ep = e & 127, nib = ep >> 6, kq = ep >> 5, l = ep & 31;
-                    int lo = p[64 * hf + (ep & 63)]; lo = nib ? lo >> 4 : lo & 15;
-                    int hi = (p[128 + 32 * hf + l] >> (2 * kq)) & 3;
-                    o[e] = d * (int8_t)p[192 + (e >> 4)] * ((lo | (hi << 4)) - 32); } } break;
-        }
-    }
+    for (int b = 0; b < K / be; b++) dequant_block(t->type, r + (size_t)b * bb, out + (size_t)b * be);
 }
 
 /* ggml quantize_row_q8_0: blocks of 32, d = amax/127 */
@@ -207,9 +212,21 @@ static inline int dot_q6_K_vnni(const uint8_t* p, const int8_t* a) {
 #endif
 
 /* y[n] = W[n,:] . x  with x pre-quantised; rows split across OpenMP threads */
-static void matvec(const cr_tensor* w, const int8_t* q8, const float* q8d, const int16_t* q8s, float* y) {
+static void matvec(const cr_tensor* w, const int8_t* q8, const float* q8d, const int16_t* q8s, const float* xf, float* y) {
     const int K = (int)w->ne0, N = (int)w->ne1, t = w->type;
     const int64_t rb = (int64_t)K / blk_elems(t) * blk_bytes(t);
+    if (g_exact) {
+        const int be = blk_elems(t), bb = blk_bytes(t);
+#pragma omp parallel for schedule(static)
+        for (int n = 0; n < N; n++) {
+            const uint8_t* r = w->data + n * rb; double acc = 0; float tmp[256];
+            for (int b = 0; b < K / be; b++) { dequant_block(t, r + (size_t)b * bb, tmp);
+                double s = 0; for (int i = 0; i < be; i++) s += (double)tmp[i] * xf[b * be + i];
+                acc += s; }
+            y[n] = (float)acc;
+        }
+        return;
+    }
 #pragma omp parallel for schedule(static)
     for (int n = 0; n < N; n++) {
         const uint8_t* r = w->data + n * rb; float acc = 0.f;
@@ -323,6 +340,7 @@ void cr_set_threads(int n) {
 }
 int cr_simd(void) { return g_simd; }          /* 1: AVX-512 VNNI integer dots, 0: scalar loops */
 int cr_has_vnni(void) { return CR_VNNI; }
+void cr_set_exact(int on) { g_exact = on; }   /* 1: float activations x dequantised weights (checker mode, not the timed baseline) */
 void cr_set_simd(int on) { g_simd = on && CR_VNNI; }
 int cr_threads(void) {
 #ifdef _OPENMP
@@ -342,11 +360,11 @@ const float* cr_eval(cr_ctx* c, int token, int want_logits) {
     for (int l = 0; l < m->n_layer; l++) {
         const cr_tensor* T = m->layers + 9 * (size_t)l;
         rmsnorm(c->x, &T[0], m->rms_eps, d, c->h);
-        quantize_for(&T[1], c->h, c); matvec(&T[1], c->q8, c->q8d, c->q8s, c->q);
+        quantize_for(&T[1], c->h, c); matvec(&T[1], c->q8, c->q8d, c->q8s, c->h, c->q);
         if (T[2].type != T[1].type) quantize_for(&T[2], c->h, c);
-        matvec(&T[2], c->q8, c->q8d, c->q8s, c->kk);
+        matvec(&T[2], c->q8, c->q8d, c->q8s, c->h, c->kk);
         if (T[3].type != T[2].type) quantize_for(&T[3], c->h, c);
-        matvec(&T[3], c->q8, c->q8d, c->q8s, c->vv);
+        matvec(&T[3], c->q8, c->q8d, c->q8s, c->h, c->vv);
         rope(c->q, m->n_head, hd, pos, c->freq); rope(c->kk, m->n_head_kv, hd, pos, c->freq);
         uint16_t* kc = c->k + ((size_t)l * m->n_ctx + pos) * kvd; uint16_t* vc = c->v + ((size_t)l * m->n_ctx + pos) * kvd;
         for (int i = 0; i < kvd; i++) { kc[i] = f2h(c->kk[i]); vc[i] = f2h(c->vv[i]); }
@@ -362,19 +380,19 @@ const float* cr_eval(cr_ctx* c, int token, int want_logits) {
             for (int t = 0; t <= pos; t++) { const uint16_t* vr = c->v + ((size_t)l * m->n_ctx + t) * kvd + kh * hd; float p = s[t] / sum;
                 for (int i = 0; i < hd; i++) o[i] += p * h2f(vr[i]); }
         }
-        quantize_for(&T[4], c->att, c); matvec(&T[4], c->q8, c->q8d, c->q8s, c->h);
+        quantize_for(&T[4], c->att, c); matvec(&T[4], c->q8, c->q8d, c->q8s, c->att, c->h);
         for (int i = 0; i < d; i++) c->x[i] += c->h[i];
         rmsnorm(c->x, &T[5], m->rms_eps, d, c->h);
-        quantize_for(&T[6], c->h, c); matvec(&T[6], c->q8, c->q8d, c->q8s, c->g);
+        quantize_for(&T[6], c->h, c); matvec(&T[6], c->q8, c->q8d, c->q8s, c->h, c->g);
         if (T[7].type != T[6].type) quantize_for(&T[7], c->h, c);
-        matvec(&T[7], c->q8, c->q8d, c->q8s, c->u);
+        matvec(&T[7], c->q8, c->q8d, c->q8s, c->h, c->u);
         for (int i = 0; i < m->n_ff; i++) c->g[i] = c->g[i] / (1.0f + expf(-c->g[i])) * c->u[i];
-        quantize_for(&T[8], c->g, c); matvec(&T[8], c->q8, c->q8d, c->q8s, c->h);
+        quantize_for(&T[8], c->g, c); matvec(&T[8], c->q8, c->q8d, c->q8s, c->g, c->h);
         for (int i = 0; i < d; i++) c->x[i] += c->h[i];
     }
     c->n_past++;
     if (!want_logits) return c->logits;
     rmsnorm(c->x, &m->out_norm, m->rms_eps, d, c->h);
-    quantize_for(&m->output, c->h, c); matvec(&m->output, c->q8, c->q8d, c->q8s, c->logits);
+    quantize_for(&m->output, c->h, c); matvec(&m->output, c->q8, c->q8d, c->q8s, c->h, c->logits);
     return c->logits;
 }

@@ -54,6 +54,7 @@ class CpuRef:
         self.lib.cr_threads.restype = c_int
         self.lib.cr_set_threads.argtypes = [c_int]
         self.lib.cr_set_simd.argtypes = [c_int]
+        self.lib.cr_set_exact.argtypes = [c_int]
         self.lib.cr_simd.restype = c_int
         if n_threads:
             self.lib.cr_set_threads(int(n_threads))
@@ -94,6 +95,11 @@ class CpuRef:
 
     def set_simd(self, on: bool):
         self.lib.cr_set_simd(1 if on else 0)
+
+    def set_exact(self, on: bool):
+        """Checker mode: float activations against dequantised weights with double accumulation (no int8 activation noise).
+        Process-wide, like set_simd."""
+        self.lib.cr_set_exact(1 if on else 0)
 
     def reset(self):
         self.lib.cr_reset(self.ctx)

@@ -45,3 +45,24 @@ def test_vnni_dots_equal_the_scalar_loops(tmp_models, arch, ftype, seed):
     c.set_simd(True)
     c.close()
     assert np.array_equal(out[True].view(np.uint32), out[False].view(np.uint32))
+
+
+def test_exact_mode_matches_the_float_oracle_tightly(tmp_models):
+    """cr_set_exact: the same graph with float activations -- the checker bench.py uses on the 32-layer benchmark model,
+    where the int8-activation noise of the timed mode is ~10% of the logit spread. Here: 1e-3 of the logit std."""
+    from llama_cpp import synth
+    from oracle.cpu_ref import CpuRef
+    from oracle.llama_ref import RefModel
+    path = os.path.join(tmp_models, "cr_exact.gguf")
+    synth.write_synthetic_model(path, "tiny", "Q4_K_M", seed=1, output_std=0.1)
+    toks = np.random.default_rng(0).integers(0, 700, size=8)
+    ref = RefModel(path).forward(toks)
+    c = CpuRef(path, 64)
+    c.set_exact(True)
+    try:
+        for i, t in enumerate(toks):
+            lg = c.eval(int(t))
+            assert np.abs(lg - ref[i]).max() < 2e-3 * ref[i].std(), i
+    finally:
+        c.set_exact(False)
+        c.close()
