@@ -308,230 +308,6 @@ def parity_check(eng, path, n_vocab, n_prompt=6, n_new=6, seed=5):
     return out
 
 
-def http_burst(path, batch, rank, barrier, n_ctx=1024, port0=18200):
-    """`batch` concurrent POST /response against an in-process uvicorn server (llama_cpp.server) that fronts one engine
-    replica on this rank's GPU. Returns generated tokens, wall time of the burst and what the scheduler saw."""
-    import asyncio
-    import aiohttp
-    import numpy as np
-    import uvicorn
-    from llama_cpp import Llama, server
-    llm = Llama(model_path=path, n_gpu_layers=-1, n_ctx=n_ctx, seed=1, verbose=False, n_seq_max=batch)
-    app = server.create_app([llm], max_queue_size=2 * batch, permits=batch, consumers=batch, timeout_seconds=600.0,
-                            max_context_tokens=n_ctx)
-    port = port0 + rank
-    srv = uvicorn.Server(uvicorn.Config(app, host="127.0.0.1", port=port, log_level="warning"))
-    th = threading.Thread(target=srv.run, daemon=True)
-    th.start()
-    for _ in range(200):
-        if srv.started:
-            break
-        time.sleep(0.05)
-    rng = np.random.default_rng(7 + rank)
-    words = ["time", "river", "blue", "seven", "music", "open", "garden", "light", "story", "window", "coffee", "travel"]
-
-    def body(i):
-        ctx = [{"turn": "user" if j % 2 == 0 else "bot", "message": " ".join(rng.choice(words, size=12))} for j in range(7)]
-        return {"bot_profile": {"name": f"Ann{i}.f", "appearance": "a,b,c,tall,green eyes", "system_prompt": ""},
-                "user_profile": {"name": "u"}, "context": ctx}
-
-    async def burst(bodies):
-        async with aiohttp.ClientSession(timeout=aiohttp.ClientTimeout(total=900)) as sess:
-            async def one(bd):
-                async with sess.post(f"http://127.0.0.1:{port}/response", json=bd) as r:
-                    return r.status, len((await r.json()).get("response", "")) if r.status == 200 else 0
-            return await asyncio.gather(*[one(bd) for bd in bodies])
-
-    asyncio.run(burst([body(-1)]))                        # warm the path (graphs, workspace)
-    st0 = dict(llm._scheduler.stats)
-    bodies = [body(i) for i in range(batch)]
-    req_bytes = sum(len(json.dumps(bd)) for bd in bodies)
-    barrier()
-    t0 = time.perf_counter()
-    res = asyncio.run(burst(bodies))
-    wall = time.perf_counter() - t0
-    barrier()
-    st = llm._scheduler.stats
-    n_gen = st["tokens"] - st0["tokens"] + batch          # + the first token of every request (sampled at admission)
-    n_prompt_tok = st["prefill_tokens"] - st0["prefill_tokens"] + st["reused_tokens"] - st0["reused_tokens"]
-    steps = max(1, st["steps"] - st0["steps"])
-    out = {"value": n_gen / wall, "unit": "tok/s", "h2d_bytes_per_step": round(4.0 * n_prompt_tok / steps, 1),
-           "d2h_bytes_per_step": round(4.0 * n_gen / steps, 1), "tokens": int(n_gen), "wall_s": wall,
-           "http_status": sorted(set(c for c, _ in res)), "requests": batch, "request_bytes": req_bytes,
-           "response_chars": int(sum(n for _, n in res)), "prompt_tokens": int(n_prompt_tok), "max_batch": st["max_batch"],
-           "note": f"{batch} concurrent POST /response (chat bodies, the reference's sampling settings, generation to the "
-                   f"{n_ctx}-token window) against llama_cpp.server over a loopback socket with permits = consumers = {batch}; "
-                   "generated tokens / wall time of the burst: JSON parsing, prompt assembly, tokenisation, prompt passes, "
-                   "batched decode steps, detokenisation and the HTTP responses are all inside"}
-    srv.should_exit = True
-    th.join(timeout=10)
-    llm.close()
-    return out
-
-
-def model_path(arch, ftype, seed=1):
-    base = "/dev/shm" if os.path.isdir("/dev/shm") else "/tmp"
-    return os.path.join(base, "b200_gguf_models", f"{arch}-{ftype}-seed{seed}.gguf")
-
-
-def ensure_model(arch, ftype, seed=1):
-    from llama_cpp import synth
-    path = model_path(arch, ftype, seed)
-    if not os.path.exists(path):
-        synth.write_synthetic_model(path, arch, ftype, seed=seed, output_std=0.1, with_vocab=True)
-    return path
-
-
-def algorithmic_bytes(gguf, ctx_mean):
-    """W_read (all tensors but token_embd, plus one embedding row) + ctx * KV bytes."""
-    md = gguf.metadata
-    total = sum(t.nbytes for t in gguf.tensors.values())
-    emb = gguf.tensors["token_embd.weight"]
-    w_read = total - emb.nbytes + emb.nbytes // emb.shape[1]
-    n_head = int(md["llama.attention.head_count"])
-    kv = int(md.get("llama.attention.head_count_kv", n_head))
-    hd = int(md["llama.embedding_length"]) // n_head
-    kv_pos = int(md["llama.block_count"]) * 2 * kv * hd * 2
-    return w_read, kv_pos, w_read + ctx_mean * kv_pos
-
-
-class ClockSampler(threading.Thread):
-    """Samples SM clock and throttle reasons of one GPU through NVML while the timed region runs."""
-
-    def __init__(self, index):
-        super().__init__(daemon=True)
-        self.index, self.samples, self.reasons, self.stop_flag, self.max_mhz = index, [], set(), False, None
-        try:
-            import pynvml
-            pynvml.nvmlInit()
-            self.nv = pynvml
-            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
-            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
-        except Exception:
-            self.nv = None
-
-    def run(self):
-        if self.nv is None:
-            return
-        nv = self.nv
-        names = {"hw_slowdown": nv.nvmlClocksThrottleReasonHwSlowdown,
-                 "hw_thermal_slowdown": nv.nvmlClocksThrottleReasonHwThermalSlowdown,
-                 "sw_thermal_slowdown": nv.nvmlClocksThrottleReasonSwThermalSlowdown,
-                 "sw_power_cap": nv.nvmlClocksThrottleReasonSwPowerCap}
-        while not self.stop_flag:
-            try:
-                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
-                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
-                for k, bit in names.items():
-                    if r & bit:
-                        self.reasons.add(k)
-            except Exception:
-                pass
-            time.sleep(0.01)
-
-    def result(self):
-        self.stop_flag = True
-        self.join(timeout=2)
-        s = sorted(self.samples)
-        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
-                "samples": len(s)}
-
-
-def measured_peak_gbs():
-    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
-    try:
-        with open(p) as f:
-            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
-    except Exception:
-        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
-
-
-def ncu_traffic_bytes(workload):
-    """dram read+write bytes per decode step from the committed ncu capture of THIS workload, else None (a figure
-    captured on another model says nothing about this one)."""
-    try:
-        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            t = json.load(f)
-        return t.get("dram_bytes_per_step") if t.get("workload") == workload else None
-    except Exception:
-        return None
-
-
-def cpu_reference_run(path, n_warm, n_steps, budget_s, prompt_len=16):
-    """Time the CPU restatement of the reference's llama.cpp CPU path: decode tokens one at a time."""
-    # torchrun exports OMP_NUM_THREADS=1 to its workers and the OpenMP runtime may already be up (torch): the thread count
-    # is set through the library's own entry point. The CPU arm is meant to use every host core it can.
-    n_threads = int(os.environ.get("B2_CPU_THREADS", "0")) or (len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else os.cpu_count())
-    from oracle.cpu_ref import CpuRef
-    import numpy as np
-    c = CpuRef(path, n_ctx=prompt_len + n_warm + n_steps + 8, n_threads=n_threads)
-    rng = np.random.default_rng(0)
-    toks = rng.integers(0, c.n_vocab, size=prompt_len + n_warm + n_steps)
-    t0 = time.perf_counter()
-    c.eval(int(toks[0]))
-    first = time.perf_counter() - t0
-    for t in toks[1:prompt_len]:
-        c.eval(int(t), want_logits=False)
-    per = max(first, 1e-4)
-    n_warm = max(0, min(n_warm, int(0.2 * budget_s / per)))
-    n_steps = max(1, min(n_steps, int(0.8 * budget_s / per)))
-    i = prompt_len
-    for _ in range(n_warm):
-        c.eval(int(toks[i])); i += 1
-    t0 = time.perf_counter()
-    for _ in range(n_steps):
-        c.eval(int(toks[i])); i += 1
-    dt = time.perf_counter() - t0
-    threads, simd = c.threads, c.simd
-    c.close()
-    return dict(value=n_steps / dt, ms_per_step=dt / n_steps * 1e3, steps=n_steps, warmup=n_warm, cores=threads,
-                sample=f"{n_steps} single-token decode steps (all layers + lm_head) after a {prompt_len}-token context, "
-                       f"{simd} integer dots on {threads} OpenMP threads; KV reads are <2% of the bytes at the workload's "
-                       f"context, weights are streamed in full")
-
-
-def parity_check(eng, path, n_vocab, n_prompt=6, n_new=8, seed=5):
-    """Run a short greedy generation on the TIMED engine instance (same weights in HBM, same CUDA graphs) and teacher-force
-    the C restatement of the reference's CPU path (oracle/cpu_ref.c, int8 activations) over the same tokens: the whole
-    32-layer graph at the benchmark geometry, checked in the benchmark process. Raises if it is off."""
-    import numpy as np
-    from llama_cpp.engine import SamplingSettings
-    from oracle.cpu_ref import CpuRef
-    rng = np.random.default_rng(seed)
-    prompt = [int(t) for t in rng.integers(0, n_vocab, size=n_prompt)]
-    slot = 0
-    with eng.lock:
-        eng.pages.release(slot)
-        eng.ensure_pages(slot, n_prompt + n_new + 2)
-        eng.seq_begin(slot, 0, [], SamplingSettings(temperature=0.0, repeat_penalty=1.0))
-        eng.prefill(slot, prompt)                 # < 8 tokens: through the mat-vec kernels, like the timed decode steps
-        gpu_logits, toks = [eng.logits(slot)], [eng.sample(slot)]
-        for _ in range(n_new - 1):
-            toks.append(eng.decode([slot])[0])
-            gpu_logits.append(eng.logits(slot))
-    c = CpuRef(path, n_ctx=n_prompt + n_new + 4, n_threads=len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else 0)
-    for t in prompt[:-1]:
-        c.eval(t, want_logits=False)
-    seq = [prompt[-1]] + toks[:-1]
-    worst, agree, clear, std = 0.0, 0, 0, 0.0
-    for t, g in zip(seq, gpu_logits):
-        r = c.eval(int(t))
-        worst = max(worst, float(np.abs(g - r).max()))
-        std = max(std, float(r.std()))
-        top2 = np.partition(r, -2)[-2:]
-        if top2[1] - top2[0] > 0.2 * r.std():     # a clear margin for int8-activation noise
-            clear += 1
-            agree += int(np.argmax(r) == np.argmax(g))
-    c.close()
-    ok = worst < 0.05 * std * 4 + 0.05 and agree == clear      # the bar of tests/test_cpu_ref.py (int8 activations)
-    out = {"max_abs_logit_diff": round(worst, 4), "logit_std": round(std, 3), "argmax_agree": f"{agree}/{clear}", "steps": n_new,
-           "against": "oracle/cpu_ref.c (int8-activation restatement of the reference CPU path), teacher-forced on the engine's tokens",
-           "ok": bool(ok)}
-    if not ok:
-        raise RuntimeError(f"parity check failed: {out}")
-    return out
-
-
 def batch_workload(args, cfg, path, n_prompt, batch, rank, world, local_rank, barrier, torch, dist):
     """Continuous-batching configs: `batch` sequences decode together, one weight pass per step (tensor-core GEMM path)."""
     import numpy as np
