@@ -111,6 +111,7 @@ def http_burst(path, batch, rank, barrier, n_ctx=1024, port0=18200):
 
     asyncio.run(burst([body(-1)]))                        # warm the path (graphs, workspace)
     st0 = dict(llm._scheduler.stats)
+    llm._scheduler.stats["first_submit"] = 0.0
     bodies = [body(i) for i in range(batch)]
     req_bytes = sum(len(json.dumps(bd)) for bd in bodies)
     barrier()
@@ -126,6 +127,9 @@ def http_burst(path, batch, rank, barrier, n_ctx=1024, port0=18200):
            "d2h_bytes_per_step": round(4.0 * n_gen / steps, 1), "tokens": int(n_gen), "wall_s": wall,
            "http_status": sorted(set(c for c, _ in res)), "requests": batch, "request_bytes": req_bytes,
            "response_chars": int(sum(n for _, n in res)), "prompt_tokens": int(n_prompt_tok), "max_batch": st["max_batch"],
+           "scheduler_s": {k: round(st[k] - st0[k], 3) for k in ("t_admit", "t_decode", "t_host")}, "decode_steps": int(steps),
+           "timeline_s": {"first_submit": round(st["first_submit"] - t0, 3), "last_submit": round(st["last_submit"] - t0, 3),
+                          "last_done": round(st["last_done"] - t0, 3)},
            "note": f"{batch} concurrent POST /response (chat bodies, the reference's sampling settings, generation to the "
                    f"{n_ctx}-token window) against llama_cpp.server over a loopback socket with permits = consumers = {batch}; "
                    "generated tokens / wall time of the burst: JSON parsing, prompt assembly, tokenisation, prompt passes, "

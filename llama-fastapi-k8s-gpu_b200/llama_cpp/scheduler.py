@@ -108,11 +108,15 @@ class Scheduler:
         self.cv = threading.Condition()
         self.thread: Optional[threading.Thread] = None
         self.stopping = False
-        self.stats = dict(steps=0, tokens=0, max_batch=0, prefill_tokens=0, reused_tokens=0, cancelled=0)
+        self.stats = dict(steps=0, tokens=0, max_batch=0, prefill_tokens=0, reused_tokens=0, cancelled=0,
+                          t_admit=0.0, t_decode=0.0, t_host=0.0)     # seconds in prompt passes / engine decode calls / host bookkeeping
 
     # ------------------------------------------------------------------ public
     def submit(self, req: Request) -> Request:
         req.t_submit = time.perf_counter()
+        self.stats["last_submit"] = req.t_submit
+        if not self.stats.get("first_submit"):
+            self.stats["first_submit"] = req.t_submit
         with self.cv:
             if self.stopping:
                 raise RuntimeError("engine is shut down")
@@ -168,13 +172,18 @@ class Scheduler:
                     admitted.append(req)
                 waiting = len(self.queue)
             with self.engine.lock:
+                t0 = time.perf_counter()
                 for s in self.slots:
                     if s.req is not None and s.req.cancelled():
                         self._cancelled(s.req)
                         s.req = None
                 for req in admitted:
                     self._admit(req)
+                t1 = time.perf_counter()
+                d0 = self.stats["t_decode"]
                 self._step(waiting)
+                self.stats["t_admit"] += t1 - t0
+                self.stats["t_host"] += (time.perf_counter() - t1) - (self.stats["t_decode"] - d0)
 
     def _fail(self, slot: _Slot, exc: BaseException):
         req = slot.req
@@ -196,6 +205,7 @@ class Scheduler:
         req = slot.req
         slot.req = None
         req.t_done = time.perf_counter()
+        self.stats["last_done"] = req.t_done
         req.done.set()
 
     def _admit(self, req: Request):
@@ -242,7 +252,9 @@ class Scheduler:
                 room = eng.n_ctx - len(s.cached)
                 n = max(1, min(self.RUN_AHEAD, req.max_tokens - len(req.completion_tokens), room))
                 base = list(s.cached)
+                td = time.perf_counter()
                 toks = eng.decode_n(s.idx, n)
+                self.stats["t_decode"] += time.perf_counter() - td
                 self.stats["steps"] += n
                 forwarded = [s.pending] + toks[:-1]          # tokens whose K/V were just written
                 for i, t in enumerate(toks):
@@ -257,7 +269,9 @@ class Scheduler:
                 s.cached = base
                 s.pending = toks[-1]
             else:
+                td = time.perf_counter()
                 toks = eng.decode([s.idx for s in live])
+                self.stats["t_decode"] += time.perf_counter() - td
                 self.stats["steps"] += 1
                 for s, t in zip(live, toks):
                     s.cached.append(s.pending)

@@ -257,7 +257,9 @@ def synth_bpe_vocab(n_vocab: int):
             types.append(3)  # CONTROL
         else:
             tokens.append(f"<|reserved_{i}|>")
-            types.append(4)  # USER_DEFINED-like filler; never produced by BPE of plain text
+            types.append(1)  # NORMAL filler (renders as its text, never produced by BPE of plain text: no merge builds it).
+            # Not USER_DEFINED: special-token parsing scans for every CONTROL / USER_DEFINED entry, and 127k of them is
+            # nothing like a real Llama-3 vocabulary (256 control tokens)
     inv = {s: i for i, s in specials.items()}
     meta = {
         "tokenizer.ggml.model": "gpt2",

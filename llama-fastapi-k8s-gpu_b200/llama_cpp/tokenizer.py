@@ -71,8 +71,8 @@ class Vocab:
                     self.eot_id = self.token_to_id[name]
                     break
         ab = md.get("tokenizer.ggml.add_bos_token")
-        # llama.cpp: SPM adds BOS unless told not to; BPE only when the file says so
-        self.add_bos = bool(ab) if ab is not None else (self.model == "llama")
+        # llama.cpp of the pinned vintage adds BOS unless the file says `add_bos_token = false`, for SPM and BPE vocabularies alike
+        self.add_bos = bool(ab) if ab is not None else (self.bos_id >= 0)
         self.add_eos = bool(md.get("tokenizer.ggml.add_eos_token", False))
         self.add_space_prefix = bool(md.get("tokenizer.ggml.add_space_prefix", True))
         self.pre = md.get("tokenizer.ggml.pre", "default")
@@ -91,28 +91,26 @@ class Vocab:
                 if i is not None:
                     self.byte_tokens[b] = i
         self._pre_re = None
+        self._special_re = None
+        self._bpe_cache: Dict[str, Tuple[int, ...]] = {}      # pre-token -> ids (chat prompts repeat their words)
+        # llama-bpe vocabularies set ignore_merges: a pre-token that is itself in the vocabulary is one token, whatever the merges say
+        self.ignore_merges = self.pre in ("llama-bpe", "llama3", "llama-v3")
 
     # ------------------------------------------------------------------ encode
     def is_eog(self, tok: int) -> bool:
         return tok >= 0 and tok in (self.eos_id, self.eot_id)
 
     def _split_special(self, text: bytes) -> List[Tuple[bool, bytes]]:
-        """[(is_special, fragment)], longest special tokens first (llama.cpp tokenizer_st_partition)."""
-        frags: List[Tuple[bool, bytes]] = [(False, text)]
-        for sp in self._special_sorted:
-            out: List[Tuple[bool, bytes]] = []
-            for is_sp, frag in frags:
-                if is_sp or sp not in frag:
-                    out.append((is_sp, frag))
-                    continue
-                parts = frag.split(sp)
-                for j, part in enumerate(parts):
-                    if part:
-                        out.append((False, part))
-                    if j + 1 < len(parts):
-                        out.append((True, sp))
-            frags = out
-        return frags
+        """[(is_special, fragment)], longest special tokens first (llama.cpp tokenizer_st_partition). One compiled
+        alternation instead of a pass over the text per special token: a Llama-3 vocabulary has hundreds of them and
+        the per-token passes cost a second per chat prompt."""
+        if not self._special_sorted:
+            return [(False, text)]
+        if self._special_re is None:
+            import re
+            self._special_re = re.compile(b"(" + b"|".join(re.escape(sp) for sp in self._special_sorted) + b")")
+        parts = self._special_re.split(text)
+        return [(i % 2 == 1, part) for i, part in enumerate(parts) if part]
 
     def tokenize(self, text: bytes, add_bos: bool = True, special: bool = False) -> List[int]:
         if self.model == "none":
@@ -191,8 +189,19 @@ class Vocab:
             import regex
             self._pre_re = regex.compile(LLAMA3_PRE_REGEX if self.pre in ("llama-bpe", "llama3", "llama-v3") else GPT2_PRE_REGEX)
         out: List[int] = []
+        cache = self._bpe_cache
         for word in self._pre_re.findall(text):
+            hit = cache.get(word)
+            if hit is not None:
+                out.extend(hit)
+                continue
+            n0 = len(out)
             syms = [_BYTE_ENC[b] for b in word.encode("utf-8")]
+            if self.ignore_merges:
+                whole = self.token_to_id.get("".join(syms).encode("utf-8"))
+                if whole is not None:
+                    syms = []
+                    out.append(whole)
             while len(syms) > 1:
                 best, bi = None, -1
                 for i in range(len(syms) - 1):
@@ -211,6 +220,8 @@ class Vocab:
                         t2 = self.token_to_id.get(ch.encode("utf-8"))
                         if t2 is not None:
                             out.append(t2)
+            if len(cache) < 200000:
+                cache[word] = tuple(out[n0:])
         return out
 
     # ------------------------------------------------------------------ decode

@@ -58,7 +58,11 @@ def test_bpe_tokenizer_round_trip_and_specials(tiny_path):
     plain = v.tokenize(b"<|eot_id|>", add_bos=False, special=False)   # not parsed: plain text
     assert v.eot_id not in plain and v.detokenize(plain) == b"<|eot_id|>"
     assert v.is_eog(v.eot_id) and v.is_eog(v.eos_id) and not v.is_eog(5)
-    assert v.tokenize(b"", add_bos=True) == []                       # BPE adds BOS only when the file says so
+    assert v.tokenize(b"", add_bos=True) == [v.bos_id]               # like upstream: BOS unless the file says add_bos_token = false
+    # ignore_merges (llama-bpe): a pre-token that is itself in the vocabulary is emitted whole
+    whole = next(t for t in v.tokens[300:500] if t.startswith(b"\xc4\xa0") and len(t) > 4)   # "Ġword" entries of the synthetic vocabulary
+    word = whole.decode().replace("\u0120", " ")
+    assert v.tokenize(word.encode(), add_bos=False) == [v.token_to_id[whole]]
 
 
 @settings(max_examples=60, deadline=None)
