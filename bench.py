@@ -36,6 +36,8 @@ WORKLOADS = {
     "llama3-8b-q8_0-bs32": ("llama-3-8b", "Q8_0", 512, 32),
     "llama3-8b-q4_k_m-bs32": ("llama-3-8b", "Q4_K_M", 512, 32),
     "mistral-7b-q4_k_m-8k": ("mistral-7b", "Q4_K_M", 8192 - 512, 1),
+    "llama3-70b-q4_k_m-tp": ("llama-3-70b", "Q4_K_M", 128, 1),       # configs[4]: tensor parallel over all ranks (N = 1: one GPU)
+    "tiny-q4_k_m-tp": ("tiny", "Q4_K_M", 32, 1),
     "tiny-q4_k_m": ("tiny", "Q4_K_M", 32, 1),
     "tiny-q4_k_m-bs8": ("tiny", "Q4_K_M", 32, 8),
 }
@@ -312,6 +314,105 @@ def parity_check(eng, path, n_vocab, n_prompt=6, n_new=6, seed=5):
     return out
 
 
+def tp_workload(args, cfg, path, n_prompt, rank, world, local_rank, barrier, torch, dist):
+    """BASELINE.json configs[4]: ONE model sharded over all ranks (column / row splits of the quantised weights, NCCL
+    all-reduce after attn_output and ffn_down, all-gather of the logits); batch-1 greedy decode. Strong scaling: the work
+    is one sequence whatever N is. N = 1 runs the whole model on one GPU (the 70B Q4_K_M file is 42.5 GB)."""
+    import numpy as np
+    from llama_cpp import Llama, replicas
+    from llama_cpp.engine import Engine, SamplingSettings
+    from llama_cpp.gguf_file import GGUFFile
+    K, W = args.steps, args.warmup
+    tp = None
+    if world > 1:
+        ids = [Engine.tp_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ids, src=0)
+        tp = (rank, world, ids[0])
+    n_ctx = n_prompt + W + 2 * K + 32
+    t_load = time.perf_counter()
+    llm = Llama(model_path=path, n_gpu_layers=-1, n_ctx=n_ctx, seed=1, verbose=False, tp=tp)
+    t_load = time.perf_counter() - t_load
+    eng = llm._engine
+    V = eng.dims.n_vocab
+    prompt = [int(t) for t in np.random.default_rng(123).integers(0, V, size=n_prompt)]      # the same on every rank
+    greedy = SamplingSettings(temperature=0.0, repeat_penalty=1.0)
+    with eng.lock:
+        eng.ensure_pages(0, n_ctx)
+        eng.seq_begin(0, 0, [], greedy)
+        t0 = time.perf_counter()
+        eng.prefill(0, prompt)
+        prefill_ms = (time.perf_counter() - t0) * 1e3
+        first = eng.sample(0)
+        warm = eng.decode_n(0, W)
+        clocks = ClockSampler(local_rank)
+        clocks.start()
+        launches0 = eng.launch_count()
+        barrier()
+        eng.timer_start()
+        toks = eng.decode_n(0, K)
+        ms = eng.timer_stop()
+        barrier()
+        launches = eng.launch_count() - launches0
+        clk = clocks.result()
+        kinds = eng.profile_decode_step(0)
+        mode = eng.mode()
+    ms_max = replicas.dist_max([ms])[0]
+    if world > 1:       # every rank must have produced the same tokens
+        allt = [None] * world
+        dist.all_gather_object(allt, [first] + warm + toks)
+        if any(t != allt[0] for t in allt):
+            raise RuntimeError("tensor-parallel ranks disagree on the generated tokens")
+    value = K / (ms_max / 1e3)
+    # end to end through the public API: host ids in, text out, every rank makes the same call
+    llm.reset()
+    barrier()
+    t0 = time.perf_counter()
+    out = llm.create_completion(prompt, max_tokens=K, temperature=0.0, repeat_penalty=1.0)
+    wall = replicas.dist_max([time.perf_counter() - t0])[0]
+    barrier()
+    n_gen = out["usage"]["completion_tokens"]
+    e2e = {"value": n_gen / wall, "unit": "tok/s", "h2d_bytes_per_step": round(4 * n_prompt / max(n_gen, 1), 2), "d2h_bytes_per_step": 4,
+           "tokens": n_gen, "wall_s": wall, "ttft_ms": llm.last_timings["ttft_ms"],
+           "note": "whole Llama.create_completion(token ids, max_tokens=K, temperature=0) call on every rank at once (prompt token "
+                   "by token through the mat-vec path in tensor-parallel mode), host-timed, max over ranks"}
+    if rank != 0:
+        llm.close()
+        return 0
+    g = GGUFFile(path)
+    ctx_mean = n_prompt + W + K / 2.0
+    w_read, kv_pos, step_bytes = algorithmic_bytes(g, ctx_mean)
+    peak, peak_src = measured_peak_gbs()
+    achieved = step_bytes / (ms_max / K / 1e3) / 1e9
+    n_coll = 2 * eng.dims.n_layer + 1 if world > 1 else 0
+    roof = {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak * world, "unit": "GB/s", "frac": round(achieved / (peak * world), 4),
+            "traffic": None, "peak_source": peak_src + f" x {world} GPUs", "bytes_per_launch": int(step_bytes),
+            "launch": "one decode step of the sharded model = one CUDA-graph launch per rank; algorithmic bytes = W_read + mean_ctx * "
+                      "KV bytes/position over all ranks",
+            "kernels": {k: {"ms": round(v["ms"], 4), "launches": v["launches"]} for k, v in kinds.items()},
+            "kernels_note": "rank 0, one un-graphed step with events around every launch; attn_out and ffn_down include their all-reduce, "
+                            "lm_head its all-gather",
+            "collectives_per_step": n_coll,
+            "limiting_collective": (f"all-reduce of {eng.dims.n_embd} floats ({eng.dims.n_embd * 4 // 1024} KB) after attn_output and ffn_down: "
+                                    f"{2 * eng.dims.n_layer} per token, latency-bound") if world > 1 else None}
+    line = {"metric": "decode_tokens_per_s", "value": round(value, 2), "unit": "tok/s", "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": round(ms_max / K, 5), "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "int8x2 activations x int4/5/6 weights (dp4a), f32 accumulate and all-reduce, f16 KV", "data": "synthetic",
+            "config": cfg, "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof, "engine": mode,
+            "prefill_ms": round(prefill_ms, 2), "load_s": round(t_load, 2), "w_read_bytes": int(w_read), "kv_bytes_per_pos": kv_pos,
+            "ctx_mean": ctx_mean}
+    if not args.no_cpu_baseline:
+        try:
+            r = cpu_reference_run(path, 1, 8, budget_s=args.cpu_budget_s)
+            line["cpu_baseline"] = {"value": round(r["value"], 3), "unit": "tok/s", "cores": r["cores"], "kind": "port", "sample": r["sample"]}
+        except Exception as exc:  # noqa: BLE001
+            line["cpu_baseline"] = {"value": None, "unit": "tok/s", "cores": 0, "kind": "port", "sample": f"failed: {exc}"}
+    if world == 1 and not args.no_parity_check:
+        line["parity_check"] = parity_check(eng, path, V, n_new=3)
+    print(json.dumps(line))
+    llm.close()
+    return 0
+
+
 def batch_workload(args, cfg, path, n_prompt, batch, rank, world, local_rank, barrier, torch, dist):
     """Continuous-batching configs: `batch` sequences decode together, one weight pass per step (tensor-core GEMM path)."""
     import numpy as np
@@ -432,6 +533,12 @@ def main():
     from llama_cpp.engine import SamplingSettings
     from llama_cpp.gguf_file import GGUFFile
     K, W = args.steps, args.warmup
+    if args.workload.endswith("-tp"):
+        cfg["parallelism"] = f"tensor parallel x{world} (column/row weight splits, NCCL all-reduce)" if world > 1 else "single GPU"
+        rc = tp_workload(args, cfg, path, n_prompt, rank, world, local_rank, barrier, torch, dist)
+        if world > 1:
+            dist.destroy_process_group()
+        return rc
     if batch > 1:
         return batch_workload(args, cfg, path, n_prompt, batch, rank, world, local_rank, barrier, torch, dist)
     n_ctx = n_prompt + W + K + 16

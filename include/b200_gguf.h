@@ -78,6 +78,16 @@ int b2_engine_destroy(b2_engine* e);
  * llama_model_loader::load_all_data). ne0 = contiguous length K, ne1 = rows (1 for vectors). */
 int b2_upload_tensor(b2_engine* e, const char* name, int ggml_type, int64_t ne0, int64_t ne1,
                      const void* host_data, int64_t nbytes);
+/* Tensor parallelism for models that do not fit (or should not occupy) one GPU: one process per GPU, each creating an
+ * engine whose b2_config carries the LOCAL head counts and n_ff (1 / world of the model's) and the FULL n_embd and n_vocab,
+ * and uploading its shard of every matrix (llama_cpp/tp_shard.py: whole rows of attn_q/k/v, ffn_gate/up and output, K
+ * ranges of attn_output and ffn_down cut at 256-element block boundaries). The engine then all-reduces (sum, NCCL) the
+ * hidden vector after attn_output and ffn_down and all-gathers the logits. No counterpart in the reference, which only
+ * runs independent replicas (/root/reference/helm/values.yaml:17). b2_tp_unique_id: rank 0 makes the 128-byte NCCL id,
+ * the host distributes it; b2_engine_tp_init: collective over all ranks, after b2_engine_create and before
+ * b2_engine_finalize. In this mode prompts and multi-slot steps run through the mat-vec path. */
+int b2_tp_unique_id(void* host_out_128_bytes);
+int b2_engine_tp_init(b2_engine* e, int rank, int world, const void* host_id_128_bytes);
 /* All tensors uploaded: validate the set, build the per-layer launch plans. */
 int b2_engine_finalize(b2_engine* e);
 int b2_engine_device_bytes(b2_engine* e, int64_t* weight_bytes, int64_t* kv_bytes);

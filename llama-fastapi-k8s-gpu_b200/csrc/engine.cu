@@ -59,6 +59,7 @@ struct Layer {
 
 struct Slot {
     float *x = nullptr, *q = nullptr, *att = nullptr, *h = nullptr, *hg = nullptr, *logits = nullptr;
+    float* tp_part = nullptr;      // tensor parallelism: this rank's partial sum of attn_output / ffn_down (rank 0: + the residual)
     int* ints = nullptr;           // [0]=token [1]=pos [2]=out_token [3]=step [4]=cursor [5]=pos_base
     int* block_table = nullptr;
     int* prompt = nullptr;         // [n_ctx]
@@ -92,6 +93,9 @@ struct b2_engine {
     int64_t launches = 0, weight_bytes = 0, kv_bytes = 0;
     bool use_graph = true, use_pdl = true, act2 = true, finalized = false, chain_pdl = true;
     int batch_attn_splits = 0;     // B2_BATCH_ATTN_SPLITS (tuning), read once at create
+    // tensor parallelism (b2_engine_tp_init): this engine holds 1 / tp_world of the heads, FFN rows and vocabulary rows
+    void* tp_comm = nullptr;
+    int tp_rank = 0, tp_world = 1;
     unsigned long long* tl = nullptr;   // B2_TIMELINE=1: 4 time stamps per kernel of a decode step (debugging aid)
     int tl_n = 0;                  // kernels recorded by the last forward_launches
     // prompt (GEMM) workspace, allocated on the first long prompt: PF_T tokens per chunk
@@ -225,6 +229,7 @@ static int engine_create_impl(b2_engine* e, const b2_config* c) {
         CK(cudaMalloc(&s.att, sizeof(float) * c->n_head * c->head_dim));
         CK(cudaMalloc(&s.h, sizeof(float) * c->n_ff));
         CK(cudaMalloc(&s.hg, sizeof(float) * c->n_ff));
+        CK(cudaMalloc(&s.tp_part, sizeof(float) * c->n_embd));
         CK(cudaMalloc(&s.logits, sizeof(float) * c->n_vocab));
         CK(cudaMalloc(&s.ints, sizeof(int) * 8));
         CK(cudaMemset(s.ints, 0, sizeof(int) * 8));
@@ -269,11 +274,12 @@ extern "C" int b2_engine_destroy(b2_engine* e) {
     for (auto& kv : e->tensors) cudaFree(kv.second.ptr);
     for (auto& s : e->slots) {
         free_slot_graphs(s);
-        cudaFree(s.x); cudaFree(s.q); cudaFree(s.att); cudaFree(s.h); cudaFree(s.hg); cudaFree(s.logits);
+        cudaFree(s.x); cudaFree(s.q); cudaFree(s.att); cudaFree(s.h); cudaFree(s.hg); cudaFree(s.tp_part); cudaFree(s.logits);
         cudaFree(s.ints); cudaFree(s.block_table); cudaFree(s.prompt); cudaFree(s.ring); cudaFree(s.sst); cudaFree(s.sp);
         cudaFree(s.uniforms);
     }
     cudaFree(e->tl);
+    tp_comm_destroy(e->tp_comm);
     cudaFree(e->k_pool); cudaFree(e->v_pool); cudaFree(e->rope_freq);
     cudaFree(e->attn_scratch); cudaFree(e->attn_counters);
     cudaFree(e->pf_x); cudaFree(e->pf_part); cudaFree(e->pf_xn); cudaFree(e->pf_qh); cudaFree(e->pf_att); cudaFree(e->pf_h);
@@ -335,6 +341,32 @@ static int plan_or_fail(MvParams& p, int n_ctas, const char* what) {
     return B2_OK;
 }
 
+extern "C" int b2_tp_unique_id(void* out128) {
+    if (!out128) return fail(B2_ERR_ARG, "null argument");
+    std::string err;
+    if (!tp_unique_id(out128, err)) return fail(B2_ERR_CUDA, err);
+    return B2_OK;
+}
+
+extern "C" int b2_engine_tp_init(b2_engine* e, int rank, int world, const void* id128) {
+    if (!e || !id128) return fail(B2_ERR_ARG, "null argument");
+    if (e->finalized) return fail(B2_ERR_STATE, "b2_engine_tp_init must come before b2_engine_finalize");
+    if (world < 2 || rank < 0 || rank >= world) return fail(B2_ERR_ARG, "bad rank / world");
+    std::lock_guard<std::mutex> lk(e->mu);
+    CK(cudaSetDevice(e->cfg.device));
+    std::string err;
+    if (!tp_comm_init(&e->tp_comm, rank, world, id128, err)) return fail(B2_ERR_CUDA, err);
+    e->tp_rank = rank; e->tp_world = world;
+    // first collective outside any stream capture: NCCL sets up its channels (and allocates) lazily
+    Slot& s = e->slots[0];
+    CK(cudaMemsetAsync(s.tp_part, 0, sizeof(float) * e->cfg.n_embd, e->stream));
+    if (!tp_all_reduce_sum(e->tp_comm, s.tp_part, s.tp_part, e->cfg.n_embd, e->stream, err)) return fail(B2_ERR_CUDA, err);
+    const int v_local = e->cfg.n_vocab / world;
+    if (!tp_all_gather(e->tp_comm, s.logits + (size_t)rank * v_local, s.logits, v_local, e->stream, err)) return fail(B2_ERR_CUDA, err);
+    CK(cudaStreamSynchronize(e->stream));
+    return B2_OK;
+}
+
 extern "C" int b2_engine_finalize(b2_engine* e) {
     if (!e) return fail(B2_ERR_ARG, "null engine");
     std::lock_guard<std::mutex> lk(e->mu);
@@ -348,7 +380,11 @@ extern "C" int b2_engine_finalize(b2_engine* e) {
         e->tok_embd = it->second;
     }
     if ((rc = get_tensor(e, "output_norm.weight", c.n_embd, 1, false, e->out_norm))) return rc;
-    if (e->tensors.count("output.weight")) {
+    const int tpw = e->tp_world;
+    if (c.n_vocab % (2 * tpw)) return fail(B2_ERR_UNSUPPORTED, "n_vocab must be a multiple of 2 * tp_world");
+    if (tpw > 1) {      // the output matrix is split by rows: this rank holds vocabulary rows [rank, rank + 1) * n_vocab / tp_world
+        if ((rc = get_tensor(e, "output.weight", c.n_embd, c.n_vocab / tpw, true, e->output))) return rc;
+    } else if (e->tensors.count("output.weight")) {
         if ((rc = get_tensor(e, "output.weight", c.n_embd, c.n_vocab, true, e->output))) return rc;
     } else {
         if ((rc = get_tensor(e, "token_embd.weight", c.n_embd, c.n_vocab, true, e->output))) return rc;  // tied
@@ -375,7 +411,9 @@ extern "C" int b2_engine_finalize(b2_engine* e) {
         if ((rc = plan_or_fail(q, e->n_ctas, "attn_q/k/v"))) return rc;
         L.p_qkv = q;
         MvParams o = {};
-        o.nseg = 1; o.seg[0] = make_seg(L.wo); o.K = qd; o.mode = MV_RESID; o.err = kernel_error_word();
+        // tensor parallelism: every rank produces a partial sum over its K range; rank 0's carries the residual, then all-reduce
+        const int part_mode = (tpw > 1 && e->tp_rank != 0) ? MV_STORE : MV_RESID;
+        o.nseg = 1; o.seg[0] = make_seg(L.wo); o.K = qd; o.mode = part_mode; o.err = kernel_error_word();
         if ((rc = plan_or_fail(o, e->n_ctas, "attn_output"))) return rc;
         L.p_o = o;
         MvParams g = {};
@@ -395,7 +433,7 @@ extern "C" int b2_engine_finalize(b2_engine* e) {
             L.p_gate = a; L.p_up = b;
         }
         MvParams d = {};
-        d.nseg = 1; d.seg[0] = make_seg(L.wdown); d.K = c.n_ff; d.mode = MV_RESID; d.err = kernel_error_word();
+        d.nseg = 1; d.seg[0] = make_seg(L.wdown); d.K = c.n_ff; d.mode = part_mode; d.err = kernel_error_word();
         if ((rc = plan_or_fail(d, e->n_ctas, "ffn_down"))) return rc;
         L.p_down = d;
     }
@@ -404,7 +442,7 @@ extern "C" int b2_engine_finalize(b2_engine* e) {
     h.norm_w = (const float*)e->out_norm.ptr; h.eps = c.rms_eps; h.err = kernel_error_word();
     if ((rc = plan_or_fail(h, e->n_ctas, "output"))) return rc;
     e->p_head = h;
-    e->gemm_ok = !getenv("B2_NO_GEMM_PREFILL");
+    e->gemm_ok = !getenv("B2_NO_GEMM_PREFILL") && tpw == 1;     // tensor parallelism: prompts and batches go through the mat-vec path
     for (auto& L : e->layers)
         for (const DevTensor* t : {&L.wq, &L.wk, &L.wv, &L.wo, &L.wgate, &L.wup, &L.wdown})
             if (block_elems(t->type) == 1) e->gemm_ok = false;
@@ -443,6 +481,8 @@ static int forward_launches(b2_engine* e, Slot& s, bool with_head, bool with_sam
     auto tock = [&](cudaEvent_t y) { if (kt) cudaEventRecord(y, st); };
     cudaEvent_t ye = nullptr;
     int* tok = s.ints + 0; int* pos = s.ints + 1;
+    const bool tp = e->tp_world > 1;
+    std::string tp_err;
     int tl_k = 0;
     auto next_tl = [&]() -> unsigned long long* { return (e->tl && !kt && tl_k < 1024) ? e->tl + 4 * (tl_k++) : nullptr; };
     tick(0, &ye);
@@ -472,9 +512,10 @@ static int forward_launches(b2_engine* e, Slot& s, bool with_head, bool with_sam
         else CK(attn_decode_launch(a, st, pdl));
         tock(ye);
         MvParams o = L.p_o;
-        o.x = s.att; o.y = s.x; o.resid = s.x; o.tl = next_tl();
+        o.x = s.att; o.y = tp ? s.tp_part : s.x; o.resid = s.x; o.tl = next_tl();
         tick(3, &ye);
         CK(mv_launch(o, e->n_ctas, st, e->act2, pdl));
+        if (tp && !tp_all_reduce_sum(e->tp_comm, s.tp_part, s.x, c.n_embd, st, tp_err)) return fail(B2_ERR_CUDA, tp_err);
         tock(ye);
         tick(4, &ye);
         if (L.gu_fused) {
@@ -491,17 +532,21 @@ static int forward_launches(b2_engine* e, Slot& s, bool with_head, bool with_sam
         }
         tock(ye);
         MvParams d = L.p_down;
-        d.x = s.h; d.y = s.x; d.resid = s.x; d.tl = next_tl();
+        d.x = s.h; d.y = tp ? s.tp_part : s.x; d.resid = s.x; d.tl = next_tl();
         tick(5, &ye);
         CK(mv_launch(d, e->n_ctas, st, e->act2, pdl));
+        if (tp && !tp_all_reduce_sum(e->tp_comm, s.tp_part, s.x, c.n_embd, st, tp_err)) return fail(B2_ERR_CUDA, tp_err);
         tock(ye);
         e->launches += 5;
     }
     if (with_head) {
         MvParams h = e->p_head;
-        h.x = s.x; h.y = s.logits; h.tl = next_tl();
+        const int v_local = c.n_vocab / e->tp_world;
+        h.x = s.x; h.y = s.logits + (size_t)e->tp_rank * v_local; h.tl = next_tl();
         tick(6, &ye);
         CK(mv_launch(h, e->n_ctas, st, e->act2, pdl));
+        // every rank ends up with the full logit vector (in place) and samples the same token from the same uniforms
+        if (tp && !tp_all_gather(e->tp_comm, s.logits + (size_t)e->tp_rank * v_local, s.logits, v_local, st, tp_err)) return fail(B2_ERR_CUDA, tp_err);
         tock(ye);
         e->launches++;
     }

@@ -5,6 +5,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <string>
 #include <utility>
 
 namespace b2 {
@@ -179,6 +180,13 @@ cudaError_t rope_store_batch_launch(const float* parts, int n_parts, long part_s
                                     int n_head, int n_kv, int hd, int bt, const float* rope_freq, float* q_out,
                                     __half* k_cache, __half* v_cache, cudaStream_t s);
 cudaError_t prefill_finish_launch(const int* prompt, int n, int pos_last, int* ints, SamplerState* st, cudaStream_t s);
+
+// ---------------------------------------------------------------- tensor-parallel collectives (tp.cu; NCCL loaded at run time)
+bool tp_unique_id(void* out128, std::string& err);
+bool tp_comm_init(void** comm, int rank, int world, const void* id128, std::string& err);
+void tp_comm_destroy(void* comm);
+bool tp_all_reduce_sum(void* comm, const float* send, float* recv, size_t n, cudaStream_t s, std::string& err);
+bool tp_all_gather(void* comm, const float* send, float* recv, size_t n, cudaStream_t s, std::string& err);
 
 // ---------------------------------------------------------------- small kernels (misc.cu)
 // One pinned, device-mapped word per process that kernel watchdogs write to; 0 = no error.

@@ -36,6 +36,8 @@ SIGNATURES = {
     "b2_engine_create": (c_int, [POINTER(B2Config), POINTER(c_void_p)]),
     "b2_engine_destroy": (c_int, [c_void_p]),
     "b2_upload_tensor": (c_int, [c_void_p, c_char_p, c_int, c_int64, c_int64, c_void_p, c_int64]),
+    "b2_tp_unique_id": (c_int, [c_void_p]),
+    "b2_engine_tp_init": (c_int, [c_void_p, c_int, c_int, c_void_p]),
     "b2_engine_finalize": (c_int, [c_void_p]),
     "b2_engine_device_bytes": (c_int, [c_void_p, POINTER(c_int64), POINTER(c_int64)]),
     "b2_seq_set_blocks": (c_int, [c_void_p, c_int, POINTER(c_int32), c_int]),

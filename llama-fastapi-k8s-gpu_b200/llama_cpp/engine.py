@@ -77,9 +77,16 @@ class Engine:
     """One model on one GPU. Calls are serialised by `self.lock` (the native side also locks)."""
 
     def __init__(self, gguf: GGUFFile, n_ctx: int, max_seqs: int = 1, device: int = 0,
-                 kv_block_tokens: int = 64, flags: int = 0, verbose: bool = False):
+                 kv_block_tokens: int = 64, flags: int = 0, verbose: bool = False, tp=None):
+        """`tp` = (rank, world, nccl_id: 128 bytes from `Engine.tp_unique_id()` of rank 0): tensor-parallel shard of the model
+        (one process per GPU; every rank constructs its engine at the same time -- the set-up is a collective)."""
         self.lib = _cabi.load_library()
         self.dims = read_dims(gguf)
+        self.tp_rank, self.tp_world = (int(tp[0]), int(tp[1])) if tp else (0, 1)
+        full_dims = self.dims
+        if self.tp_world > 1:
+            from . import tp_shard
+            self.dims = tp_shard.local_dims(full_dims, self.tp_world)     # local heads / n_ff; n_embd and n_vocab stay global
         self.n_ctx = int(n_ctx)
         self.max_seqs = int(max_seqs)
         self.device = int(device)
@@ -102,13 +109,21 @@ class Engine:
         self._h = h
         self.lock = threading.RLock()
         try:
-            for name, t in gguf.tensors.items():
-                ne0 = t.shape[0]
+            if self.tp_world > 1:
+                idb = (ctypes.c_char * 128).from_buffer_copy(bytes(tp[2]))
+                check(self.lib.b2_engine_tp_init(self._h, self.tp_rank, self.tp_world, idb), "b2_engine_tp_init")
+                from . import tp_shard
+                items = tp_shard.shard_all(gguf.tensors, self.tp_rank, self.tp_world)
+            else:
+                items = {name: (t.data, t.ggml_type, t.shape) for name, t in gguf.tensors.items()}
+            for name, (data, ggml_type, shape) in items.items():
+                ne0 = shape[0]
                 ne1 = 1
-                for s in t.shape[1:]:
+                for s in shape[1:]:
                     ne1 *= s
-                check(self.lib.b2_upload_tensor(self._h, name.encode(), t.ggml_type, ne0, ne1,
-                                                t.data.ctypes.data_as(ctypes.c_void_p), t.nbytes),
+                data = np.ascontiguousarray(data)
+                check(self.lib.b2_upload_tensor(self._h, name.encode(), ggml_type, ne0, ne1,
+                                                data.ctypes.data_as(ctypes.c_void_p), data.nbytes),
                       f"upload {name}")
             check(self.lib.b2_engine_finalize(self._h), "b2_engine_finalize")
         except Exception:
@@ -116,6 +131,13 @@ class Engine:
             raise
         self._tok = (ctypes.c_int32 * max(1, self.max_seqs))()
         self._slots = (ctypes.c_int32 * max(1, self.max_seqs))()
+
+    @staticmethod
+    def tp_unique_id() -> bytes:
+        """128-byte NCCL id (rank 0 makes it, the host distributes it to the other ranks)."""
+        buf = (ctypes.c_char * 128)()
+        check(_cabi.load_library().b2_tp_unique_id(buf), "b2_tp_unique_id")
+        return bytes(buf)
 
     # ---------------------------------------------------------------- lifecycle
     def close(self):

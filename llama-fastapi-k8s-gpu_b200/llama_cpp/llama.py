@@ -30,14 +30,16 @@ from .tokenizer import Vocab
 class Llama:
     def __init__(self, model_path: str, *, n_gpu_layers: int = 0, n_ctx: int = 512, seed: int = 0xFFFFFFFF,
                  n_batch: int = 512, last_n_tokens_size: int = 64, chat_format: Optional[str] = None,
-                 verbose: bool = True, main_gpu: int = 0, n_seq_max: Optional[int] = None, **kwargs: Any):
+                 verbose: bool = True, main_gpu: int = 0, n_seq_max: Optional[int] = None, tp=None, **kwargs: Any):
         """Load a GGUF model onto one B200.
 
         model_path / n_gpu_layers / n_ctx as in upstream. n_gpu_layers=-1 (or any non-zero value)
         means "all layers on the GPU"; 0 asks for upstream's CPU path, which this engine does not
         have. n_ctx=0 takes the model's training context. Extra upstream keywords (n_threads,
         use_mmap, rope_*, flash_attn, ...) are accepted and ignored. `n_seq_max` (or env
-        B200_MAX_SEQS) is how many callers can be batched concurrently (default 1, like the reference)."""
+        B200_MAX_SEQS) is how many callers can be batched concurrently (default 1, like the reference).
+        `tp` = (rank, world, nccl_id) makes this object one rank of a tensor-parallel group (70B-class models; one process
+        per GPU, every rank makes the same calls in the same order)."""
         if not os.path.exists(model_path):
             raise ValueError(f"Model path does not exist: {model_path}")
         if n_gpu_layers == 0:
@@ -55,7 +57,7 @@ class Llama:
         max_seqs = int(n_seq_max or os.environ.get("B200_MAX_SEQS", "1"))
         device = int(os.environ.get("B200_DEVICE", main_gpu))
         self._engine = Engine(self._gguf, n_ctx=self._n_ctx, max_seqs=max_seqs, device=device,
-                              kv_block_tokens=int(os.environ.get("B200_KV_BLOCK", "64")))
+                              kv_block_tokens=int(os.environ.get("B200_KV_BLOCK", "64")), tp=tp)
         self._vocab = Vocab(self._gguf.metadata, self._engine.dims.n_vocab)
         self._scheduler = Scheduler(self._engine, self._vocab)
         self._stream = UniformStream(seed)
