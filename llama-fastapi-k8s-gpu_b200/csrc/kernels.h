@@ -30,10 +30,11 @@ enum MvMode { MV_STORE = 0, MV_RESID = 1, MV_QKV = 2, MV_GATEUP = 3 };
 #ifndef B2_MV_NCW
 #define B2_MV_NCW 16
 #endif
-constexpr int MV_NCW = B2_MV_NCW;            // warps per CTA
-constexpr int MV_ROWS = 2;                   // rows per row group (one RoPE pair)
+constexpr int MV_NCW = B2_MV_NCW;            // consumer warps per CTA
+constexpr int MV_MAX_PROD = 4;               // TMA producer warps per CTA (upper bound; 2 are launched)
+constexpr int MV_ROWS = 4;                   // rows per row group (two RoPE pairs; one warp, one ring stage)
 constexpr int MV_MAX_STAGES = 48;            // ring stages (upper bound)
-constexpr int MV_SHARED_HDR = 6144;          // barriers + reduction scratch at the start of dynamic smem
+constexpr int MV_SHARED_HDR = 2048;          // barriers + reduction scratch at the start of dynamic smem
 
 struct MvSeg {
     const uint8_t* w;   // quantised rows, unchanged GGUF bytes
@@ -68,12 +69,13 @@ struct MvParams {
     int trigger_late;       // 1: let the next kernel launch only after this one's own dependency wait (its prologue
                             //    may then read what this kernel's predecessors wrote, e.g. the token position)
     // plan (mv_plan)
-    int n_slices;           // K-slices of 2048 elements per row = warp teams
-    int nrows;              // rows per tile: 2 (a pair), or 1 for very long rows
+    int n_slices;           // K-slices of 2048 elements per row
+    int slot_bytes;         // one row-slice slot of a stage
     int stage_bytes, n_stages; // ring: tile q of a CTA lives in stage q % n_stages
-    unsigned int inv_stages;   // 2^32 / n_stages rounded up: q / n_stages == umulhi(q, inv_stages)
+    int n_prod;             // producer warps
     int act_plane;          // bytes of one int8 activation plane (K padded to whole slices)
     int act_off;            // byte offset of the activation block in dynamic shared memory
+    int part_off;           // byte offset of the partial-sum slots (groups spanning several tiles)
     int ring_off;           // byte offset of the ring in dynamic shared memory (after the activations)
 };
 

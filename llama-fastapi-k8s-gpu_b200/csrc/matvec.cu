@@ -3,33 +3,32 @@
 // mul_mat_vec_q + the separate rms_norm / rope / cpy / silu / add launches that the reference
 // runs under llm.create_chat_completion (/root/reference/api.py:55-63; SURVEY.md 2.3 K2-K7,K11).
 //
-// Structure: one CTA of 16 warps per SM, all of the SM's shared memory as a ring of weight tiles.
-//   * Tiles. A tile is a row pair (one RoPE pair; a single row when two very long rows would not leave four
-//     ring stages). Rows are contiguous in memory, so a tile is ONE bulk copy of 4-30 KB (cp.async.bulk +
-//     mbarrier complete_tx). Measured on B200: a warp issues a cp.async.bulk only every ~110 cycles, so
-//     copies of 1-2 KB cap a CTA at ~3 TB/s chip rate however deep the ring is; copies of >= 4 KB do not.
-//   * Teams. K is cut into slices of 2048 elements; team t = the warps with warp % n_slices == t owns slice t
-//     for the whole kernel and keeps that slice's 64 quantised activations per lane (two int8 planes +
-//     scales, 40 registers) in REGISTERS: activations are read from shared memory once per kernel, not once
-//     per tile (re-reading them per row pair took most of the shared-memory bandwidth and of the issue slots).
-//     The row pairs of the CTA are dealt round-robin to the members of each team, so every tile is read by
-//     exactly one warp of every team.
-//   * Ring. Tile q of the CTA lives in stage q % S. There is no producer warp: the LAST of a tile's readers
-//     (mbarrier `empty[s]` with one arrival per team; the arrival that finds one pending is the last) refills
-//     the stage with tile q + S -- sixteen potential issuers. An mbarrier only exposes the parity of its
-//     phase and consecutive uses of a stage belong to different warps, so a warp that looked at a stage
-//     before the previous use had even landed would read "complete" for the wrong phase: the refilling warp
-//     publishes `issued[s] = use + 1` after arming the barrier, and a reader waits for that value (by then
-//     the previous use has been consumed, hence landed) before it waits on the parity.
-//   * Row sums. Each warp reduces its slice of the row pair over its lanes (5 shuffles) and drops the partial
-//     sums in a shared-memory slot; the warp that brings the last partial (mbarrier again) adds them in team
-//     order -- the result does not depend on timing -- and runs the epilogue.
-//   * The first S tiles are requested BEFORE griddepcontrol.wait (weights do not depend on the previous kernel).
-//   * prologue (after the wait): x -> optional fused RMSNorm weight -> two int8 planes + packed per-block
-//     scales in shared memory (loads of x in one batch: one L2 round trip; norm weights prefetched to L1
-//     before the wait), then every warp loads its slice into registers.
-//   * epilogue (lane 0 of the finishing warp): plain store, residual add, RoPE + paged-KV store for the fused
-//     QKV projection, or SiLU(gate) * up for the fused FFN projection.
+// Structure: one CTA per SM, 16 consumer warps + 2 TMA producer warps, the SM's shared memory as a ring of tiles.
+//   * Tiles. A tile = one K-slice (2048 elements) of a group of R = 4 consecutive rows = 4 row-slices of 1-2 KB,
+//     brought into one ring stage with 1-D bulk copies (cp.async.bulk + mbarrier complete_tx); 4 lanes of a
+//     producer warp serve a tile (one copy each), a warp issues 8 tiles per round. Producers never touch
+//     activations, so with programmatic dependent launch they start on the weights while the previous kernel
+//     is still running, and they keep the ring full independently of how the consumers are doing.
+//   * Consumers. Tile q belongs to consumer warp q % 16, whatever row group and K-slice it is: the warps of a
+//     CTA stay within one tile of each other to the end (the kernel is one link of a chain of ~160 dependent
+//     launches per token, so the last warp of the last CTA is what the next kernel waits for). Per tile a lane
+//     loads its 64 quantised activations (two int8 planes + packed scales) from shared memory and reuses them
+//     for the 4 rows; weights stay packed and go through dp4a. A warp only ever waits on its own tile's
+//     mbarrier: no block-wide barrier in the main loop.
+//     (A round-2 rewrite with warp teams owning K-slices, register-resident activations and last-reader refill
+//     was faster in a back-to-back micro-benchmark and slower inside the decode step -- 2.30 against 2.10 ms per
+//     token on the same box -- because refills depended on the slowest reader and teams finished unevenly.)
+//   * Row sums. A tile's 4 row sums are reduced over the lanes (transposed butterfly). Groups that span several
+//     tiles (K > 2048, gate/up) park them in a shared-memory slot; the warp that brings the last tile adds the
+//     partial sums in tile order -- the result does not depend on timing -- and runs the epilogue.
+//   * An mbarrier only exposes the parity of its phase and consecutive uses of a stage belong to different
+//     warps, so a consumer that looked at `full` before the previous use had even landed would read "complete"
+//     for the wrong phase: the producer publishes `issued[stage] = use + 1` after arming the barrier and a
+//     consumer waits for that value (by then the previous use has been consumed, hence landed) first.
+//   * prologue (consumers, after griddepcontrol.wait): x -> optional fused RMSNorm weight -> two int8 planes +
+//     packed per-block scales in shared memory (loads of x in one batch: one L2 round trip).
+//   * epilogue (lane 0 of the finishing warp): plain store, residual add, RoPE (cos/sin table built once per
+//     CTA) + paged-KV store for the fused QKV projection, or SiLU(gate) * up for the fused FFN projection.
 //
 // Roofline: HBM. Algorithmic bytes per launch = sum of the weight bytes of its segments.
 #include "kernels.h"
@@ -41,38 +40,35 @@
 namespace b2 {
 
 #ifndef B2_ROW_UNROLL
-#define B2_ROW_UNROLL 2
+#define B2_ROW_UNROLL 1
 #endif
-constexpr int ROW_UNROLL = B2_ROW_UNROLL;   // rows of a tile interleaved in the instruction stream
-constexpr int NCW = MV_NCW;
-constexpr int R = MV_ROWS;
-static_assert(R == 2, "a row group is one RoPE pair");
-constexpr int MV_THREADS = NCW * 32;
-#ifndef B2_MV_CTAS_PER_SM
-#define B2_MV_CTAS_PER_SM 1
-#endif
-constexpr int MV_CTAS_PER_SM = B2_MV_CTAS_PER_SM;      // experiment knob: 2 = two 8-warp CTAs per SM (build with -DB2_MV_NCW=8)
-constexpr int MV_SMEM_MAX = (MV_CTAS_PER_SM == 1 ? 224 : 112) * 1024;
-constexpr int MV_GSLOTS = 16;               // row pairs whose partial sums can be in flight at once
+constexpr int ROW_UNROLL = B2_ROW_UNROLL;   // rows of a tile interleaved in the instruction stream (more overflowed the instruction cache)
+constexpr int NCW = MV_NCW;                 // consumer warps
+constexpr int NPROD = 2;                    // producer warps
+constexpr int R = MV_ROWS;                  // rows per group
+constexpr int TPB = 32 / R;                 // tiles a producer warp issues per round
+static_assert(R == 4, "the lane reduction and the epilogue are written for groups of two RoPE pairs");
+constexpr int MV_THREADS = (NCW + NPROD) * 32;
+constexpr int MV_SMEM_MAX = 224 * 1024;
+constexpr int MV_GSLOTS = 32;               // row groups whose partial sums can be in flight at once
 
 struct __align__(16) MvShared {
     uint64_t full[MV_MAX_STAGES];           // a tile's bytes have landed (expect_tx)
-    uint64_t empty[MV_MAX_STAGES];          // one arrival per team: the tile has been read
-    uint64_t gbar[MV_GSLOTS];               // one arrival per team: the row pair's partial sums are in
+    uint64_t empty[MV_MAX_STAGES];          // the tile has been read (one arrival: its consumer warp)
     unsigned int issued[MV_MAX_STAGES];     // use number + 1 last armed on each stage
-    unsigned int gen[MV_GSLOTS];            // slot i serves row pair g with g % MV_GSLOTS == i and g / MV_GSLOTS == gen[i]
+    unsigned int gcnt[MV_GSLOTS];           // tiles of the slot's group handed in so far
+    unsigned int gen[MV_GSLOTS];            // slot i serves group g with g % MV_GSLOTS == i and g / MV_GSLOTS == gen[i]
     float red[NCW];
-    uint64_t probe;                         // scratch barrier: what does pending_count report for the last arrival?
-    unsigned int last_cnt;                  // ... this value (measured once per CTA instead of trusting a reading of the PTX manual)
-    float4 part[MV_GSLOTS][NCW];            // per team: {row0, row1, gate row0, gate row1}
+    float2 rope[64];                        // QKV launches: (cos, sin) of pos * freq[i], i < head_dim / 2
 };
 static_assert(sizeof(MvShared) <= MV_SHARED_HDR, "header does not fit");
 
 struct CtaWork {
     int seg;            // segment (non gate/up modes)
     int r0, r1;         // row range [r0, r1), both even
-    int ng;             // row groups of p.nrows rows
-    int tpg;            // tiles per group: 1, or 2 for gate/up (gate tile, up tile)
+    int ng;             // row groups (the last one may hold a single pair)
+    int tpg;            // tiles per group (slices x matrices)
+    int total;          // tiles for the whole CTA
 };
 
 __device__ __forceinline__ CtaWork cta_work(const MvParams& p, int cta, int nctas) {
@@ -89,15 +85,16 @@ __device__ __forceinline__ CtaWork cta_work(const MvParams& p, int cta, int ncta
     const int i = cta - c0;
     const long u0 = (long)units * i / nc, u1 = (long)units * (i + 1) / nc;
     w.r0 = (int)u0 * 2; w.r1 = (int)u1 * 2;
-    w.ng = (w.r1 - w.r0) / p.nrows;
-    w.tpg = gu ? 2 : 1;
+    w.ng = (w.r1 - w.r0 + R - 1) / R;
+    w.tpg = p.n_slices * (gu ? 2 : 1);
+    w.total = w.ng * w.tpg;
     return w;
 }
 
 // lane 0 of the finishing warp completes a row pair
 // (pos, page: position of the token and its KV page, fetched once per thread at kernel start; res: the residual pair,
 // fetched when the warp started on the row pair -- no global round trip is left on this path)
-__device__ __forceinline__ void epilogue_pair(const MvParams& p, int seg, int row, float v0, float v1, int pos, int page, float2 res) {
+__device__ __forceinline__ void epilogue_pair(const MvParams& p, const float2* rope, int seg, int row, float v0, float v1, int pos, int page, float2 res) {
     const MvSeg& sg = p.seg[seg];
     if (p.mode == MV_STORE) {
         *reinterpret_cast<float2*>(p.y + sg.out_off + row) = make_float2(v0, v1);
@@ -106,10 +103,8 @@ __device__ __forceinline__ void epilogue_pair(const MvParams& p, int seg, int ro
     } else if (p.mode == MV_QKV) {
         const int hd = p.head_dim;
         if (seg < 2) {                      // Q or K: rotate the adjacent pair (ggml "norm" RoPE)
-            const int i = (row % hd) >> 1;
-            const float ang = (float)pos * __ldg(p.rope_freq + i);
-            float s, c;
-            sincosf(ang, &s, &c);
+            const float2 cs = rope[(row % hd) >> 1];
+            const float c = cs.x, s = cs.y;
             const float a = v0 * c - v1 * s, b = v0 * s + v1 * c;
             v0 = a; v1 = b;
         }
@@ -138,30 +133,46 @@ __device__ __forceinline__ unsigned int ld_volatile_shared(const unsigned int* p
 __device__ __forceinline__ void st_volatile_shared(unsigned int* p, unsigned int v) {
     asm volatile("st.volatile.shared::cta.u32 [%0], %1;" ::"r"(smem_u32(p)), "r"(v) : "memory");
 }
-// arrive on an mbarrier and report the pending-arrival count of the state the arrive returns
-__device__ __forceinline__ uint32_t mbar_arrive_pending(uint64_t* bar, uint64_t& state) {
-    uint32_t cnt;
-    asm volatile("{\n\tmbarrier.arrive.shared::cta.b64 %0, [%2];\n\tmbarrier.pending_count.b64 %1, %0;\n\t}"
-                 : "=l"(state), "=r"(cnt) : "r"(smem_u32(bar)) : "memory");
-    return cnt;
-}
-__device__ __forceinline__ bool mbar_test_wait_state(uint64_t* bar, uint64_t state) {
-    uint32_t ok;
-    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.test_wait.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                 : "=r"(ok) : "r"(smem_u32(bar)), "l"(state) : "memory");
-    return ok != 0;
-}
 
-// Request tile t (0, or 1 = the second matrix of gate/up) of group g into `stage`: ONE bulk copy (lane 0 of the calling warp).
-__device__ __forceinline__ void tile_issue(const MvParams& p, const CtaWork& w, int g, int t, uint8_t* stage, uint64_t* bar,
-                                           unsigned int* issued, unsigned int use, int lane) {
-    if (lane != 0) return;
-    const MvSeg& sg = p.seg[(p.mode == MV_GATEUP) ? t : w.seg];
-    const uintptr_t start = (uintptr_t)sg.w + (size_t)(w.r0 + g * p.nrows) * sg.row_bytes;
-    const uintptr_t a0 = start & ~(uintptr_t)15, a1 = (start + (size_t)p.nrows * sg.row_bytes + 15) & ~(uintptr_t)15;
-    mbar_arrive_expect_tx(bar, (uint32_t)(a1 - a0));
-    st_volatile_shared(issued, use + 1);
-    tma_load_1d(stage, (const void*)a0, (uint32_t)(a1 - a0), bar);
+// Producer warp `prod_idx` of n_prod: ring entries prod_idx, prod_idx + n_prod, ... (n_stages is a multiple of n_prod, so a
+// stage always has the same producer, which therefore sees that stage's `empty` phases in order). Tiles are laid out
+// group-major: q -> (group q / tpg, matrix, K-slice). A round is TPB tiles, R lanes per tile (one row-slice copy each).
+__device__ __forceinline__ void mv_produce(const MvParams& p, const CtaWork& work, MvShared& sh, uint8_t* ring, int prod_idx, int lane) {
+    const uint32_t S = (uint32_t)p.n_stages;
+    const int n_prod = p.n_prod;
+    const int tsub = lane / R, rsub = lane % R;
+    for (int qb = prod_idx; qb < work.total; qb += TPB * n_prod) {
+        const int q = qb + tsub * n_prod;
+        const bool have = q < work.total;
+        const uint8_t* src = nullptr; uint32_t bytes = 0, use = 0; uint8_t* dst = nullptr; int st = 0;
+        if (have) {
+            const int gi = q / work.tpg, within = q % work.tpg;
+            const int seg = (p.mode == MV_GATEUP) ? within / p.n_slices : work.seg;
+            const int slice = within % p.n_slices;
+            const MvSeg& sg = p.seg[seg];
+            const int row0 = work.r0 + gi * R, nrows = min(R, work.r1 - row0);
+            st = (int)((uint32_t)q % S); use = (uint32_t)q / S;
+            if (rsub < nrows) {
+                const int sb = slice_bytes(sg.type);
+                const int len = min(sb, sg.row_bytes - slice * sb);        // the last slice may be shorter
+                const uintptr_t start = (uintptr_t)sg.w + (size_t)(row0 + rsub) * sg.row_bytes + (size_t)slice * sb;
+                const uintptr_t a0 = start & ~(uintptr_t)15, a1 = (start + len + 15) & ~(uintptr_t)15;
+                src = (const uint8_t*)a0; bytes = (uint32_t)(a1 - a0);
+                dst = ring + (size_t)st * p.stage_bytes + rsub * p.slot_bytes;
+            }
+            if (rsub == 0) mbar_wait(&sh.empty[st], (use & 1u) ^ 1u, p.err, 0x10001u, (unsigned)q);
+        }
+        __syncwarp();
+        uint32_t tot = bytes;                       // bytes of the tile = sum over its R lanes
+#pragma unroll
+        for (int o = 1; o < R; o <<= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
+        if (have && rsub == 0) {
+            mbar_arrive_expect_tx(&sh.full[st], tot);
+            st_volatile_shared(&sh.issued[st], use + 1u);
+        }
+        __syncwarp();
+        if (bytes) tma_load_1d(dst, src, bytes, &sh.full[st]);
+    }
 }
 
 // Consumer prologue: x (float32, global) -> optional RMSNorm weight -> two int8 planes + packed per-block
@@ -266,142 +277,128 @@ __device__ __forceinline__ ActView act_view(const MvParams& p, uint8_t* smem) {
     return v;
 }
 
-// sum over the lanes of a row pair: lanes 0-15 end with row 0, lanes 16-31 with row 1; returns both on lane 0
-__device__ __forceinline__ void pair_reduce(const float (&acc)[R], int lane, float& v0, float& v1) {
-    const bool hi = lane & 16;
-    float keep = hi ? acc[1] : acc[0];
-    const float send = hi ? acc[0] : acc[1];
-    keep += __shfl_xor_sync(0xffffffffu, send, 16);
-    keep += __shfl_xor_sync(0xffffffffu, keep, 8);
-    keep += __shfl_xor_sync(0xffffffffu, keep, 4);
-    keep += __shfl_xor_sync(0xffffffffu, keep, 2);
-    keep += __shfl_xor_sync(0xffffffffu, keep, 1);
-    v0 = keep;
-    v1 = __shfl_sync(0xffffffffu, keep, 16);
+// Sum the 4 row accumulators over the lanes (transposed butterfly, 6 shuffles + 3 broadcasts): every lane gets all sums.
+__device__ __forceinline__ void rows_reduce(const float (&acc)[R], int lane, float (&out)[R]) {
+    const bool hi16 = lane & 16, hi8 = lane & 8;
+    const float s0 = hi16 ? acc[0] : acc[2], s1 = hi16 ? acc[1] : acc[3];
+    float k0 = hi16 ? acc[2] : acc[0], k1 = hi16 ? acc[3] : acc[1];
+    k0 += __shfl_xor_sync(0xffffffffu, s0, 16);
+    k1 += __shfl_xor_sync(0xffffffffu, s1, 16);
+    const float snd = hi8 ? k0 : k1;
+    float kp = hi8 ? k1 : k0;
+    kp += __shfl_xor_sync(0xffffffffu, snd, 8);
+    kp += __shfl_xor_sync(0xffffffffu, kp, 4);
+    kp += __shfl_xor_sync(0xffffffffu, kp, 2);
+    kp += __shfl_xor_sync(0xffffffffu, kp, 1);      // lanes 0-7 / 8-15 / 16-23 / 24-31 hold row 0 / 1 / 2 / 3
+    out[0] = kp;
+    out[1] = __shfl_sync(0xffffffffu, kp, 8);
+    out[2] = __shfl_sync(0xffffffffu, kp, 16);
+    out[3] = __shfl_sync(0xffffffffu, kp, 24);
 }
 
-// One warp = (team, member): K-slice `team` of the row groups g = member, member + team size, ...
+// One consumer warp's share of the launch: every NCW-th ring entry.
 template <int T, bool ACT2>
-__device__ __forceinline__ void consume(const MvParams& p, const CtaWork& work, MvShared& sh, uint8_t* ring,
+__device__ __forceinline__ void consume(const MvParams& p, const CtaWork& work, MvShared& sh, const uint8_t* ring, float4* part,
                                         const ActView& av, float rs, int pos, int page, int warp, int lane) {
+    const uint32_t S = (uint32_t)p.n_stages;
     const bool gateup = (p.mode == MV_GATEUP);
-    const int S = p.n_stages, tpg = work.tpg, ng = work.ng, n_teams = p.n_slices, nrows = p.nrows;
-    const int team = warp % n_teams, member = warp / n_teams;
-    const int team_size = (NCW - 1 - team) / n_teams + 1;
-    const unsigned int n_tiles = (unsigned)(ng * tpg);
-    const unsigned int last_cnt = sh.last_cnt;
-    const bool active = team * B2_SLICE + lane * 64 < p.K;              // lanes past K in a partial last slice idle
-    LaneAct la;
-    if (active) load_act<T, ACT2>(la, av, team * B2_SLICE, lane);       // this warp's activations, for the whole kernel
-    const int sb = slice_bytes(T);
-    for (int g = member; g < ng; g += team_size) {
-        const int row0 = work.r0 + g * nrows;
-        float2 res = make_float2(0.f, 0.f);
-        if (p.mode == MV_RESID && lane == 0) {         // early: the round trip hides behind the tile (any team may end up finishing the group)
-            const float* rp = p.resid + p.seg[work.seg].out_off + row0;
-            if (nrows == 2) res = __ldcg(reinterpret_cast<const float2*>(rp)); else res.x = __ldcg(rp);
-        }
-        float acc[R], gacc[R];
-#pragma unroll
-        for (int r = 0; r < R; r++) { acc[r] = 0.f; gacc[r] = 0.f; }
-        for (int t = 0; t < tpg; t++) {
-            const MvSeg& sg = p.seg[gateup ? t : work.seg];
-            const unsigned int q = (unsigned)(g * tpg + t);
-            const unsigned int u = __umulhi(q, p.inv_stages);
-            const int s = (int)(q - u * (unsigned)S);
-            uint8_t* stage = ring + (size_t)s * p.stage_bytes;
-            {   // this use of the stage has been armed (see the ring note at the top), then: its bytes have landed
-                uint32_t spins = 0;
-                while (ld_volatile_shared(&sh.issued[s]) != u + 1u) {
-                    __nanosleep(20);
-                    if (++spins > (1u << 23)) {
-                        volatile unsigned int* e = reinterpret_cast<volatile unsigned int*>(p.err);
-                        if (e && e[0] == 0) { e[1] = blockIdx.x; e[2] = threadIdx.x; e[3] = (unsigned)g; e[4] = u; e[0] = 0x10003u; }
-                        break;
-                    }
+    const int tpg = work.tpg, n_sl = p.n_slices;
+    if (warp >= work.total || tpg <= 0) return;      // no tile for this warp (tpg is 0 in CTAs without rows)
+    // loop invariants out of the parameter block (a gate/up pair has one type, one K: mv_plan)
+    const int seg0 = gateup ? 0 : work.seg;
+    const uint32_t row_bytes = (uint32_t)p.seg[seg0].row_bytes;
+    const uint32_t wlo0 = (uint32_t)(uintptr_t)p.seg[seg0].w, wlo1 = gateup ? (uint32_t)(uintptr_t)p.seg[1].w : wlo0;
+    const uint32_t stage_bytes = (uint32_t)p.stage_bytes, slot_bytes = (uint32_t)p.slot_bytes;
+    const uint32_t sb = (uint32_t)slice_bytes(T);
+    // tile bookkeeping advances by NCW per iteration: carried incrementally (no integer division in the loop)
+    int gi = warp / tpg, within = warp % tpg;
+    uint32_t st = (uint32_t)warp % S, use = (uint32_t)warp / S;
+    for (int q = warp; q < work.total; q += NCW) {
+        const int m = (gateup && within >= n_sl) ? 1 : 0;
+        const int sl = within - m * n_sl;
+        const int row0 = work.r0 + gi * R, nrows = min(R, work.r1 - row0);
+        const int gi_cur = gi, within_cur = within;
+        within += NCW; while (within >= tpg) { within -= tpg; gi++; }
+        const uint32_t st_cur = st, use_cur = use;
+        st += NCW; while (st >= S) { st -= S; use++; }
+        {   // the producer has armed this use of the stage (see the note at the top), then: its bytes have landed
+            uint32_t spins = 0;
+            while (ld_volatile_shared(&sh.issued[st_cur]) != use_cur + 1u) {
+                if (++spins > (1u << 26)) {
+                    volatile unsigned int* e = reinterpret_cast<volatile unsigned int*>(p.err);
+                    if (e && e[0] == 0) { e[1] = blockIdx.x; e[2] = threadIdx.x; e[3] = (unsigned)q; e[4] = use_cur; e[0] = 0x10003u; }
+                    break;
                 }
             }
-            mbar_wait(&sh.full[s], u & 1u, p.err, 0x10002u, (unsigned)g);
-            // the copy started at the 16-byte boundary below row 0 (only Q6_K rows can sit off one: row_dot copes)
-            const uint32_t off0 = ((uint32_t)(uintptr_t)sg.w + (uint32_t)row0 * (uint32_t)sg.row_bytes) & 15u;
-            const uint8_t* r0p = stage + off0 + team * sb;
-#ifndef B2_MV_SKIP_COMPUTE      // experiment builds only (scripts/mv_variants.sh): stream the tiles, skip the dot products
-            if (active) {
-                if (nrows == 2) {
-                    const uint8_t* r1p = r0p + sg.row_bytes;
+        }
+        mbar_wait(&sh.full[st_cur], use_cur & 1u, p.err, 0x10002u, (unsigned)q);
+        const uint8_t* stage = ring + st_cur * stage_bytes;
+        float acc[R];
+#pragma unroll
+        for (int r = 0; r < R; r++) acc[r] = 0.f;
+        if (sl * B2_SLICE + lane * 64 < p.K) {                     // lanes past K in a partial last slice idle
+            LaneAct la;
+            load_act<T, ACT2>(la, av, sl * B2_SLICE, lane);
+            // each copy started at the 16-byte boundary below its row-slice (only Q6_K rows can sit off one)
+            const uint32_t row_lo = (m ? wlo1 : wlo0) + (uint32_t)row0 * row_bytes + (uint32_t)sl * sb;
 #pragma unroll ROW_UNROLL
-                    for (int r = 0; r < R; r++) {
-                        const float d = row_dot<T, ACT2>(r ? r1p : r0p, lane, la);
+            for (int r = 0; r < nrows; r++) {
+                const uint32_t off = (T == T_Q6_K) ? ((row_lo + r * row_bytes) & 15u) : 0u;
+                const float d = row_dot<T, ACT2>(stage + r * slot_bytes + off, lane, la);
 #pragma unroll
-                        for (int k = 0; k < R; k++) if (k == r) acc[k] += d;
-                    }
-                } else {
-                    acc[0] += row_dot<T, ACT2>(r0p, lane, la);
-                }
-            }
-#endif
-            if (gateup && t == 0) {                    // gate done: keep its sums, go on with up
-#pragma unroll
-                for (int r = 0; r < R; r++) { gacc[r] = acc[r]; acc[r] = 0.f; }
-            }
-            // done with the stage: the last of its readers (one warp per team) refills it
-            fence_proxy_async();    // generic-proxy reads of the stage, ordered before the TMA (async proxy) refill
-            __syncwarp();
-            bool last = false;
-            if (lane == 0) { uint64_t st; last = mbar_arrive_pending(&sh.empty[s], st) == last_cnt; }
-            last = __shfl_sync(0xffffffffu, last, 0);
-            if (last && q + (unsigned)S < n_tiles) {
-                const unsigned int q2 = q + (unsigned)S;
-                const int g2 = (int)(tpg == 2 ? q2 >> 1 : q2), t2 = (int)(tpg == 2 ? q2 & 1u : 0u);
-                tile_issue(p, work, g2, t2, stage, &sh.full[s], &sh.issued[s], u + 1u, lane);
+                for (int k = 0; k < R; k++) if (k == r) acc[k] = d;
             }
         }
-        float v0, v1, g0 = 0.f, g1 = 0.f;
-        if (nrows == 2) {
-            pair_reduce(acc, lane, v0, v1);
-            if (gateup) pair_reduce(gacc, lane, g0, g1);
+        fence_proxy_async();    // generic-proxy reads of the stage, ordered before the TMA (async proxy) refill
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sh.empty[st_cur]);             // the stage can be refilled
+        float v[R], gv[R] = {0.f, 0.f, 0.f, 0.f};
+        rows_reduce(acc, lane, v);
+        if (lane != 0) continue;
+        if (tpg > 1) {          // hand the tile's sums in; whoever brings the group's last tile adds them up in tile order
+            const int slot = gi_cur % MV_GSLOTS;
+            const unsigned int gen = (unsigned)(gi_cur / MV_GSLOTS);
+            while (ld_volatile_shared(&sh.gen[slot]) != gen) __nanosleep(20);     // the group MV_GSLOTS back is done with the slot
+            float4* ps = part + slot * tpg;
+            ps[within_cur] = make_float4(v[0], v[1], v[2], v[3]);
+            __threadfence_block();
+            const unsigned int old = atomicAdd(&sh.gcnt[slot], 1u);
+            if (old != (unsigned)tpg - 1u) continue;
+            __threadfence_block();
+#pragma unroll
+            for (int r = 0; r < R; r++) v[r] = 0.f;
+            if (gateup) {
+                for (int i = 0; i < n_sl; i++) { const float4 c = ps[i]; gv[0] += c.x; gv[1] += c.y; gv[2] += c.z; gv[3] += c.w; }
+                for (int i = n_sl; i < tpg; i++) { const float4 c = ps[i]; v[0] += c.x; v[1] += c.y; v[2] += c.z; v[3] += c.w; }
+            } else {
+                for (int i = 0; i < tpg; i++) { const float4 c = ps[i]; v[0] += c.x; v[1] += c.y; v[2] += c.z; v[3] += c.w; }
+            }
+            st_volatile_shared(&sh.gcnt[slot], 0u);
+            st_release_shared(&sh.gen[slot], gen + 1u);
+        }
+#pragma unroll
+        for (int r = 0; r < R; r++) { v[r] *= rs; gv[r] *= rs; }   // fused RMSNorm factor (a scalar: applied to the sums)
+        if (gateup) {
+            float h[R];
+#pragma unroll
+            for (int r = 0; r < R; r++) h[r] = gv[r] / (1.0f + __expf(-gv[r])) * v[r];
+            *reinterpret_cast<float2*>(p.y + row0) = make_float2(h[0], h[1]);
+            if (nrows == R) *reinterpret_cast<float2*>(p.y + row0 + 2) = make_float2(h[2], h[3]);
         } else {
-            v0 = warp_sum(acc[0]); v1 = 0.f;
-        }
-        if (lane == 0) {
-            bool finish = true;
-            if (n_teams > 1) {     // hand this team's partial sums in; the team that completes the group adds them in team order
-                const int slot = g % MV_GSLOTS;
-                const unsigned int gen = (unsigned)(g / MV_GSLOTS);
-                while (ld_volatile_shared(&sh.gen[slot]) != gen) __nanosleep(20);     // the group MV_GSLOTS back is done with the slot
-                sh.part[slot][team] = make_float4(v0, v1, g0, g1);
-                uint64_t st;
-                finish = mbar_arrive_pending(&sh.gbar[slot], st) == last_cnt;         // release: our partial sums are visible ...
-                if (finish) {
-                    while (!mbar_test_wait_state(&sh.gbar[slot], st)) {}              // ... acquire: and so are everybody else's
-                    v0 = v1 = g0 = g1 = 0.f;
-                    for (int i = 0; i < n_teams; i++) {
-                        const float4 c = sh.part[slot][i];
-                        v0 += c.x; v1 += c.y; g0 += c.z; g1 += c.w;
-                    }
-                    st_release_shared(&sh.gen[slot], gen + 1u);
-                }
+            float2 res0 = make_float2(0.f, 0.f), res1 = res0;
+            if (p.mode == MV_RESID) {                              // written by other SMs: L2
+                const float* rp = p.resid + p.seg[work.seg].out_off + row0;
+                res0 = __ldcg(reinterpret_cast<const float2*>(rp));
+                if (nrows == R) res1 = __ldcg(reinterpret_cast<const float2*>(rp + 2));
             }
-            if (finish) {
-                v0 *= rs; v1 *= rs;                        // fused RMSNorm factor (a scalar: applied to the sums)
-                if (gateup) {
-                    g0 *= rs; g1 *= rs;
-                    const float h0 = g0 / (1.0f + __expf(-g0)) * v0;
-                    const float h1 = g1 / (1.0f + __expf(-g1)) * v1;
-                    *reinterpret_cast<float2*>(p.y + row0) = make_float2(h0, h1);
-                } else if (nrows == 2) {
-                    epilogue_pair(p, work.seg, row0, v0, v1, pos, page, res);
-                } else {                                   // single rows: plain store / residual add only (mv_plan)
-                    float* y = p.y + p.seg[work.seg].out_off + row0;
-                    *y = res.x + v0;
-                }
-            }
+            epilogue_pair(p, sh.rope, work.seg, row0, v[0], v[1], pos, page, res0);
+            if (nrows == R) epilogue_pair(p, sh.rope, work.seg, row0 + 2, v[2], v[3], pos, page, res1);
         }
     }
 }
 
 template <bool ACT2>
-__global__ void __launch_bounds__(MV_THREADS, MV_CTAS_PER_SM) matvec_kernel(const MvParams p) {
+__global__ void __launch_bounds__(MV_THREADS, 1) matvec_kernel(const MvParams p) {
     extern __shared__ __align__(128) uint8_t smem_raw[];
     MvShared& sh = *reinterpret_cast<MvShared*>(smem_raw);
     uint8_t* ring = smem_raw + p.ring_off;
@@ -409,57 +406,62 @@ __global__ void __launch_bounds__(MV_THREADS, MV_CTAS_PER_SM) matvec_kernel(cons
     const CtaWork work = cta_work(p, blockIdx.x, gridDim.x);
     if (threadIdx.x == 0) tl_stamp(p.tl, 0);
 
-    // barrier set-up spread over the threads (one thread doing ~110 mbarrier.init in a row cost over a microsecond per launch)
+    // barrier set-up spread over the threads (one thread doing ~100 mbarrier.init in a row cost over a microsecond per launch)
     if ((int)threadIdx.x < p.n_stages) {
-        mbar_init(&sh.full[threadIdx.x], 1); mbar_init(&sh.empty[threadIdx.x], p.n_slices); sh.issued[threadIdx.x] = 0;
+        mbar_init(&sh.full[threadIdx.x], 1); mbar_init(&sh.empty[threadIdx.x], 1); sh.issued[threadIdx.x] = 0;
     } else if (threadIdx.x >= 64 && threadIdx.x < 64 + MV_GSLOTS) {
-        mbar_init(&sh.gbar[threadIdx.x - 64], p.n_slices); sh.gen[threadIdx.x - 64] = 0;
-    } else if (threadIdx.x == 96) {
-        mbar_init(&sh.probe, 1);
-        uint64_t st;
-        sh.last_cnt = mbar_arrive_pending(&sh.probe, st);    // the only (= last) arrival of a one-arrival barrier
+        sh.gcnt[threadIdx.x - 64] = 0; sh.gen[threadIdx.x - 64] = 0;
     }
     fence_mbar_init();
     __syncthreads();
     if (!p.trigger_late) griddep_launch();   // the next kernel may start (it will prefetch its own weights)
-    {   // first pass over the ring: weights do not depend on the previous kernel, so this runs ahead of the wait
-        const int n_first = min(p.n_stages, work.ng * work.tpg);
-        for (int q = warp; q < n_first; q += NCW)
-            tile_issue(p, work, work.tpg == 2 ? q >> 1 : q, work.tpg == 2 ? q & 1 : 0, ring + (size_t)q * p.stage_bytes,
-                       &sh.full[q], &sh.issued[q], 0u, lane);
+
+    if (warp >= NCW) {  // producer warps never touch activations: they run ahead of the dependency wait
+        if (warp - NCW < p.n_prod) mv_produce(p, work, sh, ring, warp - NCW, lane);
+        return;         // (with trigger_late they never trigger: the CTA's trigger is the consumers', after their wait)
     }
     if (p.norm_w) {     // weights, not activations: warm L1 while the previous kernel finishes
-        for (int i = threadIdx.x * 32; i < p.K; i += MV_THREADS * 32)
+        for (int i = threadIdx.x * 32; i < p.K; i += NCW * 32 * 32)
             asm volatile("prefetch.global.L1 [%0];" ::"l"(p.norm_w + i));
     }
     griddep_wait();     // activations written by the previous kernel are visible from here on
     if (threadIdx.x == 0) tl_stamp(p.tl, 1);
     if (p.trigger_late) griddep_launch();
+    int pos = 0, page = 0;      // QKV epilogue inputs: fetched once per thread, here
+    if (p.mode == MV_QKV) {
+        pos = *p.pos_ptr; page = p.block_table[pos / p.block_tokens];
+        if ((int)threadIdx.x < p.head_dim / 2) {           // head_dim <= 128; published by the barrier that ends the prologue
+            float sn, cs;
+            sincosf((float)pos * __ldg(p.rope_freq + threadIdx.x), &sn, &cs);
+            sh.rope[threadIdx.x] = make_float2(cs, sn);
+        }
+    }
     // plane layout follows the quant type this CTA reads (a gate/up pair has one type: mv_plan)
     const int type0 = (p.mode == MV_GATEUP) ? p.seg[0].type : p.seg[work.seg].type;
     mv_quantize_input<ACT2>(p, sh, smem_raw, 1 << act_layout_of(type0), warp, lane);
     const ActView av = act_view(p, smem_raw);
     const float rs = mv_rms_scale(p, sh);
-    int pos = 0, page = 0;      // QKV epilogue inputs: fetched here, consumed only after the first tile (no round trip left in the epilogue)
-    if (p.mode == MV_QKV) { pos = *p.pos_ptr; page = p.block_table[pos / p.block_tokens]; }
     if (threadIdx.x == 0) tl_stamp(p.tl, 2);
+    float4* part = reinterpret_cast<float4*>(smem_raw + p.part_off);
     switch (type0) {
-        case T_Q4_K: consume<T_Q4_K, ACT2>(p, work, sh, ring, av, rs, pos, page, warp, lane); break;
-        case T_Q6_K: consume<T_Q6_K, ACT2>(p, work, sh, ring, av, rs, pos, page, warp, lane); break;
-        case T_Q8_0: consume<T_Q8_0, ACT2>(p, work, sh, ring, av, rs, pos, page, warp, lane); break;
-        case T_Q4_0: consume<T_Q4_0, ACT2>(p, work, sh, ring, av, rs, pos, page, warp, lane); break;
-        case T_Q5_K: consume<T_Q5_K, ACT2>(p, work, sh, ring, av, rs, pos, page, warp, lane); break;
+        case T_Q4_K: consume<T_Q4_K, ACT2>(p, work, sh, ring, part, av, rs, pos, page, warp, lane); break;
+        case T_Q6_K: consume<T_Q6_K, ACT2>(p, work, sh, ring, part, av, rs, pos, page, warp, lane); break;
+        case T_Q8_0: consume<T_Q8_0, ACT2>(p, work, sh, ring, part, av, rs, pos, page, warp, lane); break;
+        case T_Q4_0: consume<T_Q4_0, ACT2>(p, work, sh, ring, part, av, rs, pos, page, warp, lane); break;
+        case T_Q5_K: consume<T_Q5_K, ACT2>(p, work, sh, ring, part, av, rs, pos, page, warp, lane); break;
     }
-    if (p.tl) { __syncthreads(); if (threadIdx.x == 0) tl_stamp(p.tl, 3); }
+    if (p.tl) { named_bar_sync(1, NCW * 32); if (threadIdx.x == 0) tl_stamp(p.tl, 3); }
 }
 
 // ---------------------------------------------------------------- host side
 static int g_stage_cap = 0;      // B2_MV_STAGES (tuning): read once in mv_init
+static int g_n_prod = NPROD;     // B2_MV_PROD (tuning)
 
-cudaError_t mv_init() {   // per device: allow > 48 KB dynamic shared memory; read the tuning knob once
+cudaError_t mv_init() {   // per device: allow > 48 KB dynamic shared memory; read the tuning knobs once
     static bool env_read = false;
     if (!env_read) {
         if (const char* s = getenv("B2_MV_STAGES")) g_stage_cap = atoi(s);
+        if (const char* s = getenv("B2_MV_PROD")) { const int v = atoi(s); if (v >= 1 && v <= NPROD) g_n_prod = v; }
         env_read = true;
     }
     cudaError_t e = cudaFuncSetAttribute(matvec_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, MV_SMEM_MAX);
@@ -469,40 +471,41 @@ cudaError_t mv_init() {   // per device: allow > 48 KB dynamic shared memory; re
 
 int mv_plan(MvParams& p, int n_ctas) {
     if (p.K % 256 || p.K <= 0) return -1;
-    p.n_slices = (p.K + B2_SLICE - 1) / B2_SLICE;
-    if (p.n_slices > NCW) return -2;                       // one warp team per K-slice: K <= 32768
-    int max_row = 0;
+    if (p.K > 32768) return -2;
+    int max_sb = 0;
     for (int s = 0; s < p.nseg; s++) {
         MvSeg& sg = p.seg[s];
         const int be = block_elems(sg.type), bb = block_bytes(sg.type);
         if (!bb || be == 1) return -3;
         sg.row_bytes = p.K / be * bb;
         if (sg.n_rows % 2) return -4;
-        max_row = sg.row_bytes > max_row ? sg.row_bytes : max_row;
+        int sb = slice_bytes(sg.type);
+        if (sb > sg.row_bytes) sb = sg.row_bytes;
+        max_sb = sb > max_sb ? sb : max_sb;
     }
     if (p.mode == MV_GATEUP) {
         if (p.nseg != 2 || p.seg[0].n_rows != p.seg[1].n_rows) return -6;
         if (p.seg[0].type != p.seg[1].type) return -8;     // a mixed pair is run unfused by the caller
     }
-    // activation block: [plane a][plane b][K/8 floats of packed scales]
+    p.n_slices = (p.K + B2_SLICE - 1) / B2_SLICE;
+    p.slot_bytes = (max_sb + 16 + 15) / 16 * 16;           // + slack for the 16-byte alignment of each copy
+    p.stage_bytes = (R * p.slot_bytes + 127) / 128 * 128;
+    // shared memory: [header][plane a][plane b][K/8 floats of packed scales][partial-sum slots][ring]
     p.act_plane = p.n_slices * B2_SLICE;
     const int act_block = (2 * p.act_plane + p.K / 2 + 127) / 128 * 128;
+    const int tpg = p.n_slices * (p.mode == MV_GATEUP ? 2 : 1);
     p.act_off = MV_SHARED_HDR;
-    p.ring_off = MV_SHARED_HDR + act_block;
-    // a tile = a row pair (ONE copy of 2 * row_bytes); single rows when pairs of very long rows would leave < 4 stages
-    p.nrows = 2;
-    p.stage_bytes = (2 * max_row + 32 + 127) / 128 * 128;  // + slack: the copy starts / ends on 16-byte boundaries
+    p.part_off = MV_SHARED_HDR + act_block;
+    p.ring_off = p.part_off + (tpg > 1 ? MV_GSLOTS * tpg * 16 : 0);
+    p.ring_off = (p.ring_off + 127) / 128 * 128;
     int S = (MV_SMEM_MAX - p.ring_off) / p.stage_bytes;
-    if (S < 4 && (p.mode == MV_STORE || p.mode == MV_RESID)) {
-        p.nrows = 1;
-        p.stage_bytes = (max_row + 32 + 127) / 128 * 128;
-        S = (MV_SMEM_MAX - p.ring_off) / p.stage_bytes;
-    }
     if (S > MV_MAX_STAGES) S = MV_MAX_STAGES;
-    if (g_stage_cap >= 2 && g_stage_cap < S) S = g_stage_cap;
-    if (S < 2) return -5;
+    if (g_stage_cap >= TPB && g_stage_cap < S) S = g_stage_cap;
+    if (S < TPB) return -5;                                // a producer warp fills TPB stages per round
+    p.n_prod = g_n_prod;
+    if (S < TPB * p.n_prod) p.n_prod = 1;
+    S -= S % p.n_prod;                                     // every stage belongs to one producer (entry % n_prod)
     p.n_stages = S;
-    p.inv_stages = 0xFFFFFFFFu / (unsigned)S + 1u;
     // CTA split proportional to bytes (gate/up: every CTA handles both matrices)
     if (p.mode == MV_GATEUP) {
         p.seg[0].cta0 = p.seg[1].cta0 = 0; p.seg[0].ncta = p.seg[1].ncta = n_ctas;
@@ -527,7 +530,7 @@ int mv_plan(MvParams& p, int n_ctas) {
     return 0;
 }
 
-int mv_ctas_per_sm() { return MV_CTAS_PER_SM; }
+int mv_ctas_per_sm() { return 1; }
 size_t mv_smem_bytes(const MvParams& p) { return (size_t)p.ring_off + (size_t)p.n_stages * p.stage_bytes; }
 
 cudaError_t mv_launch(const MvParams& p, int n_ctas, cudaStream_t stream, bool act2, bool pdl) {

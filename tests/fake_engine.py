@@ -16,7 +16,7 @@ class FakeEngine:
     eos_token = None
     fail_with = None     # raise this from prefill (error propagation tests)
 
-    def __init__(self, gguf, n_ctx, max_seqs=1, device=0, kv_block_tokens=64, flags=0, verbose=False):
+    def __init__(self, gguf, n_ctx, max_seqs=1, device=0, kv_block_tokens=64, flags=0, verbose=False, tp=None):
         md = gguf.metadata
         n_embd, n_head = int(md["llama.embedding_length"]), int(md["llama.attention.head_count"])
         self.dims = ModelDims(int(md["llama.block_count"]), n_embd, n_head,
