@@ -31,8 +31,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(HERE, "..", "include", "b200_gguf.h")]
     out = os.path.join(LIB, "libb200gguf.so")
-    if force or _newer(out, deps):
-        extra = os.environ.get("B2_NVCC_EXTRA", "").split()
+    extra = os.environ.get("B2_NVCC_EXTRA", "").split()
+    if force or extra or _newer(out, deps):      # experiment flags: always rebuild (the up-to-date check knows nothing of flags)
         headers = [d for d in deps if not d.endswith(".cu")]
 
         def compile_one(src):

@@ -7,10 +7,11 @@
 // and serves all G = n_head / n_kv query heads of that KV head from a single read of K and V
 // (GQA-aware). KV pages are [n_kv][block_tokens][head_dim] f16, so the tokens of one page for one
 // KV head are one contiguous run: thread 0 brings 64-token tiles into shared memory with 1-D TMA
-// bulk copies (double buffered, mbarrier complete_tx) while the others work on the previous tile:
-//   phase 1  scores s[g][j] = scale * q_g . k_j    thread <-> (position, quarter of head_dim)
-//   phase 2  online softmax per head (warp per head): running max / sum, rescale factor
-//   phase 3  o_g += p[g][j] * v_j                  thread <-> (pair of output dims, head set)
+// bulk copies (double buffered, mbarrier complete_tx). Inside a tile every warp is a flash-decode of its
+// own over 8 of the 64 positions, a lane owning head_dim / 32 dims (attention_body.cuh): scores of 4 heads x 8
+// positions reduced over the lanes by one transposed butterfly, online softmax inside 8-lane groups, o += p . v
+// with the probabilities passed by shuffle; running max / sum / output stay in registers across tiles and the
+// eight warps are merged once at the end. No block-wide barrier between those steps.
 // Merging the splits:
 //   * n_splits = 2, 4 or 8 (default 8): the splits of one KV head form a thread-block CLUSTER; partials stay
 //     in shared memory and are merged through distributed shared memory after one cluster barrier.
@@ -39,7 +40,10 @@ __global__ void __launch_bounds__(AT_THREADS) attn_decode_kernel(const AttnParam
     __syncthreads();
     if (threadIdx.x == 0) tl_stamp(p.tl, 0);
     griddep_launch();
-    if (!p.early) griddep_wait();     // q and this token's K/V come from the QKV kernel just before us
+    if (!p.early) {
+        griddep_wait();     // q and this token's K/V come from the QKV kernel just before us
+        if (threadIdx.x == 0) tl_stamp(p.tl, 1);
+    }
     uint32_t use[2] = {0u, 0u};
     attn_decode_body<HD, CLUSTER>(p, sh, full, use, blockIdx.x, blockIdx.y, threadIdx.x, p.early != 0);
     if (p.tl) { __syncthreads(); if (threadIdx.x == 0) tl_stamp(p.tl, 3); }

@@ -11,29 +11,55 @@ namespace cg = cooperative_groups;
 namespace b2 {
 
 constexpr int AT_THREADS = 256;
+constexpr int AT_WARPS = AT_THREADS / 32;
 constexpr int AT_TT = 64;      // positions per tile
+constexpr int AT_WT = AT_TT / AT_WARPS;   // positions of a tile served by one warp
 constexpr int AT_GMAX = 8;     // query heads per KV head
 constexpr int AT_MAX_PAGES = 512;
 constexpr int AT_BAR = 2;      // named barrier used by the 256 attention threads
+static_assert(AT_WT == 8, "the score reduction is written for 4 heads x 8 positions = 32 values per warp pass");
 
 template <int HD>
 struct __align__(16) AttnShared {
-    __half k[2][AT_TT][HD];
+    __half k[2][AT_TT][HD];            // after the last tile: the warps' un-normalised outputs, float [AT_WARPS][G][HD]
     __half v[2][AT_TT][HD];
-    float q[AT_GMAX][HD];
     float part[AT_GMAX * HD + 8];      // cluster merge: slice [r * per, (r+1) * per) = what split r sent us (its un-normalised outputs of OUR elements)
     float part_ml[8][AT_GMAX][2];      // cluster merge: (running max, running sum) of every head from every split
-    float sc[4][AT_GMAX][AT_TT];       // per head_dim-quarter partial scores; sc[0] then holds p
-    float m_run[AT_GMAX], l_run[AT_GMAX], alpha[AT_GMAX];
+    float sc[4][AT_GMAX][AT_TT];       // staging: the warps' (max, sum) per head, then the global-scratch merge weights
+    float m_run[AT_GMAX], l_run[AT_GMAX];
     int pages[AT_MAX_PAGES];
     unsigned int ticket;
 };
+static_assert(sizeof(float) * AT_WARPS * AT_GMAX * 128 <= sizeof(__half) * 2 * AT_TT * 128, "warp outputs alias the K tiles");
 
+// Sum 32 per-lane values over the 32 lanes so that lane i ends up with the total of value i (transposed butterfly:
+// 31 shuffles instead of 32 x 5).
+__device__ __forceinline__ float lanes_transpose_sum(float (&v)[32], int lane) {
+    const bool h16 = lane & 16, h8 = lane & 8, h4 = lane & 4, h2 = lane & 2, h1 = lane & 1;
+    float a[16], b[8], c[4], d[2];
+#pragma unroll
+    for (int i = 0; i < 16; i++) a[i] = (h16 ? v[i + 16] : v[i]) + __shfl_xor_sync(0xffffffffu, h16 ? v[i] : v[i + 16], 16);
+#pragma unroll
+    for (int i = 0; i < 8; i++) b[i] = (h8 ? a[i + 8] : a[i]) + __shfl_xor_sync(0xffffffffu, h8 ? a[i] : a[i + 8], 8);
+#pragma unroll
+    for (int i = 0; i < 4; i++) c[i] = (h4 ? b[i + 4] : b[i]) + __shfl_xor_sync(0xffffffffu, h4 ? b[i] : b[i + 4], 4);
+#pragma unroll
+    for (int i = 0; i < 2; i++) d[i] = (h2 ? c[i + 2] : c[i]) + __shfl_xor_sync(0xffffffffu, h2 ? c[i] : c[i + 2], 2);
+    return (h1 ? d[1] : d[0]) + __shfl_xor_sync(0xffffffffu, h1 ? d[0] : d[1], 1);
+}
 
 // The whole per-CTA job: split `sp` of KV head `h`. Runs on AT_THREADS threads (tid 0..255) that
-// synchronise on named barrier AT_BAR, so it can be a kernel of its own or a phase of the persistent
-// decode kernel (mega.cu). `full` are two mbarriers that live across calls; `use` counts how often
+// synchronise on named barrier AT_BAR. `full` are two mbarriers that live across calls; `use` counts how often
 // each has completed (the caller keeps it; every thread holds the same value).
+//
+// Inside a tile every warp is a flash-decode of its own: warp w serves positions 8w .. 8w+7 of the tile, a lane
+// owns head_dim / 32 adjacent dims. Scores of 4 heads x 8 positions are 32 per-lane partial dot products, summed
+// over the lanes with one transposed butterfly (lane i gets score i); max / sum over the 8 positions of a head are
+// three shuffles inside an 8-lane group; the probabilities go back out by shuffle for o += p . v. Running max, sum
+// and output stay in registers across tiles; there is no block-wide barrier between the phases (the first version
+// had three per tile and took ~2.5 us per 64-position tile; measured inside the decode chain). The eight warps'
+// results are merged once, through shared memory, before the splits are.
+//
 // `early`: the body is entered BEFORE griddepcontrol.wait (programmatic dependent launch). Position and page table are
 // already valid then (the kernel that writes q and this token's K/V row lets us start only after ITS dependency wait,
 // MvParams::trigger_late), so the K/V tiles of the older positions are requested first and the wait happens inside,
@@ -41,17 +67,14 @@ struct __align__(16) AttnShared {
 template <int HD, bool CLUSTER>
 __device__ __forceinline__ void attn_decode_body(const AttnParams& p, AttnShared<HD>& sh, uint64_t* full, uint32_t (&use)[2],
                                                  int sp, int h, int tid, bool early = false) {
+    constexpr int DPL = HD / 32;                  // dims per lane
     const int warp = tid >> 5, lane = tid & 31;
     const int G = p.n_head / p.n_kv;
     const int bt = p.block_tokens;
 
-    if (tid < AT_GMAX) { sh.m_run[tid] = -INFINITY; sh.l_run[tid] = 0.f; sh.alpha[tid] = 0.f; }
-
-    // one round trip: position and page table (and q, unless it is still being written)
+    // one round trip: position and page table
     const int pos = *p.pos_ptr;
     for (int i = tid; i < p.max_pages && i < AT_MAX_PAGES; i += AT_THREADS) sh.pages[i] = p.block_table[i];
-    if (!early)
-        for (int i = tid; i < G * HD; i += AT_THREADS) sh.q[i / HD][i % HD] = __ldcg(p.q + (size_t)h * G * HD + i);   // written by other SMs
     // never index past the page ids that were staged above, whatever the caller's position says
     const int ctx = min(pos + 1, min(p.max_pages, AT_MAX_PAGES) * bt);
     int chunk = (ctx + p.n_splits - 1) / p.n_splits;
@@ -86,22 +109,49 @@ __device__ __forceinline__ void attn_decode_body(const AttnParams& p, AttnShared
     if (early) {
         griddep_wait();     // q and the newest K/V row (position pos) are complete from here on
         if (tid == 0) tl_stamp(p.tl, 1);
-        for (int i = tid; i < G * HD; i += AT_THREADS) sh.q[i / HD][i % HD] = __ldcg(p.q + (size_t)h * G * HD + i);
         if (tid == 0 && pos >= p0 && pos < min(p1, p0 + n_early * AT_TT)) {
             const int ti = (pos - p0) / AT_TT;
             copy_rows(ti & 1, p0 + ti * AT_TT, pos, pos + 1);
         }
-        named_bar_sync(AT_BAR, AT_THREADS);
     }
 
-    // phase-3 ownership: a pair of output dims for a set of heads
-    constexpr int NSET3 = AT_THREADS / (HD / 2);
-    constexpr int HG3 = (AT_GMAX + NSET3 - 1) / NSET3;
-    const int dpair = tid % (HD / 2), set3 = tid / (HD / 2);
-    const int hg3 = (G + NSET3 - 1) / NSET3;          // heads per thread set
-    float acc[HG3][2];
+    // this lane's dims of every query head, scaled (written by other SMs: L2)
+    float qr[AT_GMAX][DPL];
 #pragma unroll
-    for (int i = 0; i < HG3; i++) acc[i][0] = acc[i][1] = 0.f;
+    for (int g = 0; g < AT_GMAX; g++) {
+#pragma unroll
+        for (int d = 0; d < DPL; d++) qr[g][d] = 0.f;
+        if (g < G) {
+            const float* qp = p.q + ((size_t)h * G + g) * HD + DPL * lane;
+            if (DPL == 4) { const float4 t = __ldcg(reinterpret_cast<const float4*>(qp)); qr[g][0] = t.x; qr[g][1] = t.y; qr[g][2] = t.z; qr[g][DPL - 1] = t.w; }
+            else { const float2 t = __ldcg(reinterpret_cast<const float2*>(qp)); qr[g][0] = t.x; qr[g][1] = t.y; }
+#pragma unroll
+            for (int d = 0; d < DPL; d++) qr[g][d] *= p.scale;
+        }
+    }
+    float o[AT_GMAX][DPL];
+#pragma unroll
+    for (int g = 0; g < AT_GMAX; g++)
+#pragma unroll
+        for (int d = 0; d < DPL; d++) o[g][d] = 0.f;
+    float m_run[2] = {-INFINITY, -INFINITY}, l_run[2] = {0.f, 0.f};     // of head 4 * pass + lane / 8 (the same in the 8 lanes of a group)
+    const int gg_l = lane >> 3, jj_l = lane & 7;
+
+    // rows of a tile as floats: this lane's DPL dims of the warp's 8 positions (rows past the tile's end read the last valid row: finite data, weight 0)
+    auto load_rows = [&](const __half (*tile)[HD], int j0, int tl, float (&f)[AT_WT][DPL]) {
+#pragma unroll
+        for (int jj = 0; jj < AT_WT; jj++) {
+            const __half* r = &tile[min(j0 + jj, tl - 1)][DPL * lane];
+            if (DPL == 4) {
+                const uint2 raw = *reinterpret_cast<const uint2*>(r);
+                const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&raw.x)), b = __half22float2(*reinterpret_cast<const __half2*>(&raw.y));
+                f[jj][0] = a.x; f[jj][1] = a.y; f[jj][2] = b.x; f[jj][DPL - 1] = b.y;
+            } else {
+                const float2 a = __half22float2(*reinterpret_cast<const __half2*>(r));
+                f[jj][0] = a.x; f[jj][1] = a.y;
+            }
+        }
+    };
 
     for (int ti = 0; ti < ntile; ti++) {
         const int st = ti & 1;
@@ -109,79 +159,118 @@ __device__ __forceinline__ void attn_decode_body(const AttnParams& p, AttnShared
         if (tid == 0 && ti + 1 < ntile && ti + 1 >= n_early) issue(ti + 1, 0x7fffffff);
         mbar_wait(&full[st], use[st] & 1, p.err, 0x20001u, (unsigned)ti);
         use[st]++;
-
-        // ---- phase 1: partial scores over a quarter of head_dim, all G heads
-        {
-            const int j = tid & 63, dq = tid >> 6;
-            constexpr int CPQ = HD / 32;                  // 16-byte chunks per quarter
-            float s[AT_GMAX];
+        const int j0 = warp * AT_WT;
+        if (j0 < tl) {                                   // warp-uniform
+            float rows[AT_WT][DPL];
+            load_rows(sh.k[st], j0, tl, rows);
+            float s[2] = {-INFINITY, -INFINITY};
 #pragma unroll
-            for (int g = 0; g < AT_GMAX; g++) s[g] = 0.f;
-            if (j < tl) {
-                const uint4* kr = reinterpret_cast<const uint4*>(&sh.k[st][j][0]);
+            for (int pass = 0; pass < 2; pass++) {
+                if (4 * pass < G) {
+                    float v[32];
 #pragma unroll
-                for (int c = 0; c < CPQ; c++) {
-                    int cc = dq * CPQ + ((c + j) & (CPQ - 1));   // rotate inside the quarter: fewer bank conflicts
-                    uint4 kv = kr[cc];
-                    const __half2* k2 = reinterpret_cast<const __half2*>(&kv);
-                    float2 f0 = __half22float2(k2[0]), f1 = __half22float2(k2[1]);
-                    float2 f2 = __half22float2(k2[2]), f3 = __half22float2(k2[3]);
+                    for (int gg = 0; gg < 4; gg++)
 #pragma unroll
-                    for (int g = 0; g < AT_GMAX; g++) {
-                        if (g < G) {
-                            const float4* q4 = reinterpret_cast<const float4*>(&sh.q[g][cc * 8]);
-                            float4 qa = q4[0], qb = q4[1];
-                            s[g] += f0.x * qa.x + f0.y * qa.y + f1.x * qa.z + f1.y * qa.w
-                                  + f2.x * qb.x + f2.y * qb.y + f3.x * qb.z + f3.y * qb.w;
+                        for (int jj = 0; jj < AT_WT; jj++) {
+                            float t = 0.f;
+#pragma unroll
+                            for (int d = 0; d < DPL; d++) t += qr[4 * pass + gg][d] * rows[jj][d];
+                            v[gg * 8 + jj] = t;
                         }
-                    }
+                    const float tot = lanes_transpose_sum(v, lane);
+                    s[pass] = (j0 + jj_l < tl && 4 * pass + gg_l < G) ? tot : -INFINITY;
                 }
             }
+            load_rows(sh.v[st], j0, tl, rows);
 #pragma unroll
-            for (int g = 0; g < AT_GMAX; g++)
-                if (g < G) sh.sc[dq][g][j] = s[g];
-        }
-        named_bar_sync(AT_BAR, AT_THREADS);
-        // ---- phase 2: online softmax, one warp per head
-        for (int g = warp; g < G; g += AT_THREADS / 32) {
-            float v0 = (sh.sc[0][g][lane] + sh.sc[1][g][lane]) + (sh.sc[2][g][lane] + sh.sc[3][g][lane]);
-            float v1 = (sh.sc[0][g][lane + 32] + sh.sc[1][g][lane + 32]) + (sh.sc[2][g][lane + 32] + sh.sc[3][g][lane + 32]);
-            v0 = (lane < tl) ? v0 * p.scale : -INFINITY;
-            v1 = (lane + 32 < tl) ? v1 * p.scale : -INFINITY;
-            float mx = warp_max(fmaxf(v0, v1));
-            float m_old = sh.m_run[g], m_new = fmaxf(m_old, mx);
-            float e0 = (v0 == -INFINITY) ? 0.f : expf(v0 - m_new);
-            float e1 = (v1 == -INFINITY) ? 0.f : expf(v1 - m_new);
-            float sum = warp_sum(e0 + e1);
-            sh.sc[0][g][lane] = e0; sh.sc[0][g][lane + 32] = e1;
-            if (lane == 0) {
-                float al = (m_old == -INFINITY) ? 0.f : expf(m_old - m_new);
-                sh.alpha[g] = al;
-                sh.l_run[g] = sh.l_run[g] * al + sum;
-                sh.m_run[g] = m_new;
-            }
-        }
-        named_bar_sync(AT_BAR, AT_THREADS);
-        // ---- phase 3: o += p . v
+            for (int pass = 0; pass < 2; pass++) {
+                if (4 * pass < G) {
+                    float mx = s[pass];
+                    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 4));
+                    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+                    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+                    const float m_new = fmaxf(m_run[pass], mx);
+                    const float pj = (s[pass] == -INFINITY) ? 0.f : expf(s[pass] - m_new);
+                    float sum = pj;
+                    sum += __shfl_xor_sync(0xffffffffu, sum, 4);
+                    sum += __shfl_xor_sync(0xffffffffu, sum, 2);
+                    sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+                    const float alpha = (m_run[pass] == -INFINITY) ? 0.f : expf(m_run[pass] - m_new);
+                    l_run[pass] = l_run[pass] * alpha + sum;
+                    m_run[pass] = m_new;
 #pragma unroll
-        for (int i = 0; i < HG3; i++) {
-            int g = set3 * hg3 + i;
-            if (i < hg3 && g < G) { float al = sh.alpha[g]; acc[i][0] *= al; acc[i][1] *= al; }
-        }
-#pragma unroll 4
-        for (int j = 0; j < tl; j++) {
-            float2 vv = __half22float2(*reinterpret_cast<const __half2*>(&sh.v[st][j][2 * dpair]));
+                    for (int gg = 0; gg < 4; gg++) {
+                        const float al = __shfl_sync(0xffffffffu, alpha, gg * 8);
 #pragma unroll
-            for (int i = 0; i < HG3; i++) {
-                int g = set3 * hg3 + i;
-                if (i < hg3 && g < G) { float pj = sh.sc[0][g][j]; acc[i][0] += pj * vv.x; acc[i][1] += pj * vv.y; }
+                        for (int d = 0; d < DPL; d++) o[4 * pass + gg][d] *= al;
+                    }
+#pragma unroll
+                    for (int jj = 0; jj < AT_WT; jj++)
+#pragma unroll
+                        for (int gg = 0; gg < 4; gg++) {
+                            const float pv = __shfl_sync(0xffffffffu, pj, gg * 8 + jj);
+#pragma unroll
+                            for (int d = 0; d < DPL; d++) o[4 * pass + gg][d] += pv * rows[jj][d];
+                        }
+                }
             }
         }
         fence_proxy_async();                   // this thread's reads of the tile before the next TMA (async proxy) rewrites it
-        named_bar_sync(AT_BAR, AT_THREADS);    // tile buffers and sc[] are free again
+        named_bar_sync(AT_BAR, AT_THREADS);    // the tile buffer is free again
+    }
+
+    // ---------------------------------------------------------------- merge the warps
+    // phase ownership of the merges: a pair of output dims for a set of heads
+    constexpr int NSET3 = AT_THREADS / (HD / 2);
+    constexpr int HG3 = (AT_GMAX + NSET3 - 1) / NSET3;
+    const int dpair = tid % (HD / 2), set3 = tid / (HD / 2);
+    const int hg3 = (G + NSET3 - 1) / NSET3;          // heads per thread set
+    float acc[HG3][2];
+    {
+        float* wo = reinterpret_cast<float*>(&sh.k[0][0][0]);       // [AT_WARPS][G][HD]; every tile has been consumed (barrier above)
+        float* wm = &sh.sc[0][0][0];                                // [AT_WARPS][AT_GMAX]
+        float* wl = wm + AT_WARPS * AT_GMAX;
+#pragma unroll
+        for (int g = 0; g < AT_GMAX; g++) {
+            if (g < G) {
+                float* dst = wo + ((size_t)warp * G + g) * HD + DPL * lane;
+                if (DPL == 4) *reinterpret_cast<float4*>(dst) = make_float4(o[g][0], o[g][1], o[g][2], o[g][DPL - 1]);
+                else *reinterpret_cast<float2*>(dst) = make_float2(o[g][0], o[g][1]);
+            }
+        }
+        if (jj_l == 0) {
+#pragma unroll
+            for (int pass = 0; pass < 2; pass++) {
+                const int g = 4 * pass + gg_l;
+                if (g < G) { wm[warp * AT_GMAX + g] = m_run[pass]; wl[warp * AT_GMAX + g] = l_run[pass]; }
+            }
+        }
+        named_bar_sync(AT_BAR, AT_THREADS);
+#pragma unroll
+        for (int i = 0; i < HG3; i++) {
+            acc[i][0] = acc[i][1] = 0.f;
+            const int g = set3 * hg3 + i;
+            if (i < hg3 && g < G) {
+                float M = -INFINITY;
+#pragma unroll
+                for (int w = 0; w < AT_WARPS; w++) M = fmaxf(M, wm[w * AT_GMAX + g]);
+                float l = 0.f;
+#pragma unroll
+                for (int w = 0; w < AT_WARPS; w++) {
+                    const float mw = wm[w * AT_GMAX + g];
+                    const float wgt = (mw == -INFINITY) ? 0.f : expf(mw - M);
+                    const float2 ov = *reinterpret_cast<const float2*>(wo + ((size_t)w * G + g) * HD + 2 * dpair);
+                    acc[i][0] += wgt * ov.x; acc[i][1] += wgt * ov.y;
+                    l += wgt * wl[w * AT_GMAX + g];
+                }
+                if (dpair == 0) { sh.m_run[g] = M; sh.l_run[g] = l; }
+            }
+        }
+        named_bar_sync(AT_BAR, AT_THREADS);     // m_run / l_run of the CTA are published; the staging in sc[] is free
     }
 
     // ---------------------------------------------------------------- merge the splits
+    if (tid == 0) tl_stamp(p.tl, 2);
     if (p.n_splits == 1) {
 #pragma unroll
         for (int i = 0; i < HG3; i++) {
@@ -276,7 +365,7 @@ __device__ __forceinline__ void attn_decode_body(const AttnParams& p, AttnShared
             wsp[tid * p.n_splits + s2] = w;
             den += w * lsp[tid * p.n_splits + s2];
         }
-        sh.alpha[tid] = 1.0f / den;
+        sh.l_run[tid] = 1.0f / den;      // (this CTA's own sum went to the scratch record above)
     }
     named_bar_sync(AT_BAR, AT_THREADS);
 #pragma unroll
@@ -291,7 +380,7 @@ __device__ __forceinline__ void attn_decode_body(const AttnParams& p, AttnShared
                 float w = wsp[g * p.n_splits + s2];
                 n0 += w * a2.x; n1 += w * a2.y;
             }
-            float inv = sh.alpha[g];
+            float inv = sh.l_run[g];
             float* o = p.out + ((size_t)h * G + g) * HD + 2 * dpair;
             o[0] = n0 * inv; o[1] = n1 * inv;
         }

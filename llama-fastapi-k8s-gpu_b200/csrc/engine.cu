@@ -93,6 +93,7 @@ struct b2_engine {
     int64_t launches = 0, weight_bytes = 0, kv_bytes = 0;
     bool use_graph = true, use_pdl = true, act2 = true, finalized = false, chain_pdl = true;
     int batch_attn_splits = 0;     // B2_BATCH_ATTN_SPLITS (tuning), read once at create
+    int attn_early = 1;            // B2_ATTN_EARLY=0 (tuning): attention requests nothing before its dependency wait
     // tensor parallelism (b2_engine_tp_init): this engine holds 1 / tp_world of the heads, FFN rows and vocabulary rows
     void* tp_comm = nullptr;
     int tp_rank = 0, tp_world = 1;
@@ -183,6 +184,7 @@ static int engine_create_impl(b2_engine* e, const b2_config* c) {
     // tuning knobs are read here, once; the hot path never calls getenv
     e->chain_pdl = e->use_pdl && !getenv("B2_NO_CHAIN_PDL");
     if (const char* s = getenv("B2_BATCH_ATTN_SPLITS")) e->batch_attn_splits = atoi(s);
+    if (const char* s = getenv("B2_ATTN_EARLY")) e->attn_early = atoi(s);
     if (getenv("B2_TIMELINE")) CK(cudaMalloc(&e->tl, sizeof(unsigned long long) * 4 * 1024));
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
@@ -494,7 +496,7 @@ static int forward_launches(b2_engine* e, Slot& s, bool with_head, bool with_sam
         MvParams q = L.p_qkv;
         q.x = s.x; q.q_out = s.q; q.pos_ptr = pos; q.block_table = s.block_table;
         const bool attn_plain = !(e->attn_mma == 1 || (e->attn_mma < 0 && e->n_splits > 8));
-        q.trigger_late = pdl && attn_plain;      // attention may start once we are past our own wait: it prefetches old K/V rows
+        q.trigger_late = pdl && attn_plain && e->attn_early;      // attention may start once we are past our own wait: it prefetches old K/V rows
         q.tl = next_tl();
         tick(1, &ye);
         CK(mv_launch(q, e->n_ctas, st, e->act2, pdl));
