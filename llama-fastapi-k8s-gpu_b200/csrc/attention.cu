@@ -31,10 +31,10 @@ size_t attn_scratch_floats(int n_head, int n_kv, int head_dim, int n_splits) {
     return (size_t)n_head * n_splits * (head_dim + 2);
 }
 
-template <int HD, bool CLUSTER>
-__global__ void __launch_bounds__(AT_THREADS) attn_decode_kernel(const AttnParams p) {
+template <int HD, bool CLUSTER, int NP>
+__global__ void __launch_bounds__(at_threads(NP)) attn_decode_kernel(const AttnParams p) {
     extern __shared__ __align__(128) uint8_t smem_raw[];
-    AttnShared<HD>& sh = *reinterpret_cast<AttnShared<HD>*>(smem_raw);
+    AttnShared<HD, at_tt(NP)>& sh = *reinterpret_cast<AttnShared<HD, at_tt(NP)>*>(smem_raw);
     __shared__ uint64_t full[2];
     if (threadIdx.x == 0) { mbar_init(&full[0], 1); mbar_init(&full[1], 1); fence_mbar_init(); }
     __syncthreads();
@@ -42,18 +42,21 @@ __global__ void __launch_bounds__(AT_THREADS) attn_decode_kernel(const AttnParam
     griddep_launch();
     if (!p.early) {
         griddep_wait();     // q and this token's K/V come from the QKV kernel just before us
-        if (threadIdx.x == 0) tl_stamp(p.tl, 1);
+        if (threadIdx.x == 0 && (B2_ATTN_ONE_CTA < 0 || (int)(blockIdx.y * gridDim.x + blockIdx.x) == B2_ATTN_ONE_CTA)) tl_stamp(p.tl, 1);
     }
     uint32_t use[2] = {0u, 0u};
-    attn_decode_body<HD, CLUSTER>(p, sh, full, use, blockIdx.x, blockIdx.y, threadIdx.x, p.early != 0);
-    if (p.tl) { __syncthreads(); if (threadIdx.x == 0) tl_stamp(p.tl, 3); }
+    attn_decode_body<HD, CLUSTER, NP>(p, sh, full, use, blockIdx.x, blockIdx.y, threadIdx.x, p.early != 0);
+    if (p.tl) {
+        __syncthreads();
+        if (threadIdx.x == 0 && (B2_ATTN_ONE_CTA < 0 || (int)(blockIdx.y * gridDim.x + blockIdx.x) == B2_ATTN_ONE_CTA)) tl_stamp(p.tl, 3);
+    }
 }
 
 // one launch for several sequences: blockIdx.z picks the sequence
-template <int HD, bool CLUSTER>
-__global__ void __launch_bounds__(AT_THREADS) attn_decode_batch_kernel(const AttnParams p0, const SlotDev* tab, const BatchIdx b) {
+template <int HD, bool CLUSTER, int NP>
+__global__ void __launch_bounds__(at_threads(NP)) attn_decode_batch_kernel(const AttnParams p0, const SlotDev* tab, const BatchIdx b) {
     extern __shared__ __align__(128) uint8_t smem_raw[];
-    AttnShared<HD>& sh = *reinterpret_cast<AttnShared<HD>*>(smem_raw);
+    AttnShared<HD, at_tt(NP)>& sh = *reinterpret_cast<AttnShared<HD, at_tt(NP)>*>(smem_raw);
     __shared__ uint64_t full[2];
     if (threadIdx.x == 0) { mbar_init(&full[0], 1); mbar_init(&full[1], 1); fence_mbar_init(); }
     __syncthreads();
@@ -68,28 +71,51 @@ __global__ void __launch_bounds__(AT_THREADS) attn_decode_batch_kernel(const Att
     p.scratch = p0.scratch + z * qd / p.head_dim * p.n_splits * (p.head_dim + 2);
     p.counters = p0.counters + z * p.n_kv;
     uint32_t use[2] = {0u, 0u};
-    attn_decode_body<HD, CLUSTER>(p, sh, full, use, blockIdx.x, blockIdx.y, threadIdx.x);
+    attn_decode_body<HD, CLUSTER, NP>(p, sh, full, use, blockIdx.x, blockIdx.y, threadIdx.x);
+}
+
+// kernel variants: head_dim x (cluster merge | scratch merge) x (one | two passes of 4 query heads)
+template <int HD>
+static cudaError_t set_smem_attrs() {
+    cudaError_t e;
+#define B2_ATTR(K, NP) if ((e = cudaFuncSetAttribute(K, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AttnShared<HD, at_tt(NP)>))) != cudaSuccess) return e
+    B2_ATTR((attn_decode_kernel<HD, true, 1>), 1); B2_ATTR((attn_decode_kernel<HD, true, 2>), 2);
+    B2_ATTR((attn_decode_kernel<HD, false, 1>), 1); B2_ATTR((attn_decode_kernel<HD, false, 2>), 2);
+    B2_ATTR((attn_decode_batch_kernel<HD, true, 1>), 1); B2_ATTR((attn_decode_batch_kernel<HD, true, 2>), 2);
+    B2_ATTR((attn_decode_batch_kernel<HD, false, 1>), 1); B2_ATTR((attn_decode_batch_kernel<HD, false, 2>), 2);
+#undef B2_ATTR
+    return cudaSuccess;
+}
+template <int HD>
+static cudaError_t launch_one(cudaLaunchConfig_t& cfg, bool cluster, int G, const AttnParams& p) {
+    const int np = G <= 4 ? 1 : 2;
+    cfg.blockDim = dim3(at_threads(np));
+    cfg.dynamicSmemBytes = np == 1 ? sizeof(AttnShared<HD, at_tt(1)>) : sizeof(AttnShared<HD, at_tt(2)>);
+    if (G <= 4) return cluster ? cudaLaunchKernelEx(&cfg, attn_decode_kernel<HD, true, 1>, p) : cudaLaunchKernelEx(&cfg, attn_decode_kernel<HD, false, 1>, p);
+    return cluster ? cudaLaunchKernelEx(&cfg, attn_decode_kernel<HD, true, 2>, p) : cudaLaunchKernelEx(&cfg, attn_decode_kernel<HD, false, 2>, p);
+}
+template <int HD>
+static cudaError_t launch_batch(cudaLaunchConfig_t& cfg, bool cluster, int G, const AttnParams& p, const SlotDev* tab, const BatchIdx& b) {
+    const int np = G <= 4 ? 1 : 2;
+    cfg.blockDim = dim3(at_threads(np));
+    cfg.dynamicSmemBytes = np == 1 ? sizeof(AttnShared<HD, at_tt(1)>) : sizeof(AttnShared<HD, at_tt(2)>);
+    if (G <= 4) return cluster ? cudaLaunchKernelEx(&cfg, attn_decode_batch_kernel<HD, true, 1>, p, tab, b) : cudaLaunchKernelEx(&cfg, attn_decode_batch_kernel<HD, false, 1>, p, tab, b);
+    return cluster ? cudaLaunchKernelEx(&cfg, attn_decode_batch_kernel<HD, true, 2>, p, tab, b) : cudaLaunchKernelEx(&cfg, attn_decode_batch_kernel<HD, false, 2>, p, tab, b);
 }
 
 cudaError_t attn_init() {
     cudaError_t e;
-    if ((e = cudaFuncSetAttribute(attn_decode_kernel<64, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AttnShared<64>))) != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(attn_decode_kernel<64, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AttnShared<64>))) != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(attn_decode_kernel<128, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AttnShared<128>))) != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(attn_decode_kernel<128, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AttnShared<128>))) != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(attn_decode_batch_kernel<64, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AttnShared<64>))) != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(attn_decode_batch_kernel<64, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AttnShared<64>))) != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(attn_decode_batch_kernel<128, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AttnShared<128>))) != cudaSuccess) return e;
-    return cudaFuncSetAttribute(attn_decode_batch_kernel<128, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AttnShared<128>));
+    if ((e = set_smem_attrs<64>()) != cudaSuccess) return e;
+    return set_smem_attrs<128>();
 }
 
 cudaError_t attn_decode_batch_launch(const AttnParams& p, const SlotDev* tab, const BatchIdx& b, cudaStream_t stream) {
     const int G = p.n_kv > 0 ? p.n_head / p.n_kv : 0;
     if (p.n_kv <= 0 || p.n_head % p.n_kv || G > AT_GMAX || b.n < 1 || b.n > BATCH_MAX) return cudaErrorInvalidValue;
-    if (p.n_splits < 1 || G * p.n_splits > AT_GMAX * AT_TT) return cudaErrorInvalidValue;
+    if (p.n_splits < 1 || G * p.n_splits > AT_GMAX * AT_STAGE) return cudaErrorInvalidValue;
     const bool cluster = p.n_splits == 2 || p.n_splits == 4 || p.n_splits == 8;
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(p.n_splits, p.n_kv, b.n); cfg.blockDim = dim3(AT_THREADS); cfg.stream = stream;
+    cfg.gridDim = dim3(p.n_splits, p.n_kv, b.n); cfg.stream = stream;
     cudaLaunchAttribute at[2];
     int na = 0;
     if (g_chain_pdl) {
@@ -104,13 +130,9 @@ cudaError_t attn_decode_batch_launch(const AttnParams& p, const SlotDev* tab, co
     }
     cfg.attrs = at; cfg.numAttrs = na;
     if (p.head_dim == 64) {
-        cfg.dynamicSmemBytes = sizeof(AttnShared<64>);
-        return cluster ? cudaLaunchKernelEx(&cfg, attn_decode_batch_kernel<64, true>, p, tab, b)
-                       : cudaLaunchKernelEx(&cfg, attn_decode_batch_kernel<64, false>, p, tab, b);
+        return launch_batch<64>(cfg, cluster, G, p, tab, b);
     } else if (p.head_dim == 128) {
-        cfg.dynamicSmemBytes = sizeof(AttnShared<128>);
-        return cluster ? cudaLaunchKernelEx(&cfg, attn_decode_batch_kernel<128, true>, p, tab, b)
-                       : cudaLaunchKernelEx(&cfg, attn_decode_batch_kernel<128, false>, p, tab, b);
+        return launch_batch<128>(cfg, cluster, G, p, tab, b);
     }
     return cudaErrorInvalidValue;
 }
@@ -118,10 +140,10 @@ cudaError_t attn_decode_batch_launch(const AttnParams& p, const SlotDev* tab, co
 cudaError_t attn_decode_launch(const AttnParams& p, cudaStream_t stream, bool pdl) {
     const int G = p.n_kv > 0 ? p.n_head / p.n_kv : 0;
     if (p.n_kv <= 0 || p.n_head % p.n_kv || G > AT_GMAX) return cudaErrorInvalidValue;
-    if (p.n_splits < 1 || G * p.n_splits > AT_GMAX * AT_TT) return cudaErrorInvalidValue;   // merge staging fits sc[]
+    if (p.n_splits < 1 || G * p.n_splits > AT_GMAX * AT_STAGE) return cudaErrorInvalidValue;   // merge staging fits sc[]
     const bool cluster = p.n_splits == 2 || p.n_splits == 4 || p.n_splits == 8;
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(p.n_splits, p.n_kv); cfg.blockDim = dim3(AT_THREADS); cfg.stream = stream;
+    cfg.gridDim = dim3(p.n_splits, p.n_kv); cfg.stream = stream;
     cudaLaunchAttribute at[2];
     int na = 0;
     if (pdl) {
@@ -136,13 +158,9 @@ cudaError_t attn_decode_launch(const AttnParams& p, cudaStream_t stream, bool pd
     }
     cfg.attrs = at; cfg.numAttrs = na;
     if (p.head_dim == 64) {
-        cfg.dynamicSmemBytes = sizeof(AttnShared<64>);
-        return cluster ? cudaLaunchKernelEx(&cfg, attn_decode_kernel<64, true>, p)
-                       : cudaLaunchKernelEx(&cfg, attn_decode_kernel<64, false>, p);
+        return launch_one<64>(cfg, cluster, G, p);
     } else if (p.head_dim == 128) {
-        cfg.dynamicSmemBytes = sizeof(AttnShared<128>);
-        return cluster ? cudaLaunchKernelEx(&cfg, attn_decode_kernel<128, true>, p)
-                       : cudaLaunchKernelEx(&cfg, attn_decode_kernel<128, false>, p);
+        return launch_one<128>(cfg, cluster, G, p);
     }
     return cudaErrorInvalidValue;
 }
@@ -208,14 +226,12 @@ cudaError_t attn_decode_launch_static(AttnParams p, int device, cudaStream_t str
     cudaError_t e = cudaMemsetAsync(p.counters, 0, sizeof(unsigned int) * STATIC_MAX_KV_HEADS, stream);
     if (e != cudaSuccess) return e;
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(p.n_splits, p.n_kv); cfg.blockDim = dim3(AT_THREADS); cfg.stream = stream;
+    cfg.gridDim = dim3(p.n_splits, p.n_kv); cfg.stream = stream;
     cfg.attrs = nullptr; cfg.numAttrs = 0;
     if (p.head_dim == 64) {
-        cfg.dynamicSmemBytes = sizeof(AttnShared<64>);
-        return cudaLaunchKernelEx(&cfg, attn_decode_kernel<64, false>, p);
+        return launch_one<64>(cfg, false, p.n_head / p.n_kv, p);
     }
-    cfg.dynamicSmemBytes = sizeof(AttnShared<128>);
-    return cudaLaunchKernelEx(&cfg, attn_decode_kernel<128, false>, p);
+    return launch_one<128>(cfg, false, p.n_head / p.n_kv, p);
 }
 
 }  // namespace b2

@@ -8,29 +8,38 @@
 
 namespace cg = cooperative_groups;
 
+// B2_TIMELINE=1 diagnosis: where timeline slot 2 is taken (1 q in registers, 2 first tile landed, 3 first tile done,
+// 4 all tiles done, 5 warps merged = before the split merge), and optionally for which CTA only (KV head * n_splits + split)
+#ifndef B2_ATTN_STAMP
+#define B2_ATTN_STAMP 5
+#endif
+#ifndef B2_ATTN_ONE_CTA
+#define B2_ATTN_ONE_CTA -1
+#endif
+
 namespace b2 {
 
-constexpr int AT_THREADS = 256;
-constexpr int AT_WARPS = AT_THREADS / 32;
-constexpr int AT_TT = 64;      // positions per tile
-constexpr int AT_WT = AT_TT / AT_WARPS;   // positions of a tile served by one warp
+constexpr int AT_WT = 8;       // positions of a tile served by one warp (the score reduction is written for 4 heads x 8 positions = 32 values)
 constexpr int AT_GMAX = 8;     // query heads per KV head
 constexpr int AT_MAX_PAGES = 512;
-constexpr int AT_BAR = 2;      // named barrier used by the 256 attention threads
-static_assert(AT_WT == 8, "the score reduction is written for 4 heads x 8 positions = 32 values per warp pass");
+constexpr int AT_BAR = 2;      // named barrier used by the attention threads
+constexpr int AT_STAGE = 64;   // floats per head in the merge staging area
+// Positions per tile: 128 with up to 4 query heads per KV head (NP = 1 pass; 16 warps), 64 with up to 8 (NP = 2; 8 warps:
+// the second pass doubles the registers per thread). One warp per 8 positions either way.
+__host__ __device__ constexpr int at_tt(int np) { return np == 1 ? 128 : 64; }
+__host__ __device__ constexpr int at_threads(int np) { return at_tt(np) / AT_WT * 32; }
 
-template <int HD>
+template <int HD, int TT>
 struct __align__(16) AttnShared {
-    __half k[2][AT_TT][HD];            // after the last tile: the warps' un-normalised outputs, float [AT_WARPS][G][HD]
-    __half v[2][AT_TT][HD];
+    __half k[2][TT][HD];               // after the last tile: the warps' un-normalised outputs, float [warps][G][HD]
+    __half v[2][TT][HD];
     float part[AT_GMAX * HD + 8];      // cluster merge: slice [r * per, (r+1) * per) = what split r sent us (its un-normalised outputs of OUR elements)
     float part_ml[8][AT_GMAX][2];      // cluster merge: (running max, running sum) of every head from every split
-    float sc[4][AT_GMAX][AT_TT];       // staging: the warps' (max, sum) per head, then the global-scratch merge weights
+    float sc[4][AT_GMAX][AT_STAGE];    // staging: the warps' (max, sum) per head, then the global-scratch merge weights
     float m_run[AT_GMAX], l_run[AT_GMAX];
     int pages[AT_MAX_PAGES];
     unsigned int ticket;
 };
-static_assert(sizeof(float) * AT_WARPS * AT_GMAX * 128 <= sizeof(__half) * 2 * AT_TT * 128, "warp outputs alias the K tiles");
 
 // Sum 32 per-lane values over the 32 lanes so that lane i ends up with the total of value i (transposed butterfly:
 // 31 shuffles instead of 32 x 5).
@@ -64,13 +73,21 @@ __device__ __forceinline__ float lanes_transpose_sum(float (&v)[32], int lane) {
 // already valid then (the kernel that writes q and this token's K/V row lets us start only after ITS dependency wait,
 // MvParams::trigger_late), so the K/V tiles of the older positions are requested first and the wait happens inside,
 // just before q and the newest row are needed: the copies overlap the tail of the QKV kernel.
-template <int HD, bool CLUSTER>
-__device__ __forceinline__ void attn_decode_body(const AttnParams& p, AttnShared<HD>& sh, uint64_t* full, uint32_t (&use)[2],
+// NP = passes of 4 query heads (G <= 4: 1, else 2) is a compile-time constant and every warp runs every step of a tile,
+// masked, so that the shuffles sit in straight-line code: inside `if (warp has positions)` / `if (4 * pass < G)` the
+// compiler could not prove convergence and turned each shuffle into a WARPSYNC.COLLECTIVE / branch / ENDCOLLECTIVE
+// sequence (127 of them; a 64-position tile took 2.1 us instead of ~0.5).
+template <int HD, bool CLUSTER, int NP>
+__device__ __forceinline__ void attn_decode_body(const AttnParams& p, AttnShared<HD, at_tt(NP)>& sh, uint64_t* full, uint32_t (&use)[2],
                                                  int sp, int h, int tid, bool early = false) {
+    constexpr int AT_TT = at_tt(NP), AT_THREADS = at_threads(NP), AT_WARPS = AT_THREADS / 32;
+    static_assert(AT_WARPS * 4 * NP <= AT_TT, "warp outputs alias the K tiles");
+    static_assert(AT_WARPS * AT_GMAX * 2 <= AT_GMAX * AT_STAGE, "warp (max, sum) staging fits sc[0]");
     constexpr int DPL = HD / 32;                  // dims per lane
     const int warp = tid >> 5, lane = tid & 31;
     const int G = p.n_head / p.n_kv;
     const int bt = p.block_tokens;
+    const bool rec_tl = tid == 0 && (B2_ATTN_ONE_CTA < 0 || h * p.n_splits + sp == B2_ATTN_ONE_CTA);
 
     // one round trip: position and page table
     const int pos = *p.pos_ptr;
@@ -108,7 +125,7 @@ __device__ __forceinline__ void attn_decode_body(const AttnParams& p, AttnShared
         for (int ti = 0; ti < n_early; ti++) issue(ti, early ? pos : 0x7fffffff);
     if (early) {
         griddep_wait();     // q and the newest K/V row (position pos) are complete from here on
-        if (tid == 0) tl_stamp(p.tl, 1);
+        if (rec_tl) tl_stamp(p.tl, 1);
         if (tid == 0 && pos >= p0 && pos < min(p1, p0 + n_early * AT_TT)) {
             const int ti = (pos - p0) / AT_TT;
             copy_rows(ti & 1, p0 + ti * AT_TT, pos, pos + 1);
@@ -116,9 +133,10 @@ __device__ __forceinline__ void attn_decode_body(const AttnParams& p, AttnShared
     }
 
     // this lane's dims of every query head, scaled (written by other SMs: L2)
-    float qr[AT_GMAX][DPL];
+    constexpr int NG = 4 * NP;                    // head slots in registers
+    float qr[NG][DPL];
 #pragma unroll
-    for (int g = 0; g < AT_GMAX; g++) {
+    for (int g = 0; g < NG; g++) {
 #pragma unroll
         for (int d = 0; d < DPL; d++) qr[g][d] = 0.f;
         if (g < G) {
@@ -129,12 +147,15 @@ __device__ __forceinline__ void attn_decode_body(const AttnParams& p, AttnShared
             for (int d = 0; d < DPL; d++) qr[g][d] *= p.scale;
         }
     }
-    float o[AT_GMAX][DPL];
+    if (B2_ATTN_STAMP == 1 && rec_tl && qr[0][0] != 12345.f) tl_stamp(p.tl, 2);
+    float o[NG][DPL];
 #pragma unroll
-    for (int g = 0; g < AT_GMAX; g++)
+    for (int g = 0; g < NG; g++)
 #pragma unroll
         for (int d = 0; d < DPL; d++) o[g][d] = 0.f;
-    float m_run[2] = {-INFINITY, -INFINITY}, l_run[2] = {0.f, 0.f};     // of head 4 * pass + lane / 8 (the same in the 8 lanes of a group)
+    float m_run[NP], l_run[NP];                   // of head 4 * pass + lane / 8 (the same in the 8 lanes of a group)
+#pragma unroll
+    for (int pass = 0; pass < NP; pass++) { m_run[pass] = -INFINITY; l_run[pass] = 0.f; }
     const int gg_l = lane >> 3, jj_l = lane & 7;
 
     // rows of a tile as floats: this lane's DPL dims of the warp's 8 positions (rows past the tile's end read the last valid row: finite data, weight 0)
@@ -159,65 +180,64 @@ __device__ __forceinline__ void attn_decode_body(const AttnParams& p, AttnShared
         if (tid == 0 && ti + 1 < ntile && ti + 1 >= n_early) issue(ti + 1, 0x7fffffff);
         mbar_wait(&full[st], use[st] & 1, p.err, 0x20001u, (unsigned)ti);
         use[st]++;
+        if (B2_ATTN_STAMP == 2 && rec_tl && ti == 0) tl_stamp(p.tl, 2);
         const int j0 = warp * AT_WT;
-        if (j0 < tl) {                                   // warp-uniform
+        {
             float rows[AT_WT][DPL];
             load_rows(sh.k[st], j0, tl, rows);
-            float s[2] = {-INFINITY, -INFINITY};
+            float s[NP];
 #pragma unroll
-            for (int pass = 0; pass < 2; pass++) {
-                if (4 * pass < G) {
-                    float v[32];
+            for (int pass = 0; pass < NP; pass++) {
+                float v[32];
 #pragma unroll
-                    for (int gg = 0; gg < 4; gg++)
+                for (int gg = 0; gg < 4; gg++)
 #pragma unroll
-                        for (int jj = 0; jj < AT_WT; jj++) {
-                            float t = 0.f;
+                    for (int jj = 0; jj < AT_WT; jj++) {
+                        float t = 0.f;
 #pragma unroll
-                            for (int d = 0; d < DPL; d++) t += qr[4 * pass + gg][d] * rows[jj][d];
-                            v[gg * 8 + jj] = t;
-                        }
-                    const float tot = lanes_transpose_sum(v, lane);
-                    s[pass] = (j0 + jj_l < tl && 4 * pass + gg_l < G) ? tot : -INFINITY;
-                }
+                        for (int d = 0; d < DPL; d++) t += qr[4 * pass + gg][d] * rows[jj][d];
+                        v[gg * 8 + jj] = t;
+                    }
+                const float tot = lanes_transpose_sum(v, lane);
+                s[pass] = (j0 + jj_l < tl && 4 * pass + gg_l < G) ? tot : -INFINITY;
             }
             load_rows(sh.v[st], j0, tl, rows);
 #pragma unroll
-            for (int pass = 0; pass < 2; pass++) {
-                if (4 * pass < G) {
-                    float mx = s[pass];
-                    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 4));
-                    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
-                    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
-                    const float m_new = fmaxf(m_run[pass], mx);
-                    const float pj = (s[pass] == -INFINITY) ? 0.f : expf(s[pass] - m_new);
-                    float sum = pj;
-                    sum += __shfl_xor_sync(0xffffffffu, sum, 4);
-                    sum += __shfl_xor_sync(0xffffffffu, sum, 2);
-                    sum += __shfl_xor_sync(0xffffffffu, sum, 1);
-                    const float alpha = (m_run[pass] == -INFINITY) ? 0.f : expf(m_run[pass] - m_new);
-                    l_run[pass] = l_run[pass] * alpha + sum;
-                    m_run[pass] = m_new;
+            for (int pass = 0; pass < NP; pass++) {
+                float mx = s[pass];
+                mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 4));
+                mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+                mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+                const float m_new = fmaxf(m_run[pass], mx);
+                const float pj = (s[pass] == -INFINITY) ? 0.f : expf(s[pass] - m_new);
+                float sum = pj;
+                sum += __shfl_xor_sync(0xffffffffu, sum, 4);
+                sum += __shfl_xor_sync(0xffffffffu, sum, 2);
+                sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+                const float alpha = (m_run[pass] == -INFINITY) ? 0.f : expf(m_run[pass] - m_new);
+                l_run[pass] = l_run[pass] * alpha + sum;
+                m_run[pass] = m_new;
+#pragma unroll
+                for (int gg = 0; gg < 4; gg++) {
+                    const float al = __shfl_sync(0xffffffffu, alpha, gg * 8);
+#pragma unroll
+                    for (int d = 0; d < DPL; d++) o[4 * pass + gg][d] *= al;
+                }
+#pragma unroll
+                for (int jj = 0; jj < AT_WT; jj++)
 #pragma unroll
                     for (int gg = 0; gg < 4; gg++) {
-                        const float al = __shfl_sync(0xffffffffu, alpha, gg * 8);
+                        const float pv = __shfl_sync(0xffffffffu, pj, gg * 8 + jj);
 #pragma unroll
-                        for (int d = 0; d < DPL; d++) o[4 * pass + gg][d] *= al;
+                        for (int d = 0; d < DPL; d++) o[4 * pass + gg][d] += pv * rows[jj][d];
                     }
-#pragma unroll
-                    for (int jj = 0; jj < AT_WT; jj++)
-#pragma unroll
-                        for (int gg = 0; gg < 4; gg++) {
-                            const float pv = __shfl_sync(0xffffffffu, pj, gg * 8 + jj);
-#pragma unroll
-                            for (int d = 0; d < DPL; d++) o[4 * pass + gg][d] += pv * rows[jj][d];
-                        }
-                }
             }
         }
         fence_proxy_async();                   // this thread's reads of the tile before the next TMA (async proxy) rewrites it
         named_bar_sync(AT_BAR, AT_THREADS);    // the tile buffer is free again
+        if (B2_ATTN_STAMP == 3 && rec_tl && ti == 0) tl_stamp(p.tl, 2);
     }
+    if (B2_ATTN_STAMP == 4 && rec_tl) tl_stamp(p.tl, 2);
 
     // ---------------------------------------------------------------- merge the warps
     // phase ownership of the merges: a pair of output dims for a set of heads
@@ -231,7 +251,7 @@ __device__ __forceinline__ void attn_decode_body(const AttnParams& p, AttnShared
         float* wm = &sh.sc[0][0][0];                                // [AT_WARPS][AT_GMAX]
         float* wl = wm + AT_WARPS * AT_GMAX;
 #pragma unroll
-        for (int g = 0; g < AT_GMAX; g++) {
+        for (int g = 0; g < NG; g++) {
             if (g < G) {
                 float* dst = wo + ((size_t)warp * G + g) * HD + DPL * lane;
                 if (DPL == 4) *reinterpret_cast<float4*>(dst) = make_float4(o[g][0], o[g][1], o[g][2], o[g][DPL - 1]);
@@ -240,7 +260,7 @@ __device__ __forceinline__ void attn_decode_body(const AttnParams& p, AttnShared
         }
         if (jj_l == 0) {
 #pragma unroll
-            for (int pass = 0; pass < 2; pass++) {
+            for (int pass = 0; pass < NP; pass++) {
                 const int g = 4 * pass + gg_l;
                 if (g < G) { wm[warp * AT_GMAX + g] = m_run[pass]; wl[warp * AT_GMAX + g] = l_run[pass]; }
             }
@@ -270,7 +290,7 @@ __device__ __forceinline__ void attn_decode_body(const AttnParams& p, AttnShared
     }
 
     // ---------------------------------------------------------------- merge the splits
-    if (tid == 0) tl_stamp(p.tl, 2);
+    if (B2_ATTN_STAMP == 5 && rec_tl) tl_stamp(p.tl, 2);
     if (p.n_splits == 1) {
 #pragma unroll
         for (int i = 0; i < HG3; i++) {
@@ -298,14 +318,14 @@ __device__ __forceinline__ void attn_decode_body(const AttnParams& p, AttnShared
 #pragma unroll
                 for (int k = 0; k < 2; k++) {
                     const int e = g * HD + 2 * dpair + k, r = e / per;
-                    AttnShared<HD>* rs = cluster.map_shared_rank(&sh, r);
+                    AttnShared<HD, AT_TT>* rs = cluster.map_shared_rank(&sh, r);
                     rs->part[rank * per + (e - r * per)] = acc[i][k];
                 }
             }
         }
         for (int i = tid; i < G * ns; i += AT_THREADS) {
             const int g = i / ns, r = i % ns;
-            AttnShared<HD>* rs = cluster.map_shared_rank(&sh, r);
+            AttnShared<HD, AT_TT>* rs = cluster.map_shared_rank(&sh, r);
             rs->part_ml[rank][g][0] = sh.m_run[g];
             rs->part_ml[rank][g][1] = sh.l_run[g];
         }
