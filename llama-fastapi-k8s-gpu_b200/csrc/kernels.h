@@ -28,7 +28,7 @@ inline cudaError_t launch_chain(void (*k)(KArgs...), dim3 grid, dim3 block, size
 // ---------------------------------------------------------------- mat-vec (matvec.cu)
 enum MvMode { MV_STORE = 0, MV_RESID = 1, MV_QKV = 2, MV_GATEUP = 3 };
 #ifndef B2_MV_NCW
-#define B2_MV_NCW 16
+#define B2_MV_NCW 18
 #endif
 constexpr int MV_NCW = B2_MV_NCW;            // consumer warps per CTA
 constexpr int MV_MAX_PROD = 4;               // TMA producer warps per CTA (upper bound; 2 are launched)

@@ -3,13 +3,14 @@
 // mul_mat_vec_q + the separate rms_norm / rope / cpy / silu / add launches that the reference
 // runs under llm.create_chat_completion (/root/reference/api.py:55-63; SURVEY.md 2.3 K2-K7,K11).
 //
-// Structure: one CTA per SM, 16 consumer warps + 2 TMA producer warps, the SM's shared memory as a ring of tiles.
+// Structure: one CTA per SM, 18 consumer warps + 2 TMA producer warps (20 warps x 96 registers fill the register file;
+// measured per token: 16+2 2.01 ms, 17+3 2.00, 16+4 2.05, 19+1 2.24, 18+2 1.93), the SM's shared memory as a ring of tiles.
 //   * Tiles. A tile = one K-slice (2048 elements) of a group of R = 4 consecutive rows = 4 row-slices of 1-2 KB,
 //     brought into one ring stage with 1-D bulk copies (cp.async.bulk + mbarrier complete_tx); 4 lanes of a
 //     producer warp serve a tile (one copy each), a warp issues 8 tiles per round. Producers never touch
 //     activations, so with programmatic dependent launch they start on the weights while the previous kernel
 //     is still running, and they keep the ring full independently of how the consumers are doing.
-//   * Consumers. Tile q belongs to consumer warp q % 16, whatever row group and K-slice it is: the warps of a
+//   * Consumers. Tile q belongs to consumer warp q % 18, whatever row group and K-slice it is: the warps of a
 //     CTA stay within one tile of each other to the end (the kernel is one link of a chain of ~160 dependent
 //     launches per token, so the last warp of the last CTA is what the next kernel waits for). Per tile a lane
 //     loads its 64 quantised activations (two int8 planes + packed scales) from shared memory and reuses them
@@ -44,7 +45,10 @@ namespace b2 {
 #endif
 constexpr int ROW_UNROLL = B2_ROW_UNROLL;   // rows of a tile interleaved in the instruction stream (more overflowed the instruction cache)
 constexpr int NCW = MV_NCW;                 // consumer warps
-constexpr int NPROD = 2;                    // producer warps
+#ifndef B2_MV_NPROD
+#define B2_MV_NPROD 2
+#endif
+constexpr int NPROD = B2_MV_NPROD;          // producer warps
 constexpr int R = MV_ROWS;                  // rows per group
 constexpr int TPB = 32 / R;                 // tiles a producer warp issues per round
 static_assert(R == 4, "the lane reduction and the epilogue are written for groups of two RoPE pairs");
@@ -189,7 +193,7 @@ __device__ __forceinline__ void mv_quantize_input(const MvParams& p, MvShared& s
     const float fs = ACT2 ? 1.0f / B2_ACT_RES : 1.0f;
     uint8_t* const lay0 = smem + p.act_off;
     uint8_t* const lay1 = smem + p.act_off;
-    constexpr int U = 4;                               // blocks per thread whose loads are in flight together (16 warps: K = 16384 per pass)
+    constexpr int U = 4;                               // blocks per thread whose loads are in flight together (18 warps: K = 18432 per pass)
     constexpr int QUADS = NCW * 8;
     float ssq = 0.f;
     for (int b0 = quad; b0 < nblk; b0 += QUADS * U) {
@@ -503,7 +507,7 @@ int mv_plan(MvParams& p, int n_ctas) {
     if (g_stage_cap >= TPB && g_stage_cap < S) S = g_stage_cap;
     if (S < TPB) return -5;                                // a producer warp fills TPB stages per round
     p.n_prod = g_n_prod;
-    if (S < TPB * p.n_prod) p.n_prod = 1;
+    while (p.n_prod > 1 && S < TPB * p.n_prod) p.n_prod--;
     S -= S % p.n_prod;                                     // every stage belongs to one producer (entry % n_prod)
     p.n_stages = S;
     // CTA split proportional to bytes (gate/up: every CTA handles both matrices)
