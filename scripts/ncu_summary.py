@@ -1,11 +1,12 @@
-"""Key numbers of one `ncu --set full` report as markdown: python scripts/ncu_summary.py report.ncu-rep [title]"""
+"""Key numbers of one `ncu --set full` report as markdown: python scripts/ncu_summary.py report.ncu-rep [title] [launch index in the report]"""
 import csv, subprocess, sys
 
 rep = sys.argv[1]
 title = sys.argv[2] if len(sys.argv) > 2 else rep
 raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 r = list(csv.reader(raw.splitlines()))
-h, units, v = r[0], r[1], r[2]
+idx = int(sys.argv[3]) if len(sys.argv) > 3 else 0
+h, units, v = r[0], r[1], r[2 + idx]
 col = {k: i for i, k in enumerate(h)}
 want = ["Kernel Name", "Grid Size", "Block Size", "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
         "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "dram__throughput.avg.pct_of_peak_sustained_elapsed",
