@@ -35,8 +35,8 @@ template <int HD, bool CLUSTER, int NP>
 __global__ void __launch_bounds__(at_threads(NP)) attn_decode_kernel(const AttnParams p) {
     extern __shared__ __align__(128) uint8_t smem_raw[];
     AttnShared<HD, at_tt(NP)>& sh = *reinterpret_cast<AttnShared<HD, at_tt(NP)>*>(smem_raw);
-    __shared__ uint64_t full[2];
-    if (threadIdx.x == 0) { mbar_init(&full[0], 1); mbar_init(&full[1], 1); fence_mbar_init(); }
+    __shared__ uint64_t full[AT_NST];
+    if (threadIdx.x == 0) { for (int i = 0; i < AT_NST; i++) mbar_init(&full[i], 1); fence_mbar_init(); }
     __syncthreads();
     if (threadIdx.x == 0) tl_stamp(p.tl, 0);
     griddep_launch();
@@ -44,7 +44,7 @@ __global__ void __launch_bounds__(at_threads(NP)) attn_decode_kernel(const AttnP
         griddep_wait();     // q and this token's K/V come from the QKV kernel just before us
         if (threadIdx.x == 0 && (B2_ATTN_ONE_CTA < 0 || (int)(blockIdx.y * gridDim.x + blockIdx.x) == B2_ATTN_ONE_CTA)) tl_stamp(p.tl, 1);
     }
-    uint32_t use[2] = {0u, 0u};
+    uint32_t use[AT_NST] = {};
     attn_decode_body<HD, CLUSTER, NP>(p, sh, full, use, blockIdx.x, blockIdx.y, threadIdx.x, p.early != 0);
     if (p.tl) {
         __syncthreads();
@@ -57,8 +57,8 @@ template <int HD, bool CLUSTER, int NP>
 __global__ void __launch_bounds__(at_threads(NP)) attn_decode_batch_kernel(const AttnParams p0, const SlotDev* tab, const BatchIdx b) {
     extern __shared__ __align__(128) uint8_t smem_raw[];
     AttnShared<HD, at_tt(NP)>& sh = *reinterpret_cast<AttnShared<HD, at_tt(NP)>*>(smem_raw);
-    __shared__ uint64_t full[2];
-    if (threadIdx.x == 0) { mbar_init(&full[0], 1); mbar_init(&full[1], 1); fence_mbar_init(); }
+    __shared__ uint64_t full[AT_NST];
+    if (threadIdx.x == 0) { for (int i = 0; i < AT_NST; i++) mbar_init(&full[i], 1); fence_mbar_init(); }
     __syncthreads();
     griddep_launch();
     griddep_wait();
@@ -70,7 +70,7 @@ __global__ void __launch_bounds__(at_threads(NP)) attn_decode_batch_kernel(const
     p.pos_ptr = sd.ints + 1; p.block_table = sd.block_table;
     p.scratch = p0.scratch + z * qd / p.head_dim * p.n_splits * (p.head_dim + 2);
     p.counters = p0.counters + z * p.n_kv;
-    uint32_t use[2] = {0u, 0u};
+    uint32_t use[AT_NST] = {};
     attn_decode_body<HD, CLUSTER, NP>(p, sh, full, use, blockIdx.x, blockIdx.y, threadIdx.x);
 }
 

@@ -24,6 +24,7 @@ constexpr int AT_GMAX = 8;     // query heads per KV head
 constexpr int AT_MAX_PAGES = 512;
 constexpr int AT_BAR = 2;      // named barrier used by the attention threads
 constexpr int AT_STAGE = 64;   // floats per head in the merge staging area
+constexpr int AT_NST = 3;      // K/V tile buffers (two tiles in flight behind the one being read)
 // Positions per tile: 128 with up to 4 query heads per KV head (NP = 1 pass; 16 warps), 64 with up to 8 (NP = 2; 8 warps:
 // the second pass doubles the registers per thread). One warp per 8 positions either way.
 __host__ __device__ constexpr int at_tt(int np) { return np == 1 ? 128 : 64; }
@@ -31,8 +32,8 @@ __host__ __device__ constexpr int at_threads(int np) { return at_tt(np) / AT_WT 
 
 template <int HD, int TT>
 struct __align__(16) AttnShared {
-    __half k[2][TT][HD];               // after the last tile: the warps' un-normalised outputs, float [warps][G][HD]
-    __half v[2][TT][HD];
+    __half k[AT_NST][TT][HD];          // after the last tile: the warps' un-normalised outputs, float [warps][G][HD]
+    __half v[AT_NST][TT][HD];
     float part[AT_GMAX * HD + 8];      // cluster merge: slice [r * per, (r+1) * per) = what split r sent us (its un-normalised outputs of OUR elements)
     float part_ml[8][AT_GMAX][2];      // cluster merge: (running max, running sum) of every head from every split
     float sc[4][AT_GMAX][AT_STAGE];    // staging: the warps' (max, sum) per head, then the global-scratch merge weights
@@ -78,7 +79,7 @@ __device__ __forceinline__ float lanes_transpose_sum(float (&v)[32], int lane) {
 // compiler could not prove convergence and turned each shuffle into a WARPSYNC.COLLECTIVE / branch / ENDCOLLECTIVE
 // sequence (127 of them; a 64-position tile took 2.1 us instead of ~0.5).
 template <int HD, bool CLUSTER, int NP>
-__device__ __forceinline__ void attn_decode_body(const AttnParams& p, AttnShared<HD, at_tt(NP)>& sh, uint64_t* full, uint32_t (&use)[2],
+__device__ __forceinline__ void attn_decode_body(const AttnParams& p, AttnShared<HD, at_tt(NP)>& sh, uint64_t* full, uint32_t (&use)[AT_NST],
                                                  int sp, int h, int tid, bool early = false) {
     constexpr int AT_TT = at_tt(NP), AT_THREADS = at_threads(NP), AT_WARPS = AT_THREADS / 32;
     static_assert(AT_WARPS * 4 * NP <= AT_TT, "warp outputs alias the K tiles");
@@ -115,12 +116,12 @@ __device__ __forceinline__ void attn_decode_body(const AttnParams& p, AttnShared
         }
     };
     auto issue = [&](int ti, int excl) {      // positions >= excl are left for a later copy_rows on the same barrier
-        int st = ti & 1;
+        int st = ti % AT_NST;
         int t0 = p0 + ti * AT_TT, t1 = min(p1, t0 + AT_TT);
         mbar_arrive_expect_tx(&full[st], (uint32_t)(t1 - t0) * HD * 2 * 2);
         copy_rows(st, t0, t0, min(t1, excl));
     };
-    const int n_early = early ? min(ntile, 2) : min(ntile, 1);      // tiles requested up front
+    const int n_early = min(ntile, AT_NST - 1);      // tiles requested up front (with `early`: before the dependency wait)
     if (tid == 0)
         for (int ti = 0; ti < n_early; ti++) issue(ti, early ? pos : 0x7fffffff);
     if (early) {
@@ -128,7 +129,7 @@ __device__ __forceinline__ void attn_decode_body(const AttnParams& p, AttnShared
         if (rec_tl) tl_stamp(p.tl, 1);
         if (tid == 0 && pos >= p0 && pos < min(p1, p0 + n_early * AT_TT)) {
             const int ti = (pos - p0) / AT_TT;
-            copy_rows(ti & 1, p0 + ti * AT_TT, pos, pos + 1);
+            copy_rows(ti % AT_NST, p0 + ti * AT_TT, pos, pos + 1);
         }
     }
 
@@ -175,9 +176,9 @@ __device__ __forceinline__ void attn_decode_body(const AttnParams& p, AttnShared
     };
 
     for (int ti = 0; ti < ntile; ti++) {
-        const int st = ti & 1;
+        const int st = ti % AT_NST;
         const int t0 = p0 + ti * AT_TT, tl = min(p1, t0 + AT_TT) - t0;
-        if (tid == 0 && ti + 1 < ntile && ti + 1 >= n_early) issue(ti + 1, 0x7fffffff);
+        if (tid == 0 && ti + AT_NST - 1 < ntile && ti + AT_NST - 1 >= n_early) issue(ti + AT_NST - 1, 0x7fffffff);   // into the buffer tile ti - 1 left (barrier below)
         mbar_wait(&full[st], use[st] & 1, p.err, 0x20001u, (unsigned)ti);
         use[st]++;
         if (B2_ATTN_STAMP == 2 && rec_tl && ti == 0) tl_stamp(p.tl, 2);

@@ -109,7 +109,7 @@ struct b2_engine {
     float *bd_q = nullptr, *bd_att = nullptr, *bd_scratch = nullptr;
     unsigned* bd_counters = nullptr;
     int* bd_out = nullptr;
-    int attn_mma = -1;             // tensor-core flash-decode: -1 = batched steps and > 8 splits (long contexts); 0 never; 1 always
+    int attn_mma = -1;             // tensor-core flash-decode: -1 = batched steps only; 0 never; 1 always
     int batch_min = 3;             // fewer sequences than this step one after another through the mat-vec path (measured: 3 slots 4.1 vs 6.3 ms)
     bool gemm_ok = false;          // every layer matrix is a block format the GEMM reads
     int prefill_min = 8;           // prompts chunks shorter than this go token by token through the mat-vec path
@@ -214,9 +214,9 @@ static int engine_create_impl(b2_engine* e, const b2_config* c) {
         CK(cudaMemcpy(e->rope_freq, f.data(), f.size() * 4, cudaMemcpyHostToDevice));
     }
     // 8 splits per KV head = one thread-block cluster merging through distributed shared memory
-    // long contexts: more, shorter splits (global-scratch merge) keep more SMs streaming KV: 8k context measured
-    // 3.86 ms/token with 8 splits, 2.57 ms with 32
-    int ns = c->n_ctx > 4096 ? 32 : c->n_ctx > 2048 ? 16 : 8;
+    // long contexts: 16 splits (global-scratch merge) put 128 CTAs on the 148 SMs: mistral-7b at an 8k context measured
+    // 2.15 ms/token with 16 splits against 2.36 with 32 (two waves of CTAs)
+    int ns = c->n_ctx > 2048 ? 16 : 8;
     while (ns > 1 && ns * 16 > c->n_ctx) ns >>= 1;
     if (const char* s = getenv("B2_ATTN_SPLITS")) if (atoi(s) > 0) ns = atoi(s);
     e->n_splits = ns;
@@ -495,7 +495,9 @@ static int forward_launches(b2_engine* e, Slot& s, bool with_head, bool with_sam
         Layer& L = e->layers[l];
         MvParams q = L.p_qkv;
         q.x = s.x; q.q_out = s.q; q.pos_ptr = pos; q.block_table = s.block_table;
-        const bool attn_plain = !(e->attn_mma == 1 || (e->attn_mma < 0 && e->n_splits > 8));
+        // the tensor-core kernel is for batched steps; at batch 1 the per-warp scalar kernel is faster at every context
+        // length measured (8k: 2.36 against 2.42 ms/token at equal splits) and keeps q and the probabilities in float32
+        const bool attn_plain = e->attn_mma != 1;
         q.trigger_late = pdl && attn_plain && e->attn_early;      // attention may start once we are past our own wait: it prefetches old K/V rows
         q.tl = next_tl();
         tick(1, &ye);
