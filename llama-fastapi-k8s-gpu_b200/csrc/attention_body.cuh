@@ -145,7 +145,7 @@ __device__ __forceinline__ void attn_decode_body(const AttnParams& p, AttnShared
             if (DPL == 4) { const float4 t = __ldcg(reinterpret_cast<const float4*>(qp)); qr[g][0] = t.x; qr[g][1] = t.y; qr[g][2] = t.z; qr[g][DPL - 1] = t.w; }
             else { const float2 t = __ldcg(reinterpret_cast<const float2*>(qp)); qr[g][0] = t.x; qr[g][1] = t.y; }
 #pragma unroll
-            for (int d = 0; d < DPL; d++) qr[g][d] *= p.scale;
+            for (int d = 0; d < DPL; d++) qr[g][d] *= p.scale * 1.4426950408889634f;     // scores, maxima and merges live in the log2 domain (exp2f)
         }
     }
     if (B2_ATTN_STAMP == 1 && rec_tl && qr[0][0] != 12345.f) tl_stamp(p.tl, 2);
@@ -210,12 +210,12 @@ __device__ __forceinline__ void attn_decode_body(const AttnParams& p, AttnShared
                 mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
                 mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
                 const float m_new = fmaxf(m_run[pass], mx);
-                const float pj = (s[pass] == -INFINITY) ? 0.f : expf(s[pass] - m_new);
+                const float pj = (s[pass] == -INFINITY) ? 0.f : exp2f(s[pass] - m_new);
                 float sum = pj;
                 sum += __shfl_xor_sync(0xffffffffu, sum, 4);
                 sum += __shfl_xor_sync(0xffffffffu, sum, 2);
                 sum += __shfl_xor_sync(0xffffffffu, sum, 1);
-                const float alpha = (m_run[pass] == -INFINITY) ? 0.f : expf(m_run[pass] - m_new);
+                const float alpha = (m_run[pass] == -INFINITY) ? 0.f : exp2f(m_run[pass] - m_new);
                 l_run[pass] = l_run[pass] * alpha + sum;
                 m_run[pass] = m_new;
 #pragma unroll
@@ -267,19 +267,18 @@ __device__ __forceinline__ void attn_decode_body(const AttnParams& p, AttnShared
             }
         }
         named_bar_sync(AT_BAR, AT_THREADS);
+        const int nwu = ntile > 1 ? AT_WARPS : (p1 - p0 + AT_WT - 1) / AT_WT;      // warps that had positions (the others hold -inf / 0)
 #pragma unroll
         for (int i = 0; i < HG3; i++) {
             acc[i][0] = acc[i][1] = 0.f;
             const int g = set3 * hg3 + i;
             if (i < hg3 && g < G) {
                 float M = -INFINITY;
-#pragma unroll
-                for (int w = 0; w < AT_WARPS; w++) M = fmaxf(M, wm[w * AT_GMAX + g]);
+                for (int w = 0; w < nwu; w++) M = fmaxf(M, wm[w * AT_GMAX + g]);
                 float l = 0.f;
-#pragma unroll
-                for (int w = 0; w < AT_WARPS; w++) {
+                for (int w = 0; w < nwu; w++) {
                     const float mw = wm[w * AT_GMAX + g];
-                    const float wgt = (mw == -INFINITY) ? 0.f : expf(mw - M);
+                    const float wgt = (mw == -INFINITY) ? 0.f : exp2f(mw - M);
                     const float2 ov = *reinterpret_cast<const float2*>(wo + ((size_t)w * G + g) * HD + 2 * dpair);
                     acc[i][0] += wgt * ov.x; acc[i][1] += wgt * ov.y;
                     l += wgt * wl[w * AT_GMAX + g];
@@ -341,7 +340,7 @@ __device__ __forceinline__ void attn_decode_body(const AttnParams& p, AttnShared
             for (int r = 0; r < 8; r++) {
                 if (r < ns) {
                     const float ms = sh.part_ml[r][g][0];
-                    const float w = (ms == -INFINITY) ? 0.f : expf(ms - M);
+                    const float w = (ms == -INFINITY) ? 0.f : exp2f(ms - M);
                     num += w * sh.part[r * per + (e - rank * per)]; den += w * sh.part_ml[r][g][1];
                 }
             }
@@ -382,7 +381,7 @@ __device__ __forceinline__ void attn_decode_body(const AttnParams& p, AttnShared
         for (int s2 = 0; s2 < p.n_splits; s2++) M = fmaxf(M, msp[tid * p.n_splits + s2]);
         for (int s2 = 0; s2 < p.n_splits; s2++) {
             float ms = msp[tid * p.n_splits + s2];
-            float w = (ms == -INFINITY) ? 0.f : expf(ms - M);
+            float w = (ms == -INFINITY) ? 0.f : exp2f(ms - M);
             wsp[tid * p.n_splits + s2] = w;
             den += w * lsp[tid * p.n_splits + s2];
         }
