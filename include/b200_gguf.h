@@ -137,6 +137,9 @@ int b2_kernel_launch_count(b2_engine* e, int64_t* n);   /* kernels launched sinc
 /* How the engine is running: CUDA graphs on/off, PDL on/off, int8 activation planes (1|2),
  * CTAs per mat-vec launch, attention split count. Any pointer may be NULL. */
 int b2_engine_mode(b2_engine* e, int* graph, int* pdl, int* act_planes, int* n_ctas, int* n_splits);
+/* Tensor-parallel state: rank, world size (1 = not tensor parallel) and whether the hidden-vector all-reduce runs over
+ * mapped peer memory (1) or through NCCL (0). Any pointer may be NULL. */
+int b2_engine_tp_mode(b2_engine* e, int* rank, int* world, int* peer_memory);
 /* Per-kernel-kind device time of ONE un-graphed, un-overlapped decode step of `slot`
  * (events around every launch). kinds: 0 embed, 1 qkv, 2 attention, 3 attn_out, 4 gate_up,
  * 5 ffn_down, 6 lm_head, 7 sampler. ms_out[8], launches_out[8], bytes_out[8] (algorithmic). */

@@ -97,6 +97,11 @@ struct b2_engine {
     // tensor parallelism (b2_engine_tp_init): this engine holds 1 / tp_world of the heads, FFN rows and vocabulary rows
     void* tp_comm = nullptr;
     int tp_rank = 0, tp_world = 1;
+    // all-reduce over peer memory (tp.cu): [2][n_embd] partial sums + flags + sequence number in one IPC-shared allocation
+    float* tp_shared = nullptr;
+    void* tp_peer[TP_MAX_WORLD] = {};
+    bool tp_p2p = false;
+    TpArParams tp_ar[2] = {};
     unsigned long long* tl = nullptr;   // B2_TIMELINE=1: 4 time stamps per kernel of a decode step (debugging aid)
     int tl_n = 0;                  // kernels recorded by the last forward_launches
     // prompt (GEMM) workspace, allocated on the first long prompt: PF_T tokens per chunk
@@ -281,6 +286,9 @@ extern "C" int b2_engine_destroy(b2_engine* e) {
         cudaFree(s.uniforms);
     }
     cudaFree(e->tl);
+    for (int r = 0; r < e->tp_world; r++)
+        if (e->tp_peer[r] && r != e->tp_rank) cudaIpcCloseMemHandle(e->tp_peer[r]);
+    cudaFree(e->tp_shared);
     tp_comm_destroy(e->tp_comm);
     cudaFree(e->k_pool); cudaFree(e->v_pool); cudaFree(e->rope_freq);
     cudaFree(e->attn_scratch); cudaFree(e->attn_counters);
@@ -366,6 +374,62 @@ extern "C" int b2_engine_tp_init(b2_engine* e, int rank, int world, const void* 
     const int v_local = e->cfg.n_vocab / world;
     if (!tp_all_gather(e->tp_comm, s.logits + (size_t)rank * v_local, s.logits, v_local, e->stream, err)) return fail(B2_ERR_CUDA, err);
     CK(cudaStreamSynchronize(e->stream));
+    // map every rank's reduction buffers into every other rank (CUDA IPC); when that is not possible the NCCL all-reduce stays
+    if (world <= TP_MAX_WORLD && !getenv("B2_TP_NCCL")) {
+        const size_t n = (size_t)e->cfg.n_embd;
+        const size_t bytes = 2 * n * sizeof(float) + 256;
+        CK(cudaMalloc(&e->tp_shared, bytes));
+        CK(cudaMemset(e->tp_shared, 0, bytes));
+        cudaIpcMemHandle_t mine;
+        bool ok = cudaIpcGetMemHandle(&mine, e->tp_shared) == cudaSuccess;
+        unsigned char* dh = nullptr;
+        CK(cudaMalloc(&dh, (size_t)world * (sizeof(mine) + 8)));
+        std::vector<unsigned char> rec(sizeof(mine) + 8, 0), all((size_t)world * (sizeof(mine) + 8));
+        memcpy(rec.data(), &mine, sizeof(mine)); rec[sizeof(mine)] = ok ? 1 : 0;
+        CK(cudaMemcpy(dh + (size_t)rank * rec.size(), rec.data(), rec.size(), cudaMemcpyHostToDevice));
+        if (!tp_all_gather_bytes(e->tp_comm, dh + (size_t)rank * rec.size(), dh, rec.size(), e->stream, err)) return fail(B2_ERR_CUDA, err);
+        CK(cudaStreamSynchronize(e->stream));
+        CK(cudaMemcpy(all.data(), dh, all.size(), cudaMemcpyDeviceToHost));
+        cudaFree(dh);
+        for (int r = 0; r < world && ok; r++) ok = all[(size_t)r * rec.size() + sizeof(mine)] == 1;
+        for (int r = 0; r < world && ok; r++) {
+            if (r == rank) { e->tp_peer[r] = e->tp_shared; continue; }
+            cudaIpcMemHandle_t h;
+            memcpy(&h, all.data() + (size_t)r * rec.size(), sizeof(h));
+            if (cudaIpcOpenMemHandle(&e->tp_peer[r], h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { e->tp_peer[r] = nullptr; ok = false; }
+        }
+        cudaGetLastError();
+        // everybody must agree on the path: one more (tiny) collective
+        float* flag = s.tp_part;
+        const float mine_ok = ok ? 0.f : 1.f;
+        CK(cudaMemcpy(flag, &mine_ok, 4, cudaMemcpyHostToDevice));
+        if (!tp_all_reduce_sum(e->tp_comm, flag, flag, 1, e->stream, err)) return fail(B2_ERR_CUDA, err);
+        float bad = 0.f;
+        CK(cudaMemcpyAsync(&bad, flag, 4, cudaMemcpyDeviceToHost, e->stream));
+        CK(cudaStreamSynchronize(e->stream));
+        CK(cudaMemset(flag, 0, 4));
+        e->tp_p2p = bad == 0.f;
+        if (e->tp_p2p) {
+            for (int b = 0; b < 2; b++) {
+                TpArParams& a = e->tp_ar[b];
+                a.x = nullptr;      // per call: the slot's hidden vector
+                for (int r = 0; r < world; r++) {
+                    a.part[r] = reinterpret_cast<const float*>(e->tp_peer[r]) + (size_t)b * n;
+                    a.flag_out[r] = reinterpret_cast<unsigned int*>(reinterpret_cast<float*>(e->tp_peer[r]) + 2 * n);
+                }
+                a.flags_in = reinterpret_cast<const unsigned int*>(e->tp_shared + 2 * n);
+                a.seq = reinterpret_cast<unsigned int*>(e->tp_shared + 2 * n) + 32;
+                a.rank = rank; a.world = world; a.n = (int)n; a.err = kernel_error_word();
+            }
+        }
+        if (getenv("B2_TP_VERBOSE")) fprintf(stderr, "[b2] tensor parallel rank %d/%d: hidden-vector all-reduce over %s\n", rank, world, e->tp_p2p ? "peer memory" : "NCCL");
+    }
+    return B2_OK;
+}
+
+extern "C" int b2_engine_tp_mode(b2_engine* e, int* rank, int* world, int* peer_memory) {
+    if (!e) return fail(B2_ERR_ARG, "null engine");
+    if (rank) *rank = e->tp_rank; if (world) *world = e->tp_world; if (peer_memory) *peer_memory = e->tp_p2p ? 1 : 0;
     return B2_OK;
 }
 
@@ -516,10 +580,21 @@ static int forward_launches(b2_engine* e, Slot& s, bool with_head, bool with_sam
         else CK(attn_decode_launch(a, st, pdl));
         tock(ye);
         MvParams o = L.p_o;
-        o.x = s.att; o.y = tp ? s.tp_part : s.x; o.resid = s.x; o.tl = next_tl();
+        float* part0 = !tp ? s.x : e->tp_p2p ? e->tp_shared : s.tp_part;
+        float* part1 = !tp ? s.x : e->tp_p2p ? e->tp_shared + c.n_embd : s.tp_part;
+        auto reduce = [&](int buf, float* part) -> bool {      // sum of the ranks' partials -> s.x on every rank
+            if (e->tp_p2p) {
+                TpArParams ar = e->tp_ar[buf];
+                ar.x = s.x;
+                e->launches++;
+                return tp_allreduce_launch(ar, st, pdl) == cudaSuccess;
+            }
+            return tp_all_reduce_sum(e->tp_comm, part, s.x, c.n_embd, st, tp_err);
+        };
+        o.x = s.att; o.y = part0; o.resid = s.x; o.tl = next_tl();
         tick(3, &ye);
         CK(mv_launch(o, e->n_ctas, st, e->act2, pdl));
-        if (tp && !tp_all_reduce_sum(e->tp_comm, s.tp_part, s.x, c.n_embd, st, tp_err)) return fail(B2_ERR_CUDA, tp_err);
+        if (tp && !reduce(0, part0)) return fail(B2_ERR_CUDA, tp_err.empty() ? "all-reduce launch failed" : tp_err);
         tock(ye);
         tick(4, &ye);
         if (L.gu_fused) {
@@ -536,10 +611,10 @@ static int forward_launches(b2_engine* e, Slot& s, bool with_head, bool with_sam
         }
         tock(ye);
         MvParams d = L.p_down;
-        d.x = s.h; d.y = tp ? s.tp_part : s.x; d.resid = s.x; d.tl = next_tl();
+        d.x = s.h; d.y = part1; d.resid = s.x; d.tl = next_tl();
         tick(5, &ye);
         CK(mv_launch(d, e->n_ctas, st, e->act2, pdl));
-        if (tp && !tp_all_reduce_sum(e->tp_comm, s.tp_part, s.x, c.n_embd, st, tp_err)) return fail(B2_ERR_CUDA, tp_err);
+        if (tp && !reduce(1, part1)) return fail(B2_ERR_CUDA, tp_err.empty() ? "all-reduce launch failed" : tp_err);
         tock(ye);
         e->launches += 5;
     }

@@ -189,6 +189,18 @@ bool tp_comm_init(void** comm, int rank, int world, const void* id128, std::stri
 void tp_comm_destroy(void* comm);
 bool tp_all_reduce_sum(void* comm, const float* send, float* recv, size_t n, cudaStream_t s, std::string& err);
 bool tp_all_gather(void* comm, const float* send, float* recv, size_t n, cudaStream_t s, std::string& err);
+bool tp_all_gather_bytes(void* comm, const void* send, void* recv, size_t bytes, cudaStream_t s, std::string& err);
+constexpr int TP_MAX_WORLD = 8;
+struct TpArParams {
+    float* x;                                   // out: the reduced vector (local)
+    const float* part[TP_MAX_WORLD];            // every rank's partial: [rank] local, the others mapped peer memory
+    unsigned int* flag_out[TP_MAX_WORLD];       // every peer's flag array (we write slot `rank` of it)
+    const unsigned int* flags_in;               // our flag array (peers write their slot)
+    unsigned int* seq;                          // sequence number of this reduction stream (local)
+    int rank, world, n;                         // n floats, a multiple of 4
+    unsigned int* err;
+};
+cudaError_t tp_allreduce_launch(const TpArParams& p, cudaStream_t stream, bool pdl);
 
 // ---------------------------------------------------------------- small kernels (misc.cu)
 // One pinned, device-mapped word per process that kernel watchdogs write to; 0 = no error.

@@ -4,10 +4,17 @@
 // vector after attn_output and after ffn_down, over NCCL on NVLink. The reference has no counterpart: its only multi-GPU
 // strategy is independent replicas (/root/reference/helm/values.yaml:17); llama.cpp itself has no NCCL path.
 //
+// The hidden-vector all-reduce itself does not go through NCCL when the ranks can map each other's memory (CUDA IPC):
+// tp_allreduce_kernel below exchanges 32 KB per rank with plain loads from the peers' buffers over NVLink behind a
+// flag written into the peers' memory -- one small kernel inside the decode graph, about half the latency of an
+// ncclAllReduce of that size (latency is all that matters: 160 of them per token). NCCL stays for the set-up
+// (exchange of the IPC handles), for the logits all-gather and as the fallback.
+//
 // NCCL is loaded at run time (dlopen "libnccl.so.2"): a process that already carries a copy (torch.distributed) shares
 // that one, a plain serving process picks up the system library, and a single-GPU host needs no NCCL at all.
 // Only this GPU's buffers are ever passed to NCCL; there is no peer-memory access in this library's own kernels.
 #include "kernels.h"
+#include "ptx.cuh"
 
 #include <dlfcn.h>
 #include <nccl.h>
@@ -84,6 +91,78 @@ bool tp_all_reduce_sum(void* comm, const float* send, float* recv, size_t n, cud
 // every rank contributes n floats; recv holds world * n (in place when send == recv + rank * n)
 bool tp_all_gather(void* comm, const float* send, float* recv, size_t n, cudaStream_t s, std::string& err) {
     return check(api().AllGather(send, recv, n, ncclFloat32, (ncclComm_t)comm, s), "ncclAllGather", err);
+}
+
+bool tp_all_gather_bytes(void* comm, const void* send, void* recv, size_t bytes, cudaStream_t s, std::string& err) {
+    return check(api().AllGather(send, recv, bytes, ncclInt8, (ncclComm_t)comm, s), "ncclAllGather", err);
+}
+
+// ---------------------------------------------------------------- all-reduce over peer memory
+// One CTA. Every rank: (1) after its own partial is complete (griddepcontrol.wait: the mat-vec before us has finished and
+// its stores are visible), bump the sequence number and write it into every peer's flag array, slot = our rank;
+// (2) wait until every peer's number has arrived in OUR flag array; (3) x[i] = sum over ranks, in rank order (the same
+// order everywhere: all ranks end up with bit-identical x), own partial from local memory, the others' straight from
+// their memory. The partial buffers alternate between the two reductions of a layer; a rank can only overwrite a buffer
+// two reductions later, after the peers have signalled the one in between, i.e. after they finished reading this one.
+__device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
+    unsigned int v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ float4 ld_peer_f4(const float4* p) {      // never from a stale L1 line: the peer rewrites it every token
+    float4 v;
+    asm volatile("ld.volatile.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+    return v;
+}
+
+__global__ void __launch_bounds__(1024) tp_allreduce_kernel(const TpArParams p) {
+    __shared__ unsigned int s_seq;
+    griddep_launch();       // the next mat-vec may start prefetching its weights
+    griddep_wait();         // our partial (written by the mat-vec before us) is complete
+    if (threadIdx.x == 0) {
+        const unsigned int s = *p.seq + 1u;
+        *p.seq = s;
+        s_seq = s;
+        __threadfence_system();
+        for (int r = 0; r < p.world; r++)
+            if (r != p.rank) st_release_sys(p.flag_out[r] + p.rank, s);
+    }
+    __syncthreads();
+    const unsigned int s = s_seq;
+    if ((int)threadIdx.x < p.world && (int)threadIdx.x != p.rank) {
+        unsigned int spins = 0;
+        while ((int)(ld_acquire_sys(p.flags_in + threadIdx.x) - s) < 0) {
+            __nanosleep(64);
+            if (++spins > (1u << 24)) {         // a peer that never arrives: report instead of hanging (~1 s)
+                volatile unsigned int* e = reinterpret_cast<volatile unsigned int*>(p.err);
+                if (e && e[0] == 0) { e[1] = (unsigned)p.rank; e[2] = threadIdx.x; e[3] = s; e[0] = 0x40001u; }
+                break;
+            }
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < p.n / 4; i += blockDim.x) {
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int r = 0; r < p.world; r++) {
+            const float4* src = reinterpret_cast<const float4*>(p.part[r]) + i;
+            const float4 v = (r == p.rank) ? __ldcg(src) : ld_peer_f4(src);
+            acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+        }
+        reinterpret_cast<float4*>(p.x)[i] = acc;
+    }
+}
+
+cudaError_t tp_allreduce_launch(const TpArParams& p, cudaStream_t stream, bool pdl) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(1); cfg.blockDim = dim3(1024); cfg.stream = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, tp_allreduce_kernel, p);
 }
 
 }  // namespace b2

@@ -55,6 +55,7 @@ SIGNATURES = {
     "b2_timer_stop": (c_int, [c_void_p, POINTER(c_float)]),
     "b2_kernel_launch_count": (c_int, [c_void_p, POINTER(c_int64)]),
     "b2_engine_mode": (c_int, [c_void_p, POINTER(c_int), POINTER(c_int), POINTER(c_int), POINTER(c_int), POINTER(c_int)]),
+    "b2_engine_tp_mode": (c_int, [c_void_p, POINTER(c_int), POINTER(c_int), POINTER(c_int)]),
     "b2_profile_decode_step": (c_int, [c_void_p, c_int, POINTER(c_float), POINTER(c_int32), POINTER(c_int64)]),
     "b2_bench_matvec": (c_int, [c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, POINTER(c_float)]),
     "b2_op_dequantize": (c_int, [c_int, c_int, c_void_p, c_int64, c_void_p]),

@@ -229,8 +229,13 @@ class Engine:
     def mode(self) -> dict:
         v = [ctypes.c_int() for _ in range(5)]
         check(self.lib.b2_engine_mode(self._h, *[ctypes.byref(x) for x in v]))
-        return dict(graph=bool(v[0].value), pdl=bool(v[1].value), act_planes=v[2].value,
-                    n_ctas=v[3].value, attn_splits=v[4].value)
+        t = [ctypes.c_int() for _ in range(3)]
+        check(self.lib.b2_engine_tp_mode(self._h, *[ctypes.byref(x) for x in t]))
+        out = dict(graph=bool(v[0].value), pdl=bool(v[1].value), act_planes=v[2].value,
+                   n_ctas=v[3].value, attn_splits=v[4].value)
+        if t[1].value > 1:
+            out.update(tp_rank=t[0].value, tp_world=t[1].value, tp_allreduce="peer memory" if t[2].value else "nccl")
+        return out
 
     def device_bytes(self):
         w, kv = ctypes.c_int64(), ctypes.c_int64()

@@ -44,6 +44,8 @@ def main():
         return toks, logits
 
     eng = Engine(g, n_ctx=64, max_seqs=1, device=local, tp=(rank, world, ids[0]))
+    if rank == 0:
+        print(f"tp-mode {eng.mode()}", flush=True)
     toks, logits = run(eng)
     eng.close()
     all_toks = [None] * world
