@@ -6,13 +6,15 @@
 //
 // The hidden-vector all-reduce itself does not go through NCCL when the ranks can map each other's memory (CUDA IPC):
 // tp_allreduce_kernel below exchanges 32 KB per rank with plain loads from the peers' buffers over NVLink behind a
-// flag written into the peers' memory -- one small kernel inside the decode graph, about half the latency of an
-// ncclAllReduce of that size (latency is all that matters: 160 of them per token). NCCL stays for the set-up
+// flag written into the peers' memory -- one small kernel inside the decode graph, 3.6 us less per call than
+// ncclAllReduce measured inside the 70B decode graph on 2 GPUs (latency is all that matters: 160 of them per token). NCCL stays for the set-up
 // (exchange of the IPC handles), for the logits all-gather and as the fallback.
 //
 // NCCL is loaded at run time (dlopen "libnccl.so.2"): a process that already carries a copy (torch.distributed) shares
 // that one, a plain serving process picks up the system library, and a single-GPU host needs no NCCL at all.
-// Only this GPU's buffers are ever passed to NCCL; there is no peer-memory access in this library's own kernels.
+// Only this GPU's buffers are ever passed to NCCL. The one kernel of this library that touches another GPU's memory is
+// tp_allreduce_kernel: plain loads and stores on mapped peer buffers; TMA (bulk copies, multicast) is used on this GPU's
+// own memory only.
 #include "kernels.h"
 #include "ptx.cuh"
 
