@@ -314,6 +314,7 @@ __device__ __forceinline__ void consume(const MvParams& p, const CtaWork& work, 
     const uint32_t wlo0 = (uint32_t)(uintptr_t)p.seg[seg0].w, wlo1 = gateup ? (uint32_t)(uintptr_t)p.seg[1].w : wlo0;
     const uint32_t stage_bytes = (uint32_t)p.stage_bytes, slot_bytes = (uint32_t)p.slot_bytes;
     const uint32_t sb = (uint32_t)slice_bytes(T);
+    const int resid_off = p.seg[work.seg].out_off;
     // tile bookkeeping advances by NCW per iteration: carried incrementally (no integer division in the loop)
     int gi = warp / tpg, within = warp % tpg;
     uint32_t st = (uint32_t)warp % S, use = (uint32_t)warp / S;
@@ -336,6 +337,14 @@ __device__ __forceinline__ void consume(const MvParams& p, const CtaWork& work, 
             }
         }
         mbar_wait(&sh.full[st_cur], use_cur & 1u, p.err, 0x10002u, (unsigned)q);
+        // residual of the group: requested now by every tile's lane 0 (16 bytes from L2), used by whichever warp ends up
+        // finishing the group -- the round trip hides behind the dot products instead of sitting on the kernel's tail
+        float2 res0 = make_float2(0.f, 0.f), res1 = res0;
+        if (p.mode == MV_RESID && lane == 0) {
+            const float* rp = p.resid + resid_off + row0;
+            res0 = __ldcg(reinterpret_cast<const float2*>(rp));
+            if (nrows == R) res1 = __ldcg(reinterpret_cast<const float2*>(rp + 2));
+        }
         const uint8_t* stage = ring + st_cur * stage_bytes;
         float acc[R];
 #pragma unroll
@@ -389,12 +398,6 @@ __device__ __forceinline__ void consume(const MvParams& p, const CtaWork& work, 
             *reinterpret_cast<float2*>(p.y + row0) = make_float2(h[0], h[1]);
             if (nrows == R) *reinterpret_cast<float2*>(p.y + row0 + 2) = make_float2(h[2], h[3]);
         } else {
-            float2 res0 = make_float2(0.f, 0.f), res1 = res0;
-            if (p.mode == MV_RESID) {                              // written by other SMs: L2
-                const float* rp = p.resid + p.seg[work.seg].out_off + row0;
-                res0 = __ldcg(reinterpret_cast<const float2*>(rp));
-                if (nrows == R) res1 = __ldcg(reinterpret_cast<const float2*>(rp + 2));
-            }
             epilogue_pair(p, sh.rope, work.seg, row0, v[0], v[1], pos, page, res0);
             if (nrows == R) epilogue_pair(p, sh.rope, work.seg, row0 + 2, v[2], v[3], pos, page, res1);
         }
