@@ -354,12 +354,13 @@ __device__ __forceinline__ void consume(const MvParams& p, const CtaWork& work, 
             load_act<T, ACT2>(la, av, sl * B2_SLICE, lane);
             // each copy started at the 16-byte boundary below its row-slice (only Q6_K rows can sit off one)
             const uint32_t row_lo = (m ? wlo1 : wlo0) + (uint32_t)row0 * row_bytes + (uint32_t)sl * sb;
+            // always R rows, results through a shift register (a rolled loop cannot index acc[] by r without a select per
+            // element): a group with a single pair computes two rows of stale bytes that nobody looks at
 #pragma unroll ROW_UNROLL
-            for (int r = 0; r < nrows; r++) {
+            for (int r = 0; r < R; r++) {
                 const uint32_t off = (T == T_Q6_K) ? ((row_lo + r * row_bytes) & 15u) : 0u;
                 const float d = row_dot<T, ACT2>(stage + r * slot_bytes + off, lane, la);
-#pragma unroll
-                for (int k = 0; k < R; k++) if (k == r) acc[k] = d;
+                acc[0] = acc[1]; acc[1] = acc[2]; acc[2] = acc[3]; acc[3] = d;
             }
         }
         fence_proxy_async();    // generic-proxy reads of the stage, ordered before the TMA (async proxy) refill
