@@ -14,7 +14,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.environ.get("B2_LIB_DIR") or os.path.join(HERE, "lib")   # B2_LIB_DIR: experiment builds (with B2_NVCC_EXTRA)
-CUDA_SOURCES = ["engine.cu", "matvec.cu", "attention.cu", "attention_mma.cu", "gemm.cu", "prefill.cu", "misc.cu", "sampler.cu", "tp.cu"]
+CUDA_SOURCES = ["engine.cu", "matvec.cu", "matvec_extra.cu", "attention.cu", "attention_mma.cu", "gemm.cu", "prefill.cu", "misc.cu", "sampler.cu", "tp.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xptxas", "-v", "--expt-relaxed-constexpr"]
 

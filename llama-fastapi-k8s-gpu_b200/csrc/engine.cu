@@ -433,6 +433,10 @@ extern "C" int b2_engine_tp_mode(b2_engine* e, int* rank, int* world, int* peer_
     return B2_OK;
 }
 
+// block formats the tensor-core GEMM dequantises (gemm.cu); models with other types (Q4_1, Q5_0, Q5_1, Q2_K, Q3_K) run prompts
+// and batches through the mat-vec path, one token at a time
+static bool gemm_type_ok(int t) { return t == T_Q4_0 || t == T_Q8_0 || t == T_Q4_K || t == T_Q5_K || t == T_Q6_K; }
+
 extern "C" int b2_engine_finalize(b2_engine* e) {
     if (!e) return fail(B2_ERR_ARG, "null engine");
     std::lock_guard<std::mutex> lk(e->mu);
@@ -511,7 +515,8 @@ extern "C" int b2_engine_finalize(b2_engine* e) {
     e->gemm_ok = !getenv("B2_NO_GEMM_PREFILL") && tpw == 1;     // tensor parallelism: prompts and batches go through the mat-vec path
     for (auto& L : e->layers)
         for (const DevTensor* t : {&L.wq, &L.wk, &L.wv, &L.wo, &L.wgate, &L.wup, &L.wdown})
-            if (block_elems(t->type) == 1) e->gemm_ok = false;
+            if (!gemm_type_ok(t->type)) e->gemm_ok = false;
+    if (!gemm_type_ok(e->output.type) && block_elems(e->output.type) != 1) e->gemm_ok = false;   // (an F16/F32 output matrix only rules out the batched lm_head)
     if (const char* s = getenv("B2_PREFILL_MIN")) if (atoi(s) > 0) e->prefill_min = atoi(s);
     if (const char* s = getenv("B2_BATCH_MIN")) if (atoi(s) > 0) e->batch_min = atoi(s);
     if (const char* s = getenv("B2_ATTN_MMA")) e->attn_mma = atoi(s) ? 1 : 0;

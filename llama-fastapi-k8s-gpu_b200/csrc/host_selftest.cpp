@@ -62,6 +62,7 @@ int b2_host_matvec(int type, const uint8_t* w, int n_rows, int K, const float* x
         if (layout == 0) {
             f[4 * (b >> 1) + (b & 1)] = amax / 127.0f * fs;
             f[4 * (b >> 1) + 2 + (b & 1)] = lo + hi;
+            if (type == b2::T_Q2_K || type == b2::T_Q3_K) { g[2 * b] = lo; g[2 * b + 1] = hi; }   // 16-element sums, plain order
         } else {
             f[b] = amax / 127.0f * fs;
             g[b2::act_s16p_index(2 * b)] = 32.0f * lo;
@@ -80,6 +81,11 @@ int b2_host_matvec(int type, const uint8_t* w, int n_rows, int K, const float* x
             case b2::T_Q4_K: y[r] = host_row<b2::T_Q4_K>(rowp, K, v, act2); break;
             case b2::T_Q5_K: y[r] = host_row<b2::T_Q5_K>(rowp, K, v, act2); break;
             case b2::T_Q6_K: y[r] = host_row<b2::T_Q6_K>(rowp, K, v, act2); break;
+            case b2::T_Q4_1: y[r] = host_row<b2::T_Q4_1>(rowp, K, v, act2); break;
+            case b2::T_Q5_0: y[r] = host_row<b2::T_Q5_0>(rowp, K, v, act2); break;
+            case b2::T_Q5_1: y[r] = host_row<b2::T_Q5_1>(rowp, K, v, act2); break;
+            case b2::T_Q2_K: y[r] = host_row<b2::T_Q2_K>(rowp, K, v, act2); break;
+            case b2::T_Q3_K: y[r] = host_row<b2::T_Q3_K>(rowp, K, v, act2); break;
             default: rc = -2;
         }
     }

@@ -41,6 +41,7 @@ struct MvSeg {
     int type;           // ggml type id
     int n_rows;
     int row_bytes;      // filled by mv_plan
+    int slice_bytes;    // bytes of one full 2048-element K-slice of a row (filled by mv_plan)
     int cta0, ncta;     // CTA range that works on this segment (filled by mv_plan)
     int out_off;        // element offset into y / resid
 };

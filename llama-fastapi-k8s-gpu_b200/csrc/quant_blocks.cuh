@@ -31,17 +31,23 @@
 
 namespace b2 {
 
-enum GgmlType { T_F32 = 0, T_F16 = 1, T_Q4_0 = 2, T_Q8_0 = 8, T_Q4_K = 12, T_Q5_K = 13, T_Q6_K = 14 };
+enum GgmlType { T_F32 = 0, T_F16 = 1, T_Q4_0 = 2, T_Q4_1 = 3, T_Q5_0 = 6, T_Q5_1 = 7, T_Q8_0 = 8, T_Q2_K = 10, T_Q3_K = 11,
+                T_Q4_K = 12, T_Q5_K = 13, T_Q6_K = 14 };
 
 B2_HD int block_elems(int t) {
-    return (t == T_F32 || t == T_F16) ? 1 : (t == T_Q4_0 || t == T_Q8_0) ? 32 : 256;
+    return (t == T_F32 || t == T_F16) ? 1 : (t == T_Q4_0 || t == T_Q8_0 || t == T_Q4_1 || t == T_Q5_0 || t == T_Q5_1) ? 32 : 256;
 }
 B2_HD int block_bytes(int t) {
     switch (t) {
         case T_F32: return 4;
         case T_F16: return 2;
         case T_Q4_0: return 18;
+        case T_Q4_1: return 20;
+        case T_Q5_0: return 22;
+        case T_Q5_1: return 24;
         case T_Q8_0: return 34;
+        case T_Q2_K: return 84;
+        case T_Q3_K: return 110;
         case T_Q4_K: return 144;
         case T_Q5_K: return 176;
         case T_Q6_K: return 210;
@@ -139,6 +145,37 @@ B2_D float dequant_elem(int type, const uint8_t* blk, int e) {
             float d = h2f(blk[0] | (blk[1] << 8));
             return fmul((float)(int8_t)blk[2 + e], d);
         }
+        case T_Q4_1: {
+            float d = h2f(blk[0] | (blk[1] << 8)), m = h2f(blk[2] | (blk[3] << 8));
+            int q = (e < 16) ? (blk[4 + e] & 15) : (blk[4 + e - 16] >> 4);
+            return fsub(fmul(d, (float)q), -m);
+        }
+        case T_Q5_0:
+        case T_Q5_1: {
+            const int o = type == T_Q5_0 ? 2 : 4;
+            float d = h2f(blk[0] | (blk[1] << 8));
+            uint32_t qh = blk[o] | (blk[o + 1] << 8) | (blk[o + 2] << 16) | ((uint32_t)blk[o + 3] << 24);
+            int q = (e < 16) ? (blk[o + 4 + e] & 15) : (blk[o + 4 + e - 16] >> 4);
+            q |= (int)((qh >> e) & 1u) << 4;
+            if (type == T_Q5_0) return fmul(d, (float)(q - 16));
+            return fsub(fmul(d, (float)q), -h2f(blk[2] | (blk[3] << 8)));
+        }
+        case T_Q2_K: {
+            float d = h2f(blk[80] | (blk[81] << 8)), dmin = h2f(blk[82] | (blk[83] << 8));
+            int sc = blk[e >> 4];
+            int q = (blk[16 + 32 * (e >> 7) + (e & 31)] >> (2 * ((e >> 5) & 3))) & 3;
+            float dl = fmul(d, (float)(sc & 15)), ml = fmul(dmin, (float)(sc >> 4));
+            return fsub(fmul(dl, (float)q), ml);
+        }
+        case T_Q3_K: {
+            float d = h2f(blk[108] | (blk[109] << 8));
+            int is = e >> 4;
+            int lsc = (blk[96 + (is & 7)] >> (4 * (is >> 3))) & 15, hsc = (blk[104 + (is & 3)] >> (2 * (is >> 2))) & 3;
+            int scale = (lsc | (hsc << 4)) - 32;
+            int ql = (blk[32 + 32 * (e >> 7) + (e & 31)] >> (2 * ((e >> 5) & 3))) & 3;
+            int hb = (blk[e & 31] >> (e >> 5)) & 1;
+            return fmul(fmul(d, (float)scale), (float)(ql - (hb ? 0 : 4)));
+        }
         case T_Q4_K:
         case T_Q5_K: {
             float d = h2f(blk[0] | (blk[1] << 8)), dmin = h2f(blk[2] | (blk[3] << 8));
@@ -178,6 +215,7 @@ struct ActView {
     // per-block scales, packed so a lane fetches what it needs with one or two 16-byte loads:
     //   layout 0: f[4c .. 4c+3] = {dx'(2c), dx'(2c+1), sum32(2c), sum32(2c+1)} for the 64-element chunk c
     //   layout 1: f[blk] = dx'(blk);  g[act_s16p_index(u)] = 32 * sum16(u)
+    //   layout 0 + 16-element sums (Q2_K, Q3_K): additionally g[u] = sum16(u), plain order
     // dx' = dx (one plane) or dx / 252 (two planes: the scale of the folded integer 252 a + b)
     const float* f;
     const float* g;
@@ -270,6 +308,10 @@ B2_D void load_act(LaneAct& r, const ActView& v, int e0 /* first element of the 
     } else {
         U4 f4 = ld128(reinterpret_cast<const uint8_t*>(v.f + 4 * ((e0 >> 6) + lane)));
         r.f[0] = u2f(f4.x); r.f[1] = u2f(f4.y); r.f[2] = u2f(f4.z); r.f[3] = u2f(f4.w);
+        if (T == T_Q2_K || T == T_Q3_K) {       // sums of the chunk's four 16-element runs (plain order in g)
+            U4 s4 = ld128(reinterpret_cast<const uint8_t*>(v.g + 4 * ((e0 >> 6) + lane)));
+            r.f[4] = u2f(s4.x); r.f[5] = u2f(s4.y); r.f[6] = u2f(s4.z); r.f[7] = u2f(s4.w);
+        }
     }
 }
 
@@ -417,8 +459,149 @@ B2_D float row_dot_q8_0(const uint8_t* row, int lane, const LaneAct& act) {
     return d0 * ((float)fold<ACT2>(A0, B0) * act.f[0]) + d1 * ((float)fold<ACT2>(A1, B1) * act.f[1]);
 }
 
+// bit i of x (i < 4) -> bit 0 of byte i
+B2_D uint32_t spread4(uint32_t x) { return ((x & 0xFu) * 0x00204081u) & 0x01010101u; }
+
+template <bool ACT2>
+B2_D float row_dot_q4_1(const uint8_t* row, int lane, const LaneAct& act) {
+    const uint8_t* p = row + 40 * lane;   // two 20-byte blocks; 8-byte aligned
+    uint32_t W[10];
+#pragma unroll
+    for (int i = 0; i < 10; i++) W[i] = ld32(p + 4 * i);
+    float d0 = h2f(W[0] & 0xffffu), m0 = h2f(W[0] >> 16), d1 = h2f(W[5] & 0xffffu), m1 = h2f(W[5] >> 16);
+    int A0 = 0, B0 = 0, A1 = 0, B1 = 0, A0h = 0, B0h = 0, A1h = 0, B1h = 0;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        uint32_t q0 = W[1 + k], q1 = W[6 + k];
+        int lo0 = (int)(q0 & 0x0F0F0F0Fu), lo1 = (int)(q1 & 0x0F0F0F0Fu);
+        uint32_t hi0 = q0 & 0xF0F0F0F0u, hi1 = q1 & 0xF0F0F0F0u;
+        A0 = dp4a(lo0, act.a[k], A0); A0h = dp4a_us(hi0, act.a[4 + k], A0h);
+        A1 = dp4a(lo1, act.a[8 + k], A1); A1h = dp4a_us(hi1, act.a[12 + k], A1h);
+        if (ACT2) {
+            B0 = dp4a(lo0, act.b[k], B0); B0h = dp4a_us(hi0, act.b[4 + k], B0h);
+            B1 = dp4a(lo1, act.b[8 + k], B1); B1h = dp4a_us(hi1, act.b[12 + k], B1h);
+        }
+    }
+    A0 += A0h >> 4; B0 += B0h >> 4; A1 += A1h >> 4; B1 += B1h >> 4;
+    return d0 * ((float)fold<ACT2>(A0, B0) * act.f[0]) + m0 * act.f[2] + d1 * ((float)fold<ACT2>(A1, B1) * act.f[1]) + m1 * act.f[3];
+}
+
+// Q5_0 (OFF = 2: d | qh | qs) and Q5_1 (OFF = 4: d | m | qh | qs): two blocks per lane, 4-byte aligned
+template <bool ACT2, bool HAS_MIN>
+B2_D float row_dot_q5_01(const uint8_t* row, int lane, const LaneAct& act) {
+    constexpr int BB = HAS_MIN ? 24 : 22, NW = 2 * BB / 4;
+    const uint8_t* p = row + 2 * BB * lane;
+    uint32_t W[NW];
+#pragma unroll
+    for (int i = 0; i < NW; i++) W[i] = ld32(p + 4 * i);
+    uint32_t qh0, qh1, qs0[4], qs1[4];
+    float d0, d1, m0 = 0.f, m1 = 0.f;
+    if (HAS_MIN) {
+        d0 = h2f(W[0] & 0xffffu); m0 = h2f(W[0] >> 16); qh0 = W[1];
+        d1 = h2f(W[6] & 0xffffu); m1 = h2f(W[6] >> 16); qh1 = W[7];
+#pragma unroll
+        for (int k = 0; k < 4; k++) { qs0[k] = W[2 + k]; qs1[k] = W[8 + k]; }
+    } else {
+        d0 = h2f(W[0] & 0xffffu); qh0 = fshr(W[0], W[1], 16);
+        d1 = h2f(W[5] >> 16); qh1 = W[6];
+#pragma unroll
+        for (int k = 0; k < 4; k++) { qs0[k] = fshr(W[1 + k], W[2 + k], 16); qs1[k] = W[7 + k]; }
+    }
+    int A0 = 0, B0 = 0, A1 = 0, B1 = 0;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        int lo0 = (int)((qs0[k] & 0x0F0F0F0Fu) | (spread4(qh0 >> (4 * k)) << 4));
+        int hi0 = (int)(((qs0[k] >> 4) & 0x0F0F0F0Fu) | (spread4(qh0 >> (16 + 4 * k)) << 4));
+        int lo1 = (int)((qs1[k] & 0x0F0F0F0Fu) | (spread4(qh1 >> (4 * k)) << 4));
+        int hi1 = (int)(((qs1[k] >> 4) & 0x0F0F0F0Fu) | (spread4(qh1 >> (16 + 4 * k)) << 4));
+        A0 = dp4a(lo0, act.a[k], A0); A0 = dp4a(hi0, act.a[4 + k], A0);
+        A1 = dp4a(lo1, act.a[8 + k], A1); A1 = dp4a(hi1, act.a[12 + k], A1);
+        if (ACT2) {
+            B0 = dp4a(lo0, act.b[k], B0); B0 = dp4a(hi0, act.b[4 + k], B0);
+            B1 = dp4a(lo1, act.b[8 + k], B1); B1 = dp4a(hi1, act.b[12 + k], B1);
+        }
+    }
+    const float F0 = (float)fold<ACT2>(A0, B0) * act.f[0], F1 = (float)fold<ACT2>(A1, B1) * act.f[1];
+    if (HAS_MIN) return d0 * F0 + m0 * act.f[2] + d1 * F1 + m1 * act.f[3];
+    return d0 * (F0 - 16.0f * act.f[2]) + d1 * (F1 - 16.0f * act.f[3]);
+}
+
+// Q2_K / Q3_K: lane (j, c) = (lane >> 2, lane & 3) owns elements 64c .. 64c+63 of 256-block j = four 16-element sub-blocks;
+// the 2-bit planes of 32 bytes of qs: bytes 0-15 / 16-31 at shift 4(c&1) are sub-blocks 0 / 1, at shift 4(c&1)+2 sub-blocks 2 / 3
+template <bool ACT2>
+B2_D float row_dot_q2k(const uint8_t* row, int lane, const LaneAct& act) {
+    const int j = lane >> 2, c = lane & 3;
+    const uint8_t* blk = row + j * 84;                  // 4-byte aligned
+    const uint32_t scw = ld32(blk + 4 * c), dd = ld32(blk + 80);
+    uint32_t W[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) W[i] = ld32(blk + 16 + 32 * (c >> 1) + 4 * i);
+    const uint32_t s0 = 4 * (c & 1);
+    int A[4] = {0, 0, 0, 0}, B[4] = {0, 0, 0, 0};
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int q0 = (int)((W[k] >> s0) & 0x03030303u), q2 = (int)((W[k] >> (s0 + 2)) & 0x03030303u);
+        const int q1 = (int)((W[4 + k] >> s0) & 0x03030303u), q3 = (int)((W[4 + k] >> (s0 + 2)) & 0x03030303u);
+        A[0] = dp4a(q0, act.a[k], A[0]); A[1] = dp4a(q1, act.a[4 + k], A[1]);
+        A[2] = dp4a(q2, act.a[8 + k], A[2]); A[3] = dp4a(q3, act.a[12 + k], A[3]);
+        if (ACT2) {
+            B[0] = dp4a(q0, act.b[k], B[0]); B[1] = dp4a(q1, act.b[4 + k], B[1]);
+            B[2] = dp4a(q2, act.b[8 + k], B[2]); B[3] = dp4a(q3, act.b[12 + k], B[3]);
+        }
+    }
+    int U[4];
+    float M = 0.f;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        U[i] = fold<ACT2>(A[i], B[i]) * (int)((scw >> (8 * i)) & 15u);
+        M += (float)((scw >> (8 * i + 4)) & 15u) * act.f[4 + i];
+    }
+    const float F = (float)(U[0] + U[1]) * act.f[0] + (float)(U[2] + U[3]) * act.f[1];
+    return h2f(dd & 0xffffu) * F - h2f(dd >> 16) * M;
+}
+
+template <bool ACT2>
+B2_D float row_dot_q3k(const uint8_t* row, int lane, const LaneAct& act) {
+    const int j = lane >> 2, c = lane & 3;
+    const uint8_t* blk = row + j * 110;                 // 2-byte aligned only
+    uint32_t H[8], W[8], S[3];
+    ld_words_u2<8>(blk, H);
+    ld_words_u2<8>(blk + 32 + 32 * (c >> 1), W);
+    ld_words_u2<3>(blk + 96, S);
+    const float d = h2f(ld16(blk + 108));
+    // the lane's four 6-bit scales (+32) as the bytes of one word
+    const uint32_t scw = ((((c & 1) ? S[1] : S[0]) >> (4 * (c >> 1))) & 0x0F0F0F0Fu) | (((S[2] >> (2 * c)) & 0x03030303u) << 4);
+    const uint32_t s0 = 4 * (c & 1), hb = 2 * c;
+    int A[4] = {0, 0, 0, 0}, B[4] = {0, 0, 0, 0};
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int q0 = (int)(((W[k] >> s0) & 0x03030303u) | (((H[k] >> hb) & 0x01010101u) << 2));
+        const int q2 = (int)(((W[k] >> (s0 + 2)) & 0x03030303u) | (((H[k] >> (hb + 1)) & 0x01010101u) << 2));
+        const int q1 = (int)(((W[4 + k] >> s0) & 0x03030303u) | (((H[4 + k] >> hb) & 0x01010101u) << 2));
+        const int q3 = (int)(((W[4 + k] >> (s0 + 2)) & 0x03030303u) | (((H[4 + k] >> (hb + 1)) & 0x01010101u) << 2));
+        A[0] = dp4a(q0, act.a[k], A[0]); A[1] = dp4a(q1, act.a[4 + k], A[1]);
+        A[2] = dp4a(q2, act.a[8 + k], A[2]); A[3] = dp4a(q3, act.a[12 + k], A[3]);
+        if (ACT2) {
+            B[0] = dp4a(q0, act.b[k], B[0]); B[1] = dp4a(q1, act.b[4 + k], B[1]);
+            B[2] = dp4a(q2, act.b[8 + k], B[2]); B[3] = dp4a(q3, act.b[12 + k], B[3]);
+        }
+    }
+    float r = 0.f;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const float sc = (float)((int)((scw >> (8 * i)) & 63u) - 32);
+        r += sc * ((float)fold<ACT2>(A[i], B[i]) * act.f[i >> 1] - 4.0f * act.f[4 + i]);     // sum (u - 4) x = sum u x - 4 sum x
+    }
+    return d * r;
+}
+
 template <int T, bool ACT2>
 B2_D float row_dot(const uint8_t* row, int lane, const LaneAct& act) {
+    if (T == T_Q4_1) return row_dot_q4_1<ACT2>(row, lane, act);
+    if (T == T_Q5_0) return row_dot_q5_01<ACT2, false>(row, lane, act);
+    if (T == T_Q5_1) return row_dot_q5_01<ACT2, true>(row, lane, act);
+    if (T == T_Q2_K) return row_dot_q2k<ACT2>(row, lane, act);
+    if (T == T_Q3_K) return row_dot_q3k<ACT2>(row, lane, act);
     if (T == T_Q4_K) return row_dot_q4k<ACT2>(row, lane, act);
     if (T == T_Q6_K) return row_dot_q6k<ACT2>(row, lane, act);
     if (T == T_Q5_K) return row_dot_q5k<ACT2>(row, lane, act);

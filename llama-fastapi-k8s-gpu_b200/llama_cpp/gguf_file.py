@@ -35,7 +35,12 @@ GGML_TYPES: Dict[int, Tuple[str, int, int]] = {
     0: ("F32", 1, 4),
     1: ("F16", 1, 2),
     2: ("Q4_0", 32, 18),
+    3: ("Q4_1", 32, 20),
+    6: ("Q5_0", 32, 22),
+    7: ("Q5_1", 32, 24),
     8: ("Q8_0", 32, 34),
+    10: ("Q2_K", 256, 84),
+    11: ("Q3_K", 256, 110),
     12: ("Q4_K", 256, 144),
     13: ("Q5_K", 256, 176),
     14: ("Q6_K", 256, 210),

@@ -63,7 +63,13 @@ ARCHS: Dict[str, Arch] = {
 #   Q4_K  d=1, dmin=7.5          -> 258.6   (dmin = 7.5 d centres the values)
 #   Q5_K  d=1, dmin=15.5         -> 526.7
 #   Q6_K  d=1, scales in [-32,32]-> 347.0
-_UNIT_STD = {"Q4_0": 4.611, "Q8_0": 73.91, "Q4_K": 258.6, "Q5_K": 526.7, "Q6_K": 347.0}
+#   Q4_1  d=1, m=-7.5            -> 4.612
+#   Q5_0  d=1                    -> 9.234
+#   Q5_1  d=1, m=-15.5           -> 9.228
+#   Q2_K  d=1, dmin=1.5          -> 13.87
+#   Q3_K  d=1                    -> 43.34
+_UNIT_STD = {"Q4_0": 4.611, "Q8_0": 73.91, "Q4_K": 258.6, "Q5_K": 526.7, "Q6_K": 347.0,
+             "Q4_1": 4.612, "Q5_0": 9.234, "Q5_1": 9.228, "Q2_K": 13.87, "Q3_K": 43.34}
 
 
 def _random_bytes(n: int, seed: int) -> np.ndarray:
@@ -102,9 +108,17 @@ def random_blocks(type_name: str, n_blocks: int, std: float, seed: int) -> np.nd
     b = _random_bytes(n_blocks * bb, seed).reshape(n_blocks, bb)
     rng = np.random.default_rng(seed ^ 0x5EED)
     d = (std / _UNIT_STD[type_name]) * rng.uniform(0.5, 1.5, size=n_blocks)
-    if type_name in ("Q4_0", "Q8_0"):
+    if type_name in ("Q4_0", "Q8_0", "Q5_0"):
         d *= rng.choice([-1.0, 1.0], size=n_blocks)
         b[:, 0:2] = _f16_bytes(d)
+    elif type_name in ("Q4_1", "Q5_1"):
+        b[:, 0:2] = _f16_bytes(d)
+        b[:, 2:4] = _f16_bytes((-7.5 if type_name == "Q4_1" else -15.5) * d)
+    elif type_name == "Q2_K":
+        b[:, 80:82] = _f16_bytes(d)
+        b[:, 82:84] = _f16_bytes(1.5 * d)
+    elif type_name == "Q3_K":
+        b[:, 108:110] = _f16_bytes(d)
     elif type_name == "Q4_K":
         b[:, 0:2] = _f16_bytes(d)
         b[:, 2:4] = _f16_bytes(7.5 * d)
@@ -143,8 +157,10 @@ def tensor_types(arch: Arch, ftype: str) -> Dict[str, str]:
         base, outw = "Q4_K", "Q4_K"
     elif ftype == "Q6_K":
         base, outw = "Q6_K", "Q6_K"
-    elif ftype == "Q5_K":
-        base, outw = "Q5_K", "Q5_K"
+    elif ftype in ("Q5_K", "Q4_1", "Q5_0", "Q5_1", "Q2_K", "Q3_K"):   # pure, for tests
+        base, outw = ftype, ftype
+    elif ftype == "Q2_K_mix":      # like llama.cpp's Q2_K files: Q2_K with attn_v at Q4_K, ffn_down at Q3_K, output at Q6_K
+        base, outw = "Q2_K", "Q6_K"
     elif ftype == "F16":
         base, outw = "F16", "F16"
     else:
@@ -162,8 +178,8 @@ def tensor_types(arch: Arch, ftype: str) -> Dict[str, str]:
         v_t = "Q6_K" if more else base
         if ftype == "Q4_K_M" and not more and arch.n_head // arch.n_head_kv >= 8 and arch.n_layer >= 80:
             v_t = "Q5_K"  # 70B-class rule
-        put(p + "attn_v.weight", v_t)
-        put(p + "ffn_down.weight", "Q6_K" if more else base)
+        put(p + "attn_v.weight", "Q4_K" if ftype == "Q2_K_mix" else v_t)
+        put(p + "ffn_down.weight", "Q3_K" if ftype == "Q2_K_mix" else "Q6_K" if more else base)
     return out
 
 

@@ -32,7 +32,8 @@ static int g_exact = 0;        /* cr_set_exact(1): float activations against deq
                                   the reference computes (it quantises activations to int8), but a sharp checker for deep models,
                                   where the int8 noise of 100+ mat-vecs adds up to ~10% of the logit spread */
 
-enum { T_F32 = 0, T_F16 = 1, T_Q4_0 = 2, T_Q8_0 = 8, T_Q4_K = 12, T_Q5_K = 13, T_Q6_K = 14 };
+enum { T_F32 = 0, T_F16 = 1, T_Q4_0 = 2, T_Q4_1 = 3, T_Q5_0 = 6, T_Q5_1 = 7, T_Q8_0 = 8, T_Q2_K = 10, T_Q3_K = 11,
+       T_Q4_K = 12, T_Q5_K = 13, T_Q6_K = 14 };
 
 typedef struct {
     const uint8_t* data;
@@ -89,10 +90,11 @@ static void k_scale_min(const uint8_t* s, int is, int* sc, int* m) {
     else { *sc = (s[is + 4] & 15) | ((s[is - 4] >> 6) << 4); *m = (s[is + 4] >> 4) | ((s[is] >> 6) << 4); }
 }
 
-static int blk_elems(int t) { return (t == T_F32 || t == T_F16) ? 1 : (t == T_Q4_0 || t == T_Q8_0) ? 32 : 256; }
+static int blk_elems(int t) { return (t == T_F32 || t == T_F16) ? 1 : (t == T_Q4_0 || t == T_Q8_0 || t == T_Q4_1 || t == T_Q5_0 || t == T_Q5_1) ? 32 : 256; }
 static int blk_bytes(int t) {
     switch (t) { case T_F32: return 4; case T_F16: return 2; case T_Q4_0: return 18; case T_Q8_0: return 34;
-                 case T_Q4_K: return 144; case T_Q5_K: return 176; case T_Q6_K: return 210; }
+                 case T_Q4_K: return 144; case T_Q5_K: return 176; case T_Q6_K: return 210;
+                 case T_Q4_1: return 20; case T_Q5_0: return 22; case T_Q5_1: return 24; case T_Q2_K: return 84; case T_Q3_K: return 110; }
     return 0;
 }
 
@@ -112,6 +114,22 @@ static void dequant_block(int type, const uint8_t* p, float* o) {
                 for (int l = 0; l < 32; l++) { int by = qs[(is >> 1) * 32 + l]; int q = (is & 1) ? by >> 4 : by & 15;
                     if (type == T_Q5_K) q |= ((p[16 + l] >> is) & 1) << 4;
                     o[is * 32 + l] = d * sc * q - dm * m; } } } break;
+        /* the block formats below follow gguf-py's dequantisers (Q4_1, Q5_0, Q5_1, Q2_K, Q3_K in gguf/quants.py) */
+        case T_Q4_1: { uint16_t dh, mh; memcpy(&dh, p, 2); memcpy(&mh, p + 2, 2); float d = h2f(dh), m = h2f(mh);
+            for (int j = 0; j < 16; j++) { o[j] = d * (p[4 + j] & 15) + m; o[16 + j] = d * (p[4 + j] >> 4) + m; } } break;
+        case T_Q5_0: case T_Q5_1: { const int of = type == T_Q5_0 ? 2 : 4; uint16_t dh, mh = 0; memcpy(&dh, p, 2);
+            if (type == T_Q5_1) memcpy(&mh, p + 2, 2);
+            float d = h2f(dh), m = type == T_Q5_1 ? h2f(mh) : 0.f; uint32_t qh; memcpy(&qh, p + of, 4);
+            for (int e = 0; e < 32; e++) { int q = e < 16 ? (p[of + 4 + e] & 15) : (p[of + 4 + e - 16] >> 4); q |= (int)((qh >> e) & 1u) << 4;
+                o[e] = type == T_Q5_0 ? d * (q - 16) : d * q + m; } } break;
+        case T_Q2_K: { uint16_t dh, mh; memcpy(&dh, p + 80, 2); memcpy(&mh, p + 82, 2); float d = h2f(dh), dm = h2f(mh);
+            for (int e = 0; e < 256; e++) { int sc = p[e >> 4]; int q = (p[16 + 32 * (e >> 7) + (e & 31)] >> (2 * ((e >> 5) & 3))) & 3;
+                o[e] = d * (sc & 15) * q - dm * (sc >> 4); } } break;
+        case T_Q3_K: { uint16_t dh; memcpy(&dh, p + 108, 2); float d = h2f(dh);
+            for (int e = 0; e < 256; e++) { int is = e >> 4;
+                int sc = (((p[96 + (is & 7)] >> (4 * (is >> 3))) & 15) | (((p[104 + (is & 3)] >> (2 * (is >> 2))) & 3) << 4)) - 32;
+                int ql = (p[32 + 32 * (e >> 7) + (e & 31)] >> (2 * ((e >> 5) & 3))) & 3; int hb = (p[e & 31] >> (e >> 5)) & 1;
+                o[e] = d * sc * (ql - (hb ? 0 : 4)); } } break;
         case T_Q6_K: { uint16_t dh; memcpy(&dh, p + 208, 2); float d = h2f(dh);
             for (int e = 0; e < 256; e++) { int hf = e >> 7, ep = e & 127, nib = ep >> 6, kq = ep >> 5, l = ep & 31;
                 int lo = p[64 * hf + (ep & 63)]; lo = nib ? lo >> 4 : lo & 15;
@@ -280,6 +298,11 @@ static void matvec(const cr_tensor* w, const int8_t* q8, const float* q8d, const
                         s[6 + g] += (((ql[l + 32] >> 4) | (((qh[l] >> 6) & 3) << 4)) - 32) * aa[l + 96]; }
                     for (int g = 0; g < 8; g++) sumi += sc[8 * hf + g] * s[g]; }
                 acc += h2f(dh) * q8d[b] * sumi; }
+        } else {        /* Q4_1, Q5_0, Q5_1, Q2_K, Q3_K: no integer kernel here, float dot on the dequantised block */
+            const int be = blk_elems(t), bb = blk_bytes(t); float tmp[256];
+            for (int b = 0; b < K / be; b++) { dequant_block(t, r + (size_t)b * bb, tmp);
+                float s = 0.f; for (int i = 0; i < be; i++) s += tmp[i] * xf[b * be + i];
+                acc += s; }
         }
         y[n] = acc;
     }

@@ -26,6 +26,15 @@ Published block layouts restated here (all little endian, fp16 scale fields):
         nibbles of ql[0..63], high nibbles of ql[0..63], 2-bit planes of qh[0..31];
         value = (d*scale[e/16]) * (q - 32)                    [gguf/quants.py:552-572]
 
+  Q4_1  (32 elems, 20 B): d | m | qs[16]; nibbles as Q4_0; value = q * d + m            [gguf/quants.py Q4_1]
+  Q5_0  (32 elems, 22 B): d | qh[4] | qs[16]; 5th bit of elem j = bit j of qh (u32);
+        value = ((nibble | bit << 4) - 16) * d                                          [gguf/quants.py Q5_0]
+  Q5_1  (32 elems, 24 B): d | m | qh[4] | qs[16]; value = (nibble | bit << 4) * d + m   [gguf/quants.py Q5_1]
+  Q2_K  (256 elems, 84 B): scales[16] (low nibble scale, high nibble min, per 16 elems) | qs[64] | d | dmin;
+        per 128 elems: 2-bit planes of qs[0..31]; value = (d*sc)*q - (dmin*m)           [gguf/quants.py Q2_K]
+  Q3_K  (256 elems, 110 B): hmask[32] | qs[64] | scales[12] (16 x 6 bit, minus 32) | d;
+        q = 2-bit plane of qs - (hmask bit ? 0 : 4); value = (d*scale) * q              [gguf/quants.py Q3_K]
+
 All arithmetic is float32 with separate multiply and subtract (no fused multiply-add),
 which is what the CUDA dequantisation kernels reproduce bit for bit.
 """
@@ -34,8 +43,10 @@ from __future__ import annotations
 import numpy as np
 
 F32, F16, Q4_0, Q8_0, Q4_K, Q5_K, Q6_K = 0, 1, 2, 8, 12, 13, 14
+Q4_1, Q5_0, Q5_1, Q2_K, Q3_K = 3, 6, 7, 10, 11
 BLOCK = {F32: (1, 4), F16: (1, 2), Q4_0: (32, 18), Q8_0: (32, 34),
-         Q4_K: (256, 144), Q5_K: (256, 176), Q6_K: (256, 210)}
+         Q4_K: (256, 144), Q5_K: (256, 176), Q6_K: (256, 210),
+         Q4_1: (32, 20), Q5_0: (32, 22), Q5_1: (32, 24), Q2_K: (256, 84), Q3_K: (256, 110)}
 
 
 def _f16(b: np.ndarray) -> np.ndarray:
@@ -103,6 +114,42 @@ def dequantize(raw: np.ndarray, ggml_type: int) -> np.ndarray:
         q = (lo | (h2 << 4)).astype(np.int8) - np.int8(32)
         dl = (d * sc).reshape(n, 16, 1)
         return (dl * q.reshape(n, 16, 16).astype(np.float32)).reshape(-1)
+    if ggml_type == Q4_1:
+        d, m = _f16(blk[:, 0:2]), _f16(blk[:, 2:4])
+        qs = blk[:, 4:20]
+        q = np.concatenate([qs & 15, qs >> 4], axis=1).astype(np.float32)
+        return (d * q + m).reshape(-1)
+    if ggml_type in (Q5_0, Q5_1):
+        o = 2 if ggml_type == Q5_0 else 4
+        d = _f16(blk[:, 0:2])
+        qh = np.ascontiguousarray(blk[:, o:o + 4]).view(np.uint32)                       # (n, 1)
+        bit = ((qh >> np.arange(32, dtype=np.uint32)[None, :]) & 1).astype(np.uint8)      # (n, 32)
+        qs = blk[:, o + 4:o + 20]
+        q = np.concatenate([qs & 15, qs >> 4], axis=1) | (bit << 4)
+        if ggml_type == Q5_0:
+            return (d * (q.astype(np.int8) - np.int8(16)).astype(np.float32)).reshape(-1)
+        return (d * q.astype(np.float32) + _f16(blk[:, 2:4])).reshape(-1)
+    if ggml_type == Q2_K:
+        sc = blk[:, 0:16]
+        qs = blk[:, 16:80].reshape(n, 2, 1, 32)
+        d, dmin = _f16(blk[:, 80:82]), _f16(blk[:, 82:84])
+        dl = (d * (sc & 15).astype(np.float32)).reshape(n, 16, 1)
+        ml = (dmin * (sc >> 4).astype(np.float32)).reshape(n, 16, 1)
+        q = ((qs >> np.array([0, 2, 4, 6], dtype=np.uint8).reshape(1, 1, 4, 1)) & 3).reshape(n, 16, 16).astype(np.float32)
+        return (dl * q - ml).reshape(-1)
+    if ggml_type == Q3_K:
+        hmask = blk[:, 0:32].reshape(n, 1, 1, 32)
+        qs = blk[:, 32:96].reshape(n, 2, 1, 32)
+        scb = blk[:, 96:108]
+        d = _f16(blk[:, 108:110])
+        lsc = (scb[:, 0:8].reshape(n, 1, 8) >> np.array([0, 4], dtype=np.uint8).reshape(1, 2, 1)).reshape(n, 16) & 15
+        hsc = (scb[:, 8:12].reshape(n, 1, 4) >> np.array([0, 2, 4, 6], dtype=np.uint8).reshape(1, 4, 1)).reshape(n, 16) & 3
+        scales = ((lsc | (hsc << 4)).astype(np.int8) - np.int8(32)).astype(np.float32)
+        dl = (d * scales).reshape(n, 16, 1)
+        ql = ((qs >> np.array([0, 2, 4, 6], dtype=np.uint8).reshape(1, 1, 4, 1)) & 3).reshape(n, 16, 16)
+        qh = ((hmask >> np.arange(8, dtype=np.uint8).reshape(1, 1, 8, 1)) & 1).reshape(n, 16, 16) ^ 1
+        q = (ql.astype(np.int8) - (qh << 2).astype(np.int8)).astype(np.float32)
+        return (dl * q).reshape(-1)
     raise ValueError(f"unsupported ggml type {ggml_type}")
 
 

@@ -1,5 +1,5 @@
 P=llama-fastapi-k8s-gpu_b200
-for v in lib lib_v1; do
+for v in lib lib_head lib lib_head; do
   echo "== $v"
-  for rep in 1 2; do B200_GGUF_LIB=$P/$v/libb200gguf.so timeout 120 python bench.py --steps 30 --warmup 5 --no-cpu-baseline --batch-extra 0 --no-parity-check 2>&1 | grep -o '"ms_per_step": [0-9.]*'; done
+  B200_GGUF_LIB=$P/$v/libb200gguf.so timeout 120 python bench.py --steps 30 --warmup 5 --no-cpu-baseline --batch-extra 0 --no-parity-check 2>&1 | grep -o '"ms_per_step": [0-9.]*'
 done

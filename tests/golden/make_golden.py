@@ -47,6 +47,11 @@ def main():
         raw = finite_random_blocks(tname, 64, rng)
         out[f"{tname}_raw"] = raw
         out[f"{tname}_f32"] = dequantize(raw, getattr(T, tname)).reshape(-1).astype(np.float32)
+    rng2 = np.random.default_rng(2025)          # types added in round 2: their own stream, the entries above stay as they were
+    for tname in ("Q4_1", "Q5_0", "Q5_1", "Q2_K", "Q3_K"):
+        raw = finite_random_blocks(tname, 64, rng2)
+        out[f"{tname}_raw"] = raw
+        out[f"{tname}_f32"] = dequantize(raw, getattr(T, tname)).reshape(-1).astype(np.float32)
     np.savez_compressed(os.path.join(HERE, "blocks.npz"), **out)
 
     import torch

@@ -11,7 +11,7 @@ import pytest
 from conftest import PKG
 from util import P, TYPE_IDS, finite_random_blocks
 
-QTYPES = ["Q4_0", "Q8_0", "Q4_K", "Q5_K", "Q6_K"]
+QTYPES = ["Q4_0", "Q8_0", "Q4_K", "Q5_K", "Q6_K", "Q4_1", "Q5_0", "Q5_1", "Q2_K", "Q3_K"]
 
 
 @pytest.fixture(scope="module")
@@ -46,7 +46,7 @@ def test_host_chunk_dot_vs_oracle(host_lib, tname, K):
     x = (rng.standard_normal(K) * rng.uniform(0.1, 3, size=K)).astype(np.float32)
     W = gb.dequantize(w, t).reshape(N, K).astype(np.float64)
     ref = W @ x.astype(np.float64)
-    for mis in ((0, 2) if tname == "Q6_K" else (0,)):
+    for mis in {"Q6_K": (0, 2), "Q3_K": (0, 2, 14), "Q2_K": (0, 4, 12)}.get(tname, (0,)):
         y = np.empty(N, np.float32)
         assert host_lib.b2_host_matvec(t, w.ctypes.data_as(P), N, K, x.ctypes.data_as(P), y.ctypes.data_as(P), 1, mis) == 0
         assert np.abs(y - ref).max() / np.abs(ref).std() < 1e-3, (tname, K, mis)

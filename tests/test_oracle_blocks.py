@@ -7,7 +7,7 @@ import pytest
 
 from util import TYPE_IDS, finite_random_blocks
 
-QTYPES = ["Q4_0", "Q8_0", "Q4_K", "Q5_K", "Q6_K"]
+QTYPES = ["Q4_0", "Q8_0", "Q4_K", "Q5_K", "Q6_K", "Q4_1", "Q5_0", "Q5_1", "Q2_K", "Q3_K"]
 GOLD = os.path.join(os.path.dirname(__file__), "golden", "blocks.npz")
 
 
