@@ -144,26 +144,35 @@ __device__ __forceinline__ void st_volatile_shared(unsigned int* p, unsigned int
 // group-major: q -> (group q / tpg, matrix, K-slice). A round is TPB tiles, R lanes per tile (one row-slice copy each).
 __device__ __forceinline__ void mv_produce(const MvParams& p, const CtaWork& work, MvShared& sh, uint8_t* ring, int prod_idx, int lane) {
     const uint32_t S = (uint32_t)p.n_stages;
-    const int n_prod = p.n_prod;
+    const int n_prod = p.n_prod, tpg = work.tpg, n_sl = p.n_slices;
+    if (tpg <= 0) return;
     const int tsub = lane / R, rsub = lane % R;
-    for (int qb = prod_idx; qb < work.total; qb += TPB * n_prod) {
-        const int q = qb + tsub * n_prod;
+    const bool gateup = (p.mode == MV_GATEUP);
+    // loop invariants out of the parameter block (a gate/up pair has one type, one K: mv_plan); the producers' issue rate
+    // is what keeps the ring full, so the per-round bookkeeping is carried incrementally (no division in the loop)
+    const MvSeg& sg0 = p.seg[gateup ? 0 : work.seg];
+    const int sb = sg0.slice_bytes, row_bytes = sg0.row_bytes;
+    const uintptr_t w0 = (uintptr_t)sg0.w, w1 = gateup ? (uintptr_t)p.seg[1].w : w0;
+    const uint32_t stage_bytes = (uint32_t)p.stage_bytes, slot_off = (uint32_t)(rsub * p.slot_bytes);
+    const int step = TPB * n_prod;
+    const int step_g = step / tpg, step_w = step % tpg;
+    const uint32_t step_u = (uint32_t)step / S, step_s = (uint32_t)step % S;
+    int q = prod_idx + tsub * n_prod;
+    int gi = q / tpg, within = q % tpg;
+    uint32_t st = (uint32_t)q % S, use = (uint32_t)q / S;
+    for (int qb = prod_idx; qb < work.total; qb += step) {
         const bool have = q < work.total;
-        const uint8_t* src = nullptr; uint32_t bytes = 0, use = 0; uint8_t* dst = nullptr; int st = 0;
+        const uint8_t* src = nullptr; uint32_t bytes = 0; uint8_t* dst = nullptr;
         if (have) {
-            const int gi = q / work.tpg, within = q % work.tpg;
-            const int seg = (p.mode == MV_GATEUP) ? within / p.n_slices : work.seg;
-            const int slice = within % p.n_slices;
-            const MvSeg& sg = p.seg[seg];
+            const int m = (gateup && within >= n_sl) ? 1 : 0;
+            const int slice = within - m * n_sl;
             const int row0 = work.r0 + gi * R, nrows = min(R, work.r1 - row0);
-            st = (int)((uint32_t)q % S); use = (uint32_t)q / S;
             if (rsub < nrows) {
-                const int sb = sg.slice_bytes;
-                const int len = min(sb, sg.row_bytes - slice * sb);        // the last slice may be shorter
-                const uintptr_t start = (uintptr_t)sg.w + (size_t)(row0 + rsub) * sg.row_bytes + (size_t)slice * sb;
+                const int len = min(sb, row_bytes - slice * sb);           // the last slice may be shorter
+                const uintptr_t start = (m ? w1 : w0) + (size_t)(row0 + rsub) * row_bytes + (size_t)(slice * sb);
                 const uintptr_t a0 = start & ~(uintptr_t)15, a1 = (start + len + 15) & ~(uintptr_t)15;
                 src = (const uint8_t*)a0; bytes = (uint32_t)(a1 - a0);
-                dst = ring + (size_t)st * p.stage_bytes + rsub * p.slot_bytes;
+                dst = ring + st * stage_bytes + slot_off;
             }
             if (rsub == 0) mbar_wait(&sh.empty[st], (use & 1u) ^ 1u, p.err, 0x10001u, (unsigned)q);
         }
@@ -177,6 +186,9 @@ __device__ __forceinline__ void mv_produce(const MvParams& p, const CtaWork& wor
         }
         __syncwarp();
         if (bytes) tma_load_1d(dst, src, bytes, &sh.full[st]);
+        q += step;
+        gi += step_g; within += step_w; if (within >= tpg) { within -= tpg; gi++; }
+        use += step_u; st += step_s; if (st >= S) { st -= S; use++; }
     }
 }
 
