@@ -1237,6 +1237,7 @@ static int op_matvec_common(int device, MvParams& p, const void* w0, const void*
     if (resid) CK(cudaMemcpy(dy.p, resid, (size_t)n_rows * 4, cudaMemcpyHostToDevice));
     p.y = dy.as<float>(); p.resid = dy.as<float>();
     p.err = kernel_error_word();
+    if ((rc = mv_plan(p, n_ctas))) return fail(B2_ERR_UNSUPPORTED, "mat-vec plan failed");     // again, now that the weights have their addresses (tensor maps)
     CK(mv_launch(p, n_ctas, 0, planes != 1, false));
     CK(cudaDeviceSynchronize());
     { int rc2 = check_kernel_error(); if (rc2) return rc2; }
@@ -1317,13 +1318,15 @@ extern "C" int b2_bench_matvec(int device, int mode, int type, int n_rows, int K
     CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
     CK(cudaDeviceSynchronize());
     float ms = 0.f;
+    std::vector<MvParams> pv((size_t)n_copies, p);   // one planned parameter block per weight copy (the tensor maps hold the addresses)
+    for (int c2 = 0; c2 < n_copies; c2++) {
+        const uint8_t* base = dw.as<uint8_t>() + (size_t)c2 * wpad * nmat;
+        for (int m = 0; m < nmat; m++) pv[c2].seg[m].w = base + (size_t)m * wpad;
+        if (mv_plan(pv[c2], n_ctas)) return fail(B2_ERR_UNSUPPORTED, "mat-vec plan failed");
+    }
     for (int pass = 0; pass < 2; pass++) {          // pass 0 warms up
         if (pass) CK(cudaEventRecord(e0, st));
-        for (int i = 0; i < iters; i++) {
-            const uint8_t* base = dw.as<uint8_t>() + (size_t)(i % n_copies) * wpad * nmat;
-            for (int m = 0; m < nmat; m++) p.seg[m].w = base + (size_t)m * wpad;
-            CK(mv_launch(p, n_ctas, st, planes != 1, pdl != 0));
-        }
+        for (int i = 0; i < iters; i++) CK(mv_launch(pv[i % n_copies], n_ctas, st, planes != 1, pdl != 0));
         if (pass) CK(cudaEventRecord(e1, st));
         CK(cudaStreamSynchronize(st));
     }

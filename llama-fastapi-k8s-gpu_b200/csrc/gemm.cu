@@ -272,11 +272,7 @@ struct GemmBars {
 };
 static_assert(sizeof(GemmBars) <= GM_HDR, "barrier header");
 
-// 2-D TMA tile load: box (inner = one 256-weight span of a row, outer = 128 rows) -> dense [128][box bytes] in smem
-__device__ __forceinline__ void tma_load_2d(void* dst, const void* tmap, int c0, int c1, uint64_t* bar) {
-    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-                 ::"r"(smem_u32(dst)), "l"(tmap), "r"(c0), "r"(c1), "r"(smem_u32(bar)) : "memory");
-}
+// (tma_load_2d is in ptx.cuh: box (inner = one 256-weight span of a row, outer = 128 rows) -> dense [128][box bytes] in smem)
 
 // words of one 64-weight block inside the 256-weight span W (registers; c is a compile-time constant after unrolling)
 template <int C>

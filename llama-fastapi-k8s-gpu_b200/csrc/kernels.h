@@ -28,7 +28,7 @@ inline cudaError_t launch_chain(void (*k)(KArgs...), dim3 grid, dim3 block, size
 // ---------------------------------------------------------------- mat-vec (matvec.cu)
 enum MvMode { MV_STORE = 0, MV_RESID = 1, MV_QKV = 2, MV_GATEUP = 3 };
 #ifndef B2_MV_NCW
-#define B2_MV_NCW 18
+#define B2_MV_NCW 19
 #endif
 constexpr int MV_NCW = B2_MV_NCW;            // consumer warps per CTA
 constexpr int MV_MAX_PROD = 4;               // TMA producer warps per CTA (upper bound; 2 are launched)
@@ -37,6 +37,7 @@ constexpr int MV_MAX_STAGES = 48;            // ring stages (upper bound)
 constexpr int MV_SHARED_HDR = 2048;          // barriers + reduction scratch at the start of dynamic smem
 
 struct MvSeg {
+    alignas(64) unsigned char tmap[128];   // CUtensorMap over the raw rows (8-byte elements); valid when MvParams::use_tma
     const uint8_t* w;   // quantised rows, unchanged GGUF bytes
     int type;           // ggml type id
     int n_rows;
@@ -74,6 +75,9 @@ struct MvParams {
     int slot_bytes;         // one row-slice slot of a stage
     int stage_bytes, n_stages; // ring: tile q of a CTA lives in stage q % n_stages
     int n_prod;             // producer warps
+    int use_tma;            // 1: a tile (R row-slices) is ONE 2-D tensor copy, rows land densely (pitch = slice bytes);
+                            // 2: the same as a 3-D copy of two half-slices per row (Q8_0: a slice is wider than one box);
+                            // 0: R 1-D bulk copies into slots of slot_bytes (rows or slices off a 16-byte boundary)
     int act_plane;          // bytes of one int8 activation plane (K padded to whole slices)
     int act_off;            // byte offset of the activation block in dynamic shared memory
     int part_off;           // byte offset of the partial-sum slots (groups spanning several tiles)

@@ -1,6 +1,7 @@
 // Decode mat-vec: host side (planning, launches). The kernel and its design notes are in matvec_body.cuh; this file
 // instantiates it for the block formats of llama.cpp's common mixes, matvec_extra.cu for the rest.
 #include "matvec_body.cuh"
+#include <cuda.h>
 
 namespace b2 {
 
@@ -10,12 +11,26 @@ cudaError_t mv_extra_launch(cudaLaunchConfig_t* cfg, const MvParams& p, bool act
 // ---------------------------------------------------------------- host side
 static int g_stage_cap = 0;      // B2_MV_STAGES (tuning): read once in mv_init
 static int g_n_prod = NPROD;     // B2_MV_PROD (tuning)
+static int g_no_tma2d = 0;       // B2_MV_NO_TMA2D=1 (tuning): always four 1-D copies per tile
+static int g_tma_modes = 15;     // B2_MV_TMA_MODES (diagnosis): bit m set = launches of MvMode m may use the tensor copies
+
+typedef CUresult (*MvEncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                    const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static MvEncodeTiledFn g_mv_encode = nullptr;
 
 cudaError_t mv_init() {   // per device: allow > 48 KB dynamic shared memory; read the tuning knobs once
     static bool env_read = false;
     if (!env_read) {
         if (const char* s = getenv("B2_MV_STAGES")) g_stage_cap = atoi(s);
         if (const char* s = getenv("B2_MV_PROD")) { const int v = atoi(s); if (v >= 1 && v <= NPROD) g_n_prod = v; }
+        if (const char* s = getenv("B2_MV_NO_TMA2D")) g_no_tma2d = atoi(s);
+        if (const char* s = getenv("B2_MV_TMA_MODES")) g_tma_modes = atoi(s);
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess) g_mv_encode = (MvEncodeTiledFn)fn;
+        cudaGetLastError();
         env_read = true;
     }
     cudaError_t e;
@@ -42,6 +57,40 @@ int mv_plan(MvParams& p, int n_ctas) {
     if (p.mode == MV_GATEUP) {
         if (p.nseg != 2 || p.seg[0].n_rows != p.seg[1].n_rows) return -6;
         if (p.seg[0].type != p.seg[1].type) return -8;     // a mixed pair is run unfused by the caller
+    }
+    // One 2-D tensor copy per tile where every segment allows it: rows and slices on 16-byte boundaries, a slice within
+    // the 256-element box limit (8-byte elements: 2048 B; Q8_0 slices are 2176 B), rows at least a slice long.
+    static_assert(sizeof(CUtensorMap) == sizeof(p.seg[0].tmap), "tensor map storage");
+    p.use_tma = (g_mv_encode && !g_no_tma2d && ((g_tma_modes >> p.mode) & 1)) ? 1 : 0;
+    for (int s = 0; s < p.nseg && p.use_tma; s++) {
+        const MvSeg& sg = p.seg[s];
+        if (sg.row_bytes % 16 || ((uintptr_t)sg.w & 15) || sg.slice_bytes % 16 || sg.row_bytes < sg.slice_bytes) p.use_tma = 0;
+        else if (sg.slice_bytes > 2048) {       // wider than one box of 256 8-byte elements: two half-slices (every segment then)
+            if (sg.slice_bytes % 32 || sg.slice_bytes > 4096 || sg.row_bytes % (sg.slice_bytes / 2) || (s > 0 && p.use_tma != 2)) p.use_tma = 0;
+            else p.use_tma = 2;
+        } else if (p.use_tma == 2) p.use_tma = 0;
+    }
+    for (int s = 0; s < p.nseg && p.use_tma; s++) {
+        MvSeg& sg = p.seg[s];
+        const cuuint32_t estr[3] = {1, 1, 1};
+        CUresult r;
+        if (p.use_tma == 1) {
+            const cuuint64_t dims[2] = {(cuuint64_t)sg.row_bytes / 8, (cuuint64_t)sg.n_rows};
+            const cuuint64_t strides[1] = {(cuuint64_t)sg.row_bytes};
+            const cuuint32_t boxd[2] = {(cuuint32_t)sg.slice_bytes / 8, (cuuint32_t)R};
+            r = g_mv_encode(reinterpret_cast<CUtensorMap*>(sg.tmap), CU_TENSOR_MAP_DATA_TYPE_UINT64, 2, (void*)sg.w, dims, strides, boxd, estr,
+                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        } else {
+            const int half = sg.slice_bytes / 2;
+            const cuuint64_t dims[3] = {(cuuint64_t)half / 8, (cuuint64_t)(sg.row_bytes / half), (cuuint64_t)sg.n_rows};
+            const cuuint64_t strides[2] = {(cuuint64_t)half, (cuuint64_t)sg.row_bytes};
+            const cuuint32_t boxd[3] = {(cuuint32_t)half / 8, 2, (cuuint32_t)R};
+            r = g_mv_encode(reinterpret_cast<CUtensorMap*>(sg.tmap), CU_TENSOR_MAP_DATA_TYPE_UINT64, 3, (void*)sg.w, dims, strides, boxd, estr,
+                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        }
+        if (r != CUDA_SUCCESS) p.use_tma = 0;
     }
     p.n_slices = (p.K + B2_SLICE - 1) / B2_SLICE;
     p.slot_bytes = (max_sb + 16 + 15) / 16 * 16;           // + slack for the 16-byte alignment of each copy

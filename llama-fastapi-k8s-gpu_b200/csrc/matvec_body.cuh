@@ -3,14 +3,19 @@
 // mul_mat_vec_q + the separate rms_norm / rope / cpy / silu / add launches that the reference
 // runs under llm.create_chat_completion (/root/reference/api.py:55-63; SURVEY.md 2.3 K2-K7,K11).
 //
-// Structure: one CTA per SM, 18 consumer warps + 2 TMA producer warps (20 warps x 96 registers fill the register file;
-// measured per token: 16+2 2.01 ms, 17+3 2.00, 16+4 2.05, 19+1 2.24, 18+2 1.93), the SM's shared memory as a ring of tiles.
-//   * Tiles. A tile = one K-slice (2048 elements) of a group of R = 4 consecutive rows = 4 row-slices of 1-2 KB,
-//     brought into one ring stage with 1-D bulk copies (cp.async.bulk + mbarrier complete_tx); 4 lanes of a
-//     producer warp serve a tile (one copy each), a warp issues 8 tiles per round. Producers never touch
-//     activations, so with programmatic dependent launch they start on the weights while the previous kernel
-//     is still running, and they keep the ring full independently of how the consumers are doing.
-//   * Consumers. Tile q belongs to consumer warp q % 18, whatever row group and K-slice it is: the warps of a
+// Structure: one CTA per SM, 19 consumer warps + 1 TMA producer warp (20 warps x 96 registers fill the register file),
+// the SM's shared memory as a ring of tiles.
+//   * Tiles. A tile = one K-slice (2048 elements) of a group of R = 4 consecutive rows, brought into one ring stage by ONE
+//     tensor copy (cp.async.bulk.tensor, box = slice bytes x 4 rows of a tensor map over the raw rows as 8-byte elements;
+//     Q8_0, whose slice is wider than a box, as a 3-D copy of two half-slices per row) + mbarrier complete_tx; rows land
+//     densely. Launches whose rows or slices are off a 16-byte boundary (Q6_K / Q2_K / Q3_K with K % 2048 != 0, tiny K)
+//     use four 1-D bulk copies per tile instead, into slots with room for the misalignment.
+//     The producer never touches activations, so with programmatic dependent launch it starts on the weights while the
+//     previous kernel is still running, and it keeps the ring full independently of how the consumers are doing. Its issue
+//     rate matters: with 1-D copies (4 per tile) one producer warp could not keep up (2.02 ms/token against 1.87 with two),
+//     with tensor copies one is enough and the freed warp computes (measured per token: 16+2 warps 2.01 ms, 17+3 2.00,
+//     16+4 2.05, 18+2 1.87, 19+1 with tensor copies 1.82).
+//   * Consumers. Tile q belongs to consumer warp q % 19, whatever row group and K-slice it is: the warps of a
 //     CTA stay within one tile of each other to the end (the kernel is one link of a chain of ~160 dependent
 //     launches per token, so the last warp of the last CTA is what the next kernel waits for). Per tile a lane
 //     loads its 64 quantised activations (two int8 planes + packed scales) from shared memory and reuses them
@@ -47,7 +52,7 @@ namespace b2 {
 constexpr int ROW_UNROLL = B2_ROW_UNROLL;   // rows of a tile interleaved in the instruction stream (more overflowed the instruction cache)
 constexpr int NCW = MV_NCW;                 // consumer warps
 #ifndef B2_MV_NPROD
-#define B2_MV_NPROD 2
+#define B2_MV_NPROD 1
 #endif
 constexpr int NPROD = B2_MV_NPROD;          // producer warps
 constexpr int R = MV_ROWS;                  // rows per group
@@ -160,6 +165,28 @@ __device__ __forceinline__ void mv_produce(const MvParams& p, const CtaWork& wor
     int q = prod_idx + tsub * n_prod;
     int gi = q / tpg, within = q % tpg;
     uint32_t st = (uint32_t)q % S, use = (uint32_t)q / S;
+    if (p.use_tma) {
+        // one 2-D tensor copy per tile: box = (slice bytes, R rows) at (slice, row0); rows past the matrix and bytes past
+        // the row are filled with zeros and still count towards the transaction bytes
+        const void* tm0 = p.seg[gateup ? 0 : work.seg].tmap;
+        const void* tm1 = gateup ? (const void*)p.seg[1].tmap : tm0;
+        for (int qb = prod_idx; qb < work.total; qb += step) {
+            if (q < work.total && rsub == 0) {
+                const int m = (gateup && within >= n_sl) ? 1 : 0;
+                const int slice = within - m * n_sl;
+                mbar_wait(&sh.empty[st], (use & 1u) ^ 1u, p.err, 0x10001u, (unsigned)q);
+                mbar_arrive_expect_tx(&sh.full[st], (uint32_t)(R * sb));
+                st_volatile_shared(&sh.issued[st], use + 1u);
+                if (p.use_tma == 2) tma_load_3d(ring + st * stage_bytes, m ? tm1 : tm0, 0, 2 * slice, work.r0 + gi * R, &sh.full[st]);
+                else tma_load_2d(ring + st * stage_bytes, m ? tm1 : tm0, slice * (sb >> 3), work.r0 + gi * R, &sh.full[st]);
+            }
+            __syncwarp();       // rounds stay in order: a lane that ran ahead could arm a later use of a stage before an earlier one
+            q += step;
+            gi += step_g; within += step_w; if (within >= tpg) { within -= tpg; gi++; }
+            use += step_u; st += step_s; if (st >= S) { st -= S; use++; }
+        }
+        return;
+    }
     for (int qb = prod_idx; qb < work.total; qb += step) {
         const bool have = q < work.total;
         const uint8_t* src = nullptr; uint32_t bytes = 0; uint8_t* dst = nullptr;
@@ -326,8 +353,9 @@ __device__ __forceinline__ void consume(const MvParams& p, const CtaWork& work, 
     const int seg0 = gateup ? 0 : work.seg;
     const uint32_t row_bytes = (uint32_t)p.seg[seg0].row_bytes;
     const uint32_t wlo0 = (uint32_t)(uintptr_t)p.seg[seg0].w, wlo1 = gateup ? (uint32_t)(uintptr_t)p.seg[1].w : wlo0;
-    const uint32_t stage_bytes = (uint32_t)p.stage_bytes, slot_bytes = (uint32_t)p.slot_bytes;
     const uint32_t sb = (uint32_t)slice_bytes(T);
+    const bool tma = p.use_tma != 0;                       // rows of a tile land densely at the 16-byte-aligned slice start
+    const uint32_t stage_bytes = (uint32_t)p.stage_bytes, slot_bytes = tma ? sb : (uint32_t)p.slot_bytes;
     const int resid_off = p.seg[work.seg].out_off;
     // tile bookkeeping advances by NCW per iteration: carried incrementally (no integer division in the loop)
     int gi = warp / tpg, within = warp % tpg;
@@ -372,7 +400,7 @@ __device__ __forceinline__ void consume(const MvParams& p, const CtaWork& work, 
             // element): a group with a single pair computes two rows of stale bytes that nobody looks at
 #pragma unroll ROW_UNROLL
             for (int r = 0; r < R; r++) {
-                const uint32_t off = (T == T_Q6_K || T == T_Q2_K || T == T_Q3_K) ? ((row_lo + r * row_bytes) & 15u) : 0u;
+                const uint32_t off = ((T == T_Q6_K || T == T_Q2_K || T == T_Q3_K) && !tma) ? ((row_lo + r * row_bytes) & 15u) : 0u;
                 const float d = row_dot<T, ACT2>(stage + r * slot_bytes + off, lane, la);
                 acc[0] = acc[1]; acc[1] = acc[2]; acc[2] = acc[3]; acc[3] = d;
             }
@@ -422,7 +450,7 @@ __device__ __forceinline__ void consume(const MvParams& p, const CtaWork& work, 
 // EXTRA = the instantiation for the block formats outside llama.cpp's common mixes (Q4_1, Q5_0, Q5_1, Q2_K, Q3_K): kept out of
 // the main kernel, whose code layout they disturbed (+2 % per token on Q4_K_M with all ten formats in one kernel)
 template <bool ACT2, bool EXTRA>
-__global__ void __launch_bounds__(MV_THREADS, 1) matvec_kernel(const MvParams p) {
+__global__ void __launch_bounds__(MV_THREADS, 1) matvec_kernel(const __grid_constant__ MvParams p) {
     extern __shared__ __align__(128) uint8_t smem_raw[];
     MvShared& sh = *reinterpret_cast<MvShared*>(smem_raw);
     uint8_t* ring = smem_raw + p.ring_off;
