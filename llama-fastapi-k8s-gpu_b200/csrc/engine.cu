@@ -433,9 +433,9 @@ extern "C" int b2_engine_tp_mode(b2_engine* e, int* rank, int* world, int* peer_
     return B2_OK;
 }
 
-// block formats the tensor-core GEMM dequantises (gemm.cu); models with other types (Q4_1, Q5_0, Q5_1, Q2_K, Q3_K) run prompts
-// and batches through the mat-vec path, one token at a time
-static bool gemm_type_ok(int t) { return t == T_Q4_0 || t == T_Q8_0 || t == T_Q4_K || t == T_Q5_K || t == T_Q6_K; }
+// block formats the tensor-core GEMM dequantises (gemm.cu): all of them -- Q4_0, Q8_0, Q4_K, Q5_K, Q6_K with hand-written
+// expansions, Q4_1, Q5_0, Q5_1, Q2_K, Q3_K element by element
+static bool gemm_type_ok(int t) { return block_elems(t) != 1 && block_bytes(t) != 0; }
 
 extern "C" int b2_engine_finalize(b2_engine* e) {
     if (!e) return fail(B2_ERR_ARG, "null engine");

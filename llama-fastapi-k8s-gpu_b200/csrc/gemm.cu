@@ -264,6 +264,27 @@ __device__ __forceinline__ void dequant_store(int type, const RawKB& r, int k0, 
     }
 }
 
+// Block formats without a hand-written expansion (Q4_1, Q5_0, Q5_1, Q2_K, Q3_K): element-by-element dequantisation of the
+// 64 weights of a K block straight from global memory, one f16 rounding per weight like the fast paths. Slow per weight
+// (byte loads), but it keeps prompts and batched steps of such models on the tensor cores instead of token by token.
+constexpr int T_GENERIC = -1;
+__device__ __forceinline__ void dequant_store_generic(int type, const uint8_t* row, int k0, uint8_t* dst, uint32_t lbo) {
+    const int be = block_elems(type), bb = block_bytes(type);
+#pragma unroll 1
+    for (int ch = 0; ch < 8; ch++) {
+        uint32_t h[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const int e0 = k0 + 8 * ch + 2 * j, e1 = e0 + 1;
+            const float a = dequant_elem(type, row + (size_t)(e0 / be) * bb, e0 % be);
+            const float b = dequant_elem(type, row + (size_t)(e1 / be) * bb, e1 % be);
+            const __half2 v = __floats2half2_rn(a, b);
+            h[j] = *reinterpret_cast<const uint32_t*>(&v);
+        }
+        *reinterpret_cast<uint4*>(dst + ch * lbo) = make_uint4(h[0], h[1], h[2], h[3]);
+    }
+}
+
 struct GemmBars {
     uint64_t a_full[GM_MAX_STAGES], empty[GM_MAX_STAGES];
     uint64_t b_full[GM_MAX_BSTAGES], b_empty[GM_MAX_BSTAGES];
@@ -309,7 +330,7 @@ struct DeqCtx {
     uint8_t* stage0;
     const uint8_t* raw0;
     const uint8_t* wrow;
-    int S, NR, tid, n, n_sp, sp0, kb0, use_tma, span_bytes;
+    int S, NR, tid, n, n_sp, sp0, kb0, use_tma, span_bytes, type;
     uint32_t raw_stage_bytes, box, a_bytes, lbo_a;      // weight tile: rows * 128 B per stage, rows * 16 B between K chunks
     unsigned int* err;
     long long* dbg;
@@ -325,13 +346,17 @@ __device__ __noinline__ void deq_loop(const DeqCtx cx) {
         if (cx.dbg && i < 64) cx.dbg[i * 8 + 0] = clock64();
         if (wraps > 0) mbar_wait(&sh.empty[st], (wraps - 1) & 1, cx.err, 0x40001u, (unsigned)i);   // MMAs that read the stage are done
         if (cx.dbg && i < 64) cx.dbg[i * 8 + 1] = clock64();
-        dequant_store(TYPE, r, (i & 3) * GM_BK, cx.stage0 + (size_t)st * a_bytes + cx.tid * 16, lbo_a);
+        if (TYPE == T_GENERIC) dequant_store_generic(cx.type, cx.wrow, (cx.kb0 + i) * GM_BK, cx.stage0 + (size_t)st * a_bytes + cx.tid * 16, lbo_a);
+        else dequant_store(TYPE, r, (i & 3) * GM_BK, cx.stage0 + (size_t)st * a_bytes + cx.tid * 16, lbo_a);
         fence_proxy_async();            // generic-proxy writes -> visible to the tensor core (async proxy)
         mbar_arrive(&sh.a_full[st]);
         if (cx.dbg && i < 64) cx.dbg[i * 8 + 2] = clock64();
         if (++st == cx.S) { st = 0; wraps++; }
     };
-    if (cx.use_tma) {
+    if (TYPE == T_GENERIC) {
+        RawKB none;
+        for (int i = 0; i < cx.n; i++) emit(none, i);
+    } else if (cx.use_tma) {
         // raw spans arrive in shared memory by TMA; this thread's row is one box row. The box starts at the 16-byte
         // boundary below the span (TMA needs it); only Q6_K spans (210 B) can be off it.
         constexpr int span = TYPE == T_Q4_K ? 144 : TYPE == T_Q5_K ? 176 : TYPE == T_Q6_K ? 210 : TYPE == T_Q8_0 ? 272 : 144;
@@ -449,14 +474,15 @@ __global__ void __launch_bounds__((ROWS / 32 + 3) * 32) gemm_q_kernel(const __gr
         cx.sh = &sh; cx.stage0 = stage0; cx.raw0 = raw0; cx.S = S; cx.NR = NR; cx.raw_stage_bytes = raw_stage_bytes; cx.box = box;
         cx.tid = tid; cx.n = n; cx.n_sp = n_sp; cx.sp0 = sp0; cx.kb0 = kb0; cx.err = p.err; cx.a_bytes = a_bytes; cx.lbo_a = lbo_a;
         cx.dbg = (p.dbg && blockIdx.x == 0 && tid == 0) ? p.dbg : nullptr;
-        cx.use_tma = sg.use_tma; cx.span_bytes = sg.span_bytes;
+        cx.use_tma = sg.use_tma; cx.span_bytes = sg.span_bytes; cx.type = sg.type;
         cx.wrow = sg.w + (size_t)min(m0 + tid, sg.n_rows - 1) * sg.row_bytes;      // rows past N are computed and dropped
         switch (sg.type) {
             case T_Q4_K: deq_loop<T_Q4_K>(cx); break;
             case T_Q5_K: deq_loop<T_Q5_K>(cx); break;
             case T_Q6_K: deq_loop<T_Q6_K>(cx); break;
             case T_Q8_0: deq_loop<T_Q8_0>(cx); break;
-            default: deq_loop<T_Q4_0>(cx); break;
+            case T_Q4_0: deq_loop<T_Q4_0>(cx); break;
+            default: deq_loop<T_GENERIC>(cx); break;
         }
         // ================= epilogue
         const int last = n - 1;
@@ -613,7 +639,8 @@ int gemm_plan(GemmParams& p, int n_sms, int max_splits) {
         if ((box / 16) % 2 == 0 || g.type == T_Q6_K) box = g.type == T_Q6_K ? 240 : box + 16;   // Q6_K: room for the 14-byte misalignment
         g.box_bytes = box;
         g.use_tma = 0;
-        if (!no_tma && g_encode && g.row_bytes % 16 == 0 && ((uintptr_t)g.w & 15) == 0 && (g.type != T_Q6_K || !getenv("B2_GEMM_Q6K_DIRECT"))) {
+        const bool fast_type = g.type == T_Q4_0 || g.type == T_Q8_0 || g.type == T_Q4_K || g.type == T_Q5_K || g.type == T_Q6_K;   // the others: dequant_store_generic
+        if (fast_type && !no_tma && g_encode && g.row_bytes % 16 == 0 && ((uintptr_t)g.w & 15) == 0 && (g.type != T_Q6_K || !getenv("B2_GEMM_Q6K_DIRECT"))) {
             const cuuint64_t dims[2] = {(cuuint64_t)g.row_bytes / 2, (cuuint64_t)g.n_rows};
             const cuuint64_t strides[1] = {(cuuint64_t)g.row_bytes};
             const cuuint32_t boxd[2] = {(cuuint32_t)box / 2, (cuuint32_t)ROWS};

@@ -10,7 +10,7 @@ pytestmark = pytest.mark.gpu
 
 LOGIT_TOL = 1e-2
 MODELS = [("tiny", "Q4_K_M", 1), ("tiny128", "Q4_0", 2), ("tiny", "Q8_0", 3), ("tiny128", "Q5_K", 4), ("tiny", "Q6_K", 5),
-          # block formats only the mat-vec path reads (prompts and batches then run token by token)
+          # block formats the GEMM path dequantises element by element
           ("tiny", "Q4_1", 6), ("tiny128", "Q5_0", 7), ("tiny", "Q5_1", 8), ("tiny128", "Q2_K", 9), ("tiny", "Q3_K", 10),
           ("tiny", "Q2_K_mix", 11)]          # one launch mixes formats of both kernel instantiations
 GOLD = np.load(os.path.join(os.path.dirname(__file__), "golden", "tiny_model.npz"))

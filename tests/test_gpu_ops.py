@@ -11,8 +11,8 @@ import pytest
 from util import P, TYPE_IDS, finite_random_blocks, lib_check, ptr
 
 pytestmark = pytest.mark.gpu
-GEMM_QTYPES = ["Q4_0", "Q8_0", "Q4_K", "Q5_K", "Q6_K"]        # block formats the tensor-core GEMM dequantises
-QTYPES = GEMM_QTYPES + ["Q4_1", "Q5_0", "Q5_1", "Q2_K", "Q3_K"]  # + the ones only the mat-vec path reads
+GEMM_QTYPES = ["Q4_0", "Q8_0", "Q4_K", "Q5_K", "Q6_K"]        # block formats with a hand-written expansion in the GEMM
+QTYPES = GEMM_QTYPES + ["Q4_1", "Q5_0", "Q5_1", "Q2_K", "Q3_K"]  # + the ones the GEMM dequantises element by element
 
 
 @pytest.mark.parametrize("tname", QTYPES + ["F16", "F32"])
@@ -292,7 +292,7 @@ def _gemm_case(native_lib, tname, K, N, T, accumulate=False, n_splits=0):
     return np.abs(y - ref).max() / rms
 
 
-@pytest.mark.parametrize("tname", GEMM_QTYPES)
+@pytest.mark.parametrize("tname", QTYPES)
 @pytest.mark.parametrize("K,N,T", [(256, 128, 16), (512, 256, 1), (1024, 300, 37), (4096, 1024, 128),
                                    (2048, 128, 256), (2048, 384, 300), (14336, 256, 512)])
 def test_gemm_vs_oracle(native_lib, tname, K, N, T):
