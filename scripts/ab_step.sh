@@ -1,7 +1,8 @@
-# A/B of whole-step time between library builds (B200_GGUF_LIB picks the .so)
+# A/B of whole-step time between library builds (B200_GGUF_LIB picks the .so) and knobs
 P=llama-fastapi-k8s-gpu_b200
-for v in lib lib_head lib lib_head; do
-  echo "== $v"
-  B200_GGUF_LIB=$P/$v/libb200gguf.so timeout 200 python bench.py --steps 30 --warmup 5 --no-cpu-baseline --batch-extra 0 --no-parity-check 2>&1 | grep -o '"ms_per_step": [0-9.]*'
-done
-B2_TIMELINE=1 timeout 200 python bench.py --steps 10 --warmup 5 --no-cpu-baseline --batch-extra 0 --no-parity-check 2>&1 | grep timeline | head -8
+run() { timeout 200 python bench.py --steps 30 --warmup 5 --no-cpu-baseline --batch-extra 0 --no-parity-check 2>&1 | grep -o '"ms_per_step": [0-9.]*'; }
+echo "== lib"; run
+echo "== unroll2"; B200_GGUF_LIB=$P/lib_v1/libb200gguf.so run
+echo "== stages 24"; B2_MV_STAGES=24 run
+echo "== stages 16"; B2_MV_STAGES=16 run
+echo "== lib"; run
