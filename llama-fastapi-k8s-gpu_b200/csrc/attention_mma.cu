@@ -37,6 +37,11 @@ __device__ __forceinline__ uint32_t am_pack(float a, float b) {
 __device__ __forceinline__ void am_cp16(void* dst, const void* src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
 }
+// one output element of sequence z: float vector, or f16 straight into the next GEMM's operand layout (no conversion kernel)
+__device__ __forceinline__ void am_store_out(const AttnParams& p, int z, int col, float v) {
+    if (p.out_h) p.out_h[((size_t)(col >> 3) * p.out_T_pad + z) * 8 + (col & 7)] = __float2half_rn(v);
+    else p.out[col] = v;
+}
 __device__ __forceinline__ void am_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void am_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
@@ -180,7 +185,7 @@ __global__ void __launch_bounds__(AM_THREADS) attn_decode_mma_kernel(const AttnP
             den += wt * wl[w * 8 + gg];
         }
         if (single) {
-            p.out[((size_t)h * G + gg) * HD + d] = num / den;
+            am_store_out(p, z, (h * G + gg) * HD + d, num / den);
         } else {
             float* r = p.scratch + (((size_t)h * p.n_splits + sp) * G + gg) * rec;
             r[d] = num;
@@ -225,7 +230,7 @@ __global__ void __launch_bounds__(AM_THREADS) attn_decode_mma_kernel(const AttnP
         float num = 0.f;
 #pragma unroll 8
         for (int s2 = 0; s2 < p.n_splits; s2++) num += wsp[gg * p.n_splits + s2] * __ldcg(base + (size_t)s2 * G * rec);
-        p.out[((size_t)h * G + gg) * HD + d] = num * inv[gg];
+        am_store_out(p, z, (h * G + gg) * HD + d, num * inv[gg]);
     }
     if (tid == 0) p.counters[h] = 0;                             // ready for the next launch
 }

@@ -934,9 +934,13 @@ static int batch_step(b2_engine* e, const BatchIdx& b) {
         while (ns > 1 && (long)ns * c.n_head_kv * T > 2L * e->n_sms) ns >>= 1;
         if (e->batch_attn_splits > 0 && e->batch_attn_splits <= e->n_splits) ns = e->batch_attn_splits;
         a.n_splits = ns; a.scale = 1.0f / sqrtf((float)hd); a.err = kernel_error_word(); a.max_pages = e->max_blocks;
-        if (e->attn_mma != 0) CK(attn_decode_mma_launch(a, e->slot_tab, &b, st, false));
-        else CK(attn_decode_batch_launch(a, e->slot_tab, b, st));
-        CK(to_half_blocked_launch(e->bd_att, T, T_pad, qd, e->pf_att, st));
+        if (e->attn_mma != 0) {      // the tensor-core kernel writes f16 in the o-projection GEMM's operand order itself
+            a.out_h = e->pf_att; a.out_T_pad = T_pad;
+            CK(attn_decode_mma_launch(a, e->slot_tab, &b, st, false));
+        } else {
+            CK(attn_decode_batch_launch(a, e->slot_tab, b, st));
+            CK(to_half_blocked_launch(e->bd_att, T, T_pad, qd, e->pf_att, st));
+        }
         const DevTensor* wo[1] = {&L.wo};
         if ((rc = gemm_call(e, wo, 1, e->pf_att, T, &np, &ps))) return rc;
         CK(resid_norm_half_launch(e->pf_x, e->pf_part, np, ps, (const float*)L.ffn_norm.ptr, c.rms_eps, E, T, T_pad, e->pf_xn, st));
@@ -945,7 +949,7 @@ static int batch_step(b2_engine* e, const BatchIdx& b) {
         CK(silu_mul_half_launch(e->pf_part, np, ps, F, T, T_pad, e->pf_h, st));
         const DevTensor* wd[1] = {&L.wdown};
         if ((rc = gemm_call(e, wd, 1, e->pf_h, T, &np, &ps))) return rc;
-        e->launches += 6;
+        e->launches += e->attn_mma != 0 ? 5 : 6;
     }
     // x += last ffn_down; output norm; lm_head (one K range: the logits are complete rows); sample every sequence
     CK(resid_norm_half_launch(e->pf_x, e->pf_part, np, ps, (const float*)e->out_norm.ptr, c.rms_eps, E, T, T_pad, e->pf_xn, st));

@@ -120,6 +120,8 @@ struct AttnParams {
     unsigned int* err;       // host-mapped error word (kernel watchdogs)
     unsigned long long* tl;  // optional timeline record (see MvParams::tl)
     int early;               // 1: launched with programmatic dependent launch behind a kernel that triggers late (attention_body.cuh)
+    __half* out_h;           // batched tensor-core kernel only: write the output as f16 in the GEMM's operand order
+    int out_T_pad;           //   [n_head * head_dim / 8][out_T_pad][8] (row = sequence index) instead of float `out`
 };
 cudaError_t attn_init();
 size_t attn_scratch_floats(int n_head, int n_kv, int head_dim, int n_splits);

@@ -1,2 +1,4 @@
-timeout 1200 python -m pytest tests -m gpu -q 2>&1 | tail -6
-timeout 200 python bench.py --steps 30 --warmup 5 --no-cpu-baseline --batch-extra 0 --no-parity-check 2>&1 | grep -o '"ms_per_step": [0-9.]*\|"prefill_ms": [0-9.]*'
+timeout 1200 python -m pytest tests -m gpu -q -x 2>&1 | tail -2
+timeout 600 python bench.py --workload llama3-8b-q8_0-bs32 --no-cpu-baseline --steps 32 --warmup 4 2>/dev/null | python -c "
+import sys,json
+d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('bs32', d['ms_per_step'], d['value'], d['gpu_launches'])"
