@@ -225,8 +225,9 @@ def test_tensor_core_prefill_agrees_with_token_by_token(native_lib, tmp_models, 
     assert outs[0][0] == outs[1][0]
 
 
+@pytest.mark.parametrize("attn_splits", [0, 1])      # 1: one split per sequence (what 32-sequence steps use)
 @pytest.mark.parametrize("arch,ftype,seed", [("tiny", "Q4_K_M", 1), ("tiny128", "Q8_0", 6)])
-def test_batched_decode_matches_oracle_and_serial_path(native_lib, tmp_models, arch, ftype, seed, monkeypatch):
+def test_batched_decode_matches_oracle_and_serial_path(native_lib, tmp_models, arch, ftype, seed, attn_splits, monkeypatch):
     """>= 3 sequences per b2_decode call step together through the tensor-core GEMM (weights read once per
     step), each at its own position with its own pages and sampler state. Greedy continuations must equal the
     one-sequence-at-a-time path wherever the oracle's top-2 margin is clear, logits within the tolerance."""
@@ -239,6 +240,8 @@ def test_batched_decode_matches_oracle_and_serial_path(native_lib, tmp_models, a
     runs = {}
     for mode in ("serial", "batched"):
         monkeypatch.setenv("B2_BATCH_MIN", "100" if mode == "serial" else "3")
+        if attn_splits:
+            monkeypatch.setenv("B2_BATCH_ATTN_SPLITS", str(attn_splits))
         eng = _engine(path, max_seqs=8, n_ctx=128)
         for s, pr in enumerate(prompts):
             eng.ensure_pages(s, len(pr) + n_new + 2)
