@@ -52,26 +52,6 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, unsign
         }
     }
 }
-// the same with test_wait: polls, never suspends the thread
-__device__ __forceinline__ void mbar_wait_poll(uint64_t* bar, uint32_t parity, unsigned int* err, unsigned int code,
-                                               unsigned int info = 0) {
-    uint32_t spins = 0, ok = 0;
-    for (;;) {
-        asm volatile(
-            "{\n\t.reg .pred p;\n\t"
-            "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-            "selp.u32 %0, 1, 0, p;\n\t}"
-            : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
-        if (ok) return;
-        if (++spins > (1u << 24)) {
-            if (err) {
-                volatile unsigned int* e = reinterpret_cast<volatile unsigned int*>(err);
-                if (e[0] == 0) { e[1] = blockIdx.x; e[2] = threadIdx.x; e[3] = info; e[4] = parity; e[0] = code; }
-            }
-            return;
-        }
-    }
-}
 // 1-D bulk async copy global -> shared, completion signalled on an mbarrier (complete_tx).
 // dst and src 16-byte aligned, bytes a multiple of 16.
 __device__ __forceinline__ void tma_load_1d(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
@@ -87,10 +67,6 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const void* tmap, int c0,
 __device__ __forceinline__ void tma_load_3d(void* dst, const void* tmap, int c0, int c1, int c2, uint64_t* bar) {
     asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
                  ::"r"(smem_u32(dst)), "l"(tmap), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(bar)) : "memory");
-}
-// ask L2 to fetch [src, src + bytes) (both multiples of 16); nothing is written anywhere else
-__device__ __forceinline__ void l2_prefetch_bulk(const void* src, uint32_t bytes) {
-    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
 }
 // Programmatic dependent launch (PDL): `launch` lets the next kernel in the stream start
 // its prologue (weight prefetch) early; `wait` blocks until the previous kernel has fully
