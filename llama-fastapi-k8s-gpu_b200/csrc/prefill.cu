@@ -45,8 +45,12 @@ __global__ void __launch_bounds__(RN_THREADS) resid_norm_half_kernel(float* x, c
     __shared__ float red[RN_THREADS / 32];
     const int t = blockIdx.x;
     float* xr = x + (size_t)t * K;
+    // a thread's float4s stay in registers between the sum of squares and the normalisation (K <= 2 * 4 * RN_THREADS = 8192;
+    // longer rows re-read what they wrote)
+    constexpr int KEEP = 2;
+    float4 keep[KEEP];
     float ss = 0.f;
-    for (int i = threadIdx.x; i < K / 4; i += RN_THREADS) {          // float4 per thread: the split sums are independent loads
+    auto sum_parts = [&](int i) -> float4 {                             // float4 per thread: the split sums are independent loads
         float4 v = *reinterpret_cast<const float4*>(xr + 4 * i);
         const float* pp = parts + (size_t)t * K + 4 * i;
 #pragma unroll 4
@@ -56,7 +60,15 @@ __global__ void __launch_bounds__(RN_THREADS) resid_norm_half_kernel(float* x, c
         }
         if (n_parts) *reinterpret_cast<float4*>(xr + 4 * i) = v;
         ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+        return v;
+    };
+#pragma unroll
+    for (int it = 0; it < KEEP; it++) {
+        const int i = threadIdx.x + it * RN_THREADS;
+        keep[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (i < K / 4) keep[it] = sum_parts(i);
     }
+    for (int i = threadIdx.x + KEEP * RN_THREADS; i < K / 4; i += RN_THREADS) sum_parts(i);
     if (!w) return;
     ss = warp_sum(ss);
     if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
@@ -65,15 +77,18 @@ __global__ void __launch_bounds__(RN_THREADS) resid_norm_half_kernel(float* x, c
 #pragma unroll
     for (int i = 0; i < RN_THREADS / 32; i++) tot += red[i];
     const float r = rsqrtf(tot / (float)K + eps);
-    for (int c = threadIdx.x; c < K / 8; c += RN_THREADS) {            // 8 consecutive k = one 16-byte run in operand order
-        const float4 a = *reinterpret_cast<const float4*>(xr + 8 * c), b = *reinterpret_cast<const float4*>(xr + 8 * c + 4);
-        const float4 wa = *reinterpret_cast<const float4*>(w + 8 * c), wb = *reinterpret_cast<const float4*>(w + 8 * c + 4);
+    auto emit = [&](int i, const float4& a) {                           // 4 consecutive k = half of a 16-byte run in operand order
+        const float4 wa = *reinterpret_cast<const float4*>(w + 4 * i);
         const __half2 h0 = __floats2half2_rn(a.x * r * wa.x, a.y * r * wa.y), h1 = __floats2half2_rn(a.z * r * wa.z, a.w * r * wa.w);
-        const __half2 h2 = __floats2half2_rn(b.x * r * wb.x, b.y * r * wb.y), h3 = __floats2half2_rn(b.z * r * wb.z, b.w * r * wb.w);
-        *reinterpret_cast<uint4*>(xn + ((size_t)c * T_pad + t) * 8) =
-            make_uint4(*reinterpret_cast<const uint32_t*>(&h0), *reinterpret_cast<const uint32_t*>(&h1),
-                       *reinterpret_cast<const uint32_t*>(&h2), *reinterpret_cast<const uint32_t*>(&h3));
+        *reinterpret_cast<uint2*>(xn + ((size_t)(i >> 1) * T_pad + t) * 8 + 4 * (i & 1)) =
+            make_uint2(*reinterpret_cast<const uint32_t*>(&h0), *reinterpret_cast<const uint32_t*>(&h1));
+    };
+#pragma unroll
+    for (int it = 0; it < KEEP; it++) {
+        const int i = threadIdx.x + it * RN_THREADS;
+        if (i < K / 4) emit(i, keep[it]);
     }
+    for (int i = threadIdx.x + KEEP * RN_THREADS; i < K / 4; i += RN_THREADS) emit(i, *reinterpret_cast<const float4*>(xr + 4 * i));
 }
 cudaError_t resid_norm_half_launch(float* x, const float* parts, int n_parts, long part_stride, const float* w, float eps,
                                    int K, int T, int T_pad, __half* xn, cudaStream_t s) {
